@@ -1,0 +1,482 @@
+/*
+ * oracle/tree_oracle.c -- TEST INFRASTRUCTURE ONLY (never on the product path).
+ *
+ * Plain-C, sequential restatement of the reference tree_filter_cuda operators
+ * (all paths relative to /root/reference/code/utils/TreeEnergyLoss/kernels/lib_tree_filter):
+ *
+ *   oracle_boruvka            <- src/mst/boruvka.cpp:20-158   (Boruvka + union-find by rank)
+ *   oracle_mst_forward        <- src/mst/mst.cu:41-117        (per-image loop; reference = 1 std::thread/image)
+ *   oracle_bfs_forward        <- src/bfs/bfs.cu:19-98         (meaning of the three output arrays; the reference's
+ *                                                              within-wave order is atomic-dependent, this one is the
+ *                                                              FIFO order with children sorted by vertex id)
+ *   oracle_refine_forward     <- src/refine/refine.cu:19-134, 201-249
+ *   oracle_refine_backward_feature <- src/refine/refine.cu:251-300
+ *   oracle_refine_backward_weight  <- src/refine/refine.cu:136-199, 302-370
+ *   oracle_edge_weight / _bwd <- modules/tree_filter.py:84-108 (gather, squared distance, exp) and its autograd
+ *
+ * Parity pin: the reference ships no tests or golden vectors for this path.  The restatement is
+ * pinned (a) against the reference's own boruvka.cpp compiled into oracle/_ref (tests/test_oracle_ref.py, runs
+ * where /root/reference exists), (b) against fixtures produced by running the reference's unmodified Python glue
+ * (flower_common.py / tree_filter.py / functions/*.py) on top of this module (tests/golden/make_golden.py), and
+ * (c) against a brute-force path-product filter and fp64 finite differences (tests/test_oracle_tree.py).
+ *
+ * Build:  gcc -O2 -ffp-contract=off -pthread -shared -fPIC tree_oracle.c -o liboracle_tree.so -lm
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <pthread.h>
+
+/* ------------------------------------------------------------------ tiny pthread parallel-for */
+
+static int g_threads = 0; /* 0 => use the online core count */
+
+typedef void (*job_fn)(int idx, void *ctx);
+typedef struct {
+    job_fn fn;
+    void *ctx;
+    int n;
+    int next; /* shared work counter */
+} pool_t;
+
+static void *pool_worker(void *p) {
+    pool_t *pool = (pool_t *)p;
+    for (;;) {
+        int i = __atomic_fetch_add(&pool->next, 1, __ATOMIC_RELAXED);
+        if (i >= pool->n) break;
+        pool->fn(i, pool->ctx);
+    }
+    return NULL;
+}
+
+#include <unistd.h>
+static int pool_width(void) {
+    if (g_threads > 0) return g_threads;
+    long n = sysconf(_SC_NPROCESSORS_ONLN);
+    return n > 0 ? (int)n : 1;
+}
+
+static void par_for(int n, job_fn fn, void *ctx) {
+    int nt = pool_width();
+    if (nt > n) nt = n;
+    pool_t pool = {fn, ctx, n, 0};
+    if (nt <= 1) {
+        pool_worker(&pool);
+        return;
+    }
+    pthread_t *th = (pthread_t *)malloc(sizeof(pthread_t) * (size_t)nt);
+    int started = 0;
+    for (int t = 0; t < nt - 1; ++t)
+        if (pthread_create(&th[started], NULL, pool_worker, &pool) == 0) ++started;
+    pool_worker(&pool);
+    for (int t = 0; t < started; ++t) pthread_join(th[t], NULL);
+    free(th);
+}
+
+/* ------------------------------------------------------------------ MST */
+
+typedef struct {
+    int up;   /* union-find parent */
+    int rank; /* union-by-rank height bound */
+} uf_node;
+
+static int uf_root(uf_node *s, int i) {
+    int r = i;
+    while (s[r].up != r) r = s[r].up;
+    while (s[i].up != r) { /* full path compression, same end state as the recursive form (boruvka.cpp:126-135) */
+        int n = s[i].up;
+        s[i].up = r;
+        i = n;
+    }
+    return r;
+}
+
+static void uf_join(uf_node *s, int a, int b) { /* boruvka.cpp:139-158 */
+    int ra = uf_root(s, a), rb = uf_root(s, b);
+    if (s[ra].rank < s[rb].rank) {
+        s[ra].up = rb;
+    } else if (s[ra].rank > s[rb].rank) {
+        s[rb].up = ra;
+    } else {
+        s[rb].up = ra;
+        s[ra].rank += 1;
+    }
+}
+
+/* One image.  edge_index [E,2], edge_weight [E], edge_out [(V-1),2].  Returns number of edges written.
+ * Per round: every component keeps the first edge (lowest index) of strictly smallest weight leaving it
+ * (boruvka.cpp:58-82), then components are visited in index order and their edge is added unless it now closes a
+ * cycle (boruvka.cpp:86-108).  A round that adds nothing (disconnected input) ends the loop instead of spinning. */
+int oracle_boruvka(int V, int E, const int *edge_index, const float *edge_weight, int *edge_out) {
+    uf_node *s = (uf_node *)malloc(sizeof(uf_node) * (size_t)V);
+    int *best = (int *)malloc(sizeof(int) * (size_t)V);
+    int n_out = 0, trees = V;
+    for (int v = 0; v < V; ++v) { s[v].up = v; s[v].rank = 0; }
+    while (trees > 1) {
+        for (int v = 0; v < V; ++v) best[v] = -1;
+        for (int e = 0; e < E; ++e) {
+            int a = uf_root(s, edge_index[2 * e]);
+            int b = uf_root(s, edge_index[2 * e + 1]);
+            if (a == b) continue;
+            if (best[a] < 0 || edge_weight[best[a]] > edge_weight[e]) best[a] = e;
+            if (best[b] < 0 || edge_weight[best[b]] > edge_weight[e]) best[b] = e;
+        }
+        int added = 0;
+        for (int v = 0; v < V; ++v) {
+            int e = best[v];
+            if (e < 0) continue;
+            int a = uf_root(s, edge_index[2 * e]);
+            int b = uf_root(s, edge_index[2 * e + 1]);
+            if (a == b) continue;
+            edge_out[2 * n_out] = edge_index[2 * e];
+            edge_out[2 * n_out + 1] = edge_index[2 * e + 1];
+            ++n_out;
+            uf_join(s, a, b);
+            --trees;
+            ++added;
+        }
+        if (!added) break;
+    }
+    free(s);
+    free(best);
+    return n_out;
+}
+
+/* Batch driver, mst.cu:86-117 (the reference starts one std::thread per image; here a bounded thread pool). */
+typedef struct {
+    int E, V;
+    const int *edge_index;
+    const float *edge_weight;
+    int *edge_out;
+    int bad;
+} mst_job;
+
+static void mst_one(int b, void *p) {
+    mst_job *j = (mst_job *)p;
+    int n = oracle_boruvka(j->V, j->E, j->edge_index + (size_t)b * j->E * 2, j->edge_weight + (size_t)b * j->E,
+                           j->edge_out + (size_t)b * (j->V - 1) * 2);
+    if (n != j->V - 1) __atomic_fetch_add(&j->bad, 1, __ATOMIC_RELAXED);
+}
+
+int oracle_mst_forward(int B, int E, int V, const int *edge_index, const float *edge_weight, int *edge_out) {
+    mst_job j = {E, V, edge_index, edge_weight, edge_out, 0};
+    par_for(B, mst_one, &j);
+    return j.bad ? -1 : 0;
+}
+
+/* ------------------------------------------------------------------ BFS */
+
+/* One image.  tree [(V-1),2] undirected edges.  Outputs follow bfs.cu:46-98:
+ *   sorted_index[i]  = vertex at BFS position i (position 0 = vertex 0, the root)
+ *   sorted_parent[i] = BFS position of the parent of that vertex (0 for the root)
+ *   sorted_child[i*max_adj + k] = BFS positions of its children, unused slots 0
+ * Optional level_start (length >= V+1) receives the first position of each depth; *n_levels the depth count.
+ * Returns 0, or -1 if a vertex has more than max_adj neighbours / the tree does not span. */
+int oracle_bfs(int V, const int *tree, int max_adj, int *sorted_index, int *sorted_parent, int *sorted_child,
+               int *level_start, int *n_levels) {
+    int *deg = (int *)calloc((size_t)V, sizeof(int));
+    int *adj = (int *)malloc(sizeof(int) * (size_t)V * max_adj);
+    int *par_vertex = (int *)malloc(sizeof(int) * (size_t)V);
+    int rc = 0;
+    for (int e = 0; e < V - 1 && rc == 0; ++e) {
+        int a = tree[2 * e], b = tree[2 * e + 1];
+        if (deg[a] >= max_adj || deg[b] >= max_adj) { rc = -1; break; }
+        adj[a * max_adj + deg[a]++] = b;
+        adj[b * max_adj + deg[b]++] = a;
+    }
+    if (rc == 0) {
+        for (int v = 0; v < V; ++v) { /* canonical neighbour order: increasing vertex id (= N, W, E, S on a grid) */
+            int *a = adj + v * max_adj;
+            for (int i = 1; i < deg[v]; ++i) {
+                int x = a[i], j = i - 1;
+                while (j >= 0 && a[j] > x) { a[j + 1] = a[j]; --j; }
+                a[j + 1] = x;
+            }
+        }
+        memset(sorted_child, 0, sizeof(int) * (size_t)V * max_adj);
+        sorted_index[0] = 0;
+        sorted_parent[0] = 0;
+        par_vertex[0] = 0;
+        int tail = 1, depth = 0, level_end = 1;
+        if (level_start) level_start[0] = 0;
+        for (int i = 0; i < tail; ++i) {
+            if (i == level_end) {
+                ++depth;
+                if (level_start) level_start[depth] = i;
+                level_end = tail;
+            }
+            int cur = sorted_index[i], k = 0;
+            for (int j = 0; j < deg[cur]; ++j) {
+                int nb = adj[cur * max_adj + j];
+                if (nb == par_vertex[i] && i != 0) continue;
+                sorted_index[tail] = nb;
+                par_vertex[tail] = cur;
+                sorted_parent[tail] = i;
+                sorted_child[i * max_adj + k++] = tail;
+                ++tail;
+            }
+        }
+        if (tail != V) rc = -1;
+        if (level_start) level_start[depth + 1] = tail;
+        if (n_levels) *n_levels = depth + 1;
+    }
+    free(deg);
+    free(adj);
+    free(par_vertex);
+    return rc;
+}
+
+typedef struct {
+    int V, max_adj;
+    const int *tree;
+    int *si, *sp, *sc;
+    int bad;
+} bfs_job;
+
+static void bfs_one(int b, void *p) {
+    bfs_job *j = (bfs_job *)p;
+    int V = j->V;
+    int rc = oracle_bfs(V, j->tree + (size_t)b * (V - 1) * 2, j->max_adj, j->si + (size_t)b * V,
+                        j->sp + (size_t)b * V, j->sc + (size_t)b * V * j->max_adj, NULL, NULL);
+    if (rc) __atomic_fetch_add(&j->bad, 1, __ATOMIC_RELAXED);
+}
+
+int oracle_bfs_forward(int B, int V, const int *tree, int max_adj, int *sorted_index, int *sorted_parent,
+                       int *sorted_child) {
+    bfs_job j = {V, max_adj, tree, sorted_index, sorted_parent, sorted_child, 0};
+    par_for(B, bfs_one, &j);
+    return j.bad ? -1 : 0;
+}
+
+/* ------------------------------------------------------------------ batched drivers */
+
+typedef struct {
+    int B, C, D, V, max_adj;
+    float inv_sigma;
+    const float *embed, *ew_c, *grad_ew;
+    float *ew, *grad_embed;
+    const int *si, *sp, *sc;
+    const float *feature_in, *grad_out, *feature_out_c, *feature_aggr_c, *feature_aggr_up_c, *weight_sum_c,
+        *weight_sum_up_c;
+    float *feature_out, *feature_aggr, *feature_aggr_up, *weight_sum, *weight_sum_up, *grad_feature, *grad_weight;
+} job_t;
+
+/* ---- edge weights (tree_filter.py:84-108) */
+
+static void ew_one(int b, void *p) {
+    job_t *j = (job_t *)p;
+    int V = j->V, D = j->D;
+    const float *e = j->embed + (size_t)b * D * V;
+    const int *si = j->si + (size_t)b * V, *sp = j->sp + (size_t)b * V;
+    for (int i = 0; i < V; ++i) {
+        int v = si[i], u = si[sp[i]];
+        float d = 0.f;
+        for (int c = 0; c < D; ++c) {
+            float t = e[(size_t)c * V + v] - e[(size_t)c * V + u];
+            d += t * t;
+        }
+        j->ew[(size_t)b * V + i] = expf(-d * j->inv_sigma);
+    }
+}
+
+/* embed [B,D,V] vertex order -> ew [B,V] BFS order: exp(-|e[v(i)] - e[v(par i)]|^2 * inv_sigma). */
+void oracle_edge_weight(int B, int D, int V, const float *embed, const int *sorted_index, const int *sorted_parent,
+                        float inv_sigma, float *ew) {
+    job_t j;
+    memset(&j, 0, sizeof(j));
+    j.D = D; j.V = V; j.embed = embed; j.si = sorted_index; j.sp = sorted_parent; j.inv_sigma = inv_sigma; j.ew = ew;
+    par_for(B, ew_one, &j);
+}
+
+static void ewb_one(int b, void *p) {
+    job_t *j = (job_t *)p;
+    int V = j->V, D = j->D;
+    const float *e = j->embed + (size_t)b * D * V;
+    float *g = j->grad_embed + (size_t)b * D * V;
+    const int *si = j->si + (size_t)b * V, *sp = j->sp + (size_t)b * V;
+    memset(g, 0, sizeof(float) * (size_t)D * V);
+    for (int i = 1; i < V; ++i) {
+        int v = si[i], u = si[sp[i]];
+        float k = -2.f * j->inv_sigma * j->ew_c[(size_t)b * V + i] * j->grad_ew[(size_t)b * V + i];
+        for (int c = 0; c < D; ++c) {
+            float t = k * (e[(size_t)c * V + v] - e[(size_t)c * V + u]);
+            g[(size_t)c * V + v] += t;
+            g[(size_t)c * V + u] -= t;
+        }
+    }
+}
+
+/* grad_ew [B,V] (BFS order) -> grad_embed [B,D,V] (vertex order), the autograd of the expression above. */
+void oracle_edge_weight_bwd(int B, int D, int V, const float *embed, const int *sorted_index,
+                            const int *sorted_parent, float inv_sigma, const float *ew, const float *grad_ew,
+                            float *grad_embed) {
+    job_t j;
+    memset(&j, 0, sizeof(j));
+    j.D = D; j.V = V; j.embed = embed; j.si = sorted_index; j.sp = sorted_parent; j.inv_sigma = inv_sigma;
+    j.ew_c = ew; j.grad_ew = grad_ew; j.grad_embed = grad_embed;
+    par_for(B, ewb_one, &j);
+}
+
+/* ------------------------------------------------------------------ refine sweeps */
+
+/* refine.cu:70-134.  in: vertex order (or NULL => 1), out: BFS order. */
+static void sweep_up(const float *in, float *out, const float *w, const int *si, const int *sc, int V, int max_adj) {
+    for (int i = V - 1; i >= 0; --i) {
+        float acc = in ? in[si[i]] : 1.f;
+        for (int j = 0; j < max_adj; ++j) {
+            int c = sc[i * max_adj + j];
+            if (c <= 0) break;
+            acc += out[c] * w[c];
+        }
+        out[i] = acc;
+    }
+}
+
+/* refine.cu:19-68 with w_0 treated as 0.  in: BFS order, out: vertex order. */
+static void sweep_down(const float *in, float *out, const float *w, const int *si, const int *sp, int V) {
+    out[si[0]] = in[0];
+    for (int i = 1; i < V; ++i) {
+        float wi = w[i];
+        out[si[i]] = in[i] * (1.f - wi * wi) + out[si[sp[i]]] * wi;
+    }
+}
+
+/* refine.cu:136-199.  in_data BFS, out_data vertex (data_c channels, channel k%data_c), in_grad BFS converted in
+ * place to its root-to-leaf form (grad_c channels), grad [max(data_c,grad_c), V] BFS order. */
+static void sweep_grad(const float *in_data, const float *out_data, float *in_grad, const float *w, float *grad,
+                       const int *si, const int *sp, int data_c, int grad_c, int V) {
+    int nc = data_c > grad_c ? data_c : grad_c;
+    for (int k = 0; k < nc; ++k) {
+        const float *idat = in_data + (size_t)(k % data_c) * V;
+        const float *odat = out_data + (size_t)(k % data_c) * V;
+        float *g = in_grad + (size_t)(k % grad_c) * V;
+        float *o = grad + (size_t)k * V;
+        o[0] = 0.f;
+        for (int i = 1; i < V; ++i) {
+            int p = sp[i];
+            float wi = w[i];
+            float left = g[i] * (odat[si[p]] - wi * idat[i]);
+            float right = idat[i] * (g[p] - wi * g[i]);
+            o[i] = left + right;
+            g[i] = g[i] * (1.f - wi * wi) + g[p] * wi;
+        }
+    }
+}
+
+/* ---- refine_forward, refine.cu:201-249.  edge_weight[:,0] is set to 0 in place as the reference does (:43-46). */
+
+static void fwd_one(int idx, void *p) { /* idx = b*(C+1) + c; channel C is the all-ones "weight" channel */
+    job_t *j = (job_t *)p;
+    int C = j->C, V = j->V, b = idx / (C + 1), c = idx % (C + 1);
+    const float *w = j->ew_c + (size_t)b * V;
+    const int *si = j->si + (size_t)b * V, *sp = j->sp + (size_t)b * V;
+    const int *sc = j->sc + (size_t)b * V * j->max_adj;
+    if (c < C) {
+        size_t off = ((size_t)b * C + c) * V;
+        sweep_up(j->feature_in + off, j->feature_aggr_up + off, w, si, sc, V, j->max_adj);
+        sweep_down(j->feature_aggr_up + off, j->feature_aggr + off, w, si, sp, V);
+    } else {
+        sweep_up(NULL, j->weight_sum_up + (size_t)b * V, w, si, sc, V, j->max_adj);
+        sweep_down(j->weight_sum_up + (size_t)b * V, j->weight_sum + (size_t)b * V, w, si, sp, V);
+    }
+}
+
+static void fwd_div(int idx, void *p) {
+    job_t *j = (job_t *)p;
+    int C = j->C, V = j->V, b = idx / C;
+    size_t off = (size_t)idx * V;
+    for (int v = 0; v < V; ++v) j->feature_out[off + v] = j->feature_aggr[off + v] / j->weight_sum[(size_t)b * V + v];
+}
+
+void oracle_refine_forward(int B, int C, int V, int max_adj, const float *feature_in, float *edge_weight,
+                           const int *sorted_index, const int *sorted_parent, const int *sorted_child,
+                           float *feature_out, float *feature_aggr, float *feature_aggr_up, float *weight_sum,
+                           float *weight_sum_up) {
+    for (int b = 0; b < B; ++b) edge_weight[(size_t)b * V] = 0.f;
+    job_t j;
+    memset(&j, 0, sizeof(j));
+    j.B = B; j.C = C; j.V = V; j.max_adj = max_adj; j.feature_in = feature_in; j.ew_c = edge_weight;
+    j.si = sorted_index; j.sp = sorted_parent; j.sc = sorted_child; j.feature_out = feature_out;
+    j.feature_aggr = feature_aggr; j.feature_aggr_up = feature_aggr_up; j.weight_sum = weight_sum;
+    j.weight_sum_up = weight_sum_up;
+    par_for(B * (C + 1), fwd_one, &j);
+    par_for(B * C, fwd_div, &j);
+}
+
+/* ---- refine_backward_feature, refine.cu:251-300. */
+
+static void bwdf_one(int idx, void *p) {
+    job_t *j = (job_t *)p;
+    int C = j->C, V = j->V, b = idx / C;
+    size_t off = (size_t)idx * V;
+    float *gn = (float *)malloc(sizeof(float) * (size_t)V * 2);
+    float *up = gn + V;
+    for (int v = 0; v < V; ++v) gn[v] = j->grad_out[off + v] / j->weight_sum_c[(size_t)b * V + v];
+    sweep_up(gn, up, j->ew_c + (size_t)b * V, j->si + (size_t)b * V, j->sc + (size_t)b * V * j->max_adj, V,
+             j->max_adj);
+    sweep_down(up, j->grad_feature + off, j->ew_c + (size_t)b * V, j->si + (size_t)b * V, j->sp + (size_t)b * V, V);
+    free(gn);
+}
+
+void oracle_refine_backward_feature(int B, int C, int V, int max_adj, const float *edge_weight,
+                                    const int *sorted_index, const int *sorted_parent, const int *sorted_child,
+                                    const float *weight_sum, const float *grad_out, float *grad_feature) {
+    job_t j;
+    memset(&j, 0, sizeof(j));
+    j.B = B; j.C = C; j.V = V; j.max_adj = max_adj; j.ew_c = edge_weight; j.si = sorted_index; j.sp = sorted_parent;
+    j.sc = sorted_child; j.weight_sum_c = weight_sum; j.grad_out = grad_out; j.grad_feature = grad_feature;
+    par_for(B * C, bwdf_one, &j);
+}
+
+/* ---- refine_backward_weight, refine.cu:302-370.  grad_weight [B,V] in BFS order. */
+
+static void bwdw_one(int b, void *p) {
+    job_t *j = (job_t *)p;
+    int C = j->C, V = j->V, max_adj = j->max_adj;
+    const float *w = j->ew_c + (size_t)b * V;
+    const int *si = j->si + (size_t)b * V, *sp = j->sp + (size_t)b * V;
+    const int *sc = j->sc + (size_t)b * V * max_adj;
+    size_t cv = (size_t)C * V;
+    float *buf = (float *)malloc(sizeof(float) * cv * 6);
+    float *gn = buf, *fg = buf + cv, *u1 = buf + 2 * cv, *u2 = buf + 3 * cv, *ga = buf + 4 * cv, *gb = buf + 5 * cv;
+    for (int c = 0; c < C; ++c)
+        for (int v = 0; v < V; ++v) {
+            size_t o = ((size_t)b * C + c) * V + v;
+            gn[(size_t)c * V + v] = j->grad_out[o] / j->weight_sum_c[(size_t)b * V + v];
+            fg[(size_t)c * V + v] = gn[(size_t)c * V + v] * j->feature_out_c[o];
+        }
+    for (int c = 0; c < C; ++c) {
+        sweep_up(gn + (size_t)c * V, u1 + (size_t)c * V, w, si, sc, V, max_adj);
+        sweep_up(fg + (size_t)c * V, u2 + (size_t)c * V, w, si, sc, V, max_adj);
+    }
+    sweep_grad(j->feature_aggr_up_c + (size_t)b * cv, j->feature_aggr_c + (size_t)b * cv, u1, w, ga, si, sp, C, C, V);
+    sweep_grad(j->weight_sum_up_c + (size_t)b * V, j->weight_sum_c + (size_t)b * V, u2, w, gb, si, sp, 1, C, V);
+    for (int i = 0; i < V; ++i) {
+        float acc = 0.f;
+        for (int c = 0; c < C; ++c) acc += ga[(size_t)c * V + i] - gb[(size_t)c * V + i];
+        j->grad_weight[(size_t)b * V + i] = acc;
+    }
+    free(buf);
+}
+
+void oracle_refine_backward_weight(int B, int C, int V, int max_adj, const float *edge_weight,
+                                   const int *sorted_index, const int *sorted_parent, const int *sorted_child,
+                                   const float *feature_out, const float *feature_aggr,
+                                   const float *feature_aggr_up, const float *weight_sum,
+                                   const float *weight_sum_up, const float *grad_out, float *grad_weight) {
+    job_t j;
+    memset(&j, 0, sizeof(j));
+    j.B = B; j.C = C; j.V = V; j.max_adj = max_adj; j.ew_c = edge_weight; j.si = sorted_index; j.sp = sorted_parent;
+    j.sc = sorted_child; j.feature_out_c = feature_out; j.feature_aggr_c = feature_aggr;
+    j.feature_aggr_up_c = feature_aggr_up; j.weight_sum_c = weight_sum; j.weight_sum_up_c = weight_sum_up;
+    j.grad_out = grad_out; j.grad_weight = grad_weight;
+    par_for(B, bwdw_one, &j);
+}
+
+/* ------------------------------------------------------------------ misc */
+
+int oracle_num_threads(void) { return pool_width(); }
+
+void oracle_set_num_threads(int n) { g_threads = n > 0 ? n : 0; }
