@@ -1,0 +1,284 @@
+// mst.cu -- batched minimum spanning tree on the GPU (sm_100a), Boruvka rounds with 64-bit (weight, edge id) keys.
+//
+// Replaces mst_forward of the reference (LTF = /root/reference/code/utils/TreeEnergyLoss/kernels/lib_tree_filter):
+//   LTF/src/mst/mst.cu:86-117  copies index+weights to the host, runs one std::thread per image of
+//   LTF/src/mst/boruvka.cpp:20-112 (sequential Boruvka, union-find) and copies the tree back.
+// The reference keeps, per component, the FIRST edge (lowest index) of strictly smallest weight (boruvka.cpp:74-80), so
+// its edge set is the unique MST under the total order (weight, edge index).  Here every round each component takes the
+// atomicMin of the packed key (orderable fp32 bits << 32 | edge index) over its outgoing edges -- the same total order,
+// hence the same edge set, bit for bit, whatever the tie structure.
+//
+// Also fuses MinimumSpanningTree._build_matrix_index / _build_feature_weight (LTF/modules/tree_filter.py:15-34): on the
+// implicit 4-connected grid the edge list is never materialised and the weights come straight from the embedding.
+#include "common.cuh"
+
+namespace {
+
+typedef unsigned long long u64;
+constexpr u64 KEY_INF = ~0ull;
+
+struct Ws {
+    int *comp;       // [B,V] component root of every vertex (fully compressed between rounds)
+    int *parent;     // [B,V] hook target of a root (self when not hooked)
+    u64 *best;       // [B,V] cheapest outgoing edge key of a root
+    float *wgt;      // [B,E] edge weights (grid entry point only)
+    unsigned char *intree;  // [B,E]
+    int *ncomp;      // [B]
+    int *done;       // [B]
+};
+
+size_t ws_layout(int B, int V, int E, char *base, Ws *w) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        char *p = base ? base + off : nullptr;
+        off += align_up(bytes, 256);
+        return p;
+    };
+    Ws t;
+    t.comp = (int *)take((size_t)B * V * sizeof(int));
+    t.parent = (int *)take((size_t)B * V * sizeof(int));
+    t.best = (u64 *)take((size_t)B * V * sizeof(u64));
+    t.wgt = (float *)take((size_t)B * E * sizeof(float));
+    t.intree = (unsigned char *)take((size_t)B * E);
+    t.ncomp = (int *)take((size_t)B * sizeof(int));
+    t.done = (int *)take((size_t)B * sizeof(int));
+    if (w) *w = t;
+    return off;
+}
+
+__device__ __forceinline__ unsigned orderable(float f) {
+    unsigned u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// Grid edge numbering of the reference (tree_filter.py:20-23): vertical edges row-major first, then horizontal ones.
+__device__ __forceinline__ void grid_endpoints(int e, int H, int W, int &u, int &v) {
+    const int nvert = (H - 1) * W;
+    if (e < nvert) {
+        u = e;
+        v = e + W;
+    } else {
+        const int r = e - nvert, h = r / (W - 1), w = r - h * (W - 1);
+        u = h * W + w;
+        v = u + 1;
+    }
+}
+
+__global__ void mst_init_kernel(Ws ws, int V, int E) {
+    const int b = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < V) {
+        ws.comp[(size_t)b * V + i] = i;
+        ws.parent[(size_t)b * V + i] = i;
+        ws.best[(size_t)b * V + i] = KEY_INF;
+    }
+    if (i < E) ws.intree[(size_t)b * E + i] = 0;
+    if (i == 0) {
+        ws.ncomp[b] = V;
+        ws.done[b] = (V <= 1);
+    }
+}
+
+// weight = sum_c (x_u - x_v)^2 + 1, channels in order, no fused multiply-add (bits equal to torch's, tree_filter.py:27-34)
+__global__ void grid_weight_kernel(const float *__restrict__ embed, float *__restrict__ wgt, int D, int H, int W, int E) {
+    const int b = blockIdx.y;
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= E) return;
+    int u, v;
+    grid_endpoints(e, H, W, u, v);
+    const size_t V = (size_t)H * W;
+    const float *x = embed + (size_t)b * D * V;
+    float d = 0.f;
+    for (int c = 0; c < D; ++c) {
+        const float t = __fsub_rn(x[c * V + u], x[c * V + v]);
+        d = __fadd_rn(d, __fmul_rn(t, t));
+    }
+    wgt[(size_t)b * E + e] = __fadd_rn(d, 1.f);
+}
+
+template <bool GRID>
+__global__ void mst_find_kernel(Ws ws, const int *__restrict__ edge_index, const float *__restrict__ edge_weight, int V,
+                                int E, int H, int W) {
+    const int b = blockIdx.y;
+    if (ws.done[b]) return;
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= E) return;
+    int u, v;
+    if (GRID) {
+        grid_endpoints(e, H, W, u, v);
+    } else {
+        const int2 uv = reinterpret_cast<const int2 *>(edge_index)[(size_t)b * E + e];
+        u = uv.x;
+        v = uv.y;
+    }
+    const int *comp = ws.comp + (size_t)b * V;
+    const int cu = comp[u], cv = comp[v];
+    if (cu == cv) return;
+    const u64 key = ((u64)orderable(edge_weight[(size_t)b * E + e]) << 32) | (unsigned)e;
+    u64 *best = ws.best + (size_t)b * V;
+    if (key < best[cu]) atomicMin(best + cu, key);
+    if (key < best[cv]) atomicMin(best + cv, key);
+}
+
+template <bool GRID>
+__global__ void mst_hook_kernel(Ws ws, const int *__restrict__ edge_index, int V, int E, int H, int W) {
+    const int b = blockIdx.y;
+    if (ws.done[b]) return;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= V) return;
+    const int *comp = ws.comp + (size_t)b * V;
+    if (comp[c] != c) return;  // not a component root
+    const u64 *best = ws.best + (size_t)b * V;
+    const u64 key = best[c];
+    if (key == KEY_INF) return;
+    const int e = (int)(unsigned)(key & 0xffffffffull);
+    int u, v;
+    if (GRID) {
+        grid_endpoints(e, H, W, u, v);
+    } else {
+        const int2 uv = reinterpret_cast<const int2 *>(edge_index)[(size_t)b * E + e];
+        u = uv.x;
+        v = uv.y;
+    }
+    const int cu = comp[u], cv = comp[v];
+    const int other = (cu == c) ? cv : cu;
+    // two components that picked the same edge: the smaller root stays a root, the larger one hooks and records the edge
+    if (best[other] == key && c < other) return;
+    ws.parent[(size_t)b * V + c] = other;
+    ws.intree[(size_t)b * E + e] = 1;
+    atomicSub(ws.ncomp + b, 1);
+}
+
+__global__ void mst_compress_kernel(Ws ws, int V) {
+    const int b = blockIdx.y;
+    if (ws.done[b]) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= V) return;
+    const int *parent = ws.parent + (size_t)b * V;
+    int r = ws.comp[(size_t)b * V + i];
+    int p = parent[r];
+    while (p != r) {
+        r = p;
+        p = parent[r];
+    }
+    ws.comp[(size_t)b * V + i] = r;
+    ws.best[(size_t)b * V + i] = KEY_INF;
+}
+
+__global__ void mst_finish_round_kernel(Ws ws, int B) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < B && ws.ncomp[b] <= 1) ws.done[b] = 1;
+}
+
+// One CTA per image: stable compaction of the selected edges, in increasing edge index.  Unused slots (disconnected
+// input) are filled with -1.
+template <bool GRID>
+__global__ void __launch_bounds__(1024)
+mst_compact_kernel(Ws ws, const int *__restrict__ edge_index, int *__restrict__ edge_out, int V, int E, int H, int W) {
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const unsigned char *flag = ws.intree + (size_t)b * E;
+    int2 *out = reinterpret_cast<int2 *>(edge_out) + (size_t)b * (V - 1);
+    __shared__ int s_warp[32];
+    __shared__ int s_base, s_total;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (int e0 = 0; e0 < E; e0 += 1024) {
+        const int e = e0 + tid;
+        const int f = (e < E) ? flag[e] : 0;
+        const unsigned m = __ballot_sync(0xffffffffu, f);
+        if (lane == 0) s_warp[wid] = __popc(m);
+        __syncthreads();
+        if (wid == 0) {
+            const int v = s_warp[lane];
+            int x = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, x, o);
+                if (lane >= o) x += t;
+            }
+            s_warp[lane] = x - v;  // exclusive prefix over warps
+            if (lane == 31) s_total = x;
+        }
+        __syncthreads();
+        const int pos = s_base + s_warp[wid] + __popc(m & ((1u << lane) - 1u));
+        if (f && pos < V - 1) {
+            int u, v;
+            if (GRID) {
+                grid_endpoints(e, H, W, u, v);
+            } else {
+                const int2 uv = reinterpret_cast<const int2 *>(edge_index)[(size_t)b * E + e];
+                u = uv.x;
+                v = uv.y;
+            }
+            out[pos] = make_int2(u, v);
+        }
+        __syncthreads();
+        if (tid == 0) s_base += s_total;
+        __syncthreads();
+    }
+    for (int i = s_base + tid; i < V - 1; i += 1024) out[i] = make_int2(-1, -1);
+}
+
+int rounds_for(int V) {
+    int r = 0;
+    while ((1ll << r) < V) ++r;
+    return r + 1;
+}
+
+template <bool GRID>
+int run_mst(const int *edge_index, const float *edge_weight, int B, int E, int V, int H, int W, int *edge_out, Ws ws,
+            cudaStream_t st) {
+    if (V <= 1 || E <= 0) return 0;  // a single vertex has an empty tree
+    const int n = E > V ? E : V;
+    const dim3 blk(256);
+    mst_init_kernel<<<dim3((n + 255) / 256, B), blk, 0, st>>>(ws, V, E);
+    FEDICRA_CHECK_LAUNCH("mst_init_kernel");
+    const int rounds = rounds_for(V);
+    for (int r = 0; r < rounds; ++r) {
+        mst_find_kernel<GRID><<<dim3((E + 255) / 256, B), blk, 0, st>>>(ws, edge_index, edge_weight, V, E, H, W);
+        mst_hook_kernel<GRID><<<dim3((V + 255) / 256, B), blk, 0, st>>>(ws, edge_index, V, E, H, W);
+        mst_compress_kernel<<<dim3((V + 255) / 256, B), blk, 0, st>>>(ws, V);
+        mst_finish_round_kernel<<<(B + 127) / 128, 128, 0, st>>>(ws, B);
+    }
+    FEDICRA_CHECK_LAUNCH("mst round kernels");
+    mst_compact_kernel<GRID><<<B, 1024, 0, st>>>(ws, edge_index, edge_out, V, E, H, W);
+    FEDICRA_CHECK_LAUNCH("mst_compact_kernel");
+    return 0;
+}
+
+}  // namespace
+
+extern "C" size_t fedicra_mst_workspace_bytes(int B, int V, int E) {
+    if (B <= 0 || V <= 0 || E < 0) return 0;
+    return ws_layout(B, V, E, nullptr, nullptr);
+}
+
+extern "C" int fedicra_mst_forward(const int *edge_index, const float *edge_weight, int B, int E, int V, int *edge_out,
+                                   void *workspace, size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(edge_index && edge_weight && edge_out && workspace, "mst_forward: null pointer");
+    FEDICRA_REQUIRE(B > 0 && B <= 65535 && V >= 1 && E >= V - 1, "mst_forward: bad sizes B=%d E=%d V=%d", B, E, V);
+    FEDICRA_REQUIRE(workspace_bytes >= fedicra_mst_workspace_bytes(B, V, E), "mst_forward: workspace too small");
+    FEDICRA_REQUIRE(((uintptr_t)edge_index & 7) == 0 && ((uintptr_t)edge_out & 7) == 0,
+                    "mst_forward: edge arrays must be 8-byte aligned");
+    Ws ws;
+    ws_layout(B, V, E, (char *)workspace, &ws);
+    return run_mst<false>(edge_index, edge_weight, B, E, V, 0, 0, edge_out, ws, (cudaStream_t)stream);
+}
+
+extern "C" int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out, void *workspace,
+                                size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(embed && edge_out && workspace, "mst_grid: null pointer");
+    FEDICRA_REQUIRE(B > 0 && B <= 65535 && D > 0 && H >= 1 && W >= 1 && (long long)H * W < (1ll << 30),
+                    "mst_grid: bad sizes B=%d D=%d H=%d W=%d", B, D, H, W);
+    const int V = H * W, E = 2 * H * W - H - W;
+    FEDICRA_REQUIRE(workspace_bytes >= fedicra_mst_workspace_bytes(B, V, E), "mst_grid: workspace too small");
+    FEDICRA_REQUIRE(((uintptr_t)edge_out & 7) == 0, "mst_grid: edge_out must be 8-byte aligned");
+    Ws ws;
+    ws_layout(B, V, E, (char *)workspace, &ws);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (E > 0) {
+        grid_weight_kernel<<<dim3((E + 255) / 256, B), 256, 0, st>>>(embed, ws.wgt, D, H, W, E);
+        FEDICRA_CHECK_LAUNCH("grid_weight_kernel");
+    }
+    return run_mst<true>(nullptr, ws.wgt, B, E, V, H, W, edge_out, ws, st);
+}

@@ -1,0 +1,190 @@
+"""Thin tensor-level wrappers over the C ABI: argument checks, output allocation, workspace caching, stream hand-off.
+
+PyTorch is only the allocator and the stream owner here; every function launches kernels of libfedicra_sm100.so.
+"""
+import torch
+
+from ._lib import GcrfDesc, check, lib
+
+_WORKSPACES = {}
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def workspace(tag, nbytes, device):
+    """Zero-initialised scratch buffer, cached per (purpose, device, stream) and grown on demand."""
+    key = (tag, device.index if device.index is not None else torch.cuda.current_device(), _stream())
+    buf = _WORKSPACES.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.zeros(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+        _WORKSPACES[key] = buf
+    return buf
+
+
+def _cuda(t, dtype, name):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor: fedicra_b200 has no CPU path")
+    if t.dtype != dtype:
+        raise RuntimeError(f"{name} must be {dtype}, got {t.dtype}")
+    return t.contiguous()
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+# ------------------------------------------------------------------ Gated CRF
+
+
+def gcrf_fwd_bwd(y, image, radius, descs, want_grad=True):
+    """descs: list of (weight, sigma_xy or 0, sigma_rgb or 0).  Returns (loss[1], grad_y or None)."""
+    y = _cuda(y, torch.float32, "y_hat_softmax")
+    image = _cuda(image, torch.float32, "sample")
+    N, C, H, W = y.shape
+    assert image.shape[0] == N and image.shape[2:] == (H, W)
+    with torch.cuda.device(y.device):
+        loss = torch.empty(1, dtype=torch.float32, device=y.device)
+        grad = torch.empty_like(y) if want_grad else None
+        nbytes = lib.fedicra_gcrf_workspace_bytes(N, H, W)
+        ws = workspace("gcrf", nbytes, y.device)
+        arr = (GcrfDesc * len(descs))(*[GcrfDesc(float(w), float(sx), float(sr)) for (w, sx, sr) in descs])
+        check(lib.fedicra_gcrf_fwd_bwd(_p(y), _p(image), N, C, image.shape[1], H, W, int(radius), arr, len(descs),
+                                       _p(loss), _p(grad), _p(ws), ws.numel(), _stream()), "gcrf_fwd_bwd")
+    return loss, grad
+
+
+# ------------------------------------------------------------------ MST
+
+
+def mst_forward(edge_index, edge_weight, vertex_count):
+    ei = _cuda(edge_index, torch.int32, "edge_index")
+    ew = _cuda(edge_weight, torch.float32, "edge_weight")
+    B, E = ei.shape[0], ei.shape[1]
+    V = int(vertex_count)
+    with torch.cuda.device(ei.device):
+        out = torch.empty(B, V - 1, 2, dtype=torch.int32, device=ei.device)
+        ws = workspace("mst", lib.fedicra_mst_workspace_bytes(B, V, E), ei.device)
+        check(lib.fedicra_mst_forward(_p(ei), _p(ew), B, E, V, _p(out), _p(ws), ws.numel(), _stream()), "mst_forward")
+    return out
+
+
+def mst_grid(embed):
+    e = _cuda(embed, torch.float32, "guide_in")
+    B, D, H, W = e.shape
+    V, E = H * W, 2 * H * W - H - W
+    with torch.cuda.device(e.device):
+        out = torch.empty(B, V - 1, 2, dtype=torch.int32, device=e.device)
+        ws = workspace("mst", lib.fedicra_mst_workspace_bytes(B, V, E), e.device)
+        check(lib.fedicra_mst_grid(_p(e), B, D, H, W, _p(out), _p(ws), ws.numel(), _stream()), "mst_grid")
+    return out
+
+
+# ------------------------------------------------------------------ BFS
+
+
+def bfs_forward(tree):
+    """-> sorted_index [B,V], sorted_parent [B,V], sorted_child [B,V,4], level_start [B,V+1], n_levels [B]."""
+    t = _cuda(tree, torch.int32, "tree")
+    B, V = t.shape[0], t.shape[1] + 1
+    dev = t.device
+    with torch.cuda.device(dev):
+        si = torch.zeros(B, V, dtype=torch.int32, device=dev)
+        sp = torch.zeros(B, V, dtype=torch.int32, device=dev)
+        sc = torch.zeros(B, V, 4, dtype=torch.int32, device=dev)
+        ls = torch.empty(B, V + 1, dtype=torch.int32, device=dev)
+        nl = torch.empty(B, dtype=torch.int32, device=dev)
+        ws = workspace("bfs", lib.fedicra_bfs_workspace_bytes(B, V), dev)
+        check(lib.fedicra_bfs_forward(_p(t), B, V, _p(si), _p(sp), _p(sc), _p(ls), _p(nl), _p(ws), ws.numel(),
+                                      _stream()), "bfs_forward")
+    return si, sp, sc, ls, nl
+
+
+# ------------------------------------------------------------------ edge weights
+
+
+def edge_weight_fwd(embed, si, sp, inv_sigma):
+    e = _cuda(embed, torch.float32, "embed_in")
+    B, D, V = e.shape
+    with torch.cuda.device(e.device):
+        ew = torch.empty(B, V, dtype=torch.float32, device=e.device)
+        check(lib.fedicra_edge_weight_fwd(_p(e), _p(si), _p(sp), B, D, V, float(inv_sigma), _p(ew), _stream()),
+              "edge_weight_fwd")
+    return ew
+
+
+def edge_weight_bwd(embed, si, sp, sc, ew, grad_ew, inv_sigma):
+    e = _cuda(embed, torch.float32, "embed_in")
+    g = _cuda(grad_ew, torch.float32, "grad_edge_weight")
+    B, D, V = e.shape
+    with torch.cuda.device(e.device):
+        out = torch.empty_like(e)
+        check(lib.fedicra_edge_weight_bwd(_p(e), _p(si), _p(sp), _p(sc), _p(ew), _p(g), B, D, V, float(inv_sigma),
+                                          _p(out), _stream()), "edge_weight_bwd")
+    return out
+
+
+# ------------------------------------------------------------------ refine
+
+
+def refine_forward(feature_in, edge_weight, si, sp, sc, ls, nl):
+    f = _cuda(feature_in, torch.float32, "feature_in")
+    if not (edge_weight.is_cuda and edge_weight.dtype == torch.float32 and edge_weight.is_contiguous()):
+        raise RuntimeError("edge_weight must be a contiguous float32 CUDA tensor (it is written in place)")
+    B, C, V = f.shape
+    dev = f.device
+    with torch.cuda.device(dev):
+        out, aggr, aggr_up = torch.empty_like(f), torch.empty_like(f), torch.empty_like(f)
+        wsum = torch.empty(B, V, dtype=torch.float32, device=dev)
+        wsum_up = torch.empty(B, V, dtype=torch.float32, device=dev)
+        check(lib.fedicra_refine_forward(_p(f), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(ls), _p(nl), B, C, V,
+                                         _p(out), _p(aggr), _p(aggr_up), _p(wsum), _p(wsum_up), _stream()),
+              "refine_forward")
+    return out, aggr, aggr_up, wsum, wsum_up
+
+
+def refine_backward_feature(edge_weight, si, sp, sc, ls, nl, weight_sum, grad_out):
+    g = _cuda(grad_out, torch.float32, "grad_output")
+    B, C, V = g.shape
+    with torch.cuda.device(g.device):
+        out = torch.empty_like(g)
+        ws = workspace("refine_bwd", lib.fedicra_refine_backward_workspace_bytes(B, C, V), g.device)
+        check(lib.fedicra_refine_backward_feature(_p(edge_weight), _p(si), _p(sp), _p(sc), _p(ls), _p(nl),
+                                                  _p(weight_sum), _p(g), B, C, V, _p(out), _p(ws), ws.numel(),
+                                                  _stream()), "refine_backward_feature")
+    return out
+
+
+def refine_backward_weight(edge_weight, si, sp, sc, ls, nl, feature_out, feature_aggr, feature_aggr_up, weight_sum,
+                           weight_sum_up, grad_out):
+    g = _cuda(grad_out, torch.float32, "grad_output")
+    B, C, V = g.shape
+    with torch.cuda.device(g.device):
+        out = torch.empty(B, V, dtype=torch.float32, device=g.device)
+        ws = workspace("refine_bwd", lib.fedicra_refine_backward_workspace_bytes(B, C, V), g.device)
+        check(lib.fedicra_refine_backward_weight(_p(edge_weight), _p(si), _p(sp), _p(sc), _p(ls), _p(nl),
+                                                 _p(feature_out), _p(feature_aggr), _p(feature_aggr_up),
+                                                 _p(weight_sum), _p(weight_sum_up), _p(g), B, C, V, _p(out), _p(ws),
+                                                 ws.numel(), _stream()), "refine_backward_weight")
+    return out
+
+
+# ------------------------------------------------------------------ aggregation
+
+
+def ala_update_flat(p, s, g, w, t, eta):
+    n = p.numel()
+    for name, x in (("p", p), ("s", s), ("w", w), ("t", t)):
+        if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and x.numel() == n):
+            raise RuntimeError(f"ala_update_flat: {name} must be a contiguous float32 CUDA tensor of {n} elements")
+    with torch.cuda.device(p.device):
+        check(lib.fedicra_ala_update_flat(_p(p), _p(s), _p(g), _p(w), _p(t), n, float(eta), _stream()),
+              "ala_update_flat")
+
+
+def scale_inplace(x, alpha):
+    if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()):
+        raise RuntimeError("scale_inplace: x must be a contiguous float32 CUDA tensor")
+    with torch.cuda.device(x.device):
+        check(lib.fedicra_scale_inplace(_p(x), x.numel(), float(alpha), _stream()), "scale_inplace")

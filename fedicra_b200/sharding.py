@@ -1,0 +1,29 @@
+"""Image sharding of the loss stack across the GPUs of one node.
+
+Every image owns its trees, BFS orders, filters and CRF windows, so a contiguous split of the batch needs no data-path
+collective.  The only cross-image coupling is the tree-energy normaliser N = ROI.sum() over the WHOLE batch
+(flower_common.py:777, 813-816): ranks all-reduce the two scalars (masked-L1 sum, N) before dividing, which makes the
+sharded loss and gradients equal the unsharded ones.  The Gated CRF denominator N*H*W is static.
+"""
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n_items, rank, world):
+    """Contiguous [lo, hi) of `n_items` owned by `rank`; earlier ranks take the remainder."""
+    base, extra = divmod(n_items, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def sharded_masked_l1(local_sum, local_n, group=None):
+    """(sum over ranks of local_sum) / (sum over ranks of local_n), differentiable w.r.t. local_sum."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return local_sum / local_n if float(local_n) > 0 else local_sum
+    pair = torch.stack([local_sum.detach().float(), local_n.detach().float()])
+    dist.all_reduce(pair, op=dist.ReduceOp.SUM, group=group)
+    total_n = pair[1]
+    if float(total_n) <= 0:
+        return local_sum
+    # value = global sum / global N; gradient flows through this rank's share only
+    return (local_sum + (pair[0] - local_sum.detach())) / total_n

@@ -1,0 +1,91 @@
+"""Tree-energy losses with the reference's class names and ``forward`` signatures
+(/root/reference/code/flower_common.py:646-689 TreeEnergyLoss, :692-753 MScaleAddTreeEnergyLoss,
+:756-818 MScaleRecurveTreeEnergyLoss -- the one FedICRA's training loop uses, OURS.py:64,142).
+
+The reference's own classes also run unchanged on this package (they only need MinimumSpanningTree / TreeFilter2D,
+flower_common.py:32-33); these mirrors exist so the loss stack is usable without importing flower_common.
+"""
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .tree_filter import MinimumSpanningTree, TreeFilter2D
+
+
+def _prepare(preds, low_feats, unlabeled_ROIs):
+    """flower_common.py:770-777: bring the image embedding and the ROI mask to the prediction size."""
+    with torch.no_grad():
+        h, w = preds.shape[2:]
+        if low_feats.shape[2:] != (h, w):
+            low_feats = F.interpolate(low_feats, size=(h, w), mode='bilinear', align_corners=False)
+        roi = unlabeled_ROIs.unsqueeze(1).float()
+        if roi.shape[2:] != (h, w):
+            roi = F.interpolate(roi, size=(h, w), mode='nearest')
+        return low_feats, roi, roi.sum()
+
+
+def _resize(feats, h, w):
+    """Bilinear resize of a decoder head to the prediction size (identity when already there)."""
+    if feats.shape[2:] == (h, w):
+        return feats
+    return F.interpolate(feats, size=(h, w), mode='bilinear', align_corners=False)
+
+
+def _masked_l1(roi, prob, filtered, n):
+    loss = (roi * torch.abs(prob - filtered)).sum()
+    if n > 0:  # host sync, as in the reference (flower_common.py:815)
+        loss = loss / n
+    return loss
+
+
+class _TreeLossBase(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.mst_layers = MinimumSpanningTree(TreeFilter2D.norm2_distance)
+        self.tree_filter_layers = TreeFilter2D(groups=1, sigma=0.02)
+
+    def _low(self, prob, low_feats):
+        tree = self.mst_layers(low_feats)
+        return self.tree_filter_layers(feature_in=prob, embed_in=low_feats, tree=tree)
+
+    def _high(self, feature, high_feats, h, w):
+        high_feats = _resize(high_feats, h, w)
+        tree = self.mst_layers(high_feats)
+        return self.tree_filter_layers(feature_in=feature, embed_in=high_feats, tree=tree, low_tree=False)
+
+
+class TreeEnergyLoss(_TreeLossBase):
+    def forward(self, preds, low_feats, high_feats, unlabeled_ROIs, weight):
+        low_feats, roi, n = _prepare(preds, low_feats, unlabeled_ROIs)
+        h, w = preds.shape[2:]
+        prob = torch.softmax(preds, dim=1)
+        AS = self._low(prob, low_feats)
+        if high_feats is not None:
+            AS = self._high(AS, high_feats, h, w)
+        return weight * _masked_l1(roi, prob, AS, n), AS
+
+
+class MScaleAddTreeEnergyLoss(_TreeLossBase):
+    def forward(self, preds, low_feats, high_feats_1, high_feats_2, high_feats_3, unlabeled_ROIs, weight):
+        low_feats, roi, n = _prepare(preds, low_feats, unlabeled_ROIs)
+        h, w = preds.shape[2:]
+        prob = torch.softmax(preds, dim=1)
+        AS = self._low(prob, low_feats)
+        outs = [self._high(AS, hf, h, w) for hf in (high_feats_1, high_feats_2, high_feats_3)]
+        loss = sum((roi * torch.abs(prob - o)).sum() for o in outs)
+        if n > 0:
+            loss = loss / n
+        return (weight * loss, *outs)
+
+
+class MScaleRecurveTreeEnergyLoss(_TreeLossBase):
+    def forward(self, preds, low_feats, high_feats_1, high_feats_2, high_feats_3, unlabeled_ROIs, weight):
+        low_feats, roi, n = _prepare(preds, low_feats, unlabeled_ROIs)
+        h, w = preds.shape[2:]
+        prob = torch.softmax(preds, dim=1)
+        cur = self._low(prob, low_feats)
+        outs = []
+        for hf in (high_feats_1, high_feats_2, high_feats_3):
+            cur = self._high(cur, hf, h, w)
+            outs.append(cur)
+        return (weight * _masked_l1(roi, prob, cur, n), *outs)

@@ -1,0 +1,146 @@
+/*
+ * fedicra_sm100.h -- C ABI of libfedicra_sm100.so, the B200 (sm_100a) implementation of FedICRA's weak-supervision
+ * loss hot path.  This is the drop-in boundary: plain pointers and sizes, no torch types.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer on the current CUDA device unless its name starts with `h_`;
+ *   - tensors are dense, row-major ("contiguous"), float = IEEE fp32, int = int32;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), never synchronises the host and
+ *     never allocates: scratch memory comes from the caller (`workspace`, size from the matching *_workspace_bytes);
+ *   - return value 0 = launched; negative = rejected (bad argument / launch failure), text in fedicra_last_error();
+ *   - there is no CPU fallback anywhere behind these symbols.
+ *
+ * Reference interfaces replaced (paths relative to /root/reference/code, LTF = utils/TreeEnergyLoss/kernels/
+ * lib_tree_filter):
+ *   pybind module tree_filter_cuda                       LTF/src/tree_filter.cpp:7-13
+ *   ModelLossSemsegGatedCRF.forward                      utils/gate_crf_loss.py:20-124
+ *   TreeFilter2D.build_edge_weight                       LTF/modules/tree_filter.py:91-108
+ *   MinimumSpanningTree._build_feature_weight            LTF/modules/tree_filter.py:27-34
+ *   MyModel.set_weights element-wise update              flower_common.py:553-555, 590-602
+ */
+#ifndef FEDICRA_SM100_H
+#define FEDICRA_SM100_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Text of the last error raised on the calling thread ("" if none). */
+const char *fedicra_last_error(void);
+/* ABI version of this header (bumped on any signature change). */
+int fedicra_abi_version(void);
+
+/* ------------------------------------------------------------------------------------------------ Gated CRF ---- */
+/* One kernel descriptor of the Gaussian mixture: K += weight * exp(-0.5*(|dxy|^2/sigma_xy^2 + |dI|^2/sigma_rgb^2)).
+ * A sigma <= 0 means "modality not used by this descriptor".   (gate_crf_loss.py:134-161, kernels_desc entries) */
+typedef struct {
+    float weight;
+    float sigma_xy;
+    float sigma_rgb;
+} fedicra_gcrf_desc;
+
+/* Scratch bytes needed by fedicra_gcrf_fwd_bwd for an [N,*,H,W] problem.  The scratch must be zero-filled once
+ * before its first use; the kernel leaves it reusable. */
+size_t fedicra_gcrf_workspace_bytes(int N, int H, int W);
+
+/* Fused forward + backward of ModelLossSemsegGatedCRF.forward (gate_crf_loss.py:20-124, live branch: no masks,
+ * Potts compatibility), without materialising any unfold tensor (replaces :89-99 and :163-172).
+ *   y        [N,C,H,W]   softmax probabilities
+ *   image    [N,Cin,H,W] the rgb modality already at prediction resolution (pooling, :126-132, stays on the host side)
+ *   loss     [1]         (sum K - sum_c y*(K (*) y)) / (N*H*W)
+ *   grad_y   [N,C,H,W]   d loss / d y  = -2 (K (*) y) / (N*H*W)            (may be NULL: forward only)
+ * Out-of-image taps see zero features, exactly like F.unfold's zero padding (:183-188). */
+int fedicra_gcrf_fwd_bwd(const float *y, const float *image, int N, int C, int Cin, int H, int W, int radius,
+                         const fedicra_gcrf_desc *h_descs, int n_desc, float *loss, float *grad_y, void *workspace,
+                         size_t workspace_bytes, void *stream);
+
+/* ------------------------------------------------------------------------------------------------ MST ---------- */
+/* Scratch bytes for the two MST entry points (B images, V vertices, E candidate edges each). */
+size_t fedicra_mst_workspace_bytes(int B, int V, int E);
+
+/* mst_forward (LTF/src/mst/mst.cu:86-117 + boruvka.cpp:20-112): minimum spanning tree of B graphs given as explicit
+ * edge lists.  Ties are broken by edge index, which is the edge set the reference's sequential Boruvka produces.
+ *   edge_index  [B,E,2] int32, edge_weight [B,E] fp32 (no NaN)  ->  edge_out [B,V-1,2] int32 in increasing edge index.
+ * Unlike the reference it never leaves the device (no D2H/H2D, no host threads). */
+int fedicra_mst_forward(const int *edge_index, const float *edge_weight, int B, int E, int V, int *edge_out,
+                        void *workspace, size_t workspace_bytes, void *stream);
+
+/* MinimumSpanningTree.forward on the implicit 4-connected grid (LTF/modules/tree_filter.py:15-34, 53-62 fused with
+ * mst_forward): edge e<(H-1)*W joins (h,w)-(h+1,w), the rest join (h,w)-(h,w+1); weight = sum_c (delta)^2 + 1 summed in
+ * channel order without fused multiply-add, so the fp32 bits equal torch's.
+ *   embed [B,D,H,W]  ->  edge_out [B,H*W-1,2] int32 (increasing edge index). */
+int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out, void *workspace,
+                     size_t workspace_bytes, void *stream);
+
+/* ------------------------------------------------------------------------------------------------ BFS ---------- */
+size_t fedicra_bfs_workspace_bytes(int B, int V);
+
+/* bfs_forward (LTF/src/bfs/bfs.cu:100-135) with max_adj_per_vertex = 4, from root vertex 0.
+ *   tree [B,V-1,2]  ->  sorted_index [B,V], sorted_parent [B,V], sorted_child [B,V,4]   (bfs.cu:46-98 semantics)
+ *   level_start [B,V+1] first BFS position of every depth (entry n_levels[b] = V), n_levels [B]  (extra outputs)
+ * The order is deterministic: by depth, then by parent position, then by vertex id (the reference's is whatever its
+ * atomics produce). */
+int fedicra_bfs_forward(const int *tree, int B, int V, int *sorted_index, int *sorted_parent, int *sorted_child,
+                        int *level_start, int *n_levels, void *workspace, size_t workspace_bytes, void *stream);
+
+/* ------------------------------------------------------------------------------------------------ tree filter -- */
+/* TreeFilter2D.build_edge_weight (LTF/modules/tree_filter.py:91-108): ew[b,i] = exp(-|e[v(i)] - e[v(par i)]|^2 *
+ * inv_sigma) in BFS order; embed [B,D,V] in vertex order. */
+int fedicra_edge_weight_fwd(const float *embed, const int *sorted_index, const int *sorted_parent, int B, int D, int V,
+                            float inv_sigma, float *edge_weight, void *stream);
+/* Its backward (what autograd derives from the gathers at tree_filter.py:84-89,97-106): grad_embed [B,D,V] is
+ * OVERWRITTEN with the gradient; deterministic (no atomics). sorted_child is needed to visit children. */
+int fedicra_edge_weight_bwd(const float *embed, const int *sorted_index, const int *sorted_parent,
+                            const int *sorted_child, const float *edge_weight, const float *grad_edge_weight, int B,
+                            int D, int V, float inv_sigma, float *grad_embed, void *stream);
+
+/* refine_forward (LTF/src/refine/refine.cu:201-249).  Writes 0 into edge_weight[:,0] like the reference (:43-46).
+ *   feature_in [B,C,V] vertex order; edge_weight [B,V] BFS order
+ *   -> feature_out, feature_aggr [B,C,V] vertex order; feature_aggr_up [B,C,V] BFS order;
+ *      weight_sum [B,V] vertex order; weight_sum_up [B,V] BFS order. */
+int fedicra_refine_forward(const float *feature_in, float *edge_weight, const int *sorted_index,
+                           const int *sorted_parent, const int *sorted_child, const int *level_start,
+                           const int *n_levels, int B, int C, int V, float *feature_out, float *feature_aggr,
+                           float *feature_aggr_up, float *weight_sum, float *weight_sum_up, void *stream);
+
+size_t fedicra_refine_backward_workspace_bytes(int B, int C, int V);
+
+/* refine_backward_feature (refine.cu:251-300): grad_feature [B,C,V] vertex order. */
+int fedicra_refine_backward_feature(const float *edge_weight, const int *sorted_index, const int *sorted_parent,
+                                    const int *sorted_child, const int *level_start, const int *n_levels,
+                                    const float *weight_sum, const float *grad_out, int B, int C, int V,
+                                    float *grad_feature, void *workspace, size_t workspace_bytes, void *stream);
+
+/* refine_backward_weight (refine.cu:302-370): grad_weight [B,V] BFS order. */
+int fedicra_refine_backward_weight(const float *edge_weight, const int *sorted_index, const int *sorted_parent,
+                                   const int *sorted_child, const int *level_start, const int *n_levels,
+                                   const float *feature_out, const float *feature_aggr, const float *feature_aggr_up,
+                                   const float *weight_sum, const float *weight_sum_up, const float *grad_out, int B,
+                                   int C, int V, float *grad_weight, void *workspace, size_t workspace_bytes,
+                                   void *stream);
+
+/* ------------------------------------------------------------------------------------------------ aggregation -- */
+/* Adaptive local aggregation, element-wise part of MyModel.set_weights (flower_common.py:590-602) over one flat
+ * array: w <- clamp(w - eta*g*(s-p), 0, 1);  t <- p + (s-p)*w.   No fused multiply-add: bit-exact with torch.
+ * g may be NULL (blend only, flower_common.py:553-555). */
+int fedicra_ala_update_flat(const float *p, const float *s, const float *g, float *w, float *t, int64_t n, float eta,
+                            void *stream);
+
+/* Same over a list of tensors in ONE launch.  Tables are device arrays: p/s/g/w/t [n_tensors] of pointers (g entries
+ * may be 0 = "no gradient, skip the weight update", flower_common.py:593-594), chunk_tensor/chunk_begin [n_chunks]
+ * int32/int64 describing which tensor and which element offset each CTA works on, sizes [n_tensors] int64. */
+int fedicra_ala_update_multi(const float *const *p, const float *const *s, const float *const *g, float *const *w,
+                             float *const *t, const int64_t *sizes, const int *chunk_tensor,
+                             const int64_t *chunk_begin, int n_chunks, int chunk_elems, float eta, void *stream);
+
+/* FedAvg pre-scale: x <- x * alpha (alpha = n_i / sum n), the local half of sum_i n_i W_i / sum_i n_i
+ * (flwr 1.0.0 aggregate(), called from flower_common.py:262); the sum itself is one NCCL all-reduce. */
+int fedicra_scale_inplace(float *x, int64_t n, float alpha, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEDICRA_SM100_H */

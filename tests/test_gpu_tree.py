@@ -1,0 +1,137 @@
+"""MST / BFS / edge weights / refine kernels (through the C ABI) against the CPU oracle and the golden fixtures."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import losses_cpu, tree_cpu
+from tests.helpers import edge_set, make_image, parents_and_depth, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def gpu_tree(emb):
+    from fedicra_b200 import ops
+    return ops.mst_grid(emb.cuda())
+
+
+@pytest.mark.parametrize("name", ["mst_real_faz.npz", "mst_quant8.npz", "mst_constant.npz", "mst_uniform.npz"])
+def test_mst_golden_edge_sets_bit_exact(golden_dir, name):
+    z = np.load(os.path.join(golden_dir, name))
+    emb = torch.from_numpy(z["embed"])
+    tree = gpu_tree(emb).cpu().numpy()
+    for b in range(emb.shape[0]):
+        assert np.array_equal(edge_set(tree[b]), edge_set(z["tree"][b]))
+
+
+@pytest.mark.parametrize("kind,B,D,H,W", [
+    ("quant8", 3, 3, 33, 47), ("uniform", 2, 2, 64, 64), ("constant", 1, 1, 40, 24), ("quant8", 2, 1, 1, 50),
+    ("quant8", 2, 1, 50, 1), ("uniform", 1, 3, 2, 2), ("quant8", 12, 3, 256, 256), ("quant8", 1, 3, 512, 512),
+])
+def test_mst_grid_and_explicit_equal_oracle(kind, B, D, H, W):
+    from fedicra_b200 import tree_filter_cuda
+    g = torch.Generator().manual_seed(H * 7 + W)
+    emb = make_image(kind, B, D, H, W, g)
+    ref = losses_cpu.minimum_spanning_tree(emb).numpy()
+    got = gpu_tree(emb).cpu().numpy()
+    idx = losses_cpu.grid_edges(H, W).unsqueeze(0).expand(B, -1, -1).contiguous()
+    wgt = losses_cpu.grid_weights(emb).contiguous()
+    got2 = tree_filter_cuda.mst_forward(idx.cuda(), wgt.cuda(), H * W).cpu().numpy()
+    V = H * W
+    for b in range(B):
+        want = edge_set(ref[b])
+        assert np.array_equal(edge_set(got[b]), want)       # fused grid weights + MST
+        assert np.array_equal(edge_set(got2[b]), want)      # reference-style explicit edge list
+        if V <= 4096:                                        # parent-of-vertex and depth arrays, rooted at 0
+            p_ref, d_ref = parents_and_depth(ref[b], V)
+            p_got, d_got = parents_and_depth(got[b], V)
+            assert np.array_equal(p_ref, p_got) and np.array_equal(d_ref, d_got)
+
+
+@pytest.mark.parametrize("kind,B,H,W", [("quant8", 3, 33, 47), ("constant", 1, 40, 24), ("uniform", 2, 1, 17),
+                                        ("quant8", 2, 256, 256)])
+def test_bfs_arrays_bit_exact(kind, B, H, W):
+    from fedicra_b200 import ops
+    emb = make_image(kind, B, 3, H, W, torch.Generator().manual_seed(1))
+    tree = losses_cpu.minimum_spanning_tree(emb)
+    si, sp, sc = tree_cpu.bfs_forward(tree, 4)
+    gsi, gsp, gsc, gls, gnl = ops.bfs_forward(tree.cuda())
+    assert torch.equal(gsi.cpu(), si) and torch.equal(gsp.cpu(), sp) and torch.equal(gsc.cpu(), sc)
+    for b in range(B):
+        _, _, _, ls = tree_cpu.bfs_levels(tree[b])
+        n = int(gnl[b])
+        assert n == len(ls) - 1 and torch.equal(gls[b, :n + 1].cpu(), ls)
+
+
+def test_bfs_single_vertex():
+    from fedicra_b200 import ops
+    si, sp, sc, ls, nl = ops.bfs_forward(torch.zeros(2, 0, 2, dtype=torch.int32, device="cuda"))
+    assert si.tolist() == [[0], [0]] and nl.tolist() == [1, 1] and ls.tolist() == [[0, 1], [0, 1]]
+
+
+def _tree_case(kind, B, C, D, H, W, seed=3):
+    g = torch.Generator().manual_seed(seed)
+    emb = make_image(kind, B, D, H, W, g)
+    feat = torch.rand(B, C, H * W, generator=g)
+    gout = torch.randn(B, C, H * W, generator=g)
+    tree = losses_cpu.minimum_spanning_tree(emb)
+    return emb, feat, gout, tree
+
+
+@pytest.mark.parametrize("kind,B,C,D,H,W,inv_sigma", [
+    ("uniform", 2, 2, 3, 24, 31, 1.0), ("quant8", 1, 3, 3, 40, 40, 50.0), ("constant", 1, 2, 1, 9, 7, 1.0),
+    ("uniform", 1, 1, 2, 1, 13, 1.0), ("uniform", 12, 2, 3, 256, 256, 50.0), ("quant8", 2, 3, 3, 512, 512, 1.0),
+])
+def test_reference_operator_surface_vs_oracle(kind, B, C, D, H, W, inv_sigma):
+    """tree_filter_cuda.{bfs_forward,refine_forward,refine_backward_feature,refine_backward_weight} + edge weights."""
+    from fedicra_b200 import ops, tree_filter_cuda as tfc
+    emb, feat, gout, tree = _tree_case(kind, B, C, D, H, W)
+    V = H * W
+    si, sp, sc = tree_cpu.bfs_forward(tree, 4)
+    ew = tree_cpu.edge_weight(emb.reshape(B, D, V), si, sp, inv_sigma)
+    saved = tree_cpu.refine_forward(feat, ew, si, sp, sc)
+    gf = tree_cpu.refine_backward_feature(feat, ew, si, sp, sc, *saved, gout)
+    gw = tree_cpu.refine_backward_weight(feat, ew, si, sp, sc, *saved, gout)
+    ge = tree_cpu.edge_weight_bwd(emb.reshape(B, D, V), si, sp, inv_sigma, ew, gw)
+
+    csi, csp, csc = tfc.bfs_forward(tree.cuda(), 4)
+    order = ops.bfs_forward(tree.cuda())
+    cew = ops.edge_weight_fwd(emb.reshape(B, D, V).cuda(), csi, csp, inv_sigma)
+    assert rel_err(cew.cpu()[:, 1:], tree_cpu.edge_weight(emb.reshape(B, D, V), si, sp, inv_sigma)[:, 1:]) < 1e-5
+    cf = feat.cuda()
+    csaved = tfc.refine_forward(cf, cew, csi, csp, csc)
+    assert float(cew[:, 0].abs().max()) == 0.0  # refine.cu:43-46 side effect
+    names = ("feature_out", "feature_aggr", "feature_aggr_up", "weight_sum", "weight_sum_up")
+    for n, a, b in zip(names, csaved, saved):
+        assert rel_err(a.cpu(), b) < TOL, n
+    cgf = tfc.refine_backward_feature(cf, cew, csi, csp, csc, *csaved, gout.cuda())
+    cgw = tfc.refine_backward_weight(cf, cew, csi, csp, csc, *csaved, gout.cuda())
+    assert rel_err(cgf.cpu(), gf) < TOL
+    assert rel_err(cgw.cpu(), gw) < TOL
+    cge = ops.edge_weight_bwd(emb.reshape(B, D, V).cuda(), csi, csp, csc, cew, gw.cuda(), inv_sigma)
+    assert rel_err(cge.cpu(), ge) < TOL
+
+
+def test_filter_properties_at_512():
+    """No oracle needed: a constant feature is a fixed point of the normalised filter, weight_sum >= 1, and the feature
+    gradient is the adjoint of the (symmetric) un-normalised filter: <aggr(f), g> == <f, aggr(g)>."""
+    from fedicra_b200 import ops
+    B, C, H, W = 2, 3, 512, 512
+    g = torch.Generator().manual_seed(9)
+    emb = ((torch.rand(B, 3, H, W, generator=g) * 255).round() / 255).cuda()
+    tree = ops.mst_grid(emb)
+    assert tree.shape == (B, H * W - 1, 2) and int(tree.min()) >= 0
+    si, sp, sc, ls, nl = ops.bfs_forward(tree)
+    assert torch.equal(torch.sort(si, 1).values, torch.arange(H * W, device="cuda", dtype=torch.int32).expand(B, -1))
+    ew = ops.edge_weight_fwd(emb.reshape(B, 3, -1), si, sp, 1.0)
+    ones = torch.full((B, C, H * W), 0.37, device="cuda")
+    out, aggr, _, wsum, _ = ops.refine_forward(ones, ew, si, sp, sc, ls, nl)
+    assert rel_err(out.cpu(), ones.cpu()) < 1e-5 and float(wsum.min()) >= 1.0
+    f = torch.rand(B, C, H * W, generator=g).cuda()
+    h = torch.rand(B, C, H * W, generator=g).cuda()
+    _, af, _, _, _ = ops.refine_forward(f, ew, si, sp, sc, ls, nl)
+    _, ah, _, _, _ = ops.refine_forward(h, ew, si, sp, sc, ls, nl)
+    lhs, rhs = (af.double() * h.double()).sum().item(), (f.double() * ah.double()).sum().item()
+    assert abs(lhs - rhs) < 1e-5 * abs(lhs)
