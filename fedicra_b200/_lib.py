@@ -28,6 +28,7 @@ class GcrfDesc(ctypes.Structure):
 SIGNATURES = {
     "fedicra_last_error": (ctypes.c_char_p, []),
     "fedicra_abi_version": (c_int, []),
+    "fedicra_launch_count": (ctypes.c_longlong, []),
     "fedicra_gcrf_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "fedicra_gcrf_fwd_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                      ctypes.POINTER(GcrfDesc), c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -16,3 +16,7 @@ int fedicra_fail(int code, const char *fmt, ...) {
 
 extern "C" const char *fedicra_last_error(void) { return g_err; }
 extern "C" int fedicra_abi_version(void) { return FEDICRA_ABI_VERSION; }
+
+static long long g_launches = 0;
+void fedicra_count_launches(int n) { __atomic_fetch_add(&g_launches, (long long)n, __ATOMIC_RELAXED); }
+extern "C" long long fedicra_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }

@@ -19,9 +19,13 @@ int fedicra_fail(int code, const char *fmt, ...);
 // Check the launch that was just issued (asynchronous errors surface at the caller's next sync, as with any kernel).
 #define FEDICRA_CHECK_LAUNCH(name)                                                             \
     do {                                                                                       \
+        fedicra_count_launches(1);                                                             \
         cudaError_t e_ = cudaGetLastError();                                                   \
         if (e_ != cudaSuccess) return fedicra_fail(-2, "%s: %s", name, cudaGetErrorString(e_)); \
     } while (0)
+
+// Telemetry: number of kernels this library has launched in the process (bench.py's `gpu_launches`).
+void fedicra_count_launches(int n);
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 

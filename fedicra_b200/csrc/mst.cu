@@ -240,6 +240,7 @@ int run_mst(const int *edge_index, const float *edge_weight, int B, int E, int V
         mst_compress_kernel<<<dim3((V + 255) / 256, B), blk, 0, st>>>(ws, V);
         mst_finish_round_kernel<<<(B + 127) / 128, 128, 0, st>>>(ws, B);
     }
+    fedicra_count_launches(4 * rounds - 1);
     FEDICRA_CHECK_LAUNCH("mst round kernels");
     mst_compact_kernel<GRID><<<B, 1024, 0, st>>>(ws, edge_index, edge_out, V, E, H, W);
     FEDICRA_CHECK_LAUNCH("mst_compact_kernel");

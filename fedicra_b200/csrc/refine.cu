@@ -358,6 +358,7 @@ extern "C" int fedicra_refine_backward_weight(const float *edge_weight, const in
     float *ew = const_cast<float *>(edge_weight);
     up_kernel<<<dim3(B, C), NT, 0, st>>>(a1, none, C, V, ew, sorted_index, sorted_child, level_start, n_levels);
     up_kernel<<<dim3(B, C), NT, 0, st>>>(a2, none, C, V, ew, sorted_index, sorted_child, level_start, n_levels);
+    fedicra_count_launches(1);
     FEDICRA_CHECK_LAUNCH("up_kernel");
     grad_kernel<<<dim3(B, 2 * C), NT, 0, st>>>(feature_aggr_up, feature_aggr, weight_sum_up, weight_sum, u1, u2, ga, gb,
                                                C, V, edge_weight, sorted_index, sorted_parent, level_start, n_levels);

@@ -19,11 +19,8 @@ def shard_range(n_items, rank, world):
 def sharded_masked_l1(local_sum, local_n, group=None):
     """(sum over ranks of local_sum) / (sum over ranks of local_n), differentiable w.r.t. local_sum."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
-        return local_sum / local_n if float(local_n) > 0 else local_sum
+        return local_sum / torch.clamp(local_n, min=1.0)
     pair = torch.stack([local_sum.detach().float(), local_n.detach().float()])
     dist.all_reduce(pair, op=dist.ReduceOp.SUM, group=group)
-    total_n = pair[1]
-    if float(total_n) <= 0:
-        return local_sum
-    # value = global sum / global N; gradient flows through this rank's share only
-    return (local_sum + (pair[0] - local_sum.detach())) / total_n
+    # value = global sum / max(global N, 1); the gradient flows through this rank's share only (no host sync)
+    return (local_sum + (pair[0] - local_sum.detach())) / torch.clamp(pair[1], min=1.0)

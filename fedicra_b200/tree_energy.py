@@ -31,16 +31,25 @@ def _resize(feats, h, w):
     return F.interpolate(feats, size=(h, w), mode='bilinear', align_corners=False)
 
 
-def _masked_l1(roi, prob, filtered, n):
-    loss = (roi * torch.abs(prob - filtered)).sum()
-    if n > 0:  # host sync, as in the reference (flower_common.py:815)
-        loss = loss / n
-    return loss
+def _normalise(loss_sum, n, distributed):
+    """`if N > 0: loss /= N` (flower_common.py:815-816) without the reference's device->host sync: N is a count, so
+    dividing by max(N, 1) is the same value in both branches (the sum is 0 when N is 0).  With `distributed` the two
+    scalars are summed over the ranks first (image sharding, fedicra_b200/sharding.py)."""
+    if distributed:
+        from .sharding import sharded_masked_l1
+        return sharded_masked_l1(loss_sum, n)
+    return loss_sum / torch.clamp(n, min=1.0)
+
+
+def _masked_l1(roi, prob, filtered, n, distributed=False):
+    return _normalise((roi * torch.abs(prob - filtered)).sum(), n, distributed)
 
 
 class _TreeLossBase(nn.Module):
-    def __init__(self):
+    def __init__(self, distributed=False):
+        """distributed=True: the batch is one shard of a global batch split by image over torch.distributed ranks."""
         super().__init__()
+        self.distributed = distributed
         self.mst_layers = MinimumSpanningTree(TreeFilter2D.norm2_distance)
         self.tree_filter_layers = TreeFilter2D(groups=1, sigma=0.02)
 
@@ -62,7 +71,7 @@ class TreeEnergyLoss(_TreeLossBase):
         AS = self._low(prob, low_feats)
         if high_feats is not None:
             AS = self._high(AS, high_feats, h, w)
-        return weight * _masked_l1(roi, prob, AS, n), AS
+        return weight * _masked_l1(roi, prob, AS, n, self.distributed), AS
 
 
 class MScaleAddTreeEnergyLoss(_TreeLossBase):
@@ -72,9 +81,7 @@ class MScaleAddTreeEnergyLoss(_TreeLossBase):
         prob = torch.softmax(preds, dim=1)
         AS = self._low(prob, low_feats)
         outs = [self._high(AS, hf, h, w) for hf in (high_feats_1, high_feats_2, high_feats_3)]
-        loss = sum((roi * torch.abs(prob - o)).sum() for o in outs)
-        if n > 0:
-            loss = loss / n
+        loss = _normalise(sum((roi * torch.abs(prob - o)).sum() for o in outs), n, self.distributed)
         return (weight * loss, *outs)
 
 
@@ -88,4 +95,4 @@ class MScaleRecurveTreeEnergyLoss(_TreeLossBase):
         for hf in (high_feats_1, high_feats_2, high_feats_3):
             cur = self._high(cur, hf, h, w)
             outs.append(cur)
-        return (weight * _masked_l1(roi, prob, cur, n), *outs)
+        return (weight * _masked_l1(roi, prob, cur, n, self.distributed), *outs)

@@ -32,6 +32,8 @@ extern "C" {
 const char *fedicra_last_error(void);
 /* ABI version of this header (bumped on any signature change). */
 int fedicra_abi_version(void);
+/* Telemetry: kernels launched by this library in this process so far (no counterpart in the reference). */
+long long fedicra_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------------ Gated CRF ---- */
 /* One kernel descriptor of the Gaussian mixture: K += weight * exp(-0.5*(|dxy|^2/sigma_xy^2 + |dI|^2/sigma_rgb^2)).

@@ -34,11 +34,12 @@ def grid_weights(embed):
 
 
 def minimum_spanning_tree(embed):
-    """[B,D,H,W] -> [B,V-1,2] int32 tree edges."""
+    """[B,D,H,W] -> [B,V-1,2] int32 tree edges.  Always on the fp32 embedding: tree parity is defined on fp32 weight bits,
+    also when the rest of the stack runs in fp64 as the high-precision judge."""
     B, _, H, W = embed.shape
     with torch.no_grad():
         idx = grid_edges(H, W).unsqueeze(0).expand(B, -1, -1).contiguous()
-        return tree_cpu.mst_forward(idx, grid_weights(embed.detach()).contiguous(), H * W)
+        return tree_cpu.mst_forward(idx, grid_weights(embed.detach().float()).contiguous(), H * W)
 
 
 class _Refine(torch.autograd.Function):
@@ -74,19 +75,22 @@ def tree_filter(feature, embed, tree, low_tree=True, sigma=0.02):
     return out.reshape(B, C, H, W)
 
 
-def mscale_recurve_tree_energy_loss(preds, low_feats, high_1, high_2, high_3, unlabeled_rois, weight, sigma=0.02):
-    """flower_common.py:768-818.  Returns (weight * loss, AS_1, AS_2, AS_3)."""
+def mscale_recurve_tree_energy_loss(preds, low_feats, high_1, high_2, high_3, unlabeled_rois, weight, sigma=0.02,
+                                    dtype=torch.float32):
+    """flower_common.py:768-818.  Returns (weight * loss, AS_1, AS_2, AS_3).
+
+    dtype=torch.float64 evaluates everything after the (fp32) resize and the (fp32-weight) MST in double precision."""
     h, w = preds.shape[2:]
     with torch.no_grad():
         low = F.interpolate(low_feats, size=(h, w), mode="bilinear", align_corners=False)
-        roi = F.interpolate(unlabeled_rois.unsqueeze(1).float(), size=(h, w), mode="nearest")
+        roi = F.interpolate(unlabeled_rois.unsqueeze(1).float(), size=(h, w), mode="nearest").to(dtype)
         n = roi.sum()
-    prob = torch.softmax(preds, 1)
-    cur = tree_filter(prob, low, minimum_spanning_tree(low), True, sigma)
+    prob = torch.softmax(preds.to(dtype), 1)
+    cur = tree_filter(prob, low.to(dtype), minimum_spanning_tree(low), True, sigma)
     outs = []
     for hf in (high_1, high_2, high_3):
         hf = F.interpolate(hf, size=(h, w), mode="bilinear", align_corners=False)
-        cur = tree_filter(cur, hf, minimum_spanning_tree(hf), False, sigma)
+        cur = tree_filter(cur, hf.to(dtype), minimum_spanning_tree(hf), False, sigma)
         outs.append(cur)
     loss = (roi * torch.abs(prob - cur)).sum()
     if n > 0:
@@ -99,7 +103,7 @@ RADIUS = 5  # OURS.py:69
 
 
 def loss_stack(logits, image, aux1, aux2, aux3, label, num_classes, tree_weight=0.1, crf_weight=0.1,
-               with_ce=False, gcrf="unfold"):
+               with_ce=False, gcrf="unfold", dtype=torch.float32):
     """One step's weak-supervision loss (OURS.py:132-151): w_tree*TEL + 0.1*GatedCRF (+ pCE when asked).
 
     image: [B,Cin,H,W]; the tree embedding is the image repeated to 3 channels when Cin == 1 (OURS.py:137-141), the
@@ -107,12 +111,12 @@ def loss_stack(logits, image, aux1, aux2, aux3, label, num_classes, tree_weight=
     """
     rois = label == num_classes
     three = image.repeat(1, 3, 1, 1) if image.shape[1] == 1 else image
-    tel, _, _, as3 = mscale_recurve_tree_energy_loss(logits, three, aux1, aux2, aux3, rois, tree_weight)
-    soft = torch.softmax(logits, 1)
+    tel, _, _, as3 = mscale_recurve_tree_energy_loss(logits, three, aux1, aux2, aux3, rois, tree_weight, dtype=dtype)
+    soft = torch.softmax(logits.to(dtype), 1)
     if gcrf == "unfold":
         crf = gcrf_cpu.gated_crf_loss_unfold(soft, KERNELS_DESC, RADIUS, image)
     else:
-        crf = gcrf_cpu.gated_crf_loss(soft, KERNELS_DESC, RADIUS, image)
+        crf = gcrf_cpu.gated_crf_loss(soft, KERNELS_DESC, RADIUS, image, dtype=dtype)
     total = tel + crf_weight * crf
     if with_ce:
         total = total + F.cross_entropy(logits, label.long(), ignore_index=num_classes)

@@ -15,6 +15,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
+_LIB64 = None
 _REF = None
 _MST_IMPL = "port"
 
@@ -43,6 +44,22 @@ def lib():
         _LIB.oracle_bfs_forward.restype = _I
         _LIB.oracle_num_threads.restype = _I
     return _LIB
+
+
+def lib64():
+    """The same restatement compiled with REAL = double (liboracle_tree64.so): the high-precision judge."""
+    global _LIB64
+    if _LIB64 is None:
+        path = os.path.join(_HERE, "liboracle_tree64.so")
+        if not os.path.exists(path):
+            build(ref=False)
+        _LIB64 = ctypes.CDLL(path)
+    return _LIB64
+
+
+def _for(t):
+    """(library, scalar ctype) matching the floating dtype of tensor `t`."""
+    return (lib64(), ctypes.c_double) if t.dtype == torch.float64 else (lib(), _F)
 
 
 def ref_lib():
@@ -78,8 +95,14 @@ def _i32(t):
     return t.contiguous()
 
 
-def _f32(t):
-    assert t.dtype == torch.float32 and t.device.type == "cpu"
+def _f32(t, like=None):
+    want = torch.float32 if like is None else like.dtype
+    assert t.dtype == want and t.device.type == "cpu", (t.dtype, want)
+    return t.contiguous()
+
+
+def _fl(t):
+    assert t.dtype in (torch.float32, torch.float64) and t.device.type == "cpu"
     return t.contiguous()
 
 
@@ -134,13 +157,13 @@ def bfs_levels(tree_one, max_adj=4):
 
 def refine_forward(feature_in, edge_weight, sorted_index, sorted_parent, sorted_child):
     """refine.hpp:4-11.  Like the reference, writes 0 into edge_weight[:,0] through the raw pointer."""
-    f = _f32(feature_in)
-    assert edge_weight.is_contiguous()
+    f = _fl(feature_in)
+    assert edge_weight.is_contiguous() and edge_weight.dtype == f.dtype
     B, C, V = f.shape
     A = sorted_child.shape[2]
     out, aggr, aggr_up = torch.empty_like(f), torch.empty_like(f), torch.empty_like(f)
-    ws, ws_up = torch.empty(B, V), torch.empty(B, V)
-    lib().oracle_refine_forward(_I(B), _I(C), _I(V), _I(A), _p(f), _p(edge_weight), _p(_i32(sorted_index)),
+    ws, ws_up = torch.empty(B, V, dtype=f.dtype), torch.empty(B, V, dtype=f.dtype)
+    _for(f)[0].oracle_refine_forward(_I(B), _I(C), _I(V), _I(A), _p(f), _p(edge_weight), _p(_i32(sorted_index)),
                                 _p(_i32(sorted_parent)), _p(_i32(sorted_child)), _p(out), _p(aggr), _p(aggr_up),
                                 _p(ws), _p(ws_up))
     return out, aggr, aggr_up, ws, ws_up
@@ -151,10 +174,11 @@ def refine_backward_feature(feature_in, edge_weight, sorted_index, sorted_parent
     """refine.hpp:13-25."""
     B, C, V = feature_in.shape
     A = sorted_child.shape[2]
-    g = torch.empty(B, C, V)
-    lib().oracle_refine_backward_feature(_I(B), _I(C), _I(V), _I(A), _p(_f32(edge_weight)), _p(_i32(sorted_index)),
-                                         _p(_i32(sorted_parent)), _p(_i32(sorted_child)), _p(_f32(weight_sum)),
-                                         _p(_f32(grad_out)), _p(g))
+    go = _fl(grad_out)
+    g = torch.empty(B, C, V, dtype=go.dtype)
+    _for(go)[0].oracle_refine_backward_feature(_I(B), _I(C), _I(V), _I(A), _p(_f32(edge_weight, go)),
+                                               _p(_i32(sorted_index)), _p(_i32(sorted_parent)), _p(_i32(sorted_child)),
+                                               _p(_f32(weight_sum, go)), _p(go), _p(g))
     return g
 
 
@@ -163,11 +187,13 @@ def refine_backward_weight(feature_in, edge_weight, sorted_index, sorted_parent,
     """refine.hpp:27-39."""
     B, C, V = feature_in.shape
     A = sorted_child.shape[2]
-    g = torch.empty(B, V)
-    lib().oracle_refine_backward_weight(_I(B), _I(C), _I(V), _I(A), _p(_f32(edge_weight)), _p(_i32(sorted_index)),
-                                        _p(_i32(sorted_parent)), _p(_i32(sorted_child)), _p(_f32(feature_out)),
-                                        _p(_f32(feature_aggr)), _p(_f32(feature_aggr_up)), _p(_f32(weight_sum)),
-                                        _p(_f32(weight_sum_up)), _p(_f32(grad_out)), _p(g))
+    go = _fl(grad_out)
+    g = torch.empty(B, V, dtype=go.dtype)
+    _for(go)[0].oracle_refine_backward_weight(_I(B), _I(C), _I(V), _I(A), _p(_f32(edge_weight, go)),
+                                              _p(_i32(sorted_index)), _p(_i32(sorted_parent)), _p(_i32(sorted_child)),
+                                              _p(_f32(feature_out, go)), _p(_f32(feature_aggr, go)),
+                                              _p(_f32(feature_aggr_up, go)), _p(_f32(weight_sum, go)),
+                                              _p(_f32(weight_sum_up, go)), _p(go), _p(g))
     return g
 
 
@@ -175,18 +201,19 @@ def refine_backward_weight(feature_in, edge_weight, sorted_index, sorted_parent,
 
 
 def edge_weight(embed, sorted_index, sorted_parent, inv_sigma):
-    e = _f32(embed)
+    e = _fl(embed)
     B, D, V = e.shape
-    ew = torch.empty(B, V)
-    lib().oracle_edge_weight(_I(B), _I(D), _I(V), _p(e), _p(_i32(sorted_index)), _p(_i32(sorted_parent)),
-                             _F(inv_sigma), _p(ew))
+    ew = torch.empty(B, V, dtype=e.dtype)
+    L, S = _for(e)
+    L.oracle_edge_weight(_I(B), _I(D), _I(V), _p(e), _p(_i32(sorted_index)), _p(_i32(sorted_parent)), S(inv_sigma), _p(ew))
     return ew
 
 
 def edge_weight_bwd(embed, sorted_index, sorted_parent, inv_sigma, ew, grad_ew):
-    e = _f32(embed)
+    e = _fl(embed)
     B, D, V = e.shape
-    g = torch.empty(B, D, V)
-    lib().oracle_edge_weight_bwd(_I(B), _I(D), _I(V), _p(e), _p(_i32(sorted_index)), _p(_i32(sorted_parent)),
-                                 _F(inv_sigma), _p(_f32(ew)), _p(_f32(grad_ew)), _p(g))
+    g = torch.empty(B, D, V, dtype=e.dtype)
+    L, S = _for(e)
+    L.oracle_edge_weight_bwd(_I(B), _I(D), _I(V), _p(e), _p(_i32(sorted_index)), _p(_i32(sorted_parent)), S(inv_sigma),
+                             _p(_f32(ew, e)), _p(_f32(grad_ew, e)), _p(g))
     return g

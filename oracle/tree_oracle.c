@@ -29,6 +29,16 @@
 
 #include <pthread.h>
 
+/* REAL = float (liboracle_tree.so, the fp32 restatement) or double (liboracle_tree64.so, the high-precision judge used
+ * where fp32 round-off of BOTH sides would otherwise dominate the comparison, SURVEY.md §8c last row). */
+#ifdef ORACLE_DOUBLE
+typedef double real;
+#define REAL_EXP exp
+#else
+typedef float real;
+#define REAL_EXP expf
+#endif
+
 /* ------------------------------------------------------------------ tiny pthread parallel-for */
 
 static int g_threads = 0; /* 0 => use the online core count */
@@ -254,13 +264,13 @@ int oracle_bfs_forward(int B, int V, const int *tree, int max_adj, int *sorted_i
 
 typedef struct {
     int B, C, D, V, max_adj;
-    float inv_sigma;
-    const float *embed, *ew_c, *grad_ew;
-    float *ew, *grad_embed;
+    real inv_sigma;
+    const real *embed, *ew_c, *grad_ew;
+    real *ew, *grad_embed;
     const int *si, *sp, *sc;
-    const float *feature_in, *grad_out, *feature_out_c, *feature_aggr_c, *feature_aggr_up_c, *weight_sum_c,
+    const real *feature_in, *grad_out, *feature_out_c, *feature_aggr_c, *feature_aggr_up_c, *weight_sum_c,
         *weight_sum_up_c;
-    float *feature_out, *feature_aggr, *feature_aggr_up, *weight_sum, *weight_sum_up, *grad_feature, *grad_weight;
+    real *feature_out, *feature_aggr, *feature_aggr_up, *weight_sum, *weight_sum_up, *grad_feature, *grad_weight;
 } job_t;
 
 /* ---- edge weights (tree_filter.py:84-108) */
@@ -268,22 +278,22 @@ typedef struct {
 static void ew_one(int b, void *p) {
     job_t *j = (job_t *)p;
     int V = j->V, D = j->D;
-    const float *e = j->embed + (size_t)b * D * V;
+    const real *e = j->embed + (size_t)b * D * V;
     const int *si = j->si + (size_t)b * V, *sp = j->sp + (size_t)b * V;
     for (int i = 0; i < V; ++i) {
         int v = si[i], u = si[sp[i]];
-        float d = 0.f;
+        real d = (real)0;
         for (int c = 0; c < D; ++c) {
-            float t = e[(size_t)c * V + v] - e[(size_t)c * V + u];
+            real t = e[(size_t)c * V + v] - e[(size_t)c * V + u];
             d += t * t;
         }
-        j->ew[(size_t)b * V + i] = expf(-d * j->inv_sigma);
+        j->ew[(size_t)b * V + i] = REAL_EXP(-d * j->inv_sigma);
     }
 }
 
 /* embed [B,D,V] vertex order -> ew [B,V] BFS order: exp(-|e[v(i)] - e[v(par i)]|^2 * inv_sigma). */
-void oracle_edge_weight(int B, int D, int V, const float *embed, const int *sorted_index, const int *sorted_parent,
-                        float inv_sigma, float *ew) {
+void oracle_edge_weight(int B, int D, int V, const real *embed, const int *sorted_index, const int *sorted_parent,
+                        real inv_sigma, real *ew) {
     job_t j;
     memset(&j, 0, sizeof(j));
     j.D = D; j.V = V; j.embed = embed; j.si = sorted_index; j.sp = sorted_parent; j.inv_sigma = inv_sigma; j.ew = ew;
@@ -293,15 +303,15 @@ void oracle_edge_weight(int B, int D, int V, const float *embed, const int *sort
 static void ewb_one(int b, void *p) {
     job_t *j = (job_t *)p;
     int V = j->V, D = j->D;
-    const float *e = j->embed + (size_t)b * D * V;
-    float *g = j->grad_embed + (size_t)b * D * V;
+    const real *e = j->embed + (size_t)b * D * V;
+    real *g = j->grad_embed + (size_t)b * D * V;
     const int *si = j->si + (size_t)b * V, *sp = j->sp + (size_t)b * V;
-    memset(g, 0, sizeof(float) * (size_t)D * V);
+    memset(g, 0, sizeof(real) * (size_t)D * V);
     for (int i = 1; i < V; ++i) {
         int v = si[i], u = si[sp[i]];
-        float k = -2.f * j->inv_sigma * j->ew_c[(size_t)b * V + i] * j->grad_ew[(size_t)b * V + i];
+        real k = (real)-2 * j->inv_sigma * j->ew_c[(size_t)b * V + i] * j->grad_ew[(size_t)b * V + i];
         for (int c = 0; c < D; ++c) {
-            float t = k * (e[(size_t)c * V + v] - e[(size_t)c * V + u]);
+            real t = k * (e[(size_t)c * V + v] - e[(size_t)c * V + u]);
             g[(size_t)c * V + v] += t;
             g[(size_t)c * V + u] -= t;
         }
@@ -309,9 +319,9 @@ static void ewb_one(int b, void *p) {
 }
 
 /* grad_ew [B,V] (BFS order) -> grad_embed [B,D,V] (vertex order), the autograd of the expression above. */
-void oracle_edge_weight_bwd(int B, int D, int V, const float *embed, const int *sorted_index,
-                            const int *sorted_parent, float inv_sigma, const float *ew, const float *grad_ew,
-                            float *grad_embed) {
+void oracle_edge_weight_bwd(int B, int D, int V, const real *embed, const int *sorted_index,
+                            const int *sorted_parent, real inv_sigma, const real *ew, const real *grad_ew,
+                            real *grad_embed) {
     job_t j;
     memset(&j, 0, sizeof(j));
     j.D = D; j.V = V; j.embed = embed; j.si = sorted_index; j.sp = sorted_parent; j.inv_sigma = inv_sigma;
@@ -322,9 +332,9 @@ void oracle_edge_weight_bwd(int B, int D, int V, const float *embed, const int *
 /* ------------------------------------------------------------------ refine sweeps */
 
 /* refine.cu:70-134.  in: vertex order (or NULL => 1), out: BFS order. */
-static void sweep_up(const float *in, float *out, const float *w, const int *si, const int *sc, int V, int max_adj) {
+static void sweep_up(const real *in, real *out, const real *w, const int *si, const int *sc, int V, int max_adj) {
     for (int i = V - 1; i >= 0; --i) {
-        float acc = in ? in[si[i]] : 1.f;
+        real acc = in ? in[si[i]] : (real)1;
         for (int j = 0; j < max_adj; ++j) {
             int c = sc[i * max_adj + j];
             if (c <= 0) break;
@@ -335,32 +345,32 @@ static void sweep_up(const float *in, float *out, const float *w, const int *si,
 }
 
 /* refine.cu:19-68 with w_0 treated as 0.  in: BFS order, out: vertex order. */
-static void sweep_down(const float *in, float *out, const float *w, const int *si, const int *sp, int V) {
+static void sweep_down(const real *in, real *out, const real *w, const int *si, const int *sp, int V) {
     out[si[0]] = in[0];
     for (int i = 1; i < V; ++i) {
-        float wi = w[i];
-        out[si[i]] = in[i] * (1.f - wi * wi) + out[si[sp[i]]] * wi;
+        real wi = w[i];
+        out[si[i]] = in[i] * ((real)1 - wi * wi) + out[si[sp[i]]] * wi;
     }
 }
 
 /* refine.cu:136-199.  in_data BFS, out_data vertex (data_c channels, channel k%data_c), in_grad BFS converted in
  * place to its root-to-leaf form (grad_c channels), grad [max(data_c,grad_c), V] BFS order. */
-static void sweep_grad(const float *in_data, const float *out_data, float *in_grad, const float *w, float *grad,
+static void sweep_grad(const real *in_data, const real *out_data, real *in_grad, const real *w, real *grad,
                        const int *si, const int *sp, int data_c, int grad_c, int V) {
     int nc = data_c > grad_c ? data_c : grad_c;
     for (int k = 0; k < nc; ++k) {
-        const float *idat = in_data + (size_t)(k % data_c) * V;
-        const float *odat = out_data + (size_t)(k % data_c) * V;
-        float *g = in_grad + (size_t)(k % grad_c) * V;
-        float *o = grad + (size_t)k * V;
-        o[0] = 0.f;
+        const real *idat = in_data + (size_t)(k % data_c) * V;
+        const real *odat = out_data + (size_t)(k % data_c) * V;
+        real *g = in_grad + (size_t)(k % grad_c) * V;
+        real *o = grad + (size_t)k * V;
+        o[0] = (real)0;
         for (int i = 1; i < V; ++i) {
             int p = sp[i];
-            float wi = w[i];
-            float left = g[i] * (odat[si[p]] - wi * idat[i]);
-            float right = idat[i] * (g[p] - wi * g[i]);
+            real wi = w[i];
+            real left = g[i] * (odat[si[p]] - wi * idat[i]);
+            real right = idat[i] * (g[p] - wi * g[i]);
             o[i] = left + right;
-            g[i] = g[i] * (1.f - wi * wi) + g[p] * wi;
+            g[i] = g[i] * ((real)1 - wi * wi) + g[p] * wi;
         }
     }
 }
@@ -370,7 +380,7 @@ static void sweep_grad(const float *in_data, const float *out_data, float *in_gr
 static void fwd_one(int idx, void *p) { /* idx = b*(C+1) + c; channel C is the all-ones "weight" channel */
     job_t *j = (job_t *)p;
     int C = j->C, V = j->V, b = idx / (C + 1), c = idx % (C + 1);
-    const float *w = j->ew_c + (size_t)b * V;
+    const real *w = j->ew_c + (size_t)b * V;
     const int *si = j->si + (size_t)b * V, *sp = j->sp + (size_t)b * V;
     const int *sc = j->sc + (size_t)b * V * j->max_adj;
     if (c < C) {
@@ -390,11 +400,11 @@ static void fwd_div(int idx, void *p) {
     for (int v = 0; v < V; ++v) j->feature_out[off + v] = j->feature_aggr[off + v] / j->weight_sum[(size_t)b * V + v];
 }
 
-void oracle_refine_forward(int B, int C, int V, int max_adj, const float *feature_in, float *edge_weight,
+void oracle_refine_forward(int B, int C, int V, int max_adj, const real *feature_in, real *edge_weight,
                            const int *sorted_index, const int *sorted_parent, const int *sorted_child,
-                           float *feature_out, float *feature_aggr, float *feature_aggr_up, float *weight_sum,
-                           float *weight_sum_up) {
-    for (int b = 0; b < B; ++b) edge_weight[(size_t)b * V] = 0.f;
+                           real *feature_out, real *feature_aggr, real *feature_aggr_up, real *weight_sum,
+                           real *weight_sum_up) {
+    for (int b = 0; b < B; ++b) edge_weight[(size_t)b * V] = (real)0;
     job_t j;
     memset(&j, 0, sizeof(j));
     j.B = B; j.C = C; j.V = V; j.max_adj = max_adj; j.feature_in = feature_in; j.ew_c = edge_weight;
@@ -411,8 +421,8 @@ static void bwdf_one(int idx, void *p) {
     job_t *j = (job_t *)p;
     int C = j->C, V = j->V, b = idx / C;
     size_t off = (size_t)idx * V;
-    float *gn = (float *)malloc(sizeof(float) * (size_t)V * 2);
-    float *up = gn + V;
+    real *gn = (real *)malloc(sizeof(real) * (size_t)V * 2);
+    real *up = gn + V;
     for (int v = 0; v < V; ++v) gn[v] = j->grad_out[off + v] / j->weight_sum_c[(size_t)b * V + v];
     sweep_up(gn, up, j->ew_c + (size_t)b * V, j->si + (size_t)b * V, j->sc + (size_t)b * V * j->max_adj, V,
              j->max_adj);
@@ -420,9 +430,9 @@ static void bwdf_one(int idx, void *p) {
     free(gn);
 }
 
-void oracle_refine_backward_feature(int B, int C, int V, int max_adj, const float *edge_weight,
+void oracle_refine_backward_feature(int B, int C, int V, int max_adj, const real *edge_weight,
                                     const int *sorted_index, const int *sorted_parent, const int *sorted_child,
-                                    const float *weight_sum, const float *grad_out, float *grad_feature) {
+                                    const real *weight_sum, const real *grad_out, real *grad_feature) {
     job_t j;
     memset(&j, 0, sizeof(j));
     j.B = B; j.C = C; j.V = V; j.max_adj = max_adj; j.ew_c = edge_weight; j.si = sorted_index; j.sp = sorted_parent;
@@ -435,12 +445,12 @@ void oracle_refine_backward_feature(int B, int C, int V, int max_adj, const floa
 static void bwdw_one(int b, void *p) {
     job_t *j = (job_t *)p;
     int C = j->C, V = j->V, max_adj = j->max_adj;
-    const float *w = j->ew_c + (size_t)b * V;
+    const real *w = j->ew_c + (size_t)b * V;
     const int *si = j->si + (size_t)b * V, *sp = j->sp + (size_t)b * V;
     const int *sc = j->sc + (size_t)b * V * max_adj;
     size_t cv = (size_t)C * V;
-    float *buf = (float *)malloc(sizeof(float) * cv * 6);
-    float *gn = buf, *fg = buf + cv, *u1 = buf + 2 * cv, *u2 = buf + 3 * cv, *ga = buf + 4 * cv, *gb = buf + 5 * cv;
+    real *buf = (real *)malloc(sizeof(real) * cv * 6);
+    real *gn = buf, *fg = buf + cv, *u1 = buf + 2 * cv, *u2 = buf + 3 * cv, *ga = buf + 4 * cv, *gb = buf + 5 * cv;
     for (int c = 0; c < C; ++c)
         for (int v = 0; v < V; ++v) {
             size_t o = ((size_t)b * C + c) * V + v;
@@ -454,18 +464,18 @@ static void bwdw_one(int b, void *p) {
     sweep_grad(j->feature_aggr_up_c + (size_t)b * cv, j->feature_aggr_c + (size_t)b * cv, u1, w, ga, si, sp, C, C, V);
     sweep_grad(j->weight_sum_up_c + (size_t)b * V, j->weight_sum_c + (size_t)b * V, u2, w, gb, si, sp, 1, C, V);
     for (int i = 0; i < V; ++i) {
-        float acc = 0.f;
+        real acc = (real)0;
         for (int c = 0; c < C; ++c) acc += ga[(size_t)c * V + i] - gb[(size_t)c * V + i];
         j->grad_weight[(size_t)b * V + i] = acc;
     }
     free(buf);
 }
 
-void oracle_refine_backward_weight(int B, int C, int V, int max_adj, const float *edge_weight,
+void oracle_refine_backward_weight(int B, int C, int V, int max_adj, const real *edge_weight,
                                    const int *sorted_index, const int *sorted_parent, const int *sorted_child,
-                                   const float *feature_out, const float *feature_aggr,
-                                   const float *feature_aggr_up, const float *weight_sum,
-                                   const float *weight_sum_up, const float *grad_out, float *grad_weight) {
+                                   const real *feature_out, const real *feature_aggr,
+                                   const real *feature_aggr_up, const real *weight_sum,
+                                   const real *weight_sum_up, const real *grad_out, real *grad_weight) {
     job_t j;
     memset(&j, 0, sizeof(j));
     j.B = B; j.C = C; j.V = V; j.max_adj = max_adj; j.ew_c = edge_weight; j.si = sorted_index; j.sp = sorted_parent;

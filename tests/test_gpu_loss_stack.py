@@ -4,6 +4,7 @@ import os
 import numpy as np
 import pytest
 import torch
+import torch.nn.functional as F
 
 from oracle import losses_cpu
 from tests.helpers import loss_inputs, rel_err
@@ -12,12 +13,24 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-4
 
 
+def upsampled_on_cpu(aux, h, w):
+    """Bilinear resize of a decoder head ON THE CPU (differentiable), then moved to the GPU.
+
+    torch's CPU and CUDA bilinear kernels differ in the last bit on about half the pixels; after the `+1` of the MST
+    weights (tree_filter.py:33) that flips ties and yields a different, equally valid tree.  MST parity is defined on
+    identical fp32 weight bits, so the parity tests hand both sides the same resized embedding; inside
+    the product the resize then is an identity."""
+    return F.interpolate(aux, size=(h, w), mode="bilinear", align_corners=False).cuda()
+
+
 def run_gpu(logits, image3, a1, a2, a3, roi, weight=0.1):
     from fedicra_b200 import MScaleRecurveTreeEnergyLoss
-    xs = [t.cuda().requires_grad_() for t in (logits, a1, a2, a3)]
-    out = MScaleRecurveTreeEnergyLoss()(xs[0], image3.cuda(), xs[1], xs[2], xs[3], roi.cuda(), weight)
+    h, w = logits.shape[2:]
+    leaves = [t.clone().requires_grad_() for t in (logits, a1, a2, a3)]
+    out = MScaleRecurveTreeEnergyLoss()(leaves[0].cuda(), image3.cuda(), *(upsampled_on_cpu(a, h, w) for a in leaves[1:]),
+                                        roi.cuda(), weight)
     out[0].backward()
-    return out[0].detach().cpu(), [o.detach().cpu() for o in out[1:]], [x.grad.cpu() for x in xs]
+    return out[0].detach().cpu(), [o.detach().cpu() for o in out[1:]], [x.grad for x in leaves]
 
 
 @pytest.mark.parametrize("name", ["tel_faz.npz", "tel_odoc.npz"])
@@ -32,30 +45,66 @@ def test_tree_energy_golden(golden_dir, name):
         assert rel_err(gr, t[k]) < TOL, k
 
 
-@pytest.mark.parametrize("B,C,Cin,H,W,kind", [(2, 2, 1, 64, 64, "quant8"), (1, 3, 3, 48, 80, "uniform"),
-                                              (12, 2, 1, 256, 256, "quant8")])
-def test_full_loss_stack_vs_oracle(B, C, Cin, H, W, kind):
-    """TEL + 0.1 * GatedCRF as in OURS.py:142-151, gradients w.r.t. logits and the three aux heads."""
-    from fedicra_b200 import ModelLossSemsegGatedCRF, MScaleRecurveTreeEnergyLoss
-    image, logits, a1, a2, a3, label = loss_inputs(B, C, Cin, H, W, kind)
-    xs_ref = [t.clone().requires_grad_() for t in (logits, a1, a2, a3)]
-    total_ref, tel_ref, crf_ref, as3_ref = losses_cpu.loss_stack(xs_ref[0], image, xs_ref[1], xs_ref[2], xs_ref[3],
-                                                                  label, C, gcrf="shift")
-    total_ref.backward()
+def well_conditioned_case(B, C, Cin, H, W, kind):
+    """Inputs + fp64 oracle results for which the loss is differentiable in a neighbourhood.
 
-    xs = [t.cuda().requires_grad_() for t in (logits, a1, a2, a3)]
+    The tree-energy loss is sum |prob - AS_3| (flower_common.py:813): where prob and AS_3 agree to rounding, sign() is
+    decided by the last bit and ANY two fp32 evaluations (the reference on two machines included) disagree by O(1) on
+    the gradient.  With ~10^6 pixels such a pixel turns up by chance in some batches, so the case generator walks the
+    seeds until the fp64 margin min|prob - AS_3| over the ROI is comfortably above fp32 resolution."""
+    for seed in range(2022, 2030):
+        image, logits, a1, a2, a3, label = loss_inputs(B, C, Cin, H, W, kind, seed=seed)
+        xs = [t.clone().requires_grad_() for t in (logits, a1, a2, a3)]
+        total, tel, crf, as3 = losses_cpu.loss_stack(xs[0], image, xs[1], xs[2], xs[3], label, C, gcrf="shift",
+                                                     dtype=torch.float64)
+        margin = (torch.softmax(logits.double(), 1) - as3.detach()).abs()[(label == C).unsqueeze(1).expand(-1, C, -1, -1)]
+        if margin.min() > 2e-6:
+            total.backward()
+            return (image, logits, a1, a2, a3, label), (tel.detach(), crf.detach(), as3.detach(), [x.grad for x in xs])
+    raise AssertionError("no well-conditioned seed found")
+
+
+@pytest.mark.parametrize("B,C,Cin,H,W,kind", [(2, 2, 1, 64, 64, "quant8"), (1, 3, 3, 48, 80, "uniform"),
+                                              (12, 2, 1, 256, 256, "quant8"), (3, 3, 3, 256, 256, "quant8")])
+def test_full_loss_stack_vs_oracle(B, C, Cin, H, W, kind):
+    """TEL + 0.1 * GatedCRF as in OURS.py:142-151 against the oracle evaluated in fp64 (the judge between two fp32
+    evaluations): loss terms, AS_3 and the gradients w.r.t. logits and the three aux heads."""
+    from fedicra_b200 import ModelLossSemsegGatedCRF, MScaleRecurveTreeEnergyLoss
+    (image, logits, a1, a2, a3, label), (tel_ref, crf_ref, as3_ref, g_ref) = well_conditioned_case(B, C, Cin, H, W, kind)
+    xs = [t.clone().requires_grad_() for t in (logits, a1, a2, a3)]
     img = image.cuda()
     three = img.repeat(1, 3, 1, 1) if Cin == 1 else img
     roi = (label == C).cuda()
-    tel, _, _, as3 = MScaleRecurveTreeEnergyLoss()(xs[0], three, xs[1], xs[2], xs[3], roi, 0.1)
-    crf = ModelLossSemsegGatedCRF()(torch.softmax(xs[0], 1), losses_cpu.KERNELS_DESC, 5, img, H, W)["loss"]
+    lg = xs[0].cuda()
+    tel, _, _, as3 = MScaleRecurveTreeEnergyLoss()(lg, three, *(upsampled_on_cpu(a, H, W) for a in xs[1:]), roi, 0.1)
+    crf = ModelLossSemsegGatedCRF()(torch.softmax(lg, 1), losses_cpu.KERNELS_DESC, 5, img, H, W)["loss"]
     total = tel + 0.1 * crf
     total.backward()
-    assert rel_err(tel.detach().cpu(), tel_ref.detach()) < TOL
-    assert rel_err(crf.detach().cpu(), crf_ref.detach()) < TOL
+    assert rel_err(tel.detach().cpu(), tel_ref) < TOL
+    assert rel_err(crf.detach().cpu(), crf_ref) < TOL
+    assert rel_err(as3.detach().cpu(), as3_ref) < TOL
+    for name, a, b in zip(("logits", "aux1", "aux2", "aux3"), xs, g_ref):
+        assert rel_err(a.grad, b) < TOL, name
+
+
+def test_filter_chain_gradients_of_a_smooth_functional():
+    """Gradients of <AS_3, R> (R fixed random): the whole refine backward chain without the |.| kink, full size."""
+    from fedicra_b200 import MScaleRecurveTreeEnergyLoss
+    B, C, H, W = 4, 2, 256, 256
+    image, logits, a1, a2, a3, label = loss_inputs(B, C, 1, H, W, "quant8", seed=11)
+    R = torch.randn(B, C, H, W, generator=torch.Generator().manual_seed(1))
+    three = image.repeat(1, 3, 1, 1)
+    xr = [t.clone().requires_grad_() for t in (logits, a1, a2, a3)]
+    as3_ref = losses_cpu.mscale_recurve_tree_energy_loss(xr[0], three, xr[1], xr[2], xr[3], label == C, 0.1,
+                                                         dtype=torch.float64)[3]
+    (as3_ref * R.double()).sum().backward()
+    xs = [t.clone().requires_grad_() for t in (logits, a1, a2, a3)]
+    as3 = MScaleRecurveTreeEnergyLoss()(xs[0].cuda(), three.cuda(), *(upsampled_on_cpu(a, H, W) for a in xs[1:]),
+                                        (label == C).cuda(), 0.1)[3]
+    (as3 * R.cuda()).sum().backward()
     assert rel_err(as3.detach().cpu(), as3_ref.detach()) < TOL
-    for a, b in zip(xs, xs_ref):
-        assert rel_err(a.grad.cpu(), b.grad) < TOL
+    for name, a, b in zip(("logits", "aux1", "aux2", "aux3"), xs, xr):
+        assert rel_err(a.grad, b.grad) < TOL, name
 
 
 def test_reference_glue_runs_on_the_operator_shim():
