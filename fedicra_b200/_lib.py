@@ -32,6 +32,9 @@ SIGNATURES = {
     "fedicra_gcrf_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "fedicra_gcrf_fwd_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                      ctypes.POINTER(GcrfDesc), c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "fedicra_gcrf_noalloc_max_bytes": (c_size_t, []),
+    "fedicra_gcrf_fwd_bwd_noalloc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                             ctypes.POINTER(GcrfDesc), c_int, c_void_p, c_void_p, c_void_p]),
     "fedicra_mst_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "fedicra_mst_forward": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
     "fedicra_mst_grid": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -341,3 +341,86 @@ extern "C" int fedicra_gcrf_fwd_bwd(const float *y, const float *image, int N, i
     FEDICRA_CHECK_LAUNCH("gcrf_generic_kernel");
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of fedicra_gcrf_fwd_bwd.
+//
+// Who this is for: callers that are not in a position to hand over a scratch buffer because they cannot create one.
+// Examples: a host program whose own memory manager has already reserved the GPU's memory and forbids side
+// allocations; a service loop with a fixed memory budget where a cudaMalloc (which synchronises the whole device)
+// would stall every other stream; a plugin that is handed tensors by its host but has no allocator of its own.
+// For them the scratch lives inside the library: one fixed array in device memory, created when the library is loaded
+// on a GPU and kept until the process exits.  Every GPU that loads the library pays for it, so it is kept small.
+//
+// Limit: the array is sized like the workspace fedicra_gcrf_workspace_bytes() asks for, one float per thread block of
+// the widest kernel, for at most FEDICRA_GCRF_NOALLOC_MAX_CTAS = 32768 blocks.  That covers N*H*W <= 4 194 304 pixels
+// (16 x 512 x 512, 64 x 256 x 256).  The array is 64 + 4*32768 = 131136 bytes.  Larger problems are refused with an
+// error; use fedicra_gcrf_fwd_bwd with a caller-owned workspace for those.
+//
+// The array is shared by all calls on a device and keeps whatever the previous call left in it.  The only part that
+// must start from zero is the 4-byte block counter at its front; each call clears it on `stream` before launching.
+// Because of the sharing, two calls that may run on the GPU at the same time (different streams, different host
+// threads) race on the array and give wrong losses: serialise them.
+//
+// The first call on each device looks up the array's device address (the name `g_gcrf_noalloc_scratch` below is only a
+// host-side handle, not something a kernel can be given).  That lookup is a one-off set-up step: make the first call
+// on a device before starting any stream capture on it.
+#include <mutex>
+
+namespace {
+
+constexpr int FEDICRA_GCRF_NOALLOC_MAX_CTAS = 32768;
+constexpr size_t FEDICRA_GCRF_NOALLOC_BYTES = 64 + (size_t)FEDICRA_GCRF_NOALLOC_MAX_CTAS * sizeof(float);
+constexpr int FEDICRA_MAX_DEVICES = 64;
+
+static __device__ __align__(256) unsigned char g_gcrf_noalloc_scratch[FEDICRA_GCRF_NOALLOC_BYTES];
+
+std::mutex g_noalloc_mutex;
+void *g_noalloc_ptr[FEDICRA_MAX_DEVICES] = {};  // device address of the array, per device ordinal
+
+// Returns the device address of the scratch array on the CURRENT device (looked up once per device), or nullptr with
+// the error text set.
+void *gcrf_noalloc_scratch_ptr() {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= FEDICRA_MAX_DEVICES) {
+        fedicra_fail(-2, "gcrf_fwd_bwd_noalloc: cannot identify the current device (%s)",
+                     e != cudaSuccess ? cudaGetErrorString(e) : "ordinal out of range");
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        void *ptr = nullptr;
+        e = cudaGetSymbolAddress((void **)&ptr, g_gcrf_noalloc_scratch);
+        if (e != cudaSuccess || ptr == nullptr) {
+            fedicra_fail(-2, "gcrf_fwd_bwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                         cudaGetErrorString(e));
+            return nullptr;
+        }
+        g_noalloc_ptr[dev] = ptr;
+    }
+    return g_noalloc_ptr[dev];
+}
+
+}  // namespace
+
+extern "C" size_t fedicra_gcrf_noalloc_max_bytes(void) { return FEDICRA_GCRF_NOALLOC_BYTES; }
+
+extern "C" int fedicra_gcrf_fwd_bwd_noalloc(const float *y, const float *image, int N, int C, int Cin, int H, int W,
+                                            int radius, const fedicra_gcrf_desc *h_descs, int n_desc, float *loss,
+                                            float *grad_y, void *stream) {
+    FEDICRA_REQUIRE(N > 0 && H > 0 && W > 0, "gcrf_fwd_bwd_noalloc: bad shape N=%d H=%d W=%d", N, H, W);
+    const size_t need = fedicra_gcrf_workspace_bytes(N, H, W);
+    FEDICRA_REQUIRE(need <= FEDICRA_GCRF_NOALLOC_BYTES,
+                    "gcrf_fwd_bwd_noalloc: problem N=%d H=%d W=%d needs %zu scratch bytes, the built-in array holds %zu "
+                    "(at most %d thread blocks = %d pixels); call fedicra_gcrf_fwd_bwd with your own workspace instead",
+                    N, H, W, need, FEDICRA_GCRF_NOALLOC_BYTES, FEDICRA_GCRF_NOALLOC_MAX_CTAS,
+                    FEDICRA_GCRF_NOALLOC_MAX_CTAS * 128);
+    void *scratch = gcrf_noalloc_scratch_ptr();
+    if (scratch == nullptr) return -2;
+    // the block counter must start at zero whatever an earlier (possibly failed) call left behind
+    cudaError_t e = cudaMemsetAsync(scratch, 0, 64, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fedicra_fail(-2, "gcrf_fwd_bwd_noalloc: clearing the block counter: %s", cudaGetErrorString(e));
+    return fedicra_gcrf_fwd_bwd(y, image, N, C, Cin, H, W, radius, h_descs, n_desc, loss, grad_y, scratch,
+                                FEDICRA_GCRF_NOALLOC_BYTES, stream);
+}

@@ -59,6 +59,18 @@ int fedicra_gcrf_fwd_bwd(const float *y, const float *image, int N, int C, int C
                          const fedicra_gcrf_desc *h_descs, int n_desc, float *loss, float *grad_y, void *workspace,
                          size_t workspace_bytes, void *stream);
 
+/* Allocation-free variant of fedicra_gcrf_fwd_bwd.  It has no counterpart in the reference.
+ * For callers that cannot create device memory themselves (their host framework owns all of it, or they run where a
+ * cudaMalloc -- which synchronises the device -- is not acceptable): the scratch is a fixed array inside the library,
+ * fedicra_gcrf_noalloc_max_bytes() = 131136 bytes per GPU, enough for N*H*W <= 4 194 304 pixels (16 x 512 x 512).
+ * Same arguments and results as fedicra_gcrf_fwd_bwd minus the workspace; problems beyond the limit are refused with an
+ * error.  The array is shared: calls that can overlap on the GPU race, serialise them.  The first call on a device
+ * performs a one-off address lookup and should be made before any stream capture on that device. */
+size_t fedicra_gcrf_noalloc_max_bytes(void);
+int fedicra_gcrf_fwd_bwd_noalloc(const float *y, const float *image, int N, int C, int Cin, int H, int W, int radius,
+                                 const fedicra_gcrf_desc *h_descs, int n_desc, float *loss, float *grad_y,
+                                 void *stream);
+
 /* ------------------------------------------------------------------------------------------------ MST ---------- */
 /* Scratch bytes for the two MST entry points (B images, V vertices, E candidate edges each). */
 size_t fedicra_mst_workspace_bytes(int B, int V, int E);
