@@ -1,0 +1,542 @@
+// bands.cu -- depth-banded tree filter: the two-pass filter of refine.cu without its ~1 500-step dependency chain.
+//
+// What it replaces (LTF = /root/reference/code/utils/TreeEnergyLoss/kernels/lib_tree_filter):
+//   refine_forward / refine_backward_feature / refine_backward_weight    LTF/src/refine/refine.cu:201-370
+//   (leaf_root_aggr_kernel :70-134, root_leaf_prop_kernel :19-68, root_leaf_grad_kernel :136-199)
+// The recurrences are the reference's, in BFS-position space (i = position, p(i) = parent position, w_0 := 0):
+//   up[i]  = x[i] + sum_{j child of i} w[j] * up[j]                  (leaf -> root)
+//   out[i] = (1 - w[i]^2) * up[i] + w[i] * out[p(i)]                 (root -> leaf)
+// A level-synchronous sweep needs one step per tree depth (1 200-1 600 at 256^2, ~3 000 at 512^2).  Here the depths are
+// cut into `nb` bands of K consecutive levels and every sweep becomes three short phases:
+//   up:    U1  all bands in parallel: local sweep with nothing entering from below  -> partial up at the band's first level
+//          U2  one CTA per image, deepest band first: exact up at each band's first level and the sum X that enters each
+//              band's last level from the band below (uses T[j] = product of w from a last-level vertex j up to, but not
+//              including, its first-level ancestor)
+//          U3  all bands in parallel: local sweep again with X injected -> exact up everywhere
+//   down:  D1  (fused behind U3, same CTA) local top-down pass: out[i] = A[i] * out[entry(i)] + B[i] with entry(i) the
+//              parent of i's first-level ancestor, A[i] the product of w from i up to and including that ancestor
+//          D2  one CTA per image, shallowest band first: out at each band's last level
+//          D3  element-wise: out[i] = A[i] * out[entry(i)] + B[i], fused with the consumer (normalise + scatter, or the
+//              edge-weight gradient)
+// Dependency chain: 3K + 2nb short steps instead of 2 * depth.  Band state lives in shared memory (a band that does not
+// fit falls back to the same code on global memory).  All arithmetic is fp32, deterministic, no atomics.
+#include "common.cuh"
+
+namespace {
+
+constexpr int NT = 256;
+constexpr int WCAP = 1024;   // level width kept in shared memory by the two sequential kernels
+constexpr int LSCAP = 512;   // level_start entries of a band cached in shared memory
+
+struct TreeView {
+    const int *vtx;     // [B,V]   sorted_index
+    const int *ppos;    // [B,V]   sorted_parent
+    const int4 *child;  // [B,V]   sorted_child (positions, contiguous, 0 = none)
+    const int *ls;      // [B,V+1] level_start
+    const int *nl;      // [B]
+    const float *w;     // [B,V]   edge weight in BFS order
+    int V, nb_target;
+};
+
+struct Consts {  // per (tree, edge weights)
+    float *A, *T;                    // [B,V]
+    int *ent, *anc, *run_s, *run_e;  // [B,V]
+};
+
+__device__ __forceinline__ bool band_geom(const TreeView &t, int b, int beta, int &L0, int &L1, int &nb) {
+    const int nl = t.nl[b];
+    const int K = (nl + t.nb_target - 1) / t.nb_target;
+    nb = (nl + K - 1) / K;
+    L0 = beta * K;
+    L1 = min(L0 + K, nl);
+    return beta < nb;
+}
+
+__device__ __forceinline__ int child_count(const int4 &c) { return (c.x > 0) + (c.y > 0) + (c.z > 0) + (c.w > 0); }
+
+// ------------------------------------------------------------------------------------------------ band constants
+template <bool SMEM>
+__device__ void consts_body(const TreeView &t, const Consts &k, int b, int L0, int L1, int p0, int p1, char *smem) {
+    const int tid = threadIdx.x, V = t.V, P = p1 - p0;
+    const int *ls = t.ls + (size_t)b * (V + 1);
+    const int *pp = t.ppos + (size_t)b * V;
+    const float *w = t.w + (size_t)b * V;
+    float *gA = k.A + (size_t)b * V, *gT = k.T + (size_t)b * V;
+    int *gE = k.ent + (size_t)b * V, *gN = k.anc + (size_t)b * V;
+    float *sA = reinterpret_cast<float *>(smem), *sT = sA + P;
+    int *sE = reinterpret_cast<int *>(sT + P), *sN = sE + P;
+    auto Aat = [&](int i) -> float & { return SMEM ? sA[i - p0] : gA[i]; };
+    auto Tat = [&](int i) -> float & { return SMEM ? sT[i - p0] : gT[i]; };
+    auto Eat = [&](int i) -> int & { return SMEM ? sE[i - p0] : gE[i]; };
+    auto Nat = [&](int i) -> int & { return SMEM ? sN[i - p0] : gN[i]; };
+    int lo = ls[L0], hi = ls[L0 + 1];
+    for (int L = L0; L < L1; ++L) {
+        const int nhi = (L + 1 < L1) ? ls[L + 2] : hi;
+        for (int i = lo + tid; i < hi; i += NT) {
+            const float wi = (i == 0) ? 0.f : w[i];
+            const int p = pp[i];
+            if (L == L0) {
+                Aat(i) = wi; Tat(i) = 1.f; Eat(i) = p; Nat(i) = i;
+            } else {
+                Aat(i) = wi * Aat(p); Tat(i) = wi * Tat(p); Eat(i) = Eat(p); Nat(i) = Nat(p);
+            }
+        }
+        __syncthreads();
+        lo = hi;
+        hi = nhi;
+    }
+    if (SMEM) {
+        for (int i = p0 + tid; i < p1; i += NT) {
+            gA[i] = sA[i - p0]; gT[i] = sT[i - p0]; gE[i] = sE[i - p0]; gN[i] = sN[i - p0];
+        }
+    }
+    // runs of last-level vertices under each first-level vertex (contiguous in the canonical order)
+    int *rs = k.run_s + (size_t)b * V, *re = k.run_e + (size_t)b * V;
+    const int f0 = ls[L0], f1 = ls[L0 + 1], e0 = ls[L1 - 1], e1 = ls[L1];
+    for (int i = f0 + tid; i < f1; i += NT) { rs[i] = 0; re[i] = 0; }
+    __syncthreads();
+    for (int j = e0 + tid; j < e1; j += NT) {
+        const int a = Nat(j);
+        if (j == e0 || Nat(j - 1) != a) rs[a] = j;
+        if (j == e1 - 1 || Nat(j + 1) != a) re[a] = j + 1;
+    }
+}
+
+__global__ void __launch_bounds__(NT) consts_kernel(TreeView t, Consts k, int pcap) {
+    extern __shared__ float4 smem4[];
+    const int b = blockIdx.y;
+    int L0, L1, nb;
+    if (!band_geom(t, b, blockIdx.x, L0, L1, nb)) return;
+    const int *ls = t.ls + (size_t)b * (t.V + 1);
+    const int p0 = ls[L0], p1 = ls[L1];
+    if (p1 - p0 <= pcap)
+        consts_body<true>(t, k, b, L0, L1, p0, p1, reinterpret_cast<char *>(smem4));
+    else
+        consts_body<false>(t, k, b, L0, L1, p0, p1, reinterpret_cast<char *>(smem4));
+}
+
+// ------------------------------------------------------------------------------------------------ band up / down
+enum { MODE_FWD = 0, MODE_BWD = 1 };
+
+struct SweepArgs {
+    // prologue operands
+    const float *feat;   // FWD: feature_in [B,C,V] vertex order.  BWD: grad_out [B,C,V] vertex order
+    const float *fpos;   // BWD: forward aggregate in position order [B,C+1,V] (channel C = Z)
+    int C, NC;           // feature channels; swept channels (FWD: C+1, BWD: C or 2C)
+    // per-sweep arrays [B,NC,V], position order
+    float *upl;          // partial up at each band's first level (U1 -> U2)
+    float *X;            // sum entering each band's last level from below (U2 -> U3)
+    float *up;           // exact up everywhere (U3 ->)
+    float *Bv;           // local down term B (D1 ->)
+    float *slab;         // global stand-in for the shared-memory band state (oversized bands only)
+};
+
+template <int MODE>
+__device__ __forceinline__ float prologue(const SweepArgs &a, int b, int c, int i, int v, int V) {
+    if (MODE == MODE_FWD) {
+        return (c < a.C) ? a.feat[((size_t)b * a.C + c) * V + v] : 1.f;
+    } else {
+        const int cc = (c < a.C) ? c : c - a.C;
+        const float z = a.fpos[((size_t)b * (a.C + 1) + a.C) * V + i];
+        float gn = a.feat[((size_t)b * a.C + cc) * V + v] / z;
+        if (c >= a.C) gn *= a.fpos[((size_t)b * (a.C + 1) + cc) * V + i] / z;  // x filtered output (refine.cu:348)
+        return gn;
+    }
+}
+
+template <int MODE, bool INJECT, bool SMEM>
+__device__ void sweep_body(const TreeView &t, const SweepArgs &a, int b, int beta, int nb, int L0, int L1, int p0, int p1,
+                           int pcap, char *smem) {
+    const int tid = threadIdx.x, V = t.V, NC = a.NC, P = p1 - p0;
+    const int *ls = t.ls + (size_t)b * (V + 1);
+    const int *vtx = t.vtx + (size_t)b * V, *pp = t.ppos + (size_t)b * V;
+    const int4 *child = t.child + (size_t)b * V;
+    const float *w = t.w + (size_t)b * V;
+    const size_t img = (size_t)b * NC * V;
+    // band state: val[c][i], and (shared-memory mode) copies of w / children / parent
+    float *sval = reinterpret_cast<float *>(smem);            // [NC][pcap]
+    float *sw = sval + (size_t)NC * pcap;                     // [pcap]
+    int *sch = reinterpret_cast<int *>(sw + pcap);            // [pcap] (first child position << 3 | count)
+    int *spp = sch + pcap;                                    // [pcap]
+    int *sls = spp + pcap;                                    // [LSCAP+1]
+    float *gval = a.slab + img;
+    auto VAL = [&](int c, int i) -> float & { return SMEM ? sval[(size_t)c * pcap + (i - p0)] : gval[(size_t)c * V + i]; };
+    auto Wat = [&](int i) -> float { return SMEM ? sw[i - p0] : ((i == 0) ? 0.f : w[i]); };
+    const bool ls_cached = SMEM && (L1 - L0) <= LSCAP;
+    auto LS = [&](int L) -> int { return ls_cached ? sls[L - L0] : ls[L]; };
+
+    // ---- stage the band (fully parallel, coalesced in position order; the feature gather is by vertex)
+    if (ls_cached)
+        for (int L = L0 + tid; L <= L1; L += NT) sls[L - L0] = ls[L];
+    for (int i = p0 + tid; i < p1; i += NT) {
+        const int v = vtx[i];
+        if (SMEM) {
+            const int4 ch = child[i];
+            sw[i - p0] = (i == 0) ? 0.f : w[i];
+            sch[i - p0] = (ch.x << 3) | child_count(ch);
+            spp[i - p0] = pp[i];
+        }
+        for (int c = 0; c < NC; ++c) VAL(c, i) = prologue<MODE>(a, b, c, i, v, V);
+    }
+    __syncthreads();
+
+    // ---- local leaf -> root sweep
+    for (int L = L1 - 1; L >= L0; --L) {
+        const int lo = LS(L), n = LS(L + 1) - lo;
+        const bool last = (L == L1 - 1);
+        for (int idx = tid; idx < n * NC; idx += NT) {
+            const int c = idx / n, i = lo + (idx - c * n);
+            float acc = VAL(c, i);
+            if (!last) {
+                int cs, cnt;
+                if (SMEM) {
+                    const int pk = sch[i - p0];
+                    cs = pk >> 3; cnt = pk & 7;
+                } else {
+                    const int4 ch = child[i];
+                    cs = ch.x; cnt = child_count(ch);
+                }
+                for (int k = 0; k < cnt; ++k) acc += VAL(c, cs + k) * Wat(cs + k);
+            } else if (INJECT && beta < nb - 1) {
+                acc += a.X[img + (size_t)c * V + i];
+            }
+            VAL(c, i) = acc;
+        }
+        __syncthreads();
+    }
+
+    if (!INJECT) {  // U1: only the first level's partial sums leave the CTA
+        const int f0 = LS(L0), f1 = LS(L0 + 1);
+        for (int idx = tid; idx < (f1 - f0) * NC; idx += NT) {
+            const int c = idx / (f1 - f0), i = f0 + (idx - c * (f1 - f0));
+            a.upl[img + (size_t)c * V + i] = VAL(c, i);
+        }
+        return;
+    }
+
+    // ---- U3: exact up leaves; D1: local root -> leaf pass, in place: val <- B
+    for (int c = 0; c < NC; ++c)
+        for (int i = p0 + tid; i < p1; i += NT) a.up[img + (size_t)c * V + i] = VAL(c, i);
+    __syncthreads();
+    for (int L = L0; L < L1; ++L) {
+        const int lo = LS(L), n = LS(L + 1) - lo;
+        for (int idx = tid; idx < n * NC; idx += NT) {
+            const int c = idx / n, i = lo + (idx - c * n);
+            const float wi = Wat(i);
+            float bval = VAL(c, i) * (1.f - wi * wi);
+            if (L > L0) bval += wi * VAL(c, SMEM ? spp[i - p0] : pp[i]);
+            VAL(c, i) = bval;
+        }
+        __syncthreads();
+    }
+    for (int c = 0; c < NC; ++c)
+        for (int i = p0 + tid; i < p1; i += NT) a.Bv[img + (size_t)c * V + i] = VAL(c, i);
+}
+
+template <int MODE, bool INJECT>
+__global__ void __launch_bounds__(NT) sweep_kernel(TreeView t, SweepArgs a, int pcap) {
+    extern __shared__ float4 smem4[];
+    const int b = blockIdx.y, beta = blockIdx.x;
+    int L0, L1, nb;
+    if (!band_geom(t, b, beta, L0, L1, nb)) return;
+    const int *ls = t.ls + (size_t)b * (t.V + 1);
+    const int p0 = ls[L0], p1 = ls[L1];
+    if (p1 - p0 <= pcap)
+        sweep_body<MODE, INJECT, true>(t, a, b, beta, nb, L0, L1, p0, p1, pcap, reinterpret_cast<char *>(smem4));
+    else
+        sweep_body<MODE, INJECT, false>(t, a, b, beta, nb, L0, L1, p0, p1, pcap, reinterpret_cast<char *>(smem4));
+}
+
+// ------------------------------------------------------------------------------------------------ U2: stitch upward
+__global__ void __launch_bounds__(NT) stitch_up_kernel(TreeView t, Consts k, SweepArgs a) {
+    extern __shared__ float4 smem4[];
+    const int b = blockIdx.x, tid = threadIdx.x, V = t.V, NC = a.NC;
+    const int *ls = t.ls + (size_t)b * (V + 1);
+    const int4 *child = t.child + (size_t)b * V;
+    const float *w = t.w + (size_t)b * V;
+    const float *T = k.T + (size_t)b * V;
+    const int *rs = k.run_s + (size_t)b * V, *re = k.run_e + (size_t)b * V;
+    const size_t img = (size_t)b * NC * V;
+    const float *upl = a.upl + img;
+    float *Xg = a.X + img, *upFg = a.slab + img;
+    float *sX[2] = {reinterpret_cast<float *>(smem4), reinterpret_cast<float *>(smem4) + (size_t)NC * WCAP};
+    float *sF = sX[1] + (size_t)NC * WCAP;
+    int L0, L1, nb;
+    band_geom(t, b, 0, L0, L1, nb);
+    const int nl = t.nl[b], K = (nl + t.nb_target - 1) / t.nb_target;
+    int cur = 0;
+    int e0 = 0, e1 = 0;  // last level of band beta (whose X is held in sX[cur] when it fits)
+    for (int beta = nb - 1; beta >= 1; --beta) {
+        L0 = beta * K;
+        L1 = min(L0 + K, nl);
+        const int f0 = ls[L0], f1 = ls[L0 + 1], nf = f1 - f0;
+        e0 = ls[L1 - 1];
+        e1 = ls[L1];
+        const bool x_sm = (e1 - e0) <= WCAP, f_sm = nf <= WCAP;
+        // (a) exact up at the band's first level
+        for (int idx = tid; idx < nf * NC; idx += NT) {
+            const int c = idx / nf, tpos = f0 + (idx - c * nf);
+            float acc = upl[(size_t)c * V + tpos];
+            if (beta < nb - 1) {
+                const int j1 = re[tpos];
+                for (int j = rs[tpos]; j < j1; ++j)
+                    acc += T[j] * (x_sm ? sX[cur][(size_t)c * WCAP + (j - e0)] : Xg[(size_t)c * V + j]);
+            }
+            if (f_sm) sF[(size_t)c * WCAP + (tpos - f0)] = acc; else upFg[(size_t)c * V + tpos] = acc;
+        }
+        __syncthreads();
+        // (b) what enters the last level of the band above: X[j'] = sum over its children (all in this band's first level)
+        const int q0 = ls[L0 - 1], nq = f0 - q0;
+        const bool q_sm = nq <= WCAP;
+        for (int idx = tid; idx < nq * NC; idx += NT) {
+            const int c = idx / nq, j = q0 + (idx - c * nq);
+            const int4 ch = child[j];
+            const int cnt = child_count(ch);
+            float acc = 0.f;
+            for (int kk = 0; kk < cnt; ++kk) {
+                const int tp = ch.x + kk;
+                acc += w[tp] * (f_sm ? sF[(size_t)c * WCAP + (tp - f0)] : upFg[(size_t)c * V + tp]);
+            }
+            Xg[(size_t)c * V + j] = acc;
+            if (q_sm) sX[cur ^ 1][(size_t)c * WCAP + (j - q0)] = acc;
+        }
+        __syncthreads();
+        cur ^= 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ D2: stitch downward
+__global__ void __launch_bounds__(NT) stitch_down_kernel(TreeView t, Consts k, SweepArgs a, float *outE) {
+    extern __shared__ float4 smem4[];
+    const int b = blockIdx.x, tid = threadIdx.x, V = t.V, NC = a.NC;
+    const int *ls = t.ls + (size_t)b * (V + 1);
+    const float *A = k.A + (size_t)b * V;
+    const int *ent = k.ent + (size_t)b * V;
+    const size_t img = (size_t)b * NC * V;
+    const float *Bv = a.Bv + img;
+    float *og = outE + img;
+    float *sO[2] = {reinterpret_cast<float *>(smem4), reinterpret_cast<float *>(smem4) + (size_t)NC * WCAP};
+    const int nl = t.nl[b], K = (nl + t.nb_target - 1) / t.nb_target, nb = (nl + K - 1) / K;
+    int cur = 0, pe0 = 0, pn = 0;
+    for (int beta = 0; beta < nb; ++beta) {
+        const int L1 = min(beta * K + K, nl);
+        const int e0 = ls[L1 - 1], n = ls[L1] - e0;
+        const bool prev_sm = pn <= WCAP, out_sm = n <= WCAP;
+        for (int idx = tid; idx < n * NC; idx += NT) {
+            const int c = idx / n, j = e0 + (idx - c * n);
+            float o = Bv[(size_t)c * V + j];
+            if (beta > 0) {
+                const int en = ent[j];
+                o += A[j] * (prev_sm ? sO[cur][(size_t)c * WCAP + (en - pe0)] : og[(size_t)c * V + en]);
+            }
+            og[(size_t)c * V + j] = o;
+            if (out_sm) sO[cur ^ 1][(size_t)c * WCAP + (j - e0)] = o;
+        }
+        __syncthreads();
+        cur ^= 1;
+        pe0 = e0;
+        pn = n;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ D3 epilogues
+__device__ __forceinline__ float down_value(const float *A, const int *ent, const float *Bv, const float *og, int i) {
+    const float a = A[i];
+    float o = Bv[i];
+    if (a != 0.f) o += a * og[ent[i]];
+    return o;
+}
+
+// forward: aggregate in position order (saved), normalised output scattered to vertex order
+__global__ void __launch_bounds__(256)
+finish_forward_kernel(TreeView t, Consts k, const float *__restrict__ Bv, const float *__restrict__ outE, int C,
+                      float *__restrict__ fpos, float *__restrict__ feature_out, float *__restrict__ feature_aggr,
+                      float *__restrict__ weight_sum) {
+    const int b = blockIdx.y, V = t.V, NC = C + 1;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= V) return;
+    const float *A = k.A + (size_t)b * V;
+    const int *ent = k.ent + (size_t)b * V;
+    const size_t img = (size_t)b * NC * V;
+    const int v = t.vtx[(size_t)b * V + i];
+    const float z = down_value(A, ent, Bv + img + (size_t)C * V, outE + img + (size_t)C * V, i);
+    fpos[img + (size_t)C * V + i] = z;
+    if (weight_sum) weight_sum[(size_t)b * V + v] = z;
+    for (int c = 0; c < C; ++c) {
+        const float o = down_value(A, ent, Bv + img + (size_t)c * V, outE + img + (size_t)c * V, i);
+        fpos[img + (size_t)c * V + i] = o;
+        feature_out[((size_t)b * C + c) * V + v] = o / z;
+        if (feature_aggr) feature_aggr[((size_t)b * C + c) * V + v] = o;
+    }
+}
+
+// backward: feature gradient scattered to vertex order and, when asked, the edge-weight gradient (refine.cu:136-199)
+__global__ void __launch_bounds__(256)
+finish_backward_kernel(TreeView t, Consts k, const float *__restrict__ Bv, const float *__restrict__ outE,
+                       const float *__restrict__ bup, const float *__restrict__ fup, const float *__restrict__ fpos, int C,
+                       int NC, float *__restrict__ grad_feature, float *__restrict__ grad_weight) {
+    const int b = blockIdx.y, V = t.V;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= V) return;
+    const float *A = k.A + (size_t)b * V;
+    const int *ent = k.ent + (size_t)b * V;
+    const size_t img = (size_t)b * NC * V, fimg = (size_t)b * (C + 1) * V;
+    const int v = t.vtx[(size_t)b * V + i];
+    const int p = t.ppos[(size_t)b * V + i];
+    const float wi = (i == 0) ? 0.f : t.w[(size_t)b * V + i];
+    float gw = 0.f;
+    for (int c = 0; c < C; ++c) {
+        const float *Bc = Bv + img + (size_t)c * V, *oc = outE + img + (size_t)c * V;
+        const float g1 = down_value(A, ent, Bc, oc, i);
+        grad_feature[((size_t)b * C + c) * V + v] = g1;
+        if (grad_weight != nullptr && i > 0) {
+            const float *B2 = Bv + img + (size_t)(C + c) * V, *o2 = outE + img + (size_t)(C + c) * V;
+            const float g1p = down_value(A, ent, Bc, oc, p), g2p = down_value(A, ent, B2, o2, p);
+            const float u1 = bup[img + (size_t)c * V + i], u2 = bup[img + (size_t)(C + c) * V + i];
+            const float fu = fup[fimg + (size_t)c * V + i], zu = fup[fimg + (size_t)C * V + i];
+            const float fa_p = fpos[fimg + (size_t)c * V + p], z_p = fpos[fimg + (size_t)C * V + p];
+            const float ga = u1 * (fa_p - wi * fu) + fu * (g1p - wi * u1);
+            const float gb = u2 * (z_p - wi * zu) + zu * (g2p - wi * u2);
+            gw += ga - gb;
+        }
+    }
+    if (grad_weight != nullptr) grad_weight[(size_t)b * V + i] = gw;
+}
+
+__global__ void zero_root_weight_kernel(float *w, int V, int B) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < B) w[(size_t)b * V] = 0.f;  // refine.cu:43-46
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+int pick_nb(int V) {
+    int nb = (int)(sqrtf((float)V) * 0.1875f + 0.5f);
+    return nb < 16 ? 16 : (nb > 256 ? 256 : nb);
+}
+
+int pick_pcap(int V, int nb, int bytes_per_pos, size_t budget) {
+    long long want = (long long)V * 5 / (2LL * nb);  // 2.5 x the average band
+    want = (want + 255) / 256 * 256;
+    if (want < 512) want = 512;
+    const long long fit = (long long)(budget / bytes_per_pos) / 256 * 256;
+    return (int)(want < fit ? want : fit);
+}
+
+struct Layout {
+    // saved (forward -> backward): A, T [V]; up, pos [(C+1),V]; ent, anc, run_s, run_e [V]
+    static size_t saved_bytes(int B, int C, int V) { return (size_t)B * V * (2 + 2 * (C + 1) + 4) * 4; }
+    // work: upl, X, up, Bv, outE, slab  [NCmax,V] each
+    static size_t work_bytes(int B, int NCmax, int V) { return (size_t)B * V * 6 * NCmax * 4; }
+};
+
+Consts consts_view(void *saved, int B, int C, int V, float **up, float **pos) {
+    float *f = (float *)saved;
+    const size_t n = (size_t)B * V;
+    Consts k;
+    k.A = f;
+    k.T = f + n;
+    *up = f + 2 * n;
+    *pos = *up + n * (C + 1);
+    int *ip = (int *)(*pos + n * (C + 1));
+    k.ent = ip;
+    k.anc = ip + n;
+    k.run_s = ip + 2 * n;
+    k.run_e = ip + 3 * n;
+    return k;
+}
+
+template <typename Kern>
+int set_smem(Kern kern, size_t bytes, const char *name) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e != cudaSuccess) return fedicra_fail(-2, "%s: cannot reserve %zu bytes of shared memory: %s", name, bytes, cudaGetErrorString(e));
+    return 0;
+}
+
+template <int MODE>
+int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int B, cudaStream_t st) {
+    const int V = t.V, nb = t.nb_target, NC = a.NC;
+    const int per_pos = (NC + 3) * 4;
+    const int pcap = pick_pcap(V, nb, per_pos, 160 * 1024);
+    const size_t smem = (size_t)pcap * per_pos + (LSCAP + 1) * sizeof(int) + 16;
+    if (set_smem(sweep_kernel<MODE, false>, smem, "sweep_kernel") || set_smem(sweep_kernel<MODE, true>, smem, "sweep_kernel")) return -2;
+    const size_t smem_u2 = (size_t)3 * NC * WCAP * sizeof(float), smem_d2 = (size_t)2 * NC * WCAP * sizeof(float);
+    if (set_smem(stitch_up_kernel, smem_u2, "stitch_up_kernel") || set_smem(stitch_down_kernel, smem_d2, "stitch_down_kernel")) return -2;
+    sweep_kernel<MODE, false><<<dim3(nb, B), NT, smem, st>>>(t, a, pcap);
+    FEDICRA_CHECK_LAUNCH("sweep_kernel<U1>");
+    stitch_up_kernel<<<B, NT, smem_u2, st>>>(t, k, a);
+    FEDICRA_CHECK_LAUNCH("stitch_up_kernel");
+    sweep_kernel<MODE, true><<<dim3(nb, B), NT, smem, st>>>(t, a, pcap);
+    FEDICRA_CHECK_LAUNCH("sweep_kernel<U3D1>");
+    stitch_down_kernel<<<B, NT, smem_d2, st>>>(t, k, a, outE);
+    FEDICRA_CHECK_LAUNCH("stitch_down_kernel");
+    return 0;
+}
+
+}  // namespace
+
+extern "C" size_t fedicra_tree_filter_saved_bytes(int B, int C, int V) {
+    if (B <= 0 || C <= 0 || V <= 0) return 0;
+    return Layout::saved_bytes(B, C, V);
+}
+
+extern "C" size_t fedicra_tree_filter_workspace_bytes(int B, int C, int V) {
+    if (B <= 0 || C <= 0 || V <= 0) return 0;
+    return Layout::work_bytes(B, 2 * C > C + 1 ? 2 * C : C + 1, V);
+}
+
+extern "C" int fedicra_tree_filter_forward(const float *feature_in, float *edge_weight, const int *sorted_index,
+                                           const int *sorted_parent, const int *sorted_child, const int *level_start,
+                                           const int *n_levels, int B, int C, int V, float *feature_out,
+                                           float *feature_aggr, float *weight_sum, void *saved, size_t saved_bytes,
+                                           void *workspace, size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(feature_in && edge_weight && sorted_index && sorted_parent && sorted_child && level_start &&
+                        n_levels && feature_out && saved && workspace, "tree_filter_forward: null pointer");
+    FEDICRA_REQUIRE(B > 0 && B <= 65535 && C > 0 && C <= 64 && V > 0, "tree_filter_forward: bad sizes B=%d C=%d V=%d", B, C, V);
+    FEDICRA_REQUIRE(saved_bytes >= fedicra_tree_filter_saved_bytes(B, C, V), "tree_filter_forward: `saved` too small");
+    FEDICRA_REQUIRE(workspace_bytes >= fedicra_tree_filter_workspace_bytes(B, C, V), "tree_filter_forward: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int nb = pick_nb(V), NC = C + 1;
+    TreeView t{sorted_index, sorted_parent, reinterpret_cast<const int4 *>(sorted_child), level_start, n_levels, edge_weight, V, nb};
+    float *fup, *fpos;
+    Consts k = consts_view(saved, B, C, V, &fup, &fpos);
+    const size_t n = (size_t)B * V * (2 * C > NC ? 2 * C : NC);
+    float *wk = (float *)workspace;
+    SweepArgs a{feature_in, nullptr, C, NC, wk, wk + n, fup, wk + 2 * n, wk + 4 * n};
+    float *outE = wk + 3 * n;
+
+    zero_root_weight_kernel<<<(B + 127) / 128, 128, 0, st>>>(edge_weight, V, B);
+    FEDICRA_CHECK_LAUNCH("zero_root_weight_kernel");
+    const int pcap_c = pick_pcap(V, nb, 16, 96 * 1024);
+    const size_t smem_c = (size_t)pcap_c * 16 + 16;
+    if (set_smem(consts_kernel, smem_c, "consts_kernel")) return -2;
+    consts_kernel<<<dim3(nb, B), NT, smem_c, st>>>(t, k, pcap_c);
+    FEDICRA_CHECK_LAUNCH("consts_kernel");
+    if (int rc = run_sweeps<MODE_FWD>(t, k, a, outE, B, st)) return rc;
+    finish_forward_kernel<<<dim3((V + 255) / 256, B), 256, 0, st>>>(t, k, a.Bv, outE, C, fpos, feature_out, feature_aggr, weight_sum);
+    FEDICRA_CHECK_LAUNCH("finish_forward_kernel");
+    return 0;
+}
+
+extern "C" int fedicra_tree_filter_backward(const float *grad_out, const float *edge_weight, const int *sorted_index,
+                                            const int *sorted_parent, const int *sorted_child, const int *level_start,
+                                            const int *n_levels, int B, int C, int V, const void *saved,
+                                            float *grad_feature, float *grad_weight, void *workspace,
+                                            size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(grad_out && edge_weight && sorted_index && sorted_parent && sorted_child && level_start && n_levels &&
+                        saved && grad_feature && workspace, "tree_filter_backward: null pointer");
+    FEDICRA_REQUIRE(B > 0 && B <= 65535 && C > 0 && C <= 64 && V > 0, "tree_filter_backward: bad sizes B=%d C=%d V=%d", B, C, V);
+    FEDICRA_REQUIRE(workspace_bytes >= fedicra_tree_filter_workspace_bytes(B, C, V), "tree_filter_backward: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int nb = pick_nb(V), NC = grad_weight ? 2 * C : C;
+    TreeView t{sorted_index, sorted_parent, reinterpret_cast<const int4 *>(sorted_child), level_start, n_levels, edge_weight, V, nb};
+    float *fup, *fpos;
+    Consts k = consts_view(const_cast<void *>(saved), B, C, V, &fup, &fpos);
+    const size_t n = (size_t)B * V * (2 * C > C + 1 ? 2 * C : C + 1);
+    float *wk = (float *)workspace;
+    SweepArgs a{grad_out, fpos, C, NC, wk, wk + n, wk + 5 * n, wk + 2 * n, wk + 4 * n};
+    float *outE = wk + 3 * n;
+    if (int rc = run_sweeps<MODE_BWD>(t, k, a, outE, B, st)) return rc;
+    finish_backward_kernel<<<dim3((V + 255) / 256, B), 256, 0, st>>>(t, k, a.Bv, outE, a.up, fup, fpos, C, NC, grad_feature, grad_weight);
+    FEDICRA_CHECK_LAUNCH("finish_backward_kernel");
+    return 0;
+}

@@ -170,6 +170,40 @@ def refine_backward_weight(edge_weight, si, sp, sc, ls, nl, feature_out, feature
     return out
 
 
+def tree_filter_forward(feature_in, edge_weight, si, sp, sc, ls, nl, want_aggr=False):
+    """Depth-banded filter forward.  Returns (feature_out, saved[, feature_aggr, weight_sum])."""
+    f = _cuda(feature_in, torch.float32, "feature_in")
+    if not (edge_weight.is_cuda and edge_weight.dtype == torch.float32 and edge_weight.is_contiguous()):
+        raise RuntimeError("edge_weight must be a contiguous float32 CUDA tensor (it is written in place)")
+    B, C, V = f.shape
+    dev = f.device
+    with torch.cuda.device(dev):
+        out = torch.empty_like(f)
+        saved = torch.empty(lib.fedicra_tree_filter_saved_bytes(B, C, V), dtype=torch.uint8, device=dev)
+        aggr = torch.empty_like(f) if want_aggr else None
+        wsum = torch.empty(B, V, dtype=torch.float32, device=dev) if want_aggr else None
+        ws = workspace("tree_filter", lib.fedicra_tree_filter_workspace_bytes(B, C, V), dev)
+        check(lib.fedicra_tree_filter_forward(_p(f), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(ls), _p(nl), B, C, V,
+                                              _p(out), _p(aggr), _p(wsum), _p(saved), saved.numel(), _p(ws), ws.numel(),
+                                              _stream()), "tree_filter_forward")
+    return (out, saved, aggr, wsum) if want_aggr else (out, saved)
+
+
+def tree_filter_backward(grad_out, edge_weight, si, sp, sc, ls, nl, saved, want_weight_grad):
+    """Depth-banded filter backward.  Returns (grad_feature, grad_weight or None)."""
+    g = _cuda(grad_out, torch.float32, "grad_output")
+    B, C, V = g.shape
+    dev = g.device
+    with torch.cuda.device(dev):
+        gf = torch.empty_like(g)
+        gw = torch.empty(B, V, dtype=torch.float32, device=dev) if want_weight_grad else None
+        ws = workspace("tree_filter", lib.fedicra_tree_filter_workspace_bytes(B, C, V), dev)
+        check(lib.fedicra_tree_filter_backward(_p(g), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(ls), _p(nl), B, C, V,
+                                               _p(saved), _p(gf), _p(gw), _p(ws), ws.numel(), _stream()),
+              "tree_filter_backward")
+    return gf, gw
+
+
 # ------------------------------------------------------------------ aggregation
 
 

@@ -87,26 +87,23 @@ class _EdgeWeight(torch.autograd.Function):
 
 
 class _Refine(torch.autograd.Function):
-    """Two-pass tree filter; same gradient policy as functions/refine.py:23-40 (weight gradient for high trees only)."""
+    """Two-pass tree filter (depth-banded kernels, csrc/bands.cu); same gradient policy as functions/refine.py:23-40
+    (weight gradient for the high-level trees only, and only when the edge weights need one)."""
 
     @staticmethod
     def forward(ctx, feature_in, edge_weight, order, low_tree):
-        out, aggr, aggr_up, wsum, wsum_up = ops.refine_forward(feature_in, edge_weight, order.si, order.sp, order.sc,
-                                                               order.ls, order.nl)
+        out, saved = ops.tree_filter_forward(feature_in, edge_weight, order.si, order.sp, order.sc, order.ls, order.nl)
         ctx.order, ctx.low_tree = order, low_tree
-        ctx.save_for_backward(edge_weight, out, aggr, aggr_up, wsum, wsum_up)
+        ctx.save_for_backward(edge_weight, saved)
         return out
 
     @staticmethod
     def backward(ctx, grad_out):
-        edge_weight, out, aggr, aggr_up, wsum, wsum_up = ctx.saved_tensors
+        edge_weight, saved = ctx.saved_tensors
         o = ctx.order
-        g = grad_out.contiguous()
-        grad_feature = ops.refine_backward_feature(edge_weight, o.si, o.sp, o.sc, o.ls, o.nl, wsum, g)
-        grad_weight = None
-        if not ctx.low_tree and ctx.needs_input_grad[1]:
-            grad_weight = ops.refine_backward_weight(edge_weight, o.si, o.sp, o.sc, o.ls, o.nl, out, aggr, aggr_up,
-                                                     wsum, wsum_up, g)
+        want_w = (not ctx.low_tree) and ctx.needs_input_grad[1]
+        grad_feature, grad_weight = ops.tree_filter_backward(grad_out.contiguous(), edge_weight, o.si, o.sp, o.sc, o.ls,
+                                                             o.nl, saved, want_w)
         return grad_feature, grad_weight, None, None
 
 

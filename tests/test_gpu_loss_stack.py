@@ -45,32 +45,18 @@ def test_tree_energy_golden(golden_dir, name):
         assert rel_err(gr, t[k]) < TOL, k
 
 
-def well_conditioned_case(B, C, Cin, H, W, kind):
-    """Inputs + fp64 oracle results for which the loss is differentiable in a neighbourhood.
-
-    The tree-energy loss is sum |prob - AS_3| (flower_common.py:813): where prob and AS_3 agree to rounding, sign() is
-    decided by the last bit and ANY two fp32 evaluations (the reference on two machines included) disagree by O(1) on
-    the gradient.  With ~10^6 pixels such a pixel turns up by chance in some batches, so the case generator walks the
-    seeds until the fp64 margin min|prob - AS_3| over the ROI is comfortably above fp32 resolution."""
-    for seed in range(2022, 2030):
-        image, logits, a1, a2, a3, label = loss_inputs(B, C, Cin, H, W, kind, seed=seed)
-        xs = [t.clone().requires_grad_() for t in (logits, a1, a2, a3)]
-        total, tel, crf, as3 = losses_cpu.loss_stack(xs[0], image, xs[1], xs[2], xs[3], label, C, gcrf="shift",
-                                                     dtype=torch.float64)
-        margin = (torch.softmax(logits.double(), 1) - as3.detach()).abs()[(label == C).unsqueeze(1).expand(-1, C, -1, -1)]
-        if margin.min() > 2e-6:
-            total.backward()
-            return (image, logits, a1, a2, a3, label), (tel.detach(), crf.detach(), as3.detach(), [x.grad for x in xs])
-    raise AssertionError("no well-conditioned seed found")
-
-
 @pytest.mark.parametrize("B,C,Cin,H,W,kind", [(2, 2, 1, 64, 64, "quant8"), (1, 3, 3, 48, 80, "uniform"),
                                               (12, 2, 1, 256, 256, "quant8"), (3, 3, 3, 256, 256, "quant8")])
 def test_full_loss_stack_vs_oracle(B, C, Cin, H, W, kind):
     """TEL + 0.1 * GatedCRF as in OURS.py:142-151 against the oracle evaluated in fp64 (the judge between two fp32
-    evaluations): loss terms, AS_3 and the gradients w.r.t. logits and the three aux heads."""
+    evaluations): loss terms, AS_3 and the gradients w.r.t. logits and the three aux heads.
+
+    The tree-energy loss is sum |prob - AS_3| (flower_common.py:813).  Where prob and AS_3 agree to rounding, sign() hangs
+    on the last bit, and any two fp32 evaluations (the reference on two machines included) differ by O(1) in the
+    gradient; among ~10^6 pixels there is always such a pixel.  So the oracle's gradient is taken with the SIGN PATTERN
+    THE GPU USED, after checking that the two patterns differ only where |prob - AS_3| is below fp32 resolution."""
     from fedicra_b200 import ModelLossSemsegGatedCRF, MScaleRecurveTreeEnergyLoss
-    (image, logits, a1, a2, a3, label), (tel_ref, crf_ref, as3_ref, g_ref) = well_conditioned_case(B, C, Cin, H, W, kind)
+    image, logits, a1, a2, a3, label = loss_inputs(B, C, Cin, H, W, kind)
     xs = [t.clone().requires_grad_() for t in (logits, a1, a2, a3)]
     img = image.cuda()
     three = img.repeat(1, 3, 1, 1) if Cin == 1 else img
@@ -78,13 +64,26 @@ def test_full_loss_stack_vs_oracle(B, C, Cin, H, W, kind):
     lg = xs[0].cuda()
     tel, _, _, as3 = MScaleRecurveTreeEnergyLoss()(lg, three, *(upsampled_on_cpu(a, H, W) for a in xs[1:]), roi, 0.1)
     crf = ModelLossSemsegGatedCRF()(torch.softmax(lg, 1), losses_cpu.KERNELS_DESC, 5, img, H, W)["loss"]
-    total = tel + 0.1 * crf
-    total.backward()
-    assert rel_err(tel.detach().cpu(), tel_ref) < TOL
-    assert rel_err(crf.detach().cpu(), crf_ref) < TOL
-    assert rel_err(as3.detach().cpu(), as3_ref) < TOL
-    for name, a, b in zip(("logits", "aux1", "aux2", "aux3"), xs, g_ref):
-        assert rel_err(a.grad, b) < TOL, name
+    (tel + 0.1 * crf).backward()
+    sign_gpu = torch.sign(torch.softmax(lg.detach(), 1) - as3.detach()).cpu().double()
+
+    xr = [t.clone().requires_grad_() for t in (logits, a1, a2, a3)]
+    three_cpu = image.repeat(1, 3, 1, 1) if Cin == 1 else image
+    _, tel_ref, crf_ref, as3_ref = losses_cpu.loss_stack(xr[0], image, xr[1], xr[2], xr[3], label, C, gcrf="shift",
+                                                        dtype=torch.float64)
+    prob_ref = torch.softmax(xr[0].double(), 1)
+    roi_ref = (label == C).unsqueeze(1).double()
+    diff = prob_ref - as3_ref
+    flipped = (torch.sign(diff.detach()) != sign_gpu) & (roi_ref > 0)
+    assert float(diff.detach().abs()[flipped].max() if flipped.any() else 0.0) < 1e-6, "sign differs away from the kink"
+    tel_signed = 0.1 * (roi_ref * sign_gpu * diff).sum() / roi_ref.sum().clamp(min=1)
+    (tel_signed + 0.1 * crf_ref).backward()
+
+    assert rel_err(tel.detach().cpu(), tel_ref.detach()) < TOL
+    assert rel_err(crf.detach().cpu(), crf_ref.detach()) < TOL
+    assert rel_err(as3.detach().cpu(), as3_ref.detach()) < TOL
+    for name, a, b in zip(("logits", "aux1", "aux2", "aux3"), xs, xr):
+        assert rel_err(a.grad, b.grad) < TOL, name
 
 
 def test_filter_chain_gradients_of_a_smooth_functional():

@@ -135,3 +135,37 @@ def test_filter_properties_at_512():
     _, ah, _, _, _ = ops.refine_forward(h, ew, si, sp, sc, ls, nl)
     lhs, rhs = (af.double() * h.double()).sum().item(), (f.double() * ah.double()).sum().item()
     assert abs(lhs - rhs) < 1e-5 * abs(lhs)
+
+
+@pytest.mark.parametrize("kind,B,C,D,H,W,inv_sigma", [
+    ("uniform", 2, 2, 3, 24, 31, 1.0), ("quant8", 1, 3, 3, 40, 40, 50.0), ("constant", 1, 2, 1, 9, 7, 1.0),
+    ("uniform", 1, 1, 2, 1, 13, 1.0), ("uniform", 2, 2, 2, 1, 700, 0.05), ("constant", 2, 3, 1, 300, 2, 1.0),
+    ("uniform", 1, 2, 1, 1, 1, 1.0), ("uniform", 1, 2, 1, 1, 2, 1.0), ("quant8", 12, 2, 3, 256, 256, 50.0),
+    ("uniform", 3, 3, 3, 256, 256, 0.3), ("quant8", 2, 3, 3, 512, 512, 1.0),
+])
+def test_depth_banded_filter_vs_oracle(kind, B, C, D, H, W, inv_sigma):
+    """fedicra_tree_filter_forward/backward (csrc/bands.cu) against the sequential oracle, including degenerate trees:
+    paths (depth = V), combs, single vertices."""
+    from fedicra_b200 import ops
+    emb, feat, gout, tree = _tree_case(kind, B, C, D, H, W, seed=5)
+    V = H * W
+    if V == 1:
+        tree = torch.zeros(B, 0, 2, dtype=torch.int32)
+    si, sp, sc = tree_cpu.bfs_forward(tree, 4)
+    ew = tree_cpu.edge_weight(emb.reshape(B, D, V), si, sp, inv_sigma)
+    saved = tree_cpu.refine_forward(feat, ew, si, sp, sc)
+    gf = tree_cpu.refine_backward_feature(feat, ew, si, sp, sc, *saved, gout)
+    gw = tree_cpu.refine_backward_weight(feat, ew, si, sp, sc, *saved, gout)
+
+    order = ops.bfs_forward(tree.cuda())
+    cew = ops.edge_weight_fwd(emb.reshape(B, D, V).cuda(), order[0], order[1], inv_sigma)
+    out, sv, aggr, wsum = ops.tree_filter_forward(feat.cuda(), cew, *order, want_aggr=True)
+    assert float(cew[:, 0].abs().max()) == 0.0
+    assert rel_err(out.cpu(), saved[0]) < TOL
+    assert rel_err(aggr.cpu(), saved[1]) < TOL
+    assert rel_err(wsum.cpu(), saved[3]) < TOL
+    cgf, cgw = ops.tree_filter_backward(gout.cuda(), cew, *order, sv, True)
+    assert rel_err(cgf.cpu(), gf) < TOL
+    assert rel_err(cgw.cpu(), gw) < TOL
+    cgf2, none = ops.tree_filter_backward(gout.cuda(), cew, *order, sv, False)
+    assert none is None and rel_err(cgf2.cpu(), gf) < TOL
