@@ -140,6 +140,36 @@ class GpuStep:
         return loss.detach(), [x.grad for x in leaves]
 
 
+class GraphedStep:
+    """The same step captured once into a CUDA graph and replayed: static input buffers, outputs in the graph's pool.
+    Every kernel of the library launches on the capturing stream and none of them synchronises or allocates outside
+    torch's allocator, so the step is capture-safe.  Removes the host launch cost (~350 launches per step)."""
+
+    def __init__(self, step, example):
+        self.static_in = {k: v.clone() for k, v in example.items()}
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                step(self.static_in)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss, self.grads = step(self.static_in)
+        torch.cuda.synchronize()
+
+    def load(self, src, non_blocking=True):
+        for k, v in src.items():
+            self.static_in[k].copy_(v, non_blocking=non_blocking)
+
+    def __call__(self, d=None):
+        if d is not None and d is not self.static_in:
+            self.load(d)
+        self.graph.replay()
+        return self.loss, self.grads
+
+
 def flush_l2(buf):
     buf.zero_()
 
@@ -161,8 +191,8 @@ def time_steps(fn, steps, flush_buf):
 def profile_ops(step, data, steps, flush_buf):
     """Second, instrumented pass: CUDA events around every C-ABI call, to attribute the step time to kernel groups."""
     from fedicra_b200 import ops
-    names = ["gcrf_fwd_bwd", "mst_grid", "bfs_forward", "edge_weight_fwd", "edge_weight_bwd", "refine_forward",
-             "refine_backward_feature", "refine_backward_weight"]
+    names = ["gcrf_fwd_bwd", "mst_grid", "bfs_forward", "bfs_grid", "edge_weight_fwd", "edge_weight_bwd", "refine_forward",
+             "refine_backward_feature", "refine_backward_weight", "tree_filter_forward", "tree_filter_backward"]
     records, originals = {n: [] for n in names}, {}
 
     def wrap(name, fn):
@@ -263,7 +293,17 @@ def run_ours(args, wl):
     host = make_inputs(B, Cin, C, H, W, 2022 + rank)     # each rank owns its contiguous shard of the global batch
     pinned = {k: v.pin_memory() for k, v in host.items()}
     data = {k: v.to(dev) for k, v in host.items()}
-    step = GpuStep(C, H, W, world, B)
+    eager_step = GpuStep(C, H, W, world, B)
+    step = eager_step
+    graphed = False
+    if not args.no_graph and world == 1:  # (the 2-scalar all-reduce of N>1 stays eager: NCCL capture is not needed)
+        try:
+            step = GraphedStep(eager_step, data)
+            data = step.static_in
+            graphed = True
+        except Exception as exc:  # capture not possible: say so and time the eager step
+            print(f"[bench] CUDA graph capture failed, timing the eager step: {exc}", file=sys.stderr)
+            step = eager_step
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # 2x the 126 MB L2
 
     def barrier():
@@ -279,6 +319,10 @@ def run_ours(args, wl):
     launches0 = _lib.lib.fedicra_launch_count()
     times = time_steps(lambda: step(data), args.steps, flush_buf)
     launches = _lib.lib.fedicra_launch_count() - launches0
+    if graphed:  # replayed launches are not seen by the host-side counter: count one eager step instead
+        launches0 = _lib.lib.fedicra_launch_count()
+        eager_step(data)
+        launches = (_lib.lib.fedicra_launch_count() - launches0) * args.steps
     barrier()
     total_ms = torch.tensor([sum(times)], dtype=torch.float64, device=dev)
     if world > 1:
@@ -290,8 +334,11 @@ def run_ours(args, wl):
 
     def e2e_step():
         nonlocal grads_host
-        d = {k: v.to(dev, non_blocking=True) for k, v in pinned.items()}
-        loss, grads = step(d)
+        if graphed:
+            step.load(pinned)          # H2D of every input into the graph's static buffers
+            loss, grads = step()
+        else:
+            loss, grads = step({k: v.to(dev, non_blocking=True) for k, v in pinned.items()})
         if grads_host is None:
             grads_host = [torch.empty(g.shape, dtype=g.dtype).pin_memory() for g in grads]
         for h, g in zip(grads_host, grads):
@@ -317,7 +364,7 @@ def run_ours(args, wl):
         return
 
     # ---- attribution + roofline of the dominant kernel group (rank 0, separate instrumented pass)
-    ops_prof = profile_ops(step, data, min(args.steps, 10), flush_buf)
+    ops_prof = profile_ops(eager_step, data, min(args.steps, 10), flush_buf)
     ab = algorithmic_bytes(Cin, C, H, W)
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
@@ -327,9 +374,12 @@ def run_ours(args, wl):
     group_bytes = {  # algorithmic bytes per CALL of each kernel group (all B images of the batch)
         "mst_grid": lambda k: B * (ab["stages"][k]["mst_bfs"] - ab["u"]),
         "bfs_forward": lambda k: B * ab["u"],
+        "bfs_grid": lambda k: B * ab["u"],
         "refine_forward": lambda k: B * ab["stages"][k]["filter_fwd"],
         "refine_backward_feature": lambda k: B * (2 * C + 3) * ab["u"],
         "refine_backward_weight": lambda k: B * (2 * C + 2 * C) * ab["u"],
+        "tree_filter_forward": lambda k: B * ab["stages"][k]["filter_fwd"],
+        "tree_filter_backward": lambda k: B * ab["stages"][k]["filter_bwd"],
         "gcrf_fwd_bwd": lambda k: B * ab["gcrf"],
         "edge_weight_fwd": lambda k: B * (C + 3) * ab["u"],
         "edge_weight_bwd": lambda k: B * (2 * C + 4) * ab["u"],
@@ -373,7 +423,8 @@ def run_ours(args, wl):
         "config": {"workload": args.workload, "describes": desc, "batch_per_gpu": B, "global_batch": B * world, "H": H,
                    "W": W, "classes": C, "image_channels": Cin, "parallelism": f"image-sharded x{world}",
                    "l2": "256 MiB device memset between timed steps (not timed); per-step CUDA events on the current stream",
-                   "collective": "2-scalar all-reduce of the tree-energy normaliser per step" if world > 1 else "none"},
+                   "collective": "2-scalar all-reduce of the tree-energy normaliser per step" if world > 1 else "none",
+                   "cuda_graph": graphed},
         "e2e": {"value": n_images / (e2e_ms * 1e-3), "unit": "images/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": int(launches),
@@ -396,6 +447,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="faz256", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="time the eager step instead of a CUDA-graph replay")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":

@@ -37,7 +37,8 @@ SIGNATURES = {
                                              ctypes.POINTER(GcrfDesc), c_int, c_void_p, c_void_p, c_void_p]),
     "fedicra_mst_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "fedicra_mst_forward": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
-    "fedicra_mst_grid": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "fedicra_mst_grid": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "fedicra_bfs_grid": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "fedicra_bfs_workspace_bytes": (c_size_t, [c_int, c_int]),
     "fedicra_bfs_forward": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                     c_size_t, c_void_p]),

@@ -162,7 +162,167 @@ bfs_kernel(Ws ws, int V, int *__restrict__ sorted_index, int *__restrict__ sorte
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Grid specialisation: the tree is given as the 4-bit adjacency mask fedicra_mst_grid writes.  One warp per image walks
+// the depths; the masks (packed two per byte) and the frontier live in shared memory, children positions come from
+// warp ballots -- no block barrier and no global load on the per-depth dependency chain.  Same outputs, same canonical
+// order (children in direction order up, left, right, down = increasing vertex id).
+constexpr int GNT = 128;     // threads per CTA: one frontier entry per thread and round
+constexpr int SCAP = 4096;   // ring of BFS positions staged in shared memory (power of two)
+constexpr int LCAP = 4096;   // level starts staged in shared memory
+
+// A __syncthreads() that follows global stores waits for them to drain (~0.5 us each on B200), so the walk keeps
+// everything it produces -- vertex, parent position, children -- in a shared-memory ring indexed by BFS position and
+// writes it to global memory in bulk, coalesced, only when the ring is about to wrap (every ~90 depths).
+__global__ void __launch_bounds__(GNT)
+bfs_grid_kernel(const unsigned char *__restrict__ tree_mask, int V, int W, int *__restrict__ sorted_index,
+                int *__restrict__ sorted_parent, int *__restrict__ sorted_child, int *__restrict__ level_start,
+                int *__restrict__ n_levels) {
+    extern __shared__ unsigned s_raw[];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    unsigned *s_v = s_raw;                                    // [SCAP] vertex | (mask bit pointing back to the parent << 28)
+    int *s_p = reinterpret_cast<int *>(s_raw + SCAP);         // [SCAP] parent position
+    int *s_c = reinterpret_cast<int *>(s_raw + 2 * SCAP);     // [SCAP] first child position << 3 | child count
+    unsigned char *s_mask = reinterpret_cast<unsigned char *>(s_raw + 3 * SCAP);  // [ceil(V/2)] two vertices per byte
+    __shared__ int s_wtot[GNT / 32];
+    __shared__ int s_ls[LCAP];  // level starts, flushed at the end (deeper trees write the rest directly)
+    const unsigned char *gm = tree_mask + (size_t)b * V;
+    int *order = sorted_index + (size_t)b * V;
+    int *ppos = sorted_parent + (size_t)b * V;
+    int4 *child = reinterpret_cast<int4 *>(sorted_child) + (size_t)b * V;
+    int *lstart = level_start + (size_t)b * (V + 1);
+
+    for (int k = tid; k < (V + 1) / 2; k += GNT) {
+        const unsigned lo = gm[2 * k], hi = (2 * k + 1 < V) ? gm[2 * k + 1] : 0u;
+        s_mask[k] = (unsigned char)(lo | (hi << 4));
+    }
+    if (tid == 0) {
+        s_v[0] = 0u | (4u << 28);  // the root has no parent: bit 4 is outside the mask
+        s_p[0] = 0;
+        s_ls[0] = 0;
+    }
+    __syncthreads();
+
+    auto flush = [&](int from, int to) {  // ring -> global for positions [from, to), all of them completed
+        for (int pos = from + tid; pos < to; pos += GNT) {
+            const int r = pos & (SCAP - 1), pk = s_c[r], p0 = pk >> 3, cnt = pk & 7;
+            order[pos] = (int)(s_v[r] & 0x0fffffffu);
+            ppos[pos] = s_p[r];
+            child[pos] = make_int4(cnt > 0 ? p0 : 0, cnt > 1 ? p0 + 1 : 0, cnt > 2 ? p0 + 2 : 0, cnt > 3 ? p0 + 3 : 0);
+        }
+    };
+
+    const unsigned lt = (1u << lane) - 1u;
+    int lo = 0, hi = 1, depth = 0, base = 0;  // ring holds positions [base, ...)
+    bool cur_ring = true;                     // entries of the current depth are in the ring (else in global memory)
+    while (true) {
+        const int n = hi - lo;
+        if (!cur_ring) {  // this depth lives in global memory: the ring only holds older, completed positions
+            if (base < lo) flush(base, lo);
+            base = hi;
+            __syncthreads();
+        }
+        // room for this depth's children (at most 3 per vertex, 4 for the root)?
+        bool next_ring = (long long)hi + 3LL * n + 1 - base <= SCAP;
+        if (!next_ring && cur_ring) {
+            flush(base, lo);
+            base = lo;
+            next_ring = (long long)hi + 3LL * n + 1 - base <= SCAP;
+            __syncthreads();
+        }
+        int produced = 0;
+        for (int b0i = 0; b0i < n; b0i += GNT) {
+            const int j = b0i + tid, i = lo + j;
+            int v = 0;
+            unsigned m = 0;
+            if (j < n) {
+                unsigned back;
+                if (cur_ring) {
+                    const unsigned e = s_v[i & (SCAP - 1)];
+                    v = (int)(e & 0x0fffffffu);
+                    back = e >> 28;
+                } else {  // oversized depth, kept in global memory: re-derive the direction of the parent
+                    v = order[i];
+                    const int d = order[ppos[i]] - v;
+                    back = (i == 0) ? 4u : ((d == -W) ? 0u : (d == -1 ? 1u : (d == 1 ? 2u : 3u)));
+                }
+                const unsigned byte = s_mask[v >> 1];
+                m = ((v & 1) ? (byte >> 4) : (byte & 15u)) & ~(1u << back);
+            }
+            const int cnt = __popc(m);
+            const unsigned b0 = __ballot_sync(0xffffffffu, cnt & 1), b1 = __ballot_sync(0xffffffffu, cnt & 2),
+                           b2 = __ballot_sync(0xffffffffu, cnt & 4);
+            if (lane == 0) s_wtot[wid] = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
+            __syncthreads();
+            int woff = 0, ctot = 0;
+#pragma unroll
+            for (int w = 0; w < GNT / 32; ++w) {
+                const int t = s_wtot[w];
+                woff += (w < wid) ? t : 0;
+                ctot += t;
+            }
+            if (j < n) {
+                const int p0 = hi + produced + woff + __popc(b0 & lt) + 2 * __popc(b1 & lt) + 4 * __popc(b2 & lt);
+                int k = 0;
+#pragma unroll
+                for (int d = 0; d < 4; ++d) {  // up, left, right, down = increasing vertex id
+                    if (m & (1u << d)) {
+                        const int c = v + ((d == 0) ? -W : (d == 1 ? -1 : (d == 2 ? 1 : W)));
+                        const int q = p0 + k;
+                        if (next_ring) {
+                            s_v[q & (SCAP - 1)] = (unsigned)c | ((unsigned)(3 - d) << 28);
+                            s_p[q & (SCAP - 1)] = i;
+                        } else {
+                            order[q] = c;
+                            ppos[q] = i;
+                        }
+                        ++k;
+                    }
+                }
+                if (cur_ring)
+                    s_c[i & (SCAP - 1)] = (p0 << 3) | cnt;
+                else
+                    child[i] = make_int4(cnt > 0 ? p0 : 0, cnt > 1 ? p0 + 1 : 0, cnt > 2 ? p0 + 2 : 0, cnt > 3 ? p0 + 3 : 0);
+            }
+            produced += ctot;
+            __syncthreads();
+        }
+        if (produced == 0) break;
+        lo = hi;
+        hi += produced;
+        ++depth;
+        cur_ring = next_ring;
+        if (tid == 0) {
+            if (depth < LCAP) s_ls[depth] = lo; else lstart[depth] = lo;
+        }
+    }
+    if (cur_ring) flush(base, hi);
+    __syncthreads();
+    for (int L = tid; L <= depth && L < LCAP; L += GNT) lstart[L] = s_ls[L];
+    if (tid == 0) {
+        lstart[depth + 1] = hi;
+        n_levels[b] = depth + 1;
+    }
+}
+
 }  // namespace
+
+extern "C" int fedicra_bfs_grid(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index,
+                                int *sorted_parent, int *sorted_child, int *level_start, int *n_levels, void *stream) {
+    FEDICRA_REQUIRE(tree_mask && sorted_index && sorted_parent && sorted_child && level_start && n_levels,
+                    "bfs_grid: null pointer");
+    FEDICRA_REQUIRE(B > 0 && H >= 1 && W >= 1 && (long long)H * W < (1ll << 28), "bfs_grid: bad sizes B=%d H=%d W=%d", B, H, W);
+    FEDICRA_REQUIRE(((uintptr_t)sorted_child & 15) == 0, "bfs_grid: sorted_child must be 16-byte aligned");
+    const int V = H * W;
+    const size_t smem = (size_t)3 * SCAP * sizeof(unsigned) + (size_t)(V + 1) / 2 + 16;  // + 16 KB static
+    FEDICRA_REQUIRE(smem + 17 * 1024 <= 227 * 1024, "bfs_grid: %d x %d does not fit the shared-memory walk (use fedicra_bfs_forward)", H, W);
+    cudaError_t e = cudaFuncSetAttribute(bfs_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fedicra_fail(-2, "bfs_grid: shared memory: %s", cudaGetErrorString(e));
+    bfs_grid_kernel<<<B, GNT, smem, (cudaStream_t)stream>>>(tree_mask, V, W, sorted_index, sorted_parent, sorted_child,
+                                                          level_start, n_levels);
+    FEDICRA_CHECK_LAUNCH("bfs_grid_kernel");
+    return 0;
+}
 
 extern "C" size_t fedicra_bfs_workspace_bytes(int B, int V) {
     if (B <= 0 || V <= 0) return 0;

@@ -219,6 +219,23 @@ mst_compact_kernel(Ws ws, const int *__restrict__ edge_index, int *__restrict__ 
     for (int i = s_base + tid; i < V - 1; i += 1024) out[i] = make_int2(-1, -1);
 }
 
+// 4-bit tree adjacency per vertex: bit 0 = up (v-W), 1 = left (v-1), 2 = right (v+1), 3 = down (v+W).  Gathered from the
+// selected-edge flags, no atomics.
+__global__ void grid_mask_kernel(Ws ws, unsigned char *__restrict__ mask, int H, int W, int E) {
+    const int b = blockIdx.y;
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    const int V = H * W;
+    if (v >= V) return;
+    const unsigned char *f = ws.intree + (size_t)b * E;
+    const int h = v / W, w = v - h * W, nvert = (H - 1) * W;
+    unsigned m = 0;
+    if (h > 0 && f[v - W]) m |= 1u;                                   // vertical edge (h-1,w)-(h,w) has id (h-1)*W+w
+    if (w > 0 && f[nvert + h * (W - 1) + w - 1]) m |= 2u;             // horizontal edge (h,w-1)-(h,w)
+    if (w < W - 1 && f[nvert + h * (W - 1) + w]) m |= 4u;             // horizontal edge (h,w)-(h,w+1)
+    if (h < H - 1 && f[v]) m |= 8u;                                   // vertical edge (h,w)-(h+1,w)
+    mask[(size_t)b * V + v] = (unsigned char)m;
+}
+
 int rounds_for(int V) {
     int r = 0;
     while ((1ll << r) < V) ++r;
@@ -266,9 +283,9 @@ extern "C" int fedicra_mst_forward(const int *edge_index, const float *edge_weig
     return run_mst<false>(edge_index, edge_weight, B, E, V, 0, 0, edge_out, ws, (cudaStream_t)stream);
 }
 
-extern "C" int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out, void *workspace,
-                                size_t workspace_bytes, void *stream) {
-    FEDICRA_REQUIRE(embed && edge_out && workspace, "mst_grid: null pointer");
+extern "C" int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out,
+                                unsigned char *tree_mask, void *workspace, size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(embed && workspace && (edge_out || (long long)H * W <= 1), "mst_grid: null pointer");
     FEDICRA_REQUIRE(B > 0 && B <= 65535 && D > 0 && H >= 1 && W >= 1 && (long long)H * W < (1ll << 30),
                     "mst_grid: bad sizes B=%d D=%d H=%d W=%d", B, D, H, W);
     const int V = H * W, E = 2 * H * W - H - W;
@@ -281,5 +298,14 @@ extern "C" int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, 
         grid_weight_kernel<<<dim3((E + 255) / 256, B), 256, 0, st>>>(embed, ws.wgt, D, H, W, E);
         FEDICRA_CHECK_LAUNCH("grid_weight_kernel");
     }
-    return run_mst<true>(nullptr, ws.wgt, B, E, V, H, W, edge_out, ws, st);
+    if (int rc = run_mst<true>(nullptr, ws.wgt, B, E, V, H, W, edge_out, ws, st)) return rc;
+    if (tree_mask != nullptr) {
+        if (E > 0) {
+            grid_mask_kernel<<<dim3((V + 255) / 256, B), 256, 0, st>>>(ws, tree_mask, H, W, E);
+            FEDICRA_CHECK_LAUNCH("grid_mask_kernel");
+        } else {
+            cudaMemsetAsync(tree_mask, 0, (size_t)B * V, st);
+        }
+    }
+    return 0;
 }

@@ -70,15 +70,35 @@ def mst_forward(edge_index, edge_weight, vertex_count):
     return out
 
 
-def mst_grid(embed):
+def mst_grid(embed, want_mask=False):
+    """MST of the 4-connected grid.  Returns the edge list [B,V-1,2] (and the 4-bit adjacency mask [B,V] when asked)."""
     e = _cuda(embed, torch.float32, "guide_in")
     B, D, H, W = e.shape
     V, E = H * W, 2 * H * W - H - W
     with torch.cuda.device(e.device):
         out = torch.empty(B, V - 1, 2, dtype=torch.int32, device=e.device)
+        mask = torch.empty(B, V, dtype=torch.uint8, device=e.device) if want_mask else None
         ws = workspace("mst", lib.fedicra_mst_workspace_bytes(B, V, E), e.device)
-        check(lib.fedicra_mst_grid(_p(e), B, D, H, W, _p(out), _p(ws), ws.numel(), _stream()), "mst_grid")
-    return out
+        check(lib.fedicra_mst_grid(_p(e), B, D, H, W, _p(out), _p(mask), _p(ws), ws.numel(), _stream()), "mst_grid")
+    return (out, mask) if want_mask else out
+
+
+BFS_GRID_MAX_V = 2 * (227 * 1024 - 4 * 4096 * 4 - 256)
+
+
+def bfs_grid(mask, H, W):
+    """BFS arrays from the adjacency mask of mst_grid (shared-memory walk); same outputs as bfs_forward."""
+    m = _cuda(mask, torch.uint8, "tree_mask")
+    B, V = m.shape
+    dev = m.device
+    with torch.cuda.device(dev):
+        si = torch.empty(B, V, dtype=torch.int32, device=dev)
+        sp = torch.empty(B, V, dtype=torch.int32, device=dev)
+        sc = torch.empty(B, V, 4, dtype=torch.int32, device=dev)
+        ls = torch.empty(B, V + 1, dtype=torch.int32, device=dev)
+        nl = torch.empty(B, dtype=torch.int32, device=dev)
+        check(lib.fedicra_bfs_grid(_p(m), B, H, W, _p(si), _p(sp), _p(sc), _p(ls), _p(nl), _stream()), "bfs_grid")
+    return si, sp, sc, ls, nl
 
 
 # ------------------------------------------------------------------ BFS

@@ -9,7 +9,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .tree_filter import MinimumSpanningTree, TreeFilter2D
+from .tree_filter import MinimumSpanningTree, TreeFilter2D, batched_tree_orders
 
 
 def _prepare(preds, low_feats, unlabeled_ROIs):
@@ -53,13 +53,19 @@ class _TreeLossBase(nn.Module):
         self.mst_layers = MinimumSpanningTree(TreeFilter2D.norm2_distance)
         self.tree_filter_layers = TreeFilter2D(groups=1, sigma=0.02)
 
-    def _low(self, prob, low_feats):
-        tree = self.mst_layers(low_feats)
+    def _trees(self, embeds):
+        """Topology of all the embeddings of this step at once (they do not depend on the filter chain)."""
+        if all(e.is_cuda for e in embeds) and len({(e.shape[0],) + tuple(e.shape[2:]) for e in embeds}) == 1:
+            return batched_tree_orders(embeds)
+        return [self.mst_layers(e) for e in embeds]
+
+    def _low(self, prob, low_feats, tree=None):
+        tree = self.mst_layers(low_feats) if tree is None else tree
         return self.tree_filter_layers(feature_in=prob, embed_in=low_feats, tree=tree)
 
-    def _high(self, feature, high_feats, h, w):
+    def _high(self, feature, high_feats, h, w, tree=None):
         high_feats = _resize(high_feats, h, w)
-        tree = self.mst_layers(high_feats)
+        tree = self.mst_layers(high_feats) if tree is None else tree
         return self.tree_filter_layers(feature_in=feature, embed_in=high_feats, tree=tree, low_tree=False)
 
 
@@ -68,9 +74,11 @@ class TreeEnergyLoss(_TreeLossBase):
         low_feats, roi, n = _prepare(preds, low_feats, unlabeled_ROIs)
         h, w = preds.shape[2:]
         prob = torch.softmax(preds, dim=1)
-        AS = self._low(prob, low_feats)
-        if high_feats is not None:
-            AS = self._high(AS, high_feats, h, w)
+        highs = [] if high_feats is None else [_resize(high_feats, h, w)]
+        trees = self._trees([low_feats] + highs)
+        AS = self._low(prob, low_feats, trees[0])
+        if highs:
+            AS = self._high(AS, highs[0], h, w, trees[1])
         return weight * _masked_l1(roi, prob, AS, n, self.distributed), AS
 
 
@@ -79,8 +87,10 @@ class MScaleAddTreeEnergyLoss(_TreeLossBase):
         low_feats, roi, n = _prepare(preds, low_feats, unlabeled_ROIs)
         h, w = preds.shape[2:]
         prob = torch.softmax(preds, dim=1)
-        AS = self._low(prob, low_feats)
-        outs = [self._high(AS, hf, h, w) for hf in (high_feats_1, high_feats_2, high_feats_3)]
+        highs = [_resize(hf, h, w) for hf in (high_feats_1, high_feats_2, high_feats_3)]
+        trees = self._trees([low_feats] + highs)
+        AS = self._low(prob, low_feats, trees[0])
+        outs = [self._high(AS, hf, h, w, t) for hf, t in zip(highs, trees[1:])]
         loss = _normalise(sum((roi * torch.abs(prob - o)).sum() for o in outs), n, self.distributed)
         return (weight * loss, *outs)
 
@@ -90,9 +100,11 @@ class MScaleRecurveTreeEnergyLoss(_TreeLossBase):
         low_feats, roi, n = _prepare(preds, low_feats, unlabeled_ROIs)
         h, w = preds.shape[2:]
         prob = torch.softmax(preds, dim=1)
-        cur = self._low(prob, low_feats)
+        highs = [_resize(hf, h, w) for hf in (high_feats_1, high_feats_2, high_feats_3)]
+        trees = self._trees([low_feats] + highs)
+        cur = self._low(prob, low_feats, trees[0])
         outs = []
-        for hf in (high_feats_1, high_feats_2, high_feats_3):
-            cur = self._high(cur, hf, h, w)
+        for hf, t in zip(highs, trees[1:]):
+            cur = self._high(cur, hf, h, w, t)
             outs.append(cur)
         return (weight * _masked_l1(roi, prob, cur, n, self.distributed), *outs)

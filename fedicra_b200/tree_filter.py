@@ -21,11 +21,36 @@ class _TreeOrder:
 
     __slots__ = ("si", "sp", "sc", "ls", "nl")
 
-    def __init__(self, tree):
-        self.si, self.sp, self.sc, self.ls, self.nl = ops.bfs_forward(tree)
+    def __init__(self, tree=None, arrays=None):
+        if arrays is not None:
+            self.si, self.sp, self.sc, self.ls, self.nl = arrays
+            return
+        mask, hw = getattr(tree, "_fedicra_mask", None), getattr(tree, "_fedicra_hw", None)
+        if mask is not None and hw[0] * hw[1] <= ops.BFS_GRID_MAX_V:
+            self.si, self.sp, self.sc, self.ls, self.nl = ops.bfs_grid(mask, *hw)
+        else:
+            self.si, self.sp, self.sc, self.ls, self.nl = ops.bfs_forward(tree)
+
+
+def batched_tree_orders(embeds):
+    """MST + BFS of several embeddings of one batch in ONE pass: the embeddings ([B,D_k,H,W], same B/H/W) are stacked
+    along the batch axis (channels zero-padded to the widest: adding 0*0 leaves every fp32 edge weight bit-identical) so
+    that each kernel of the topology stage is launched once for all of them.  Returns one _TreeOrder per embedding."""
+    B, _, H, W = embeds[0].shape
+    D = max(e.shape[1] for e in embeds)
+    with torch.no_grad():
+        stacked = torch.cat([torch.nn.functional.pad(e.detach().float(), (0, 0, 0, 0, 0, D - e.shape[1])) for e in embeds], 0)
+        tree, mask = ops.mst_grid(stacked, want_mask=True)
+        if H * W <= ops.BFS_GRID_MAX_V:
+            arrays = ops.bfs_grid(mask, H, W)
+        else:
+            arrays = ops.bfs_forward(tree)
+    return [_TreeOrder(arrays=tuple(a[k * B:(k + 1) * B] for a in arrays)) for k in range(len(embeds))]
 
 
 def tree_order(tree):
+    if isinstance(tree, _TreeOrder):
+        return tree
     order = getattr(tree, "_fedicra_order", None)
     if order is None:
         order = _TreeOrder(tree)
@@ -61,7 +86,9 @@ class MinimumSpanningTree(nn.Module):
             raise NotImplementedError("fedicra_b200 MinimumSpanningTree: the `label` branch is not implemented")
         with torch.no_grad():
             if _is_norm2(self.distance_func):
-                tree = ops.mst_grid(guide_in.detach().float())  # weights + MST fused, edge list never materialised
+                # weights + MST fused, edge list never materialised; the adjacency mask rides along for the BFS
+                tree, mask = ops.mst_grid(guide_in.detach().float(), want_mask=True)
+                tree._fedicra_mask, tree._fedicra_hw = mask, tuple(guide_in.shape[2:])
             else:
                 index = self._build_matrix_index(guide_in).contiguous()
                 weight = self._build_feature_weight(guide_in).contiguous()

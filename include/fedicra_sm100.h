@@ -85,9 +85,11 @@ int fedicra_mst_forward(const int *edge_index, const float *edge_weight, int B, 
 /* MinimumSpanningTree.forward on the implicit 4-connected grid (LTF/modules/tree_filter.py:15-34, 53-62 fused with
  * mst_forward): edge e<(H-1)*W joins (h,w)-(h+1,w), the rest join (h,w)-(h,w+1); weight = sum_c (delta)^2 + 1 summed in
  * channel order without fused multiply-add, so the fp32 bits equal torch's.
- *   embed [B,D,H,W]  ->  edge_out [B,H*W-1,2] int32 (increasing edge index). */
-int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out, void *workspace,
-                     size_t workspace_bytes, void *stream);
+ *   embed [B,D,H,W]  ->  edge_out [B,H*W-1,2] int32 (increasing edge index);
+ *   tree_mask [B,H*W] uint8 (may be NULL): per vertex, bit 0/1/2/3 set when the tree holds the edge to the pixel
+ *   above / left / right / below -- the compact form fedicra_bfs_grid consumes. */
+int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out, unsigned char *tree_mask,
+                     void *workspace, size_t workspace_bytes, void *stream);
 
 /* ------------------------------------------------------------------------------------------------ BFS ---------- */
 size_t fedicra_bfs_workspace_bytes(int B, int V);
@@ -99,6 +101,11 @@ size_t fedicra_bfs_workspace_bytes(int B, int V);
  * atomics produce). */
 int fedicra_bfs_forward(const int *tree, int B, int V, int *sorted_index, int *sorted_parent, int *sorted_child,
                         int *level_start, int *n_levels, void *workspace, size_t workspace_bytes, void *stream);
+
+/* Same outputs for a tree given as the 4-bit adjacency mask of fedicra_mst_grid (images up to ~440 k pixels; larger
+ * ones are refused, use fedicra_bfs_forward).  No workspace.  One warp per image walks the depths out of shared memory. */
+int fedicra_bfs_grid(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index, int *sorted_parent,
+                     int *sorted_child, int *level_start, int *n_levels, void *stream);
 
 /* ------------------------------------------------------------------------------------------------ tree filter -- */
 /* TreeFilter2D.build_edge_weight (LTF/modules/tree_filter.py:91-108): ew[b,i] = exp(-|e[v(i)] - e[v(par i)]|^2 *

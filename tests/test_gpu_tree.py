@@ -169,3 +169,27 @@ def test_depth_banded_filter_vs_oracle(kind, B, C, D, H, W, inv_sigma):
     assert rel_err(cgw.cpu(), gw) < TOL
     cgf2, none = ops.tree_filter_backward(gout.cuda(), cew, *order, sv, False)
     assert none is None and rel_err(cgf2.cpu(), gf) < TOL
+
+
+@pytest.mark.parametrize("kind,B,D,H,W", [("quant8", 3, 3, 33, 47), ("constant", 1, 1, 40, 24), ("uniform", 2, 2, 1, 17),
+                                          ("uniform", 2, 2, 19, 1), ("uniform", 1, 1, 1, 1), ("quant8", 12, 3, 256, 256),
+                                          ("constant", 1, 1, 300, 300), ("quant8", 2, 3, 512, 512)])
+def test_bfs_from_adjacency_mask_bit_exact(kind, B, D, H, W):
+    """fedicra_mst_grid's 4-bit mask + fedicra_bfs_grid (warp walk in shared memory) == oracle BFS of the oracle MST."""
+    from fedicra_b200 import ops
+    emb = make_image(kind, B, D, H, W, torch.Generator().manual_seed(2))
+    V = H * W
+    tree = losses_cpu.minimum_spanning_tree(emb) if V > 1 else torch.zeros(B, 0, 2, dtype=torch.int32)
+    si, sp, sc = tree_cpu.bfs_forward(tree, 4)
+    gtree, mask = ops.mst_grid(emb.cuda(), want_mask=True)
+    deg = torch.zeros(B, V, dtype=torch.int64)
+    for b in range(B):
+        deg[b] = torch.bincount(tree[b].reshape(-1).long(), minlength=V)
+    pop = sum(((mask.cpu().long() >> k) & 1) for k in range(4))
+    assert torch.equal(pop, deg)
+    gsi, gsp, gsc, gls, gnl = ops.bfs_grid(mask, H, W)
+    assert torch.equal(gsi.cpu(), si) and torch.equal(gsp.cpu(), sp) and torch.equal(gsc.cpu(), sc)
+    for b in range(B):
+        _, _, _, ls = tree_cpu.bfs_levels(tree[b])
+        n = int(gnl[b])
+        assert n == len(ls) - 1 and torch.equal(gls[b, :n + 1].cpu(), ls)
