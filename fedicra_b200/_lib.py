@@ -53,9 +53,11 @@ SIGNATURES = {
                                                                  c_void_p]),
     "fedicra_tree_filter_saved_bytes": (c_size_t, [c_int, c_int, c_int]),
     "fedicra_tree_filter_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
-    "fedicra_tree_filter_forward": (c_int, [c_void_p] * 7 + [c_int, c_int, c_int] + [c_void_p] * 4 + [c_size_t, c_void_p,
+    "fedicra_band_plan_ints": (c_size_t, [c_int]),
+    "fedicra_band_plan": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "fedicra_tree_filter_forward": (c_int, [c_void_p] * 8 + [c_int, c_int, c_int] + [c_void_p] * 4 + [c_size_t, c_void_p,
                                                                                                     c_size_t, c_void_p]),
-    "fedicra_tree_filter_backward": (c_int, [c_void_p] * 7 + [c_int, c_int, c_int] + [c_void_p] * 4 + [c_size_t, c_void_p]),
+    "fedicra_tree_filter_backward": (c_int, [c_void_p] * 8 + [c_int, c_int, c_int] + [c_void_p] * 4 + [c_size_t, c_void_p]),
     "fedicra_ala_update_flat": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_void_p]),
     "fedicra_ala_update_multi": (c_int, [c_void_p] * 8 + [c_int, c_int, c_float, c_void_p]),
     "fedicra_scale_inplace": (c_int, [c_void_p, c_int64, c_float, c_void_p]),

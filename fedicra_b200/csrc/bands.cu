@@ -25,7 +25,6 @@
 namespace {
 
 constexpr int NT = 256;
-constexpr int WCAP = 1024;   // level width kept in shared memory by the two sequential kernels
 constexpr int LSCAP = 512;   // level_start entries of a band cached in shared memory
 
 struct TreeView {
@@ -35,8 +34,12 @@ struct TreeView {
     const int *ls;      // [B,V+1] level_start
     const int *nl;      // [B]
     const float *w;     // [B,V]   edge weight in BFS order
-    int V, nb_target;
+    const int *bands;   // [B,MAXBANDS+2] band plan: [0] = number of bands nb, [1+k] = first level of band k, [1+nb] = n_levels
+    int V;
 };
+
+constexpr int MAXBANDS = 256;
+constexpr int PLAN_STRIDE = MAXBANDS + 2;
 
 struct Consts {  // per (tree, edge weights)
     float *A, *T;                    // [B,V]
@@ -44,12 +47,53 @@ struct Consts {  // per (tree, edge weights)
 };
 
 __device__ __forceinline__ bool band_geom(const TreeView &t, int b, int beta, int &L0, int &L1, int &nb) {
-    const int nl = t.nl[b];
-    const int K = (nl + t.nb_target - 1) / t.nb_target;
-    nb = (nl + K - 1) / K;
-    L0 = beta * K;
-    L1 = min(L0 + K, nl);
-    return beta < nb;
+    const int *plan = t.bands + (size_t)b * PLAN_STRIDE;
+    nb = plan[0];
+    if (beta >= nb) return false;
+    L0 = plan[1 + beta];
+    L1 = plan[2 + beta];
+    return true;
+}
+
+// Band plan: consecutive levels are grouped greedily so that a band holds at most `pmax` positions (it must fit the
+// shared-memory band state) and at most ceil(n_levels / kdiv) levels (the length of the parallel phases); if that needs
+// more than MAXBANDS bands both limits are doubled (oversized bands then run on global memory).  One warp per image.
+__global__ void band_plan_kernel(const int *__restrict__ level_start, const int *__restrict__ n_levels, int V, int pmax,
+                                 int kdiv, int *__restrict__ bands) {
+    const int b = blockIdx.x, lane = threadIdx.x;
+    const int *ls = level_start + (size_t)b * (V + 1);
+    int *plan = bands + (size_t)b * PLAN_STRIDE;
+    const int nl = n_levels[b];
+    int kmax = max(4, (nl + kdiv - 1) / kdiv);
+    while (true) {
+        // The cut points are sequential, so every lane runs the same greedy walk; level ends are fetched 32 at a time
+        // (one coalesced load) and handed over by shuffle.  Only lane 0 writes.
+        int nb = 0, band_first = 0, band_pos0 = 0, prev_end = 0;
+        bool overflow = false;
+        if (lane == 0) plan[1] = 0;
+        for (int base = 0; base < nl && !overflow; base += 32) {
+            const int mine = (base + lane < nl) ? ls[base + lane + 1] : 0;  // end of level base+lane
+            const int kend = min(32, nl - base);
+            for (int k = 0; k < kend; ++k) {
+                const int end = __shfl_sync(0xffffffffu, mine, k), l = base + k;
+                if (l > band_first && ((end - band_pos0) > pmax || (l - band_first) >= kmax)) {  // close before level l
+                    ++nb;
+                    if (nb >= MAXBANDS) { overflow = true; break; }
+                    band_first = l;
+                    band_pos0 = prev_end;
+                    if (lane == 0) plan[1 + nb] = l;
+                }
+                prev_end = end;
+            }
+        }
+        if (!overflow) {
+            ++nb;
+            if (lane == 0) { plan[0] = nb; plan[1 + nb] = nl; }
+            return;
+        }
+        pmax *= 2;
+        kmax *= 2;
+    }
 }
 
 __device__ __forceinline__ int child_count(const int4 &c) { return (c.x > 0) + (c.y > 0) + (c.z > 0) + (c.w > 0); }
@@ -65,6 +109,12 @@ __device__ void consts_body(const TreeView &t, const Consts &k, int b, int L0, i
     int *gE = k.ent + (size_t)b * V, *gN = k.anc + (size_t)b * V;
     float *sA = reinterpret_cast<float *>(smem), *sT = sA + P;
     int *sE = reinterpret_cast<int *>(sT + P), *sN = sE + P;
+    float *sW = reinterpret_cast<float *>(sN + P);
+    int *sP = reinterpret_cast<int *>(sW + P);
+    if (SMEM) {  // parents and weights first, in one coalesced pass, so that the level loop never waits on global memory
+        for (int i = p0 + tid; i < p1; i += NT) { sW[i - p0] = (i == 0) ? 0.f : w[i]; sP[i - p0] = pp[i]; }
+        __syncthreads();
+    }
     auto Aat = [&](int i) -> float & { return SMEM ? sA[i - p0] : gA[i]; };
     auto Tat = [&](int i) -> float & { return SMEM ? sT[i - p0] : gT[i]; };
     auto Eat = [&](int i) -> int & { return SMEM ? sE[i - p0] : gE[i]; };
@@ -73,8 +123,8 @@ __device__ void consts_body(const TreeView &t, const Consts &k, int b, int L0, i
     for (int L = L0; L < L1; ++L) {
         const int nhi = (L + 1 < L1) ? ls[L + 2] : hi;
         for (int i = lo + tid; i < hi; i += NT) {
-            const float wi = (i == 0) ? 0.f : w[i];
-            const int p = pp[i];
+            const float wi = SMEM ? sW[i - p0] : ((i == 0) ? 0.f : w[i]);
+            const int p = SMEM ? sP[i - p0] : pp[i];
             if (L == L0) {
                 Aat(i) = wi; Tat(i) = 1.f; Eat(i) = p; Nat(i) = i;
             } else {
@@ -146,37 +196,52 @@ __device__ __forceinline__ float prologue(const SweepArgs &a, int b, int c, int 
 
 template <int MODE, bool INJECT, bool SMEM>
 __device__ void sweep_body(const TreeView &t, const SweepArgs &a, int b, int beta, int nb, int L0, int L1, int p0, int p1,
-                           int pcap, char *smem) {
+                           int pcap, int slot_shift, char *smem) {
     const int tid = threadIdx.x, V = t.V, NC = a.NC, P = p1 - p0;
     const int *ls = t.ls + (size_t)b * (V + 1);
     const int *vtx = t.vtx + (size_t)b * V, *pp = t.ppos + (size_t)b * V;
     const int4 *child = t.child + (size_t)b * V;
     const float *w = t.w + (size_t)b * V;
     const size_t img = (size_t)b * NC * V;
-    // band state: val[c][i], and (shared-memory mode) copies of w / children / parent
+    // band state: val[c][i], and (shared-memory mode) copies of w / children / parent / vertex
     float *sval = reinterpret_cast<float *>(smem);            // [NC][pcap]
     float *sw = sval + (size_t)NC * pcap;                     // [pcap]
     int *sch = reinterpret_cast<int *>(sw + pcap);            // [pcap] (first child position << 3 | count)
     int *spp = sch + pcap;                                    // [pcap]
-    int *sls = spp + pcap;                                    // [LSCAP+1]
+    int *svx = spp + pcap;                                    // [pcap]
+    int *sls = svx + pcap;                                    // [LSCAP+1]
     float *gval = a.slab + img;
     auto VAL = [&](int c, int i) -> float & { return SMEM ? sval[(size_t)c * pcap + (i - p0)] : gval[(size_t)c * V + i]; };
     auto Wat = [&](int i) -> float { return SMEM ? sw[i - p0] : ((i == 0) ? 0.f : w[i]); };
     const bool ls_cached = SMEM && (L1 - L0) <= LSCAP;
     auto LS = [&](int L) -> int { return ls_cached ? sls[L - L0] : ls[L]; };
+    // thread -> (channel, slot) without a division: SLOTS = NT >> slot_shift... channels beyond NC idle
+    const int SLOTS = 1 << slot_shift, ch_of_thread = tid >> slot_shift, slot = tid & (SLOTS - 1);
+    const bool ch_active = ch_of_thread < NC;
 
-    // ---- stage the band (fully parallel, coalesced in position order; the feature gather is by vertex)
+    // ---- stage the band: topology first (coalesced), then the feature gather with the loads batched four deep
     if (ls_cached)
         for (int L = L0 + tid; L <= L1; L += NT) sls[L - L0] = ls[L];
-    for (int i = p0 + tid; i < p1; i += NT) {
-        const int v = vtx[i];
-        if (SMEM) {
+    if (SMEM) {
+        for (int i = p0 + tid; i < p1; i += NT) {
             const int4 ch = child[i];
             sw[i - p0] = (i == 0) ? 0.f : w[i];
             sch[i - p0] = (ch.x << 3) | child_count(ch);
             spp[i - p0] = pp[i];
+            svx[i - p0] = vtx[i];
         }
-        for (int c = 0; c < NC; ++c) VAL(c, i) = prologue<MODE>(a, b, c, i, v, V);
+        __syncthreads();
+    }
+    for (int c = 0; c < NC; ++c) {
+        int i = p0 + tid;
+        for (; i + 3 * NT < p1; i += 4 * NT) {
+            float v0 = prologue<MODE>(a, b, c, i, SMEM ? svx[i - p0] : vtx[i], V);
+            float v1 = prologue<MODE>(a, b, c, i + NT, SMEM ? svx[i + NT - p0] : vtx[i + NT], V);
+            float v2 = prologue<MODE>(a, b, c, i + 2 * NT, SMEM ? svx[i + 2 * NT - p0] : vtx[i + 2 * NT], V);
+            float v3 = prologue<MODE>(a, b, c, i + 3 * NT, SMEM ? svx[i + 3 * NT - p0] : vtx[i + 3 * NT], V);
+            VAL(c, i) = v0; VAL(c, i + NT) = v1; VAL(c, i + 2 * NT) = v2; VAL(c, i + 3 * NT) = v3;
+        }
+        for (; i < p1; i += NT) VAL(c, i) = prologue<MODE>(a, b, c, i, SMEM ? svx[i - p0] : vtx[i], V);
     }
     __syncthreads();
 
@@ -184,33 +249,34 @@ __device__ void sweep_body(const TreeView &t, const SweepArgs &a, int b, int bet
     for (int L = L1 - 1; L >= L0; --L) {
         const int lo = LS(L), n = LS(L + 1) - lo;
         const bool last = (L == L1 - 1);
-        for (int idx = tid; idx < n * NC; idx += NT) {
-            const int c = idx / n, i = lo + (idx - c * n);
-            float acc = VAL(c, i);
-            if (!last) {
-                int cs, cnt;
-                if (SMEM) {
-                    const int pk = sch[i - p0];
-                    cs = pk >> 3; cnt = pk & 7;
-                } else {
-                    const int4 ch = child[i];
-                    cs = ch.x; cnt = child_count(ch);
+        if (ch_active) {
+            const int c = ch_of_thread;
+            for (int s = slot; s < n; s += SLOTS) {
+                const int i = lo + s;
+                float acc = VAL(c, i);
+                if (!last) {
+                    int cs, cnt;
+                    if (SMEM) {
+                        const int pk = sch[i - p0];
+                        cs = pk >> 3; cnt = pk & 7;
+                    } else {
+                        const int4 ch = child[i];
+                        cs = ch.x; cnt = child_count(ch);
+                    }
+                    for (int k = 0; k < cnt; ++k) acc += VAL(c, cs + k) * Wat(cs + k);
+                } else if (INJECT && beta < nb - 1) {
+                    acc += a.X[img + (size_t)c * V + i];
                 }
-                for (int k = 0; k < cnt; ++k) acc += VAL(c, cs + k) * Wat(cs + k);
-            } else if (INJECT && beta < nb - 1) {
-                acc += a.X[img + (size_t)c * V + i];
+                VAL(c, i) = acc;
             }
-            VAL(c, i) = acc;
         }
         __syncthreads();
     }
 
     if (!INJECT) {  // U1: only the first level's partial sums leave the CTA
-        const int f0 = LS(L0), f1 = LS(L0 + 1);
-        for (int idx = tid; idx < (f1 - f0) * NC; idx += NT) {
-            const int c = idx / (f1 - f0), i = f0 + (idx - c * (f1 - f0));
-            a.upl[img + (size_t)c * V + i] = VAL(c, i);
-        }
+        const int f0 = LS(L0), nf = LS(L0 + 1) - f0;
+        if (ch_active)
+            for (int s = slot; s < nf; s += SLOTS) a.upl[img + (size_t)ch_of_thread * V + f0 + s] = VAL(ch_of_thread, f0 + s);
         return;
     }
 
@@ -220,12 +286,15 @@ __device__ void sweep_body(const TreeView &t, const SweepArgs &a, int b, int bet
     __syncthreads();
     for (int L = L0; L < L1; ++L) {
         const int lo = LS(L), n = LS(L + 1) - lo;
-        for (int idx = tid; idx < n * NC; idx += NT) {
-            const int c = idx / n, i = lo + (idx - c * n);
-            const float wi = Wat(i);
-            float bval = VAL(c, i) * (1.f - wi * wi);
-            if (L > L0) bval += wi * VAL(c, SMEM ? spp[i - p0] : pp[i]);
-            VAL(c, i) = bval;
+        if (ch_active) {
+            const int c = ch_of_thread;
+            for (int s = slot; s < n; s += SLOTS) {
+                const int i = lo + s;
+                const float wi = Wat(i);
+                float bval = VAL(c, i) * (1.f - wi * wi);
+                if (L > L0) bval += wi * VAL(c, SMEM ? spp[i - p0] : pp[i]);
+                VAL(c, i) = bval;
+            }
         }
         __syncthreads();
     }
@@ -234,7 +303,7 @@ __device__ void sweep_body(const TreeView &t, const SweepArgs &a, int b, int bet
 }
 
 template <int MODE, bool INJECT>
-__global__ void __launch_bounds__(NT) sweep_kernel(TreeView t, SweepArgs a, int pcap) {
+__global__ void __launch_bounds__(NT) sweep_kernel(TreeView t, SweepArgs a, int pcap, int slot_shift) {
     extern __shared__ float4 smem4[];
     const int b = blockIdx.y, beta = blockIdx.x;
     int L0, L1, nb;
@@ -242,14 +311,36 @@ __global__ void __launch_bounds__(NT) sweep_kernel(TreeView t, SweepArgs a, int 
     const int *ls = t.ls + (size_t)b * (t.V + 1);
     const int p0 = ls[L0], p1 = ls[L1];
     if (p1 - p0 <= pcap)
-        sweep_body<MODE, INJECT, true>(t, a, b, beta, nb, L0, L1, p0, p1, pcap, reinterpret_cast<char *>(smem4));
+        sweep_body<MODE, INJECT, true>(t, a, b, beta, nb, L0, L1, p0, p1, pcap, slot_shift, reinterpret_cast<char *>(smem4));
     else
-        sweep_body<MODE, INJECT, false>(t, a, b, beta, nb, L0, L1, p0, p1, pcap, reinterpret_cast<char *>(smem4));
+        sweep_body<MODE, INJECT, false>(t, a, b, beta, nb, L0, L1, p0, p1, pcap, slot_shift, reinterpret_cast<char *>(smem4));
 }
 
+// ------------------------------------------------------------------------------------------------ async staging
+__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+constexpr int SCAPW = 512;    // level width staged in shared memory by the two stitch kernels
+
+struct BandEdges {  // per band: first level [f0,f1), last level [e0,e1)
+    int f0, f1, e0, e1;
+};
+
 // ------------------------------------------------------------------------------------------------ U2: stitch upward
+// One CTA per image walks the bands from the deepest to the shallowest.  Everything a band needs (contiguous slices of
+// position-indexed arrays) is fetched with cp.async one band ahead, so the per-band chain only touches shared memory.
 __global__ void __launch_bounds__(NT) stitch_up_kernel(TreeView t, Consts k, SweepArgs a) {
     extern __shared__ float4 smem4[];
+    __shared__ BandEdges s_be[MAXBANDS];
     const int b = blockIdx.x, tid = threadIdx.x, V = t.V, NC = a.NC;
     const int *ls = t.ls + (size_t)b * (V + 1);
     const int4 *child = t.child + (size_t)b * V;
@@ -259,46 +350,82 @@ __global__ void __launch_bounds__(NT) stitch_up_kernel(TreeView t, Consts k, Swe
     const size_t img = (size_t)b * NC * V;
     const float *upl = a.upl + img;
     float *Xg = a.X + img, *upFg = a.slab + img;
-    float *sX[2] = {reinterpret_cast<float *>(smem4), reinterpret_cast<float *>(smem4) + (size_t)NC * WCAP};
-    float *sF = sX[1] + (size_t)NC * WCAP;
-    int L0, L1, nb;
-    band_geom(t, b, 0, L0, L1, nb);
-    const int nl = t.nl[b], K = (nl + t.nb_target - 1) / t.nb_target;
+    const int *plan = t.bands + (size_t)b * PLAN_STRIDE;
+    const int nb = plan[0];
+    for (int beta = tid; beta < nb; beta += NT) {
+        const int L0 = plan[1 + beta], L1 = plan[2 + beta];
+        s_be[beta] = BandEdges{ls[L0], ls[L0 + 1], ls[L1 - 1], ls[L1]};
+    }
+    // shared memory: 2 staging buffers {upl[NC], w, rs, re, T, child(int4)} + X[2][NC] + upF[NC], SCAPW entries each
+    float *base = reinterpret_cast<float *>(smem4);
+    const int stage_words = (NC + 8) * SCAPW;
+    float *sX[2] = {base + 2 * stage_words, base + 2 * stage_words + NC * SCAPW};
+    float *sF = base + 2 * stage_words + 2 * NC * SCAPW;
+    __syncthreads();
+
+    auto fits = [&](int beta) {
+        const BandEdges be = s_be[beta];
+        const int nq = be.f0 - s_be[beta - 1].e0;  // last level of the band above = [e0(beta-1), f0(beta))
+        return (be.f1 - be.f0) <= SCAPW && (be.e1 - be.e0) <= SCAPW && nq <= SCAPW;
+    };
+    auto prefetch = [&](int beta) {
+        if (beta >= 1 && fits(beta)) {
+            const BandEdges be = s_be[beta];
+            const int q0 = s_be[beta - 1].e0, nf = be.f1 - be.f0, ne = be.e1 - be.e0, nq = be.f0 - q0;
+            float *st = base + (beta & 1) * stage_words;
+            for (int i = tid; i < nf; i += NT) {
+                for (int c = 0; c < NC; ++c) cp_async4(st + c * SCAPW + i, upl + (size_t)c * V + be.f0 + i);
+                cp_async4(st + NC * SCAPW + i, w + be.f0 + i);
+                cp_async4(st + (NC + 1) * SCAPW + i, rs + be.f0 + i);
+                cp_async4(st + (NC + 2) * SCAPW + i, re + be.f0 + i);
+            }
+            for (int i = tid; i < ne; i += NT) cp_async4(st + (NC + 3) * SCAPW + i, T + be.e0 + i);
+            for (int i = tid; i < nq; i += NT) cp_async16(st + (NC + 4) * SCAPW + 4 * i, child + q0 + i);
+        }
+        cp_async_commit();
+    };
+
     int cur = 0;
-    int e0 = 0, e1 = 0;  // last level of band beta (whose X is held in sX[cur] when it fits)
+    prefetch(nb - 1);
     for (int beta = nb - 1; beta >= 1; --beta) {
-        L0 = beta * K;
-        L1 = min(L0 + K, nl);
-        const int f0 = ls[L0], f1 = ls[L0 + 1], nf = f1 - f0;
-        e0 = ls[L1 - 1];
-        e1 = ls[L1];
-        const bool x_sm = (e1 - e0) <= WCAP, f_sm = nf <= WCAP;
+        prefetch(beta - 1);       // (an empty group for beta - 1 == 0)
+        cp_async_wait<1>();       // band beta's operands have landed
+        __syncthreads();
+        const BandEdges be = s_be[beta];
+        const int f0 = be.f0, nf = be.f1 - be.f0, e0 = be.e0, ne = be.e1 - be.e0;
+        const int q0 = s_be[beta - 1].e0, nq = f0 - q0;
+        const bool sm = fits(beta);
+        const float *st = base + (beta & 1) * stage_words;
+        const int *st_rs = reinterpret_cast<const int *>(st + (NC + 1) * SCAPW);
+        const int *st_re = reinterpret_cast<const int *>(st + (NC + 2) * SCAPW);
+        const int4 *st_ch = reinterpret_cast<const int4 *>(st + (NC + 4) * SCAPW);
         // (a) exact up at the band's first level
         for (int idx = tid; idx < nf * NC; idx += NT) {
-            const int c = idx / nf, tpos = f0 + (idx - c * nf);
-            float acc = upl[(size_t)c * V + tpos];
+            const int c = idx / nf, tl = idx - c * nf, tpos = f0 + tl;
+            float acc = sm ? st[c * SCAPW + tl] : upl[(size_t)c * V + tpos];
             if (beta < nb - 1) {
-                const int j1 = re[tpos];
-                for (int j = rs[tpos]; j < j1; ++j)
-                    acc += T[j] * (x_sm ? sX[cur][(size_t)c * WCAP + (j - e0)] : Xg[(size_t)c * V + j]);
+                const int j0 = sm ? st_rs[tl] : rs[tpos], j1 = sm ? st_re[tl] : re[tpos];
+                for (int j = j0; j < j1; ++j) {
+                    const float tj = sm ? st[(NC + 3) * SCAPW + (j - e0)] : T[j];
+                    acc += tj * (ne <= SCAPW ? sX[cur][c * SCAPW + (j - e0)] : Xg[(size_t)c * V + j]);
+                }
             }
-            if (f_sm) sF[(size_t)c * WCAP + (tpos - f0)] = acc; else upFg[(size_t)c * V + tpos] = acc;
+            if (nf <= SCAPW) sF[c * SCAPW + tl] = acc; else upFg[(size_t)c * V + tpos] = acc;
         }
         __syncthreads();
         // (b) what enters the last level of the band above: X[j'] = sum over its children (all in this band's first level)
-        const int q0 = ls[L0 - 1], nq = f0 - q0;
-        const bool q_sm = nq <= WCAP;
         for (int idx = tid; idx < nq * NC; idx += NT) {
-            const int c = idx / nq, j = q0 + (idx - c * nq);
-            const int4 ch = child[j];
+            const int c = idx / nq, jl = idx - c * nq, j = q0 + jl;
+            const int4 ch = sm ? st_ch[jl] : child[j];
             const int cnt = child_count(ch);
             float acc = 0.f;
             for (int kk = 0; kk < cnt; ++kk) {
                 const int tp = ch.x + kk;
-                acc += w[tp] * (f_sm ? sF[(size_t)c * WCAP + (tp - f0)] : upFg[(size_t)c * V + tp]);
+                const float wt = sm ? st[NC * SCAPW + (tp - f0)] : w[tp];
+                acc += wt * (nf <= SCAPW ? sF[c * SCAPW + (tp - f0)] : upFg[(size_t)c * V + tp]);
             }
             Xg[(size_t)c * V + j] = acc;
-            if (q_sm) sX[cur ^ 1][(size_t)c * WCAP + (j - q0)] = acc;
+            if (nq <= SCAPW) sX[cur ^ 1][c * SCAPW + jl] = acc;
         }
         __syncthreads();
         cur ^= 1;
@@ -308,6 +435,8 @@ __global__ void __launch_bounds__(NT) stitch_up_kernel(TreeView t, Consts k, Swe
 // ------------------------------------------------------------------------------------------------ D2: stitch downward
 __global__ void __launch_bounds__(NT) stitch_down_kernel(TreeView t, Consts k, SweepArgs a, float *outE) {
     extern __shared__ float4 smem4[];
+    __shared__ int s_e0[MAXBANDS + 1];  // first position of every band's last level; entry nb = end
+    __shared__ int s_e1[MAXBANDS];
     const int b = blockIdx.x, tid = threadIdx.x, V = t.V, NC = a.NC;
     const int *ls = t.ls + (size_t)b * (V + 1);
     const float *A = k.A + (size_t)b * V;
@@ -315,22 +444,54 @@ __global__ void __launch_bounds__(NT) stitch_down_kernel(TreeView t, Consts k, S
     const size_t img = (size_t)b * NC * V;
     const float *Bv = a.Bv + img;
     float *og = outE + img;
-    float *sO[2] = {reinterpret_cast<float *>(smem4), reinterpret_cast<float *>(smem4) + (size_t)NC * WCAP};
-    const int nl = t.nl[b], K = (nl + t.nb_target - 1) / t.nb_target, nb = (nl + K - 1) / K;
+    const int *plan = t.bands + (size_t)b * PLAN_STRIDE;
+    const int nb = plan[0];
+    for (int beta = tid; beta < nb; beta += NT) {
+        const int L1 = plan[2 + beta];
+        s_e0[beta] = ls[L1 - 1];
+        s_e1[beta] = ls[L1];
+    }
+    // shared memory: 2 staging buffers {Bv[NC], A, ent} + out[2][NC], SCAPW entries each
+    float *base = reinterpret_cast<float *>(smem4);
+    const int stage_words = (NC + 2) * SCAPW;
+    float *sO[2] = {base + 2 * stage_words, base + 2 * stage_words + NC * SCAPW};
+    __syncthreads();
+
+    auto prefetch = [&](int beta) {
+        if (beta < nb) {
+            const int e0 = s_e0[beta], n = s_e1[beta] - e0;
+            if (n <= SCAPW) {
+                float *st = base + (beta & 1) * stage_words;
+                for (int i = tid; i < n; i += NT) {
+                    for (int c = 0; c < NC; ++c) cp_async4(st + c * SCAPW + i, Bv + (size_t)c * V + e0 + i);
+                    cp_async4(st + NC * SCAPW + i, A + e0 + i);
+                    cp_async4(st + (NC + 1) * SCAPW + i, ent + e0 + i);
+                }
+            }
+        }
+        cp_async_commit();
+    };
+
     int cur = 0, pe0 = 0, pn = 0;
+    prefetch(0);
     for (int beta = 0; beta < nb; ++beta) {
-        const int L1 = min(beta * K + K, nl);
-        const int e0 = ls[L1 - 1], n = ls[L1] - e0;
-        const bool prev_sm = pn <= WCAP, out_sm = n <= WCAP;
+        prefetch(beta + 1);
+        cp_async_wait<1>();
+        __syncthreads();
+        const int e0 = s_e0[beta], n = s_e1[beta] - e0;
+        const bool sm = n <= SCAPW;
+        const float *st = base + (beta & 1) * stage_words;
+        const int *st_ent = reinterpret_cast<const int *>(st + (NC + 1) * SCAPW);
         for (int idx = tid; idx < n * NC; idx += NT) {
-            const int c = idx / n, j = e0 + (idx - c * n);
-            float o = Bv[(size_t)c * V + j];
+            const int c = idx / n, jl = idx - c * n, j = e0 + jl;
+            float o = sm ? st[c * SCAPW + jl] : Bv[(size_t)c * V + j];
             if (beta > 0) {
-                const int en = ent[j];
-                o += A[j] * (prev_sm ? sO[cur][(size_t)c * WCAP + (en - pe0)] : og[(size_t)c * V + en]);
+                const int en = sm ? st_ent[jl] : ent[j];
+                const float aj = sm ? st[NC * SCAPW + jl] : A[j];
+                o += aj * (pn <= SCAPW ? sO[cur][c * SCAPW + (en - pe0)] : og[(size_t)c * V + en]);
             }
             og[(size_t)c * V + j] = o;
-            if (out_sm) sO[cur ^ 1][(size_t)c * WCAP + (j - e0)] = o;
+            if (sm) sO[cur ^ 1][c * SCAPW + jl] = o;
         }
         __syncthreads();
         cur ^= 1;
@@ -409,17 +570,13 @@ __global__ void zero_root_weight_kernel(float *w, int V, int B) {
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-int pick_nb(int V) {
-    int nb = (int)(sqrtf((float)V) * 0.1875f + 0.5f);
-    return nb < 16 ? 16 : (nb > 256 ? 256 : nb);
-}
-
-int pick_pcap(int V, int nb, int bytes_per_pos, size_t budget) {
-    long long want = (long long)V * 5 / (2LL * nb);  // 2.5 x the average band
-    want = (want + 255) / 256 * 256;
-    if (want < 512) want = 512;
-    const long long fit = (long long)(budget / bytes_per_pos) / 256 * 256;
-    return (int)(want < fit ? want : fit);
+// Band limits (host side, functions of the image size only).
+int plan_pmax(int V) { return V <= (1 << 17) ? 2048 : 3072; }   // positions per band (shared-memory band state)
+constexpr int PLAN_KDIV = 32;                                     // a band holds at most ceil(n_levels / 32) levels
+int plan_grid(int V) {                                            // upper bound of the number of bands
+    const int pm = plan_pmax(V);
+    long long g = 2LL * ((V + pm - 1) / pm) + PLAN_KDIV + 2;
+    return (int)(g > MAXBANDS ? MAXBANDS : g);
 }
 
 struct Layout {
@@ -454,18 +611,22 @@ int set_smem(Kern kern, size_t bytes, const char *name) {
 
 template <int MODE>
 int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int B, cudaStream_t st) {
-    const int V = t.V, nb = t.nb_target, NC = a.NC;
-    const int per_pos = (NC + 3) * 4;
-    const int pcap = pick_pcap(V, nb, per_pos, 160 * 1024);
+    const int V = t.V, nb = plan_grid(V), NC = a.NC;
+    const int per_pos = (NC + 4) * 4;
+    int ncp = 1, slot_shift = 8;  // NT = 256 threads = ncp channel groups x (256 >> log2 ncp) slots
+    while (ncp < NC) { ncp <<= 1; --slot_shift; }
+    if (NC > NT) return fedicra_fail(-1, "tree filter: %d channels per sweep exceed %d", NC, NT);
+    const int pcap = plan_pmax(V);
     const size_t smem = (size_t)pcap * per_pos + (LSCAP + 1) * sizeof(int) + 16;
     if (set_smem(sweep_kernel<MODE, false>, smem, "sweep_kernel") || set_smem(sweep_kernel<MODE, true>, smem, "sweep_kernel")) return -2;
-    const size_t smem_u2 = (size_t)3 * NC * WCAP * sizeof(float), smem_d2 = (size_t)2 * NC * WCAP * sizeof(float);
+    const size_t smem_u2 = (size_t)(2 * (NC + 8) + 3 * NC) * SCAPW * sizeof(float) + 16;
+    const size_t smem_d2 = (size_t)(2 * (NC + 2) + 2 * NC) * SCAPW * sizeof(float) + 16;
     if (set_smem(stitch_up_kernel, smem_u2, "stitch_up_kernel") || set_smem(stitch_down_kernel, smem_d2, "stitch_down_kernel")) return -2;
-    sweep_kernel<MODE, false><<<dim3(nb, B), NT, smem, st>>>(t, a, pcap);
+    sweep_kernel<MODE, false><<<dim3(nb, B), NT, smem, st>>>(t, a, pcap, slot_shift);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U1>");
     stitch_up_kernel<<<B, NT, smem_u2, st>>>(t, k, a);
     FEDICRA_CHECK_LAUNCH("stitch_up_kernel");
-    sweep_kernel<MODE, true><<<dim3(nb, B), NT, smem, st>>>(t, a, pcap);
+    sweep_kernel<MODE, true><<<dim3(nb, B), NT, smem, st>>>(t, a, pcap, slot_shift);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U3D1>");
     stitch_down_kernel<<<B, NT, smem_d2, st>>>(t, k, a, outE);
     FEDICRA_CHECK_LAUNCH("stitch_down_kernel");
@@ -473,6 +634,16 @@ int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int
 }
 
 }  // namespace
+
+extern "C" size_t fedicra_band_plan_ints(int B) { return B > 0 ? (size_t)B * PLAN_STRIDE : 0; }
+
+extern "C" int fedicra_band_plan(const int *level_start, const int *n_levels, int B, int V, int *bands, void *stream) {
+    FEDICRA_REQUIRE(level_start && n_levels && bands, "band_plan: null pointer");
+    FEDICRA_REQUIRE(B > 0 && V > 0, "band_plan: bad sizes B=%d V=%d", B, V);
+    band_plan_kernel<<<B, 32, 0, (cudaStream_t)stream>>>(level_start, n_levels, V, plan_pmax(V), PLAN_KDIV, bands);
+    FEDICRA_CHECK_LAUNCH("band_plan_kernel");
+    return 0;
+}
 
 extern "C" size_t fedicra_tree_filter_saved_bytes(int B, int C, int V) {
     if (B <= 0 || C <= 0 || V <= 0) return 0;
@@ -486,17 +657,18 @@ extern "C" size_t fedicra_tree_filter_workspace_bytes(int B, int C, int V) {
 
 extern "C" int fedicra_tree_filter_forward(const float *feature_in, float *edge_weight, const int *sorted_index,
                                            const int *sorted_parent, const int *sorted_child, const int *level_start,
-                                           const int *n_levels, int B, int C, int V, float *feature_out,
-                                           float *feature_aggr, float *weight_sum, void *saved, size_t saved_bytes,
+                                           const int *n_levels, const int *bands, int B, int C, int V,
+                                           float *feature_out, float *feature_aggr, float *weight_sum, void *saved,
+                                           size_t saved_bytes,
                                            void *workspace, size_t workspace_bytes, void *stream) {
     FEDICRA_REQUIRE(feature_in && edge_weight && sorted_index && sorted_parent && sorted_child && level_start &&
-                        n_levels && feature_out && saved && workspace, "tree_filter_forward: null pointer");
+                        n_levels && bands && feature_out && saved && workspace, "tree_filter_forward: null pointer");
     FEDICRA_REQUIRE(B > 0 && B <= 65535 && C > 0 && C <= 64 && V > 0, "tree_filter_forward: bad sizes B=%d C=%d V=%d", B, C, V);
     FEDICRA_REQUIRE(saved_bytes >= fedicra_tree_filter_saved_bytes(B, C, V), "tree_filter_forward: `saved` too small");
     FEDICRA_REQUIRE(workspace_bytes >= fedicra_tree_filter_workspace_bytes(B, C, V), "tree_filter_forward: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
-    const int nb = pick_nb(V), NC = C + 1;
-    TreeView t{sorted_index, sorted_parent, reinterpret_cast<const int4 *>(sorted_child), level_start, n_levels, edge_weight, V, nb};
+    const int nb = plan_grid(V), NC = C + 1;
+    TreeView t{sorted_index, sorted_parent, reinterpret_cast<const int4 *>(sorted_child), level_start, n_levels, edge_weight, bands, V};
     float *fup, *fpos;
     Consts k = consts_view(saved, B, C, V, &fup, &fpos);
     const size_t n = (size_t)B * V * (2 * C > NC ? 2 * C : NC);
@@ -506,8 +678,8 @@ extern "C" int fedicra_tree_filter_forward(const float *feature_in, float *edge_
 
     zero_root_weight_kernel<<<(B + 127) / 128, 128, 0, st>>>(edge_weight, V, B);
     FEDICRA_CHECK_LAUNCH("zero_root_weight_kernel");
-    const int pcap_c = pick_pcap(V, nb, 16, 96 * 1024);
-    const size_t smem_c = (size_t)pcap_c * 16 + 16;
+    const int pcap_c = plan_pmax(V);
+    const size_t smem_c = (size_t)pcap_c * 24 + 16;
     if (set_smem(consts_kernel, smem_c, "consts_kernel")) return -2;
     consts_kernel<<<dim3(nb, B), NT, smem_c, st>>>(t, k, pcap_c);
     FEDICRA_CHECK_LAUNCH("consts_kernel");
@@ -519,16 +691,16 @@ extern "C" int fedicra_tree_filter_forward(const float *feature_in, float *edge_
 
 extern "C" int fedicra_tree_filter_backward(const float *grad_out, const float *edge_weight, const int *sorted_index,
                                             const int *sorted_parent, const int *sorted_child, const int *level_start,
-                                            const int *n_levels, int B, int C, int V, const void *saved,
-                                            float *grad_feature, float *grad_weight, void *workspace,
+                                            const int *n_levels, const int *bands, int B, int C, int V,
+                                            const void *saved, float *grad_feature, float *grad_weight, void *workspace,
                                             size_t workspace_bytes, void *stream) {
     FEDICRA_REQUIRE(grad_out && edge_weight && sorted_index && sorted_parent && sorted_child && level_start && n_levels &&
-                        saved && grad_feature && workspace, "tree_filter_backward: null pointer");
+                        bands && saved && grad_feature && workspace, "tree_filter_backward: null pointer");
     FEDICRA_REQUIRE(B > 0 && B <= 65535 && C > 0 && C <= 64 && V > 0, "tree_filter_backward: bad sizes B=%d C=%d V=%d", B, C, V);
     FEDICRA_REQUIRE(workspace_bytes >= fedicra_tree_filter_workspace_bytes(B, C, V), "tree_filter_backward: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
-    const int nb = pick_nb(V), NC = grad_weight ? 2 * C : C;
-    TreeView t{sorted_index, sorted_parent, reinterpret_cast<const int4 *>(sorted_child), level_start, n_levels, edge_weight, V, nb};
+    const int NC = grad_weight ? 2 * C : C;
+    TreeView t{sorted_index, sorted_parent, reinterpret_cast<const int4 *>(sorted_child), level_start, n_levels, edge_weight, bands, V};
     float *fup, *fpos;
     Consts k = consts_view(const_cast<void *>(saved), B, C, V, &fup, &fpos);
     const size_t n = (size_t)B * V * (2 * C > C + 1 ? 2 * C : C + 1);

@@ -190,7 +190,16 @@ def refine_backward_weight(edge_weight, si, sp, sc, ls, nl, feature_out, feature
     return out
 
 
-def tree_filter_forward(feature_in, edge_weight, si, sp, sc, ls, nl, want_aggr=False):
+def band_plan(ls, nl):
+    """Band plan of a batch of trees from their BFS level structure (one per topology, shared by all filter calls)."""
+    B, V = ls.shape[0], ls.shape[1] - 1
+    with torch.cuda.device(ls.device):
+        bands = torch.empty(lib.fedicra_band_plan_ints(B), dtype=torch.int32, device=ls.device)
+        check(lib.fedicra_band_plan(_p(ls), _p(nl), B, V, _p(bands), _stream()), "band_plan")
+    return bands
+
+
+def tree_filter_forward(feature_in, edge_weight, si, sp, sc, ls, nl, bands, want_aggr=False):
     """Depth-banded filter forward.  Returns (feature_out, saved[, feature_aggr, weight_sum])."""
     f = _cuda(feature_in, torch.float32, "feature_in")
     if not (edge_weight.is_cuda and edge_weight.dtype == torch.float32 and edge_weight.is_contiguous()):
@@ -203,13 +212,13 @@ def tree_filter_forward(feature_in, edge_weight, si, sp, sc, ls, nl, want_aggr=F
         aggr = torch.empty_like(f) if want_aggr else None
         wsum = torch.empty(B, V, dtype=torch.float32, device=dev) if want_aggr else None
         ws = workspace("tree_filter", lib.fedicra_tree_filter_workspace_bytes(B, C, V), dev)
-        check(lib.fedicra_tree_filter_forward(_p(f), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(ls), _p(nl), B, C, V,
+        check(lib.fedicra_tree_filter_forward(_p(f), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(ls), _p(nl), _p(bands), B, C, V,
                                               _p(out), _p(aggr), _p(wsum), _p(saved), saved.numel(), _p(ws), ws.numel(),
                                               _stream()), "tree_filter_forward")
     return (out, saved, aggr, wsum) if want_aggr else (out, saved)
 
 
-def tree_filter_backward(grad_out, edge_weight, si, sp, sc, ls, nl, saved, want_weight_grad):
+def tree_filter_backward(grad_out, edge_weight, si, sp, sc, ls, nl, bands, saved, want_weight_grad):
     """Depth-banded filter backward.  Returns (grad_feature, grad_weight or None)."""
     g = _cuda(grad_out, torch.float32, "grad_output")
     B, C, V = g.shape
@@ -218,7 +227,7 @@ def tree_filter_backward(grad_out, edge_weight, si, sp, sc, ls, nl, saved, want_
         gf = torch.empty_like(g)
         gw = torch.empty(B, V, dtype=torch.float32, device=dev) if want_weight_grad else None
         ws = workspace("tree_filter", lib.fedicra_tree_filter_workspace_bytes(B, C, V), dev)
-        check(lib.fedicra_tree_filter_backward(_p(g), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(ls), _p(nl), B, C, V,
+        check(lib.fedicra_tree_filter_backward(_p(g), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(ls), _p(nl), _p(bands), B, C, V,
                                                _p(saved), _p(gf), _p(gw), _p(ws), ws.numel(), _stream()),
               "tree_filter_backward")
     return gf, gw

@@ -19,17 +19,18 @@ def _is_norm2(fn):
 class _TreeOrder:
     """BFS arrays of a batch of trees (sorted_index, sorted_parent, sorted_child, level_start, n_levels)."""
 
-    __slots__ = ("si", "sp", "sc", "ls", "nl")
+    __slots__ = ("si", "sp", "sc", "ls", "nl", "bands")
 
     def __init__(self, tree=None, arrays=None):
         if arrays is not None:
-            self.si, self.sp, self.sc, self.ls, self.nl = arrays
+            self.si, self.sp, self.sc, self.ls, self.nl, self.bands = arrays
             return
         mask, hw = getattr(tree, "_fedicra_mask", None), getattr(tree, "_fedicra_hw", None)
         if mask is not None and hw[0] * hw[1] <= ops.BFS_GRID_MAX_V:
             self.si, self.sp, self.sc, self.ls, self.nl = ops.bfs_grid(mask, *hw)
         else:
             self.si, self.sp, self.sc, self.ls, self.nl = ops.bfs_forward(tree)
+        self.bands = ops.band_plan(self.ls, self.nl)
 
 
 def batched_tree_orders(embeds):
@@ -45,7 +46,8 @@ def batched_tree_orders(embeds):
             arrays = ops.bfs_grid(mask, H, W)
         else:
             arrays = ops.bfs_forward(tree)
-    return [_TreeOrder(arrays=tuple(a[k * B:(k + 1) * B] for a in arrays)) for k in range(len(embeds))]
+        bands = ops.band_plan(arrays[3], arrays[4]).view(len(embeds) * B, -1)
+    return [_TreeOrder(arrays=tuple(a[k * B:(k + 1) * B] for a in (*arrays, bands))) for k in range(len(embeds))]
 
 
 def tree_order(tree):
@@ -119,7 +121,8 @@ class _Refine(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, feature_in, edge_weight, order, low_tree):
-        out, saved = ops.tree_filter_forward(feature_in, edge_weight, order.si, order.sp, order.sc, order.ls, order.nl)
+        out, saved = ops.tree_filter_forward(feature_in, edge_weight, order.si, order.sp, order.sc, order.ls, order.nl,
+                                             order.bands)
         ctx.order, ctx.low_tree = order, low_tree
         ctx.save_for_backward(edge_weight, saved)
         return out
@@ -130,7 +133,7 @@ class _Refine(torch.autograd.Function):
         o = ctx.order
         want_w = (not ctx.low_tree) and ctx.needs_input_grad[1]
         grad_feature, grad_weight = ops.tree_filter_backward(grad_out.contiguous(), edge_weight, o.si, o.sp, o.sc, o.ls,
-                                                             o.nl, saved, want_w)
+                                                             o.nl, o.bands, saved, want_w)
         return grad_feature, grad_weight, None, None
 
 

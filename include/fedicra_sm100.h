@@ -149,18 +149,23 @@ int fedicra_refine_backward_weight(const float *edge_weight, const int *sorted_i
  *   forward : refine_forward (refine.cu:201-249).  feature_aggr / weight_sum (vertex order) may be NULL.  `saved`
  *             (fedicra_tree_filter_saved_bytes) carries what backward needs; edge_weight[:,0] is set to 0.
  *   backward: refine_backward_feature + refine_backward_weight (refine.cu:251-370) in one pass; grad_weight [B,V] (BFS
- *             order) may be NULL (low-level tree: no weight gradient, LTF/functions/refine.py:32-33). */
+ *             order) may be NULL (low-level tree: no weight gradient, LTF/functions/refine.py:32-33).
+ *   bands   : the band plan of the trees, fedicra_band_plan_ints(B) ints written by fedicra_band_plan from the BFS level
+ *             structure (consecutive depths grouped so that a band fits shared memory); one plan per topology. */
+size_t fedicra_band_plan_ints(int B);
+int fedicra_band_plan(const int *level_start, const int *n_levels, int B, int V, int *bands, void *stream);
 size_t fedicra_tree_filter_saved_bytes(int B, int C, int V);
 size_t fedicra_tree_filter_workspace_bytes(int B, int C, int V);
 int fedicra_tree_filter_forward(const float *feature_in, float *edge_weight, const int *sorted_index,
                                 const int *sorted_parent, const int *sorted_child, const int *level_start,
-                                const int *n_levels, int B, int C, int V, float *feature_out, float *feature_aggr,
-                                float *weight_sum, void *saved, size_t saved_bytes, void *workspace,
-                                size_t workspace_bytes, void *stream);
+                                const int *n_levels, const int *bands, int B, int C, int V, float *feature_out,
+                                float *feature_aggr, float *weight_sum, void *saved, size_t saved_bytes,
+                                void *workspace, size_t workspace_bytes, void *stream);
 int fedicra_tree_filter_backward(const float *grad_out, const float *edge_weight, const int *sorted_index,
                                  const int *sorted_parent, const int *sorted_child, const int *level_start,
-                                 const int *n_levels, int B, int C, int V, const void *saved, float *grad_feature,
-                                 float *grad_weight, void *workspace, size_t workspace_bytes, void *stream);
+                                 const int *n_levels, const int *bands, int B, int C, int V, const void *saved,
+                                 float *grad_feature, float *grad_weight, void *workspace, size_t workspace_bytes,
+                                 void *stream);
 
 /* ------------------------------------------------------------------------------------------------ aggregation -- */
 /* Adaptive local aggregation, element-wise part of MyModel.set_weights (flower_common.py:590-602) over one flat

@@ -159,15 +159,20 @@ def test_depth_banded_filter_vs_oracle(kind, B, C, D, H, W, inv_sigma):
 
     order = ops.bfs_forward(tree.cuda())
     cew = ops.edge_weight_fwd(emb.reshape(B, D, V).cuda(), order[0], order[1], inv_sigma)
-    out, sv, aggr, wsum = ops.tree_filter_forward(feat.cuda(), cew, *order, want_aggr=True)
+    bands = ops.band_plan(order[3], order[4])
+    plan = bands.view(B, -1).cpu()
+    for b in range(B):                                  # the plan partitions the depths into non-empty bands
+        nb = int(plan[b, 0]); cuts = plan[b, 1:nb + 2]
+        assert cuts[0] == 0 and cuts[-1] == int(order[4][b]) and bool((cuts[1:] > cuts[:-1]).all())
+    out, sv, aggr, wsum = ops.tree_filter_forward(feat.cuda(), cew, *order, bands, want_aggr=True)
     assert float(cew[:, 0].abs().max()) == 0.0
     assert rel_err(out.cpu(), saved[0]) < TOL
     assert rel_err(aggr.cpu(), saved[1]) < TOL
     assert rel_err(wsum.cpu(), saved[3]) < TOL
-    cgf, cgw = ops.tree_filter_backward(gout.cuda(), cew, *order, sv, True)
+    cgf, cgw = ops.tree_filter_backward(gout.cuda(), cew, *order, bands, sv, True)
     assert rel_err(cgf.cpu(), gf) < TOL
     assert rel_err(cgw.cpu(), gw) < TOL
-    cgf2, none = ops.tree_filter_backward(gout.cuda(), cew, *order, sv, False)
+    cgf2, none = ops.tree_filter_backward(gout.cuda(), cew, *order, bands, sv, False)
     assert none is None and rel_err(cgf2.cpu(), gf) < TOL
 
 
