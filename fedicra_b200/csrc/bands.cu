@@ -9,9 +9,9 @@
 // A level-synchronous sweep needs one step per tree depth (1 200-1 600 at 256^2, ~3 000 at 512^2).  Here the depths are
 // cut into `nb` bands of K consecutive levels and every sweep becomes three short phases:
 //   up:    U1  all bands in parallel: local sweep with nothing entering from below  -> partial up at the band's first level
-//          U2  one CTA per image, deepest band first: exact up at each band's first level and the sum X that enters each
-//              band's last level from the band below (uses T[j] = product of w from a last-level vertex j up to, but not
-//              including, its first-level ancestor)
+//          U2  one CTA per image, deepest band first: the sum X that enters each band's last level from the band below,
+//              X'[j'] = base[j'] + sum_{j in last level of the band below, entry(j) = j'} A[j] * X[j]   (a segmented sum over
+//              contiguous runs, done with a warp segmented scan; base = the children's partial sums, written by U1)
 //          U3  all bands in parallel: local sweep again with X injected -> exact up everywhere
 //   down:  D1  (fused behind U3, same CTA) local top-down pass: out[i] = A[i] * out[entry(i)] + B[i] with entry(i) the
 //              parent of i's first-level ancestor, A[i] the product of w from i up to and including that ancestor
@@ -41,9 +41,10 @@ struct TreeView {
 constexpr int MAXBANDS = 256;
 constexpr int PLAN_STRIDE = MAXBANDS + 2;
 
-struct Consts {  // per (tree, edge weights)
-    float *A, *T;                    // [B,V]
-    int *ent, *anc, *run_s, *run_e;  // [B,V]
+struct Consts {  // per (tree, edge weights), all [B,V] in position order
+    float *A;           // product of w from i up to and including its band's first-level ancestor
+    int *ent;           // entry(i): position of the parent of that ancestor (in the last level of the band above)
+    int *run_s, *run_e; // for j' in a band's last level: the run of positions j in the NEXT band's last level with entry(j) = j'
 };
 
 __device__ __forceinline__ bool band_geom(const TreeView &t, int b, int beta, int &L0, int &L1, int &nb) {
@@ -100,25 +101,23 @@ __device__ __forceinline__ int child_count(const int4 &c) { return (c.x > 0) + (
 
 // ------------------------------------------------------------------------------------------------ band constants
 template <bool SMEM>
-__device__ void consts_body(const TreeView &t, const Consts &k, int b, int L0, int L1, int p0, int p1, char *smem) {
+__device__ void consts_body(const TreeView &t, const Consts &k, int b, int beta, int L0, int L1, int p0, int p1, char *smem) {
     const int tid = threadIdx.x, V = t.V, P = p1 - p0;
     const int *ls = t.ls + (size_t)b * (V + 1);
     const int *pp = t.ppos + (size_t)b * V;
     const float *w = t.w + (size_t)b * V;
-    float *gA = k.A + (size_t)b * V, *gT = k.T + (size_t)b * V;
-    int *gE = k.ent + (size_t)b * V, *gN = k.anc + (size_t)b * V;
-    float *sA = reinterpret_cast<float *>(smem), *sT = sA + P;
-    int *sE = reinterpret_cast<int *>(sT + P), *sN = sE + P;
-    float *sW = reinterpret_cast<float *>(sN + P);
+    float *gA = k.A + (size_t)b * V;
+    int *gE = k.ent + (size_t)b * V;
+    float *sA = reinterpret_cast<float *>(smem);
+    int *sE = reinterpret_cast<int *>(sA + P);
+    float *sW = reinterpret_cast<float *>(sE + P);
     int *sP = reinterpret_cast<int *>(sW + P);
     if (SMEM) {  // parents and weights first, in one coalesced pass, so that the level loop never waits on global memory
         for (int i = p0 + tid; i < p1; i += NT) { sW[i - p0] = (i == 0) ? 0.f : w[i]; sP[i - p0] = pp[i]; }
         __syncthreads();
     }
     auto Aat = [&](int i) -> float & { return SMEM ? sA[i - p0] : gA[i]; };
-    auto Tat = [&](int i) -> float & { return SMEM ? sT[i - p0] : gT[i]; };
     auto Eat = [&](int i) -> int & { return SMEM ? sE[i - p0] : gE[i]; };
-    auto Nat = [&](int i) -> int & { return SMEM ? sN[i - p0] : gN[i]; };
     int lo = ls[L0], hi = ls[L0 + 1];
     for (int L = L0; L < L1; ++L) {
         const int nhi = (L + 1 < L1) ? ls[L + 2] : hi;
@@ -126,29 +125,28 @@ __device__ void consts_body(const TreeView &t, const Consts &k, int b, int L0, i
             const float wi = SMEM ? sW[i - p0] : ((i == 0) ? 0.f : w[i]);
             const int p = SMEM ? sP[i - p0] : pp[i];
             if (L == L0) {
-                Aat(i) = wi; Tat(i) = 1.f; Eat(i) = p; Nat(i) = i;
+                Aat(i) = wi; Eat(i) = p;
             } else {
-                Aat(i) = wi * Aat(p); Tat(i) = wi * Tat(p); Eat(i) = Eat(p); Nat(i) = Nat(p);
+                Aat(i) = wi * Aat(p); Eat(i) = Eat(p);
             }
         }
         __syncthreads();
         lo = hi;
         hi = nhi;
     }
-    if (SMEM) {
-        for (int i = p0 + tid; i < p1; i += NT) {
-            gA[i] = sA[i - p0]; gT[i] = sT[i - p0]; gE[i] = sE[i - p0]; gN[i] = sN[i - p0];
-        }
-    }
-    // runs of last-level vertices under each first-level vertex (contiguous in the canonical order)
+    if (SMEM)
+        for (int i = p0 + tid; i < p1; i += NT) { gA[i] = sA[i - p0]; gE[i] = sE[i - p0]; }
+    // runs of this band's last-level vertices under each vertex of the previous band's last level (contiguous in the
+    // canonical order); written by this CTA for the level just above the band
+    if (beta == 0) return;
     int *rs = k.run_s + (size_t)b * V, *re = k.run_e + (size_t)b * V;
-    const int f0 = ls[L0], f1 = ls[L0 + 1], e0 = ls[L1 - 1], e1 = ls[L1];
-    for (int i = f0 + tid; i < f1; i += NT) { rs[i] = 0; re[i] = 0; }
+    const int q0 = ls[L0 - 1], q1 = ls[L0], e0 = ls[L1 - 1], e1 = ls[L1];
+    for (int i = q0 + tid; i < q1; i += NT) { rs[i] = 0; re[i] = 0; }
     __syncthreads();
     for (int j = e0 + tid; j < e1; j += NT) {
-        const int a = Nat(j);
-        if (j == e0 || Nat(j - 1) != a) rs[a] = j;
-        if (j == e1 - 1 || Nat(j + 1) != a) re[a] = j + 1;
+        const int en = Eat(j);
+        if (j == e0 || Eat(j - 1) != en) rs[en] = j;
+        if (j == e1 - 1 || Eat(j + 1) != en) re[en] = j + 1;
     }
 }
 
@@ -160,9 +158,9 @@ __global__ void __launch_bounds__(NT) consts_kernel(TreeView t, Consts k, int pc
     const int *ls = t.ls + (size_t)b * (t.V + 1);
     const int p0 = ls[L0], p1 = ls[L1];
     if (p1 - p0 <= pcap)
-        consts_body<true>(t, k, b, L0, L1, p0, p1, reinterpret_cast<char *>(smem4));
+        consts_body<true>(t, k, b, blockIdx.x, L0, L1, p0, p1, reinterpret_cast<char *>(smem4));
     else
-        consts_body<false>(t, k, b, L0, L1, p0, p1, reinterpret_cast<char *>(smem4));
+        consts_body<false>(t, k, b, blockIdx.x, L0, L1, p0, p1, reinterpret_cast<char *>(smem4));
 }
 
 // ------------------------------------------------------------------------------------------------ band up / down
@@ -174,8 +172,8 @@ struct SweepArgs {
     const float *fpos;   // BWD: forward aggregate in position order [B,C+1,V] (channel C = Z)
     int C, NC;           // feature channels; swept channels (FWD: C+1, BWD: C or 2C)
     // per-sweep arrays [B,NC,V], position order
-    float *upl;          // partial up at each band's first level (U1 -> U2)
-    float *X;            // sum entering each band's last level from below (U2 -> U3)
+    float *upl;          // (unused slot, kept for the workspace layout)
+    float *X;            // sum entering each band's last level from below: U1 writes its base, U2 completes it, U3 injects it
     float *up;           // exact up everywhere (U3 ->)
     float *Bv;           // local down term B (D1 ->)
     float *slab;         // global stand-in for the shared-memory band state (oversized bands only)
@@ -273,10 +271,17 @@ __device__ void sweep_body(const TreeView &t, const SweepArgs &a, int b, int bet
         __syncthreads();
     }
 
-    if (!INJECT) {  // U1: only the first level's partial sums leave the CTA
-        const int f0 = LS(L0), nf = LS(L0 + 1) - f0;
-        if (ch_active)
-            for (int s = slot; s < nf; s += SLOTS) a.upl[img + (size_t)ch_of_thread * V + f0 + s] = VAL(ch_of_thread, f0 + s);
+    if (!INJECT) {  // U1: what this band's first level sends up, summed per parent = the base of X for the level above
+        if (beta > 0 && ch_active) {
+            const int c = ch_of_thread, q0 = ls[L0 - 1], nq = LS(L0) - q0;
+            for (int s = slot; s < nq; s += SLOTS) {
+                const int4 ch = child[q0 + s];
+                const int cnt = child_count(ch);
+                float acc = 0.f;
+                for (int k = 0; k < cnt; ++k) acc += VAL(c, ch.x + k) * Wat(ch.x + k);
+                a.X[img + (size_t)c * V + q0 + s] = acc;
+            }
+        }
         return;
     }
 
@@ -330,113 +335,119 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 constexpr int SCAPW = 512;    // level width staged in shared memory by the two stitch kernels
-
-struct BandEdges {  // per band: first level [f0,f1), last level [e0,e1)
-    int f0, f1, e0, e1;
-};
+constexpr int NSTAGE = 4;     // staging buffers: operands are fetched NSTAGE-1 bands ahead (one L2 round trip ~ 2 bands)
 
 // ------------------------------------------------------------------------------------------------ U2: stitch upward
-// One CTA per image walks the bands from the deepest to the shallowest.  Everything a band needs (contiguous slices of
-// position-indexed arrays) is fetched with cp.async one band ahead, so the per-band chain only touches shared memory.
-__global__ void __launch_bounds__(NT) stitch_up_kernel(TreeView t, Consts k, SweepArgs a) {
+// One CTA per image walks the bands from the deepest to the shallowest.  Per band (two barriers):
+//   A  S = segmented inclusive scan over the band's last level E of A[j] * X[j], segments = runs of equal entry(j)
+//      (32 entries per warp pass, shuffles only)
+//   B  for every j' of the last level of the band above: X'[j'] = base[j'] + the run's total, read off S at the run's end
+//      inside every 32-entry chunk it overlaps.
+// Operands are contiguous slices of position-indexed arrays, fetched by cp.async NSTAGE-1 bands ahead.
+__global__ void __launch_bounds__(NT) stitch_up_kernel(TreeView t, Consts k, SweepArgs a, int slot_shift) {
     extern __shared__ float4 smem4[];
-    __shared__ BandEdges s_be[MAXBANDS];
-    const int b = blockIdx.x, tid = threadIdx.x, V = t.V, NC = a.NC;
+    __shared__ int s_e0[MAXBANDS], s_e1[MAXBANDS];  // last level of every band
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = t.V, NC = a.NC;
     const int *ls = t.ls + (size_t)b * (V + 1);
-    const int4 *child = t.child + (size_t)b * V;
-    const float *w = t.w + (size_t)b * V;
-    const float *T = k.T + (size_t)b * V;
+    const float *A = k.A + (size_t)b * V;
+    const int *ent = k.ent + (size_t)b * V;
     const int *rs = k.run_s + (size_t)b * V, *re = k.run_e + (size_t)b * V;
     const size_t img = (size_t)b * NC * V;
-    const float *upl = a.upl + img;
-    float *Xg = a.X + img, *upFg = a.slab + img;
+    float *Xg = a.X + img;
     const int *plan = t.bands + (size_t)b * PLAN_STRIDE;
     const int nb = plan[0];
     for (int beta = tid; beta < nb; beta += NT) {
-        const int L0 = plan[1 + beta], L1 = plan[2 + beta];
-        s_be[beta] = BandEdges{ls[L0], ls[L0 + 1], ls[L1 - 1], ls[L1]};
+        const int L1 = plan[2 + beta];
+        s_e0[beta] = ls[L1 - 1];
+        s_e1[beta] = ls[L1];
     }
-    // shared memory: 2 staging buffers {upl[NC], w, rs, re, T, child(int4)} + X[2][NC] + upF[NC], SCAPW entries each
+    // shared memory: NSTAGE staging buffers {A[E], ent[E], base X[NC][E'], rs[E'], re[E']} + X[2][NC] + S[NC], SCAPW each
     float *base = reinterpret_cast<float *>(smem4);
-    const int stage_words = (NC + 8) * SCAPW;
-    float *sX[2] = {base + 2 * stage_words, base + 2 * stage_words + NC * SCAPW};
-    float *sF = base + 2 * stage_words + 2 * NC * SCAPW;
+    const int stage_words = (NC + 4) * SCAPW;
+    float *sX[2] = {base + NSTAGE * stage_words, base + NSTAGE * stage_words + NC * SCAPW};
+    float *sS = base + NSTAGE * stage_words + 2 * NC * SCAPW;
+    const int SLOTS = 1 << slot_shift, c = tid >> slot_shift, slot = tid & (SLOTS - 1);
+    const bool ch_active = c < NC;
     __syncthreads();
 
-    auto fits = [&](int beta) {
-        const BandEdges be = s_be[beta];
-        const int nq = be.f0 - s_be[beta - 1].e0;  // last level of the band above = [e0(beta-1), f0(beta))
-        return (be.f1 - be.f0) <= SCAPW && (be.e1 - be.e0) <= SCAPW && nq <= SCAPW;
-    };
+    // step `beta` consumes X of E(beta) and produces X of E(beta-1)
+    auto fits = [&](int beta) { return (s_e1[beta] - s_e0[beta]) <= SCAPW && (s_e1[beta - 1] - s_e0[beta - 1]) <= SCAPW; };
     auto prefetch = [&](int beta) {
         if (beta >= 1 && fits(beta)) {
-            const BandEdges be = s_be[beta];
-            const int q0 = s_be[beta - 1].e0, nf = be.f1 - be.f0, ne = be.e1 - be.e0, nq = be.f0 - q0;
-            float *st = base + (beta & 1) * stage_words;
-            for (int i = tid; i < nf; i += NT) {
-                for (int c = 0; c < NC; ++c) cp_async4(st + c * SCAPW + i, upl + (size_t)c * V + be.f0 + i);
-                cp_async4(st + NC * SCAPW + i, w + be.f0 + i);
-                cp_async4(st + (NC + 1) * SCAPW + i, rs + be.f0 + i);
-                cp_async4(st + (NC + 2) * SCAPW + i, re + be.f0 + i);
+            const int e0 = s_e0[beta], ne = s_e1[beta] - e0, q0 = s_e0[beta - 1], nq = s_e1[beta - 1] - q0;
+            float *st = base + (beta % NSTAGE) * stage_words;
+            for (int i = tid; i < ne; i += NT) {
+                cp_async4(st + i, A + e0 + i);
+                cp_async4(st + SCAPW + i, ent + e0 + i);
             }
-            for (int i = tid; i < ne; i += NT) cp_async4(st + (NC + 3) * SCAPW + i, T + be.e0 + i);
-            for (int i = tid; i < nq; i += NT) cp_async16(st + (NC + 4) * SCAPW + 4 * i, child + q0 + i);
+            for (int i = tid; i < nq; i += NT) {
+                for (int cc = 0; cc < NC; ++cc) cp_async4(st + (2 + cc) * SCAPW + i, Xg + (size_t)cc * V + q0 + i);
+                cp_async4(st + (2 + NC) * SCAPW + i, rs + q0 + i);
+                cp_async4(st + (3 + NC) * SCAPW + i, re + q0 + i);
+            }
         }
         cp_async_commit();
     };
 
     int cur = 0;
-    prefetch(nb - 1);
+    for (int d = 0; d < NSTAGE - 1; ++d) prefetch(nb - 1 - d);
     for (int beta = nb - 1; beta >= 1; --beta) {
-        prefetch(beta - 1);       // (an empty group for beta - 1 == 0)
-        cp_async_wait<1>();       // band beta's operands have landed
-        __syncthreads();
-        const BandEdges be = s_be[beta];
-        const int f0 = be.f0, nf = be.f1 - be.f0, e0 = be.e0, ne = be.e1 - be.e0;
-        const int q0 = s_be[beta - 1].e0, nq = f0 - q0;
-        const bool sm = fits(beta);
-        const float *st = base + (beta & 1) * stage_words;
-        const int *st_rs = reinterpret_cast<const int *>(st + (NC + 1) * SCAPW);
-        const int *st_re = reinterpret_cast<const int *>(st + (NC + 2) * SCAPW);
-        const int4 *st_ch = reinterpret_cast<const int4 *>(st + (NC + 4) * SCAPW);
-        // (a) exact up at the band's first level
-        for (int idx = tid; idx < nf * NC; idx += NT) {
-            const int c = idx / nf, tl = idx - c * nf, tpos = f0 + tl;
-            float acc = sm ? st[c * SCAPW + tl] : upl[(size_t)c * V + tpos];
-            if (beta < nb - 1) {
-                const int j0 = sm ? st_rs[tl] : rs[tpos], j1 = sm ? st_re[tl] : re[tpos];
-                for (int j = j0; j < j1; ++j) {
-                    const float tj = sm ? st[(NC + 3) * SCAPW + (j - e0)] : T[j];
-                    acc += tj * (ne <= SCAPW ? sX[cur][c * SCAPW + (j - e0)] : Xg[(size_t)c * V + j]);
+        cp_async_wait<NSTAGE - 2>();  // band beta's operands have landed (this thread's part) ...
+        __syncthreads();              // ... and everybody's; the previous step's X is complete
+        prefetch(beta - (NSTAGE - 1));
+        const int e0 = s_e0[beta], ne = s_e1[beta] - e0, q0 = s_e0[beta - 1], nq = s_e1[beta - 1] - q0;
+        const bool sm = fits(beta), has_x = beta < nb - 1;
+        const float *st = base + (beta % NSTAGE) * stage_words;
+        const int *st_ent = reinterpret_cast<const int *>(st + SCAPW);
+        const int *st_rs = reinterpret_cast<const int *>(st + (2 + NC) * SCAPW);
+        const int *st_re = reinterpret_cast<const int *>(st + (3 + NC) * SCAPW);
+        // A: segmented scan, one (channel, 32-entry chunk) task per warp pass
+        if (has_x && ne <= SCAPW) {
+            const int nchunk = (ne + 31) >> 5;
+            for (int task = wid; task < NC * nchunk; task += NT / 32) {
+                const int cc = task / nchunk, jl = (task - cc * nchunk) * 32 + lane;
+                const bool ok = jl < ne;
+                const int seg = ok ? (sm ? st_ent[jl] : ent[e0 + jl]) : -1 - lane;
+                float v = ok ? (sm ? st[jl] : A[e0 + jl]) * sX[cur][cc * SCAPW + jl] : 0.f;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const float pv = __shfl_up_sync(0xffffffffu, v, o);
+                    const int ps = __shfl_up_sync(0xffffffffu, seg, o);
+                    if (lane >= o && ps == seg) v += pv;
                 }
+                if (ok) sS[cc * SCAPW + jl] = v;
             }
-            if (nf <= SCAPW) sF[c * SCAPW + tl] = acc; else upFg[(size_t)c * V + tpos] = acc;
         }
         __syncthreads();
-        // (b) what enters the last level of the band above: X[j'] = sum over its children (all in this band's first level)
-        for (int idx = tid; idx < nq * NC; idx += NT) {
-            const int c = idx / nq, jl = idx - c * nq, j = q0 + jl;
-            const int4 ch = sm ? st_ch[jl] : child[j];
-            const int cnt = child_count(ch);
-            float acc = 0.f;
-            for (int kk = 0; kk < cnt; ++kk) {
-                const int tp = ch.x + kk;
-                const float wt = sm ? st[NC * SCAPW + (tp - f0)] : w[tp];
-                acc += wt * (nf <= SCAPW ? sF[c * SCAPW + (tp - f0)] : upFg[(size_t)c * V + tp]);
+        // B: complete X for the last level of the band above
+        if (ch_active) {
+            for (int jl = slot; jl < nq; jl += SLOTS) {
+                const int j = q0 + jl;
+                float acc = sm ? st[(2 + c) * SCAPW + jl] : Xg[(size_t)c * V + j];
+                if (has_x) {
+                    const int j0 = sm ? st_rs[jl] : rs[j], j1 = sm ? st_re[jl] : re[j];
+                    if (ne <= SCAPW) {
+                        for (int hi = j1; hi > j0;) {  // one partial per 32-entry chunk the run overlaps, from its end
+                            acc += sS[c * SCAPW + (hi - 1 - e0)];
+                            const int chunk_start = e0 + (((hi - 1 - e0) >> 5) << 5);
+                            hi = chunk_start;  // continue in the previous chunk (its last entry belongs to the run if > j0)
+                        }
+                    } else {  // oversized level: plain sequential run sum from global memory
+                        for (int jj = j0; jj < j1; ++jj) acc += A[jj] * Xg[(size_t)c * V + jj];
+                    }
+                }
+                Xg[(size_t)c * V + j] = acc;
+                if (nq <= SCAPW) sX[cur ^ 1][c * SCAPW + jl] = acc;
             }
-            Xg[(size_t)c * V + j] = acc;
-            if (nq <= SCAPW) sX[cur ^ 1][c * SCAPW + jl] = acc;
         }
-        __syncthreads();
         cur ^= 1;
     }
 }
 
 // ------------------------------------------------------------------------------------------------ D2: stitch downward
-__global__ void __launch_bounds__(NT) stitch_down_kernel(TreeView t, Consts k, SweepArgs a, float *outE) {
+__global__ void __launch_bounds__(NT) stitch_down_kernel(TreeView t, Consts k, SweepArgs a, float *outE, int slot_shift) {
     extern __shared__ float4 smem4[];
-    __shared__ int s_e0[MAXBANDS + 1];  // first position of every band's last level; entry nb = end
-    __shared__ int s_e1[MAXBANDS];
+    __shared__ int s_e0[MAXBANDS], s_e1[MAXBANDS];
     const int b = blockIdx.x, tid = threadIdx.x, V = t.V, NC = a.NC;
     const int *ls = t.ls + (size_t)b * (V + 1);
     const float *A = k.A + (size_t)b * V;
@@ -451,19 +462,19 @@ __global__ void __launch_bounds__(NT) stitch_down_kernel(TreeView t, Consts k, S
         s_e0[beta] = ls[L1 - 1];
         s_e1[beta] = ls[L1];
     }
-    // shared memory: 2 staging buffers {Bv[NC], A, ent} + out[2][NC], SCAPW entries each
+    // shared memory: NSTAGE staging buffers {Bv[NC], A, ent} + out[2][NC], SCAPW entries each
     float *base = reinterpret_cast<float *>(smem4);
     const int stage_words = (NC + 2) * SCAPW;
-    float *sO[2] = {base + 2 * stage_words, base + 2 * stage_words + NC * SCAPW};
+    float *sO[2] = {base + NSTAGE * stage_words, base + NSTAGE * stage_words + NC * SCAPW};
     __syncthreads();
 
     auto prefetch = [&](int beta) {
         if (beta < nb) {
             const int e0 = s_e0[beta], n = s_e1[beta] - e0;
             if (n <= SCAPW) {
-                float *st = base + (beta & 1) * stage_words;
+                float *st = base + (beta % NSTAGE) * stage_words;
                 for (int i = tid; i < n; i += NT) {
-                    for (int c = 0; c < NC; ++c) cp_async4(st + c * SCAPW + i, Bv + (size_t)c * V + e0 + i);
+                    for (int cc = 0; cc < NC; ++cc) cp_async4(st + cc * SCAPW + i, Bv + (size_t)cc * V + e0 + i);
                     cp_async4(st + NC * SCAPW + i, A + e0 + i);
                     cp_async4(st + (NC + 1) * SCAPW + i, ent + e0 + i);
                 }
@@ -472,28 +483,31 @@ __global__ void __launch_bounds__(NT) stitch_down_kernel(TreeView t, Consts k, S
         cp_async_commit();
     };
 
+    const int SLOTS = 1 << slot_shift, c = tid >> slot_shift, slot = tid & (SLOTS - 1);
+    const bool ch_active = c < NC;
     int cur = 0, pe0 = 0, pn = 0;
-    prefetch(0);
+    for (int d = 0; d < NSTAGE - 1; ++d) prefetch(d);
     for (int beta = 0; beta < nb; ++beta) {
-        prefetch(beta + 1);
-        cp_async_wait<1>();
-        __syncthreads();
+        cp_async_wait<NSTAGE - 2>();
+        __syncthreads();          // band beta's operands are in shared memory and the previous band's outputs complete
+        prefetch(beta + NSTAGE - 1);
         const int e0 = s_e0[beta], n = s_e1[beta] - e0;
         const bool sm = n <= SCAPW;
-        const float *st = base + (beta & 1) * stage_words;
+        const float *st = base + (beta % NSTAGE) * stage_words;
         const int *st_ent = reinterpret_cast<const int *>(st + (NC + 1) * SCAPW);
-        for (int idx = tid; idx < n * NC; idx += NT) {
-            const int c = idx / n, jl = idx - c * n, j = e0 + jl;
-            float o = sm ? st[c * SCAPW + jl] : Bv[(size_t)c * V + j];
-            if (beta > 0) {
-                const int en = sm ? st_ent[jl] : ent[j];
-                const float aj = sm ? st[NC * SCAPW + jl] : A[j];
-                o += aj * (pn <= SCAPW ? sO[cur][c * SCAPW + (en - pe0)] : og[(size_t)c * V + en]);
+        if (ch_active) {
+            for (int jl = slot; jl < n; jl += SLOTS) {
+                const int j = e0 + jl;
+                float o = sm ? st[c * SCAPW + jl] : Bv[(size_t)c * V + j];
+                if (beta > 0) {
+                    const int en = sm ? st_ent[jl] : ent[j];
+                    const float aj = sm ? st[NC * SCAPW + jl] : A[j];
+                    o += aj * (pn <= SCAPW ? sO[cur][c * SCAPW + (en - pe0)] : og[(size_t)c * V + en]);
+                }
+                og[(size_t)c * V + j] = o;
+                if (sm) sO[cur ^ 1][c * SCAPW + jl] = o;
             }
-            og[(size_t)c * V + j] = o;
-            if (sm) sO[cur ^ 1][c * SCAPW + jl] = o;
         }
-        __syncthreads();
         cur ^= 1;
         pe0 = e0;
         pn = n;
@@ -580,8 +594,8 @@ int plan_grid(int V) {                                            // upper bound
 }
 
 struct Layout {
-    // saved (forward -> backward): A, T [V]; up, pos [(C+1),V]; ent, anc, run_s, run_e [V]
-    static size_t saved_bytes(int B, int C, int V) { return (size_t)B * V * (2 + 2 * (C + 1) + 4) * 4; }
+    // saved (forward -> backward): A [V]; up, pos [(C+1),V]; ent, run_s, run_e [V]
+    static size_t saved_bytes(int B, int C, int V) { return (size_t)B * V * (1 + 2 * (C + 1) + 3) * 4; }
     // work: upl, X, up, Bv, outE, slab  [NCmax,V] each
     static size_t work_bytes(int B, int NCmax, int V) { return (size_t)B * V * 6 * NCmax * 4; }
 };
@@ -591,14 +605,12 @@ Consts consts_view(void *saved, int B, int C, int V, float **up, float **pos) {
     const size_t n = (size_t)B * V;
     Consts k;
     k.A = f;
-    k.T = f + n;
-    *up = f + 2 * n;
+    *up = f + n;
     *pos = *up + n * (C + 1);
     int *ip = (int *)(*pos + n * (C + 1));
     k.ent = ip;
-    k.anc = ip + n;
-    k.run_s = ip + 2 * n;
-    k.run_e = ip + 3 * n;
+    k.run_s = ip + n;
+    k.run_e = ip + 2 * n;
     return k;
 }
 
@@ -619,16 +631,16 @@ int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int
     const int pcap = plan_pmax(V);
     const size_t smem = (size_t)pcap * per_pos + (LSCAP + 1) * sizeof(int) + 16;
     if (set_smem(sweep_kernel<MODE, false>, smem, "sweep_kernel") || set_smem(sweep_kernel<MODE, true>, smem, "sweep_kernel")) return -2;
-    const size_t smem_u2 = (size_t)(2 * (NC + 8) + 3 * NC) * SCAPW * sizeof(float) + 16;
-    const size_t smem_d2 = (size_t)(2 * (NC + 2) + 2 * NC) * SCAPW * sizeof(float) + 16;
+    const size_t smem_u2 = (size_t)(NSTAGE * (NC + 4) + 3 * NC) * SCAPW * sizeof(float) + 16;
+    const size_t smem_d2 = (size_t)(NSTAGE * (NC + 2) + 2 * NC) * SCAPW * sizeof(float) + 16;
     if (set_smem(stitch_up_kernel, smem_u2, "stitch_up_kernel") || set_smem(stitch_down_kernel, smem_d2, "stitch_down_kernel")) return -2;
     sweep_kernel<MODE, false><<<dim3(nb, B), NT, smem, st>>>(t, a, pcap, slot_shift);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U1>");
-    stitch_up_kernel<<<B, NT, smem_u2, st>>>(t, k, a);
+    stitch_up_kernel<<<B, NT, smem_u2, st>>>(t, k, a, slot_shift);
     FEDICRA_CHECK_LAUNCH("stitch_up_kernel");
     sweep_kernel<MODE, true><<<dim3(nb, B), NT, smem, st>>>(t, a, pcap, slot_shift);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U3D1>");
-    stitch_down_kernel<<<B, NT, smem_d2, st>>>(t, k, a, outE);
+    stitch_down_kernel<<<B, NT, smem_d2, st>>>(t, k, a, outE, slot_shift);
     FEDICRA_CHECK_LAUNCH("stitch_down_kernel");
     return 0;
 }
@@ -679,7 +691,7 @@ extern "C" int fedicra_tree_filter_forward(const float *feature_in, float *edge_
     zero_root_weight_kernel<<<(B + 127) / 128, 128, 0, st>>>(edge_weight, V, B);
     FEDICRA_CHECK_LAUNCH("zero_root_weight_kernel");
     const int pcap_c = plan_pmax(V);
-    const size_t smem_c = (size_t)pcap_c * 24 + 16;
+    const size_t smem_c = (size_t)pcap_c * 16 + 16;
     if (set_smem(consts_kernel, smem_c, "consts_kernel")) return -2;
     consts_kernel<<<dim3(nb, B), NT, smem_c, st>>>(t, k, pcap_c);
     FEDICRA_CHECK_LAUNCH("consts_kernel");

@@ -100,7 +100,7 @@ template <bool GRID>
 __global__ void mst_find_kernel(Ws ws, const int *__restrict__ edge_index, const float *__restrict__ edge_weight, int V,
                                 int E, int H, int W) {
     const int b = blockIdx.y;
-    if (ws.done[b]) return;
+    if (ws.ncomp[b] <= 1) return;  // this image's tree is complete
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= E) return;
     int u, v;
@@ -123,7 +123,7 @@ __global__ void mst_find_kernel(Ws ws, const int *__restrict__ edge_index, const
 template <bool GRID>
 __global__ void mst_hook_kernel(Ws ws, const int *__restrict__ edge_index, int V, int E, int H, int W) {
     const int b = blockIdx.y;
-    if (ws.done[b]) return;
+    if (ws.ncomp[b] <= 1) return;
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= V) return;
     const int *comp = ws.comp + (size_t)b * V;
@@ -151,7 +151,7 @@ __global__ void mst_hook_kernel(Ws ws, const int *__restrict__ edge_index, int V
 
 __global__ void mst_compress_kernel(Ws ws, int V) {
     const int b = blockIdx.y;
-    if (ws.done[b]) return;
+    if (ws.ncomp[b] <= 1 && ws.done[b]) return;  // one last compression after the final hook, then nothing
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= V) return;
     const int *parent = ws.parent + (size_t)b * V;
@@ -163,6 +163,7 @@ __global__ void mst_compress_kernel(Ws ws, int V) {
     }
     ws.comp[(size_t)b * V + i] = r;
     ws.best[(size_t)b * V + i] = KEY_INF;
+    if (i == 0 && ws.ncomp[b] <= 1) ws.done[b] = 1;
 }
 
 __global__ void mst_finish_round_kernel(Ws ws, int B) {
@@ -255,12 +256,13 @@ int run_mst(const int *edge_index, const float *edge_weight, int B, int E, int V
         mst_find_kernel<GRID><<<dim3((E + 255) / 256, B), blk, 0, st>>>(ws, edge_index, edge_weight, V, E, H, W);
         mst_hook_kernel<GRID><<<dim3((V + 255) / 256, B), blk, 0, st>>>(ws, edge_index, V, E, H, W);
         mst_compress_kernel<<<dim3((V + 255) / 256, B), blk, 0, st>>>(ws, V);
-        mst_finish_round_kernel<<<(B + 127) / 128, 128, 0, st>>>(ws, B);
     }
-    fedicra_count_launches(4 * rounds - 1);
+    fedicra_count_launches(3 * rounds - 1);
     FEDICRA_CHECK_LAUNCH("mst round kernels");
-    mst_compact_kernel<GRID><<<B, 1024, 0, st>>>(ws, edge_index, edge_out, V, E, H, W);
-    FEDICRA_CHECK_LAUNCH("mst_compact_kernel");
+    if (edge_out != nullptr) {
+        mst_compact_kernel<GRID><<<B, 1024, 0, st>>>(ws, edge_index, edge_out, V, E, H, W);
+        FEDICRA_CHECK_LAUNCH("mst_compact_kernel");
+    }
     return 0;
 }
 
@@ -285,12 +287,13 @@ extern "C" int fedicra_mst_forward(const int *edge_index, const float *edge_weig
 
 extern "C" int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out,
                                 unsigned char *tree_mask, void *workspace, size_t workspace_bytes, void *stream) {
-    FEDICRA_REQUIRE(embed && workspace && (edge_out || (long long)H * W <= 1), "mst_grid: null pointer");
+    FEDICRA_REQUIRE(embed && workspace && (edge_out || tree_mask || (long long)H * W <= 1),
+                    "mst_grid: null pointer (edge_out and tree_mask cannot both be NULL)");
     FEDICRA_REQUIRE(B > 0 && B <= 65535 && D > 0 && H >= 1 && W >= 1 && (long long)H * W < (1ll << 30),
                     "mst_grid: bad sizes B=%d D=%d H=%d W=%d", B, D, H, W);
     const int V = H * W, E = 2 * H * W - H - W;
     FEDICRA_REQUIRE(workspace_bytes >= fedicra_mst_workspace_bytes(B, V, E), "mst_grid: workspace too small");
-    FEDICRA_REQUIRE(((uintptr_t)edge_out & 7) == 0, "mst_grid: edge_out must be 8-byte aligned");
+    FEDICRA_REQUIRE(((uintptr_t)edge_out & 7) == 0, "mst_grid: edge_out must be 8-byte aligned");  // (NULL passes)
     Ws ws;
     ws_layout(B, V, E, (char *)workspace, &ws);
     cudaStream_t st = (cudaStream_t)stream;

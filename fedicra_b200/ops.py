@@ -70,13 +70,13 @@ def mst_forward(edge_index, edge_weight, vertex_count):
     return out
 
 
-def mst_grid(embed, want_mask=False):
+def mst_grid(embed, want_mask=False, want_edges=True):
     """MST of the 4-connected grid.  Returns the edge list [B,V-1,2] (and the 4-bit adjacency mask [B,V] when asked)."""
     e = _cuda(embed, torch.float32, "guide_in")
     B, D, H, W = e.shape
     V, E = H * W, 2 * H * W - H - W
     with torch.cuda.device(e.device):
-        out = torch.empty(B, V - 1, 2, dtype=torch.int32, device=e.device)
+        out = torch.empty(B, V - 1, 2, dtype=torch.int32, device=e.device) if want_edges else None
         mask = torch.empty(B, V, dtype=torch.uint8, device=e.device) if want_mask else None
         ws = workspace("mst", lib.fedicra_mst_workspace_bytes(B, V, E), e.device)
         check(lib.fedicra_mst_grid(_p(e), B, D, H, W, _p(out), _p(mask), _p(ws), ws.numel(), _stream()), "mst_grid")

@@ -41,11 +41,9 @@ def batched_tree_orders(embeds):
     D = max(e.shape[1] for e in embeds)
     with torch.no_grad():
         stacked = torch.cat([torch.nn.functional.pad(e.detach().float(), (0, 0, 0, 0, 0, D - e.shape[1])) for e in embeds], 0)
-        tree, mask = ops.mst_grid(stacked, want_mask=True)
-        if H * W <= ops.BFS_GRID_MAX_V:
-            arrays = ops.bfs_grid(mask, H, W)
-        else:
-            arrays = ops.bfs_forward(tree)
+        fits = H * W <= ops.BFS_GRID_MAX_V
+        tree, mask = ops.mst_grid(stacked, want_mask=True, want_edges=not fits)  # the mask alone feeds the grid BFS
+        arrays = ops.bfs_grid(mask, H, W) if fits else ops.bfs_forward(tree)
         bands = ops.band_plan(arrays[3], arrays[4]).view(len(embeds) * B, -1)
     return [_TreeOrder(arrays=tuple(a[k * B:(k + 1) * B] for a in (*arrays, bands))) for k in range(len(embeds))]
 

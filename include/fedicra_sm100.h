@@ -85,7 +85,7 @@ int fedicra_mst_forward(const int *edge_index, const float *edge_weight, int B, 
 /* MinimumSpanningTree.forward on the implicit 4-connected grid (LTF/modules/tree_filter.py:15-34, 53-62 fused with
  * mst_forward): edge e<(H-1)*W joins (h,w)-(h+1,w), the rest join (h,w)-(h,w+1); weight = sum_c (delta)^2 + 1 summed in
  * channel order without fused multiply-add, so the fp32 bits equal torch's.
- *   embed [B,D,H,W]  ->  edge_out [B,H*W-1,2] int32 (increasing edge index);
+ *   embed [B,D,H,W]  ->  edge_out [B,H*W-1,2] int32 (increasing edge index; may be NULL when only the mask is wanted);
  *   tree_mask [B,H*W] uint8 (may be NULL): per vertex, bit 0/1/2/3 set when the tree holds the edge to the pixel
  *   above / left / right / below -- the compact form fedicra_bfs_grid consumes. */
 int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out, unsigned char *tree_mask,
