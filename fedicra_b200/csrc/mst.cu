@@ -10,7 +10,11 @@
 //
 // Also fuses MinimumSpanningTree._build_matrix_index / _build_feature_weight (LTF/modules/tree_filter.py:15-34): on the
 // implicit 4-connected grid the edge list is never materialised and the weights come straight from the embedding.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -237,6 +241,180 @@ __global__ void grid_mask_kernel(Ws ws, unsigned char *__restrict__ mask, int H,
     mask[(size_t)b * V + v] = (unsigned char)m;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Persistent variant for the implicit grid: ONE launch for the whole batch.  A thread-block cluster of CL CTAs owns an
+// image and runs every Boruvka round itself -- vertex-centric find (each vertex scans its <= 4 grid edges and issues at
+// most one atomicMin on its component), hook, pointer chase -- separated by cluster barriers instead of kernel
+// boundaries.  Same keys, same hooks, hence the same edge set as the multi-launch path (and as the reference).
+constexpr int PNT = 512;
+
+__global__ void __launch_bounds__(PNT)
+mst_grid_cluster_kernel(Ws ws, const float *__restrict__ embed, unsigned char *__restrict__ mask, int D, int H, int W,
+                        int max_rounds) {
+    cg::cluster_group cluster = cg::this_cluster();
+    const int CL = (int)cluster.num_blocks(), rank = (int)cluster.block_rank();
+    const int b = blockIdx.x / CL, tid = threadIdx.x;
+    const int V = H * W, E = 2 * H * W - H - W, nvert = (H - 1) * W;
+    int *comp = ws.comp + (size_t)b * V, *parent = ws.parent + (size_t)b * V;
+    u64 *best = ws.best + (size_t)b * V;
+    float *wgt = ws.wgt + (size_t)b * E;
+    unsigned char *intree = ws.intree + (size_t)b * E;
+    int *ncomp = ws.ncomp + b;
+    const int stride = CL * PNT, first = rank * PNT + tid;
+    __shared__ int s_merges;
+
+    // ---- init: weights (tree_filter.py:27-34, no fused multiply-add), union state
+    const float *x = embed + (size_t)b * D * V;
+    for (int e = first; e < E; e += stride) {
+        int u, v;
+        grid_endpoints(e, H, W, u, v);
+        float d = 0.f;
+        for (int c = 0; c < D; ++c) {
+            const float t = __fsub_rn(x[(size_t)c * V + u], x[(size_t)c * V + v]);
+            d = __fadd_rn(d, __fmul_rn(t, t));
+        }
+        wgt[e] = __fadd_rn(d, 1.f);
+        intree[e] = 0;
+    }
+    for (int v = first; v < V; v += stride) {
+        comp[v] = v;
+        parent[v] = v;
+        best[v] = KEY_INF;
+    }
+    if (rank == 0 && tid == 0) *ncomp = V;
+    cluster.sync();
+
+    // Every loop below handles IL vertices per iteration with the loads of all of them issued before the first use: the
+    // phases are chains of dependent L2 round trips, and one cluster only has CL*512 threads to hide them with.
+    constexpr int IL = 4;
+    for (int round = 0; round < max_rounds; ++round) {
+        // ---- find: cheapest outgoing edge per component
+        for (int v0 = first; v0 < V; v0 += stride * IL) {
+            int vv[IL], cv[IL], nb_[IL][4], ee[IL][4];
+#pragma unroll
+            for (int k = 0; k < IL; ++k) {
+                const int v = v0 + k * stride;
+                vv[k] = v;
+                cv[k] = (v < V) ? comp[v] : -1;
+            }
+#pragma unroll
+            for (int k = 0; k < IL; ++k) {
+                const int v = vv[k], h = v / W, w = v - h * W;
+                const bool ok = v < V;
+                ee[k][0] = (ok && h > 0) ? v - W : -1;
+                ee[k][1] = (ok && w > 0) ? nvert + h * (W - 1) + w - 1 : -1;
+                ee[k][2] = (ok && w < W - 1) ? nvert + h * (W - 1) + w : -1;
+                ee[k][3] = (ok && h < H - 1) ? v : -1;
+                nb_[k][0] = ee[k][0] >= 0 ? comp[v - W] : cv[k];
+                nb_[k][1] = ee[k][1] >= 0 ? comp[v - 1] : cv[k];
+                nb_[k][2] = ee[k][2] >= 0 ? comp[v + 1] : cv[k];
+                nb_[k][3] = ee[k][3] >= 0 ? comp[v + W] : cv[k];
+            }
+            float wv[IL][4];
+#pragma unroll
+            for (int k = 0; k < IL; ++k)
+#pragma unroll
+                for (int d = 0; d < 4; ++d) wv[k][d] = (nb_[k][d] != cv[k]) ? wgt[ee[k][d]] : 0.f;
+#pragma unroll
+            for (int k = 0; k < IL; ++k) {
+                u64 key = KEY_INF;
+#pragma unroll
+                for (int d = 0; d < 4; ++d)
+                    if (nb_[k][d] != cv[k]) key = min(key, ((u64)orderable(wv[k][d]) << 32) | (unsigned)ee[k][d]);
+                if (key != KEY_INF) atomicMin(best + cv[k], key);
+            }
+        }
+        if (tid == 0) s_merges = 0;
+        cluster.sync();
+        // ---- hook: every root follows its edge; of two roots that picked the same edge the larger one hooks
+        int merges = 0;
+        for (int c0 = first; c0 < V; c0 += stride * IL) {
+            int cc[IL];
+            u64 key[IL];
+#pragma unroll
+            for (int k = 0; k < IL; ++k) {
+                const int c = c0 + k * stride;
+                cc[k] = (c < V && comp[c] == c) ? c : -1;
+            }
+#pragma unroll
+            for (int k = 0; k < IL; ++k) key[k] = (cc[k] >= 0) ? best[cc[k]] : KEY_INF;
+            int other[IL], eid[IL];
+#pragma unroll
+            for (int k = 0; k < IL; ++k) {
+                other[k] = -1;
+                eid[k] = 0;
+                if (key[k] != KEY_INF) {
+                    const int e = (int)(unsigned)(key[k] & 0xffffffffull);
+                    int u, v;
+                    grid_endpoints(e, H, W, u, v);
+                    const int cu = comp[u], cvv = comp[v];
+                    other[k] = (cu == cc[k]) ? cvv : cu;
+                    eid[k] = e;
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < IL; ++k) {
+                if (other[k] < 0) continue;
+                if (best[other[k]] == key[k] && cc[k] < other[k]) continue;
+                parent[cc[k]] = other[k];
+                intree[eid[k]] = 1;
+                ++merges;
+            }
+        }
+        if (merges) atomicAdd(&s_merges, merges);
+        __syncthreads();
+        if (tid == 0 && s_merges) atomicSub(ncomp, s_merges);
+        cluster.sync();
+        // ---- compress: every vertex chases the hooks to its new root
+        for (int v0 = first; v0 < V; v0 += stride * IL) {
+            int r[IL], p[IL];
+#pragma unroll
+            for (int k = 0; k < IL; ++k) r[k] = (v0 + k * stride < V) ? comp[v0 + k * stride] : 0;
+#pragma unroll
+            for (int k = 0; k < IL; ++k) p[k] = parent[r[k]];
+            bool moving = true;
+            while (moving) {
+                moving = false;
+#pragma unroll
+                for (int k = 0; k < IL; ++k) {
+                    if (p[k] != r[k]) {
+                        r[k] = p[k];
+                        moving = true;
+                    }
+                }
+                if (moving) {
+#pragma unroll
+                    for (int k = 0; k < IL; ++k) p[k] = parent[r[k]];
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < IL; ++k) {
+                const int v = v0 + k * stride;
+                if (v < V) {
+                    comp[v] = r[k];
+                    best[v] = KEY_INF;
+                }
+            }
+        }
+        cluster.sync();
+        if (*reinterpret_cast<volatile int *>(ncomp) <= 1) break;
+    }
+
+    // ---- 4-bit adjacency mask from the selected-edge flags
+    if (mask != nullptr) {
+        unsigned char *m = mask + (size_t)b * V;
+        for (int v = first; v < V; v += stride) {
+            const int h = v / W, w = v - h * W;
+            unsigned bits = 0;
+            if (h > 0 && intree[v - W]) bits |= 1u;
+            if (w > 0 && intree[nvert + h * (W - 1) + w - 1]) bits |= 2u;
+            if (w < W - 1 && intree[nvert + h * (W - 1) + w]) bits |= 4u;
+            if (h < H - 1 && intree[v]) bits |= 8u;
+            m[v] = (unsigned char)bits;
+        }
+    }
+}
+
 int rounds_for(int V) {
     int r = 0;
     while ((1ll << r) < V) ++r;
@@ -298,8 +476,29 @@ extern "C" int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, 
     ws_layout(B, V, E, (char *)workspace, &ws);
     cudaStream_t st = (cudaStream_t)stream;
     if (E > 0) {
-        grid_weight_kernel<<<dim3((E + 255) / 256, B), 256, 0, st>>>(embed, ws.wgt, D, H, W, E);
-        FEDICRA_CHECK_LAUNCH("grid_weight_kernel");
+        // one persistent launch: a cluster of CL CTAs per image (as many as keep the whole batch in one wave)
+        int CL = 8;
+        while (CL > 1 && (long long)B * CL > 2 * 148) CL >>= 1;  // 62 registers x 512 threads: two CTAs per SM
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(B * CL));
+        cfg.blockDim = dim3(PNT);
+        cfg.dynamicSmemBytes = 0;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)CL;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, mst_grid_cluster_kernel, ws, embed, tree_mask, D, H, W, rounds_for(V));
+        fedicra_count_launches(1);
+        if (e != cudaSuccess) return fedicra_fail(-2, "mst_grid_cluster_kernel: %s", cudaGetErrorString(e));
+        if (edge_out != nullptr) {
+            mst_compact_kernel<true><<<B, 1024, 0, st>>>(ws, nullptr, edge_out, V, E, H, W);
+            FEDICRA_CHECK_LAUNCH("mst_compact_kernel");
+        }
+        return 0;
     }
     if (int rc = run_mst<true>(nullptr, ws.wgt, B, E, V, H, W, edge_out, ws, st)) return rc;
     if (tree_mask != nullptr) {
