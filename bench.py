@@ -191,7 +191,7 @@ def time_steps(fn, steps, flush_buf):
 def profile_ops(step, data, steps, flush_buf):
     """Second, instrumented pass: CUDA events around every C-ABI call, to attribute the step time to kernel groups."""
     from fedicra_b200 import ops
-    names = ["gcrf_fwd_bwd", "mst_grid", "bfs_forward", "bfs_grid", "edge_weight_fwd", "edge_weight_bwd", "refine_forward",
+    names = ["gcrf_fwd_bwd", "mst_grid", "bfs_forward", "bfs_grid", "bfs_euler", "edge_weight_fwd", "edge_weight_bwd", "refine_forward",
              "refine_backward_feature", "refine_backward_weight", "tree_filter_forward", "tree_filter_backward"]
     records, originals = {n: [] for n in names}, {}
 
@@ -375,6 +375,7 @@ def run_ours(args, wl):
         "mst_grid": lambda k: B * (ab["stages"][k]["mst_bfs"] - ab["u"]),
         "bfs_forward": lambda k: B * ab["u"],
         "bfs_grid": lambda k: B * ab["u"],
+        "bfs_euler": lambda k: B * ab["u"],
         "refine_forward": lambda k: B * ab["stages"][k]["filter_fwd"],
         "refine_backward_feature": lambda k: B * (2 * C + 3) * ab["u"],
         "refine_backward_weight": lambda k: B * (2 * C + 2 * C) * ab["u"],

@@ -1,0 +1,516 @@
+// euler.cu -- breadth-first ORDER of grid spanning trees without walking them depth by depth (sm_100a).
+//
+// Same outputs as fedicra_bfs_grid / the reference's bfs_forward (LTF/src/bfs/bfs.cu:46-98 semantics, canonical order:
+// depth, then parent position, then vertex id), but every step is data-parallel over the whole batch.  A level-by-level
+// walk needs one dependent step per tree depth (1 100 - 2 200 at 256^2); here the depth of the dependency chain is
+// logarithmic:
+//   1. Euler tour of the tree (each tree edge = two arcs; successor of the arc into u = next tree edge around u)
+//      ranked with a splitter walk: one thread per 16 vertices walks its stretch of the tour (~32 arcs), the ~4 096
+//      stretches are ranked by pointer jumping in shared memory.
+//   2. From the ranks: the parent of u is where the tour first enters u; subtree size = half the span between entering
+//      and leaving u.
+//   3. One prefix sum along the tour of (+1,-1) gives the depth, of (+o,-o) with o(u) = 1 + sizes of u's smaller siblings
+//      gives the preorder index that visits children by increasing vertex id.
+//   4. BFS position = level_start[depth] + rank of the preorder index among the vertices of that depth (the BFS queue
+//      order equals "sort by depth, then preorder"): counted per level.
+// Integer-only, deterministic (atomics are used for counters whose order does not reach the result).
+#include "common.cuh"
+
+namespace {
+
+constexpr int NT = 256;
+constexpr int NIL = -1;
+constexpr int SPLIT_PER_CTA = 1024;  // splitters handed out dynamically inside one CTA of the tour walk
+
+__device__ __forceinline__ int dir_delta(int d, int W) { return d == 0 ? -W : (d == 1 ? -1 : (d == 2 ? 1 : W)); }
+
+// Splitter s sits on a pseudo-randomly chosen vertex of its block of SP = 2^sp_log consecutive vertices (a regular
+// placement would put all splitters on a few image columns, and a tour can run for thousands of arcs between two
+// columns).  splitter_vertex() and is_splitter_vertex() are inverse to each other.
+__device__ __forceinline__ int splitter_vertex(int s, int sp_log, int V) {
+    const int v = (s << sp_log) + (int)(((unsigned)s * 2654435761u) >> (32 - sp_log));
+    return v < V ? v : (s << sp_log);
+}
+__device__ __forceinline__ bool is_splitter_vertex(int v, int sp_log, int V) { return splitter_vertex(v >> sp_log, sp_log, V) == v; }
+
+// next tree edge around a vertex with adjacency mask m, cyclically after direction r (r itself when it is the only one)
+__device__ __forceinline__ int next_dir(unsigned m, int r) {
+    const unsigned rot = ((m | (m << 4)) >> (r + 1)) & 0xFu;
+    return (r + __ffs(rot)) & 3;
+}
+
+struct Ws {
+    unsigned *arc;                  // [B,4V] splitter owning the arc << 19 | offset of the arc inside the splitter's stretch
+                                    //        (packed so that the whole table stays L2-resident: its writes are random)
+    int *snext, *slen, *sbase;      // [B,NS] next splitter on the tour, stretch length, tour rank of the splitter arc
+    int *rin, *rout, *pdir, *size;  // [B,V]  tour rank entering / leaving u, direction of the parent (4 = root), subtree size
+    int4 *S;                        // [B,2V] tour-ordered (d depth, d preorder, vertex entered or -1, 0)
+    int2 *bsum;                     // [B,NBLK] per-block sums of S
+    int *depth, *pre;               // [B,V]
+    int *cnt, *cursor;              // [B,V+1] vertices per depth; bucket fill cursors   (zeroed per call)
+    int2 *tmp;                      // [B,V]  per level, unordered: (preorder, vertex)
+    int *pos;                       // [B,V]  BFS position of a vertex
+};
+
+struct Dims {
+    int B, V, H, W, SP, SPLOG, NS, T, NBLK;  // T = 2(V-1) arcs on the tour; NBLK = ceil(T / 1024)
+};
+
+size_t ws_layout(const Dims &d, char *base, Ws *w) {
+    size_t offb = 0;
+    auto take = [&](size_t bytes) {
+        char *p = base ? base + offb : nullptr;
+        offb += align_up(bytes, 256);
+        return p;
+    };
+    const size_t B = d.B, V = d.V;
+    Ws t;
+    t.cnt = (int *)take(B * (V + 1) * 4);      // cnt and cursor first and adjacent: one memset clears both
+    t.cursor = (int *)take(B * (V + 1) * 4);
+    t.arc = (unsigned *)take(B * 4 * V * 4);
+    t.snext = (int *)take(B * d.NS * 4);
+    t.slen = (int *)take(B * d.NS * 4);
+    t.sbase = (int *)take(B * d.NS * 4);
+    t.rin = (int *)take(B * V * 4);
+    t.rout = (int *)take(B * V * 4);
+    t.pdir = (int *)take(B * V * 4);
+    t.size = (int *)take(B * V * 4);
+    t.S = (int4 *)take(B * 2 * V * 16);
+    t.bsum = (int2 *)take(B * (size_t)(d.NBLK > 0 ? d.NBLK : 1) * 8);
+    t.depth = (int *)take(B * V * 4);
+    t.pre = (int *)take(B * V * 4);
+    t.tmp = (int2 *)take(B * V * 8);
+    t.pos = (int *)take(B * V * 4);
+    if (w) *w = t;
+    return offb;
+}
+
+Dims make_dims(int B, int H, int W) {
+    Dims d;
+    d.B = B; d.H = H; d.W = W; d.V = H * W;
+    d.SP = 16;
+    d.SPLOG = 4;
+    while ((d.V + d.SP - 1) / d.SP > 8192) { d.SP <<= 1; ++d.SPLOG; }  // at most 8 192 splitters per image (shared-memory ranking)
+    d.NS = (d.V + d.SP - 1) / d.SP;
+    d.T = 2 * (d.V - 1);
+    d.NBLK = (d.T + 1023) / 1024;
+    return d;
+}
+
+// ---- 1a. every splitter walks its stretch of the tour.  The walk is a chain of dependent mask look-ups (~32 on average,
+// a few hundred for the longest stretch), so every CTA first copies the image's masks into shared memory, two per byte.
+template <bool SMEM>
+__global__ void __launch_bounds__(NT) walk_kernel(const unsigned char *__restrict__ mask, Ws ws, Dims dm) {
+    extern __shared__ unsigned char s_mask[];
+    const int b = blockIdx.y, V = dm.V, W = dm.W, spl = dm.SPLOG;
+    const unsigned char *m = mask + (size_t)b * V;
+    if (SMEM) {
+        if ((V & 15) == 0 && (((uintptr_t)m) & 15) == 0) {  // 16 masks per load, packed to 8 bytes
+            const uint4 *m4 = reinterpret_cast<const uint4 *>(m);
+            uint2 *s2 = reinterpret_cast<uint2 *>(s_mask);
+            for (int k = threadIdx.x; k < V / 16; k += NT) {
+                const uint4 q = m4[k];
+                auto pack = [](unsigned x) {  // 4 bytes (one mask each) -> 16 bits (one nibble each)
+                    return (x & 0xFu) | ((x >> 4) & 0xF0u) | ((x >> 8) & 0xF00u) | ((x >> 12) & 0xF000u);
+                };
+                s2[k] = make_uint2(pack(q.x) | (pack(q.y) << 16), pack(q.z) | (pack(q.w) << 16));
+            }
+        } else {
+            for (int k = threadIdx.x; k < (V + 1) / 2; k += NT) {
+                const unsigned lo = m[2 * k], hi = (2 * k + 1 < V) ? m[2 * k + 1] : 0u;
+                s_mask[k] = (unsigned char)(lo | (hi << 4));
+            }
+        }
+        __syncthreads();
+    }
+    auto mask_of = [&](int v) -> unsigned {
+        if (SMEM) {
+            const unsigned byte = s_mask[v >> 1];
+            return (v & 1) ? (byte >> 4) : (byte & 15u);
+        }
+        return m[v];
+    };
+    // Stretch lengths are geometric (mean ~2 SP, longest a few hundred), so a fixed splitter per thread leaves most lanes
+    // idle; instead every CTA owns SPLIT_PER_CTA consecutive splitters and its lanes pull the next one when they are done.
+    __shared__ int s_next;
+    const int s_begin = blockIdx.x * SPLIT_PER_CTA, s_end = min(s_begin + SPLIT_PER_CTA, dm.NS);
+    if (threadIdx.x == 0) s_next = s_begin + NT;
+    __syncthreads();
+    unsigned *arc = ws.arc + (size_t)b * 4 * V;
+    const int limit = 2 * V;  // a consistent tree mask closes the tour after 2(V-1) arcs; guard against a bad one
+    int s = s_begin + threadIdx.x, v = 0, d = 0, steps = 0;
+    bool walking = false;
+    while (true) {
+        if (!walking) {
+            if (s >= s_end) break;
+            v = splitter_vertex(s, spl, V);
+            const unsigned mv0 = mask_of(v);
+            if (mv0 == 0) {  // single-vertex tree
+                ws.snext[(size_t)b * dm.NS + s] = s;
+                ws.slen[(size_t)b * dm.NS + s] = 0;
+                s = atomicAdd(&s_next, 1);
+                continue;
+            }
+            d = __ffs(mv0) - 1;
+            steps = 0;
+            walking = true;
+        }
+        arc[4 * v + d] = ((unsigned)s << 19) | (unsigned)steps;
+        ++steps;
+        v += dir_delta(d, W);
+        const unsigned mv = mask_of(v);
+        d = next_dir(mv, 3 - d);
+        if ((d == __ffs(mv) - 1 && is_splitter_vertex(v, spl, V)) || steps >= limit) {
+            ws.snext[(size_t)b * dm.NS + s] = v >> spl;
+            ws.slen[(size_t)b * dm.NS + s] = steps;
+            walking = false;
+            s = atomicAdd(&s_next, 1);
+        }
+    }
+}
+
+// ---- 1b. rank the splitters: suffix sums of the stretch lengths by pointer jumping, one CTA per image
+__global__ void __launch_bounds__(1024) rank_splitters_kernel(Ws ws, Dims dm) {
+    extern __shared__ int s_mem[];
+    const int b = blockIdx.x, tid = threadIdx.x, NS = dm.NS;
+    int *val[2] = {s_mem, s_mem + NS}, *nxt[2] = {s_mem + 2 * NS, s_mem + 3 * NS};
+    const int *snext = ws.snext + (size_t)b * NS, *slen = ws.slen + (size_t)b * NS;
+    for (int s = tid; s < NS; s += 1024) {
+        const int n = snext[s];
+        val[0][s] = slen[s];
+        nxt[0][s] = (n == 0) ? NIL : n;  // the tour is a cycle through splitter 0 (vertex 0, the root): cut it there
+    }
+    __syncthreads();
+    int cur = 0;
+    for (int span = 1; span < NS; span <<= 1) {
+        for (int s = tid; s < NS; s += 1024) {
+            const int n = nxt[cur][s];
+            val[cur ^ 1][s] = val[cur][s] + (n >= 0 ? val[cur][n] : 0);
+            nxt[cur ^ 1][s] = (n >= 0) ? nxt[cur][n] : NIL;
+        }
+        __syncthreads();
+        cur ^= 1;
+    }
+    const int total = val[cur][0];
+    for (int s = tid; s < NS; s += 1024) ws.sbase[(size_t)b * NS + s] = total - val[cur][s];
+}
+
+__device__ __forceinline__ int arc_rank(const unsigned *arc, const int *sbase, int a) {
+    const unsigned r = arc[a];
+    return sbase[r >> 19] + (int)(r & 0x7ffffu);
+}
+
+// ---- 2. where the tour enters and leaves every vertex
+__global__ void __launch_bounds__(NT) enter_leave_kernel(const unsigned char *__restrict__ mask, Ws ws, Dims dm) {
+    const long long idx = (long long)blockIdx.x * NT + threadIdx.x;
+    if (idx >= (long long)dm.B * dm.V) return;
+    const int b = (int)(idx / dm.V), u = (int)(idx - (long long)b * dm.V), V = dm.V, W = dm.W;
+    const unsigned *arc = ws.arc + (size_t)b * 4 * V;
+    const int *sbase = ws.sbase + (size_t)b * dm.NS;
+    const size_t o = (size_t)b * V + u;
+    if (u == 0) {
+        ws.rin[o] = -1; ws.rout[o] = dm.T; ws.pdir[o] = 4; ws.size[o] = V;
+        return;
+    }
+    const unsigned m = mask[o];
+    int best = 0x7fffffff, pd = 0;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        if (m & (1u << d)) {
+            const int r = arc_rank(arc, sbase, 4 * (u + dir_delta(d, W)) + (3 - d));  // the arc neighbour -> u
+            if (r < best) { best = r; pd = d; }
+        }
+    }
+    const int out = arc_rank(arc, sbase, 4 * u + pd);
+    ws.rin[o] = best; ws.rout[o] = out; ws.pdir[o] = pd; ws.size[o] = (out - best + 1) >> 1;
+}
+
+// ---- 3a. tour-ordered increments: +1 / -1 for the depth, +o / -o for the preorder with children by increasing id
+__global__ void __launch_bounds__(NT) increments_kernel(const unsigned char *__restrict__ mask, Ws ws, Dims dm) {
+    const long long idx = (long long)blockIdx.x * NT + threadIdx.x;
+    if (idx >= (long long)dm.B * dm.V) return;
+    const int b = (int)(idx / dm.V), u = (int)(idx - (long long)b * dm.V), V = dm.V, W = dm.W;
+    if (u == 0) return;
+    const size_t o = (size_t)b * V;
+    const int pd = ws.pdir[o + u], p = u + dir_delta(pd, W), du = 3 - pd;  // u is p's child in direction du
+    const unsigned mp = mask[o + p];
+    const int ppd = ws.pdir[o + p];
+    int offs = 1;
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+        if (d < du && (mp & (1u << d)) && d != ppd) offs += ws.size[o + p + dir_delta(d, W)];
+    int4 *S = ws.S + (size_t)b * 2 * V;
+    S[ws.rin[o + u]] = make_int4(1, offs, u, 0);
+    S[ws.rout[o + u]] = make_int4(-1, -offs, -1, 0);
+}
+
+// ---- 3b. prefix sums along the tour (block sums, scan of block sums, apply)
+__global__ void __launch_bounds__(1024) tour_block_sum_kernel(Ws ws, Dims dm) {
+    const int b = blockIdx.y, blk = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int r = blk * 1024 + tid;
+    int2 v = make_int2(0, 0);
+    if (r < dm.T) {
+        const int4 s = ws.S[(size_t)b * 2 * dm.V + r];
+        v = make_int2(s.x, s.y);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+        v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+    }
+    __shared__ int2 s_w[32];
+    if (lane == 0) s_w[wid] = v;
+    __syncthreads();
+    if (wid == 0) {
+        int2 t = s_w[lane];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            t.x += __shfl_xor_sync(0xffffffffu, t.x, o);
+            t.y += __shfl_xor_sync(0xffffffffu, t.y, o);
+        }
+        if (lane == 0) ws.bsum[(size_t)b * dm.NBLK + blk] = t;
+    }
+}
+
+__global__ void __launch_bounds__(1024) tour_scan_sums_kernel(Ws ws, Dims dm) {  // one CTA per image: exclusive scan
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    int2 *bs = ws.bsum + (size_t)b * dm.NBLK;
+    __shared__ int2 s_w[32];
+    __shared__ int2 s_carry;
+    if (tid == 0) s_carry = make_int2(0, 0);
+    __syncthreads();
+    for (int base = 0; base < dm.NBLK; base += 1024) {
+        const int i = base + tid;
+        const int2 mine = (i < dm.NBLK) ? bs[i] : make_int2(0, 0);
+        int2 x = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int tx = __shfl_up_sync(0xffffffffu, x.x, o), ty = __shfl_up_sync(0xffffffffu, x.y, o);
+            if (lane >= o) { x.x += tx; x.y += ty; }
+        }
+        if (lane == 31) s_w[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            int2 t = s_w[lane], y = t;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int tx = __shfl_up_sync(0xffffffffu, y.x, o), ty = __shfl_up_sync(0xffffffffu, y.y, o);
+                if (lane >= o) { y.x += tx; y.y += ty; }
+            }
+            s_w[lane] = make_int2(y.x - t.x, y.y - t.y);
+        }
+        __syncthreads();
+        const int2 carry = s_carry, wo = s_w[wid];
+        if (i < dm.NBLK) bs[i] = make_int2(carry.x + wo.x + x.x - mine.x, carry.y + wo.y + x.y - mine.y);
+        __syncthreads();
+        if (tid == 1023) s_carry = make_int2(carry.x + wo.x + x.x, carry.y + wo.y + x.y);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(1024) tour_apply_kernel(Ws ws, Dims dm) {
+    const int b = blockIdx.y, blk = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = dm.V;
+    const int r = blk * 1024 + tid;
+    int4 s = make_int4(0, 0, -1, 0);
+    if (r < dm.T) s = ws.S[(size_t)b * 2 * V + r];
+    int2 x = make_int2(s.x, s.y);
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int tx = __shfl_up_sync(0xffffffffu, x.x, o), ty = __shfl_up_sync(0xffffffffu, x.y, o);
+        if (lane >= o) { x.x += tx; x.y += ty; }
+    }
+    __shared__ int2 s_w[32];
+    if (lane == 31) s_w[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+        int2 t = s_w[lane], y = t;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int tx = __shfl_up_sync(0xffffffffu, y.x, o), ty = __shfl_up_sync(0xffffffffu, y.y, o);
+            if (lane >= o) { y.x += tx; y.y += ty; }
+        }
+        s_w[lane] = make_int2(y.x - t.x, y.y - t.y);
+    }
+    __syncthreads();
+    const size_t o = (size_t)b * V;
+    if (blk == 0 && tid == 0) {  // the root is never entered
+        ws.depth[o] = 0;
+        ws.pre[o] = 0;
+        atomicAdd(ws.cnt + (size_t)b * (V + 1), 1);
+    }
+    if (s.z >= 0) {  // the tour enters vertex s.z here: inclusive sums = its depth and preorder index
+        const int2 base = ws.bsum[(size_t)b * dm.NBLK + blk], wo = s_w[wid];
+        const int depth = base.x + wo.x + x.x, pre = base.y + wo.y + x.y;
+        ws.depth[o + s.z] = depth;
+        ws.pre[o + s.z] = pre;
+        atomicAdd(ws.cnt + (size_t)b * (V + 1) + depth, 1);
+    }
+}
+
+// ---- 4a. level_start = exclusive scan of the per-depth counts; stops as soon as all V vertices are accounted for
+__global__ void __launch_bounds__(1024) level_scan_kernel(Ws ws, Dims dm, int *__restrict__ level_start,
+                                                          int *__restrict__ n_levels) {
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = dm.V;
+    const int *cnt = ws.cnt + (size_t)b * (V + 1);
+    int *ls = level_start + (size_t)b * (V + 1);
+    __shared__ int s_w[32];
+    __shared__ int s_carry, s_levels;
+    if (tid == 0) { s_carry = 0; s_levels = 0; }
+    __syncthreads();
+    for (int base = 0; base <= V; base += 1024) {
+        const int i = base + tid;
+        const int c = (i <= V) ? cnt[i] : 0;
+        int x = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += t;
+        }
+        if (lane == 31) s_w[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            int t = s_w[lane], y = t;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int tt = __shfl_up_sync(0xffffffffu, y, o);
+                if (lane >= o) y += tt;
+            }
+            s_w[lane] = y - t;
+        }
+        __syncthreads();
+        const int carry = s_carry, excl = carry + s_w[wid] + x - c;
+        if (i <= V && (c > 0 || excl == V)) {  // depths that exist, plus the closing entry ls[n_levels] = V
+            ls[i] = excl;
+            if (c > 0) atomicMax(&s_levels, i + 1);
+        }
+        __syncthreads();
+        if (tid == 1023) s_carry = excl + c;
+        __syncthreads();
+        if (s_carry >= V) {  // everything placed; make sure the closing entry lands right after the last depth
+            if (tid == 0) {
+                ls[s_levels] = V;
+                n_levels[b] = s_levels;
+            }
+            return;
+        }
+    }
+    if (tid == 0) {
+        ls[s_levels] = V;
+        n_levels[b] = s_levels;
+    }
+}
+
+// ---- 4b. drop every vertex into its level's bucket (arbitrary order inside the bucket)
+__global__ void __launch_bounds__(NT) bucket_kernel(Ws ws, Dims dm, const int *__restrict__ level_start) {
+    const long long idx = (long long)blockIdx.x * NT + threadIdx.x;
+    if (idx >= (long long)dm.B * dm.V) return;
+    const int b = (int)(idx / dm.V), u = (int)(idx - (long long)b * dm.V), V = dm.V;
+    const int d = ws.depth[(size_t)b * V + u];
+    const int slot = atomicAdd(ws.cursor + (size_t)b * (V + 1) + d, 1);
+    ws.tmp[(size_t)b * V + level_start[(size_t)b * (V + 1) + d] + slot] = make_int2(ws.pre[(size_t)b * V + u], u);
+}
+
+// ---- 4c. order every level by preorder index: rank = number of smaller keys (levels are ~45 wide); one warp per level
+__global__ void __launch_bounds__(NT) level_rank_kernel(Ws ws, Dims dm, const int *__restrict__ level_start,
+                                                        const int *__restrict__ n_levels, int *__restrict__ sorted_index,
+                                                        int warps_per_image) {
+    const int b = blockIdx.y, lane = threadIdx.x & 31, V = dm.V;
+    const int warp = blockIdx.x * (NT / 32) + (threadIdx.x >> 5);
+    const int nl = n_levels[b];
+    const int *ls = level_start + (size_t)b * (V + 1);
+    const int2 *tmp = ws.tmp + (size_t)b * V;
+    int *pos = ws.pos + (size_t)b * V, *order = sorted_index + (size_t)b * V;
+    for (int L = warp; L < nl; L += warps_per_image) {
+        const int lo = ls[L], n = ls[L + 1] - lo;
+        for (int i = lane; i < n; i += 32) {
+            const int2 me = tmp[lo + i];
+            int rank = 0;
+            for (int j = 0; j < n; ++j) rank += (tmp[lo + j].x < me.x);
+            order[lo + rank] = me.y;
+            pos[me.y] = lo + rank;
+        }
+    }
+}
+
+// ---- 5. parent position and children positions of every vertex
+__global__ void __launch_bounds__(NT) finalize_kernel(const unsigned char *__restrict__ mask, Ws ws, Dims dm,
+                                                      int *__restrict__ sorted_parent, int *__restrict__ sorted_child) {
+    const long long idx = (long long)blockIdx.x * NT + threadIdx.x;
+    if (idx >= (long long)dm.B * dm.V) return;
+    const int b = (int)(idx / dm.V), u = (int)(idx - (long long)b * dm.V), V = dm.V, W = dm.W;
+    const size_t o = (size_t)b * V;
+    const int *pos = ws.pos + o;
+    const int i = pos[u], pd = ws.pdir[o + u];
+    const unsigned m = mask[o + u];
+    sorted_parent[o + i] = (u == 0) ? 0 : pos[u + dir_delta(pd, W)];
+    int c[4] = {0, 0, 0, 0}, k = 0;
+#pragma unroll
+    for (int d = 0; d < 4; ++d)
+        if ((m & (1u << d)) && d != pd) c[k++] = pos[u + dir_delta(d, W)];
+    reinterpret_cast<int4 *>(sorted_child)[o + i] = make_int4(c[0], c[1], c[2], c[3]);
+}
+
+}  // namespace
+
+extern "C" size_t fedicra_bfs_euler_workspace_bytes(int B, int H, int W) {
+    if (B <= 0 || H <= 0 || W <= 0) return 0;
+    return ws_layout(make_dims(B, H, W), nullptr, nullptr);
+}
+
+extern "C" int fedicra_bfs_euler(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index,
+                                 int *sorted_parent, int *sorted_child, int *level_start, int *n_levels,
+                                 void *workspace, size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(tree_mask && sorted_index && sorted_parent && sorted_child && level_start && n_levels && workspace,
+                    "bfs_euler: null pointer");
+    FEDICRA_REQUIRE(B > 0 && B <= 65535 && H >= 1 && W >= 1 && (long long)H * W <= (1ll << 18),
+                    "bfs_euler: bad sizes B=%d H=%d W=%d (at most 262144 pixels per image)", B, H, W);
+    FEDICRA_REQUIRE(((uintptr_t)sorted_child & 15) == 0, "bfs_euler: sorted_child must be 16-byte aligned");
+    const Dims dm = make_dims(B, H, W);
+    FEDICRA_REQUIRE(workspace_bytes >= ws_layout(dm, nullptr, nullptr), "bfs_euler: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    Ws ws;
+    ws_layout(dm, (char *)workspace, &ws);
+    const int V = dm.V;
+    // cnt + cursor must start at zero; the arc table is cleared too so that its lines are L2-resident when the walk
+    // scatters 4-byte records into them (otherwise every partial-sector write costs a DRAM read-modify-write)
+    cudaError_t e = cudaMemsetAsync(ws.cnt, 0, (size_t)((char *)ws.snext - (char *)ws.cnt), st);
+    if (e != cudaSuccess) return fedicra_fail(-2, "bfs_euler: memset: %s", cudaGetErrorString(e));
+    const unsigned vb = (unsigned)(((long long)B * V + NT - 1) / NT);
+    const size_t smem_mask = (size_t)(V + 1) / 2;
+    if (smem_mask <= 200 * 1024) {
+        e = cudaFuncSetAttribute(walk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_mask);
+        if (e != cudaSuccess) return fedicra_fail(-2, "bfs_euler: shared memory: %s", cudaGetErrorString(e));
+        walk_kernel<true><<<dim3((dm.NS + SPLIT_PER_CTA - 1) / SPLIT_PER_CTA, B), NT, smem_mask, st>>>(tree_mask, ws, dm);
+    } else {
+        walk_kernel<false><<<dim3((dm.NS + SPLIT_PER_CTA - 1) / SPLIT_PER_CTA, B), NT, 0, st>>>(tree_mask, ws, dm);
+    }
+    FEDICRA_CHECK_LAUNCH("walk_kernel");
+    const size_t smem_rank = (size_t)4 * dm.NS * sizeof(int);
+    e = cudaFuncSetAttribute(rank_splitters_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rank);
+    if (e != cudaSuccess) return fedicra_fail(-2, "bfs_euler: shared memory: %s", cudaGetErrorString(e));
+    rank_splitters_kernel<<<B, 1024, smem_rank, st>>>(ws, dm);
+    FEDICRA_CHECK_LAUNCH("rank_splitters_kernel");
+    enter_leave_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm);
+    FEDICRA_CHECK_LAUNCH("enter_leave_kernel");
+    if (dm.T > 0) {
+        increments_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm);
+        FEDICRA_CHECK_LAUNCH("increments_kernel");
+        tour_block_sum_kernel<<<dim3(dm.NBLK, B), 1024, 0, st>>>(ws, dm);
+        FEDICRA_CHECK_LAUNCH("tour_block_sum_kernel");
+        tour_scan_sums_kernel<<<B, 1024, 0, st>>>(ws, dm);
+        FEDICRA_CHECK_LAUNCH("tour_scan_sums_kernel");
+    }
+    tour_apply_kernel<<<dim3(dm.NBLK > 0 ? dm.NBLK : 1, B), 1024, 0, st>>>(ws, dm);
+    FEDICRA_CHECK_LAUNCH("tour_apply_kernel");
+    level_scan_kernel<<<B, 1024, 0, st>>>(ws, dm, level_start, n_levels);
+    FEDICRA_CHECK_LAUNCH("level_scan_kernel");
+    bucket_kernel<<<vb, NT, 0, st>>>(ws, dm, level_start);
+    FEDICRA_CHECK_LAUNCH("bucket_kernel");
+    const int warps_per_image = 2048;
+    level_rank_kernel<<<dim3(warps_per_image / (NT / 32), B), NT, 0, st>>>(ws, dm, level_start, n_levels, sorted_index,
+                                                                        warps_per_image);
+    FEDICRA_CHECK_LAUNCH("level_rank_kernel");
+    finalize_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm, sorted_parent, sorted_child);
+    FEDICRA_CHECK_LAUNCH("finalize_kernel");
+    return 0;
+}

@@ -84,6 +84,17 @@ def mst_grid(embed, want_mask=False, want_edges=True):
 
 
 BFS_GRID_MAX_V = 2 * (227 * 1024 - 4 * 4096 * 4 - 256)
+BFS_EULER_MAX_V = 1 << 18
+
+
+def bfs_from_mask(mask, H, W):
+    """Fastest BFS ordering available for an H x W grid tree given as adjacency mask (all three give identical arrays):
+    Euler tour + prefix sums up to 262 144 pixels, else the shared-memory depth walk; None when neither applies."""
+    if H * W <= BFS_EULER_MAX_V:
+        return bfs_euler(mask, H, W)
+    if H * W <= BFS_GRID_MAX_V:
+        return bfs_grid(mask, H, W)
+    return None
 
 
 def bfs_grid(mask, H, W):
@@ -118,6 +129,23 @@ def bfs_forward(tree):
         ws = workspace("bfs", lib.fedicra_bfs_workspace_bytes(B, V), dev)
         check(lib.fedicra_bfs_forward(_p(t), B, V, _p(si), _p(sp), _p(sc), _p(ls), _p(nl), _p(ws), ws.numel(),
                                       _stream()), "bfs_forward")
+    return si, sp, sc, ls, nl
+
+
+def bfs_euler(mask, H, W):
+    """BFS arrays from the adjacency mask via Euler tour + prefix sums (no per-depth step); same outputs as bfs_grid."""
+    m = _cuda(mask, torch.uint8, "tree_mask")
+    B, V = m.shape
+    dev = m.device
+    with torch.cuda.device(dev):
+        si = torch.empty(B, V, dtype=torch.int32, device=dev)
+        sp = torch.empty(B, V, dtype=torch.int32, device=dev)
+        sc = torch.empty(B, V, 4, dtype=torch.int32, device=dev)
+        ls = torch.empty(B, V + 1, dtype=torch.int32, device=dev)
+        nl = torch.empty(B, dtype=torch.int32, device=dev)
+        ws = workspace("bfs_euler", lib.fedicra_bfs_euler_workspace_bytes(B, H, W), dev)
+        check(lib.fedicra_bfs_euler(_p(m), B, H, W, _p(si), _p(sp), _p(sc), _p(ls), _p(nl), _p(ws), ws.numel(), _stream()),
+              "bfs_euler")
     return si, sp, sc, ls, nl
 
 

@@ -107,6 +107,14 @@ int fedicra_bfs_forward(const int *tree, int B, int V, int *sorted_index, int *s
 int fedicra_bfs_grid(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index, int *sorted_parent,
                      int *sorted_child, int *level_start, int *n_levels, void *stream);
 
+/* Same outputs again, without any per-depth step: Euler tour of the tree ranked by a splitter walk, depth and preorder
+ * from one prefix sum along the tour, BFS position = level start + rank of the preorder index inside the level
+ * (csrc/euler.cu).  Images up to 262 144 pixels (larger ones: fedicra_bfs_forward); ~100 bytes of workspace per vertex. */
+size_t fedicra_bfs_euler_workspace_bytes(int B, int H, int W);
+int fedicra_bfs_euler(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index, int *sorted_parent,
+                      int *sorted_child, int *level_start, int *n_levels, void *workspace, size_t workspace_bytes,
+                      void *stream);
+
 /* ------------------------------------------------------------------------------------------------ tree filter -- */
 /* TreeFilter2D.build_edge_weight (LTF/modules/tree_filter.py:91-108): ew[b,i] = exp(-|e[v(i)] - e[v(par i)]|^2 *
  * inv_sigma) in BFS order; embed [B,D,V] in vertex order. */

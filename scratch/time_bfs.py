@@ -14,4 +14,4 @@ for (B,H,W) in [(12,256,256),(1,256,256),(48,256,256),(12,512,512)]:
     tree,mask=ops.mst_grid(emb,want_mask=True)
     si,sp,sc,ls,nl=ops.bfs_grid(mask,H,W)
     print(B,H,W,'levels',nl.min().item(),nl.max().item(),'max width',int((ls[:,1:]-ls[:,:-1]).clamp(min=0).max()))
-    print('  bfs_grid ms',t(lambda: ops.bfs_grid(mask,H,W)),' mst_grid ms',t(lambda: ops.mst_grid(emb,want_mask=True)), ' bfs_forward ms', t(lambda: ops.bfs_forward(tree)))
+    print('  bfs_grid ms',t(lambda: ops.bfs_grid(mask,H,W)),' mst_grid ms',t(lambda: ops.mst_grid(emb,want_mask=True)), ' bfs_forward ms', t(lambda: ops.bfs_forward(tree)), ' bfs_euler ms', t(lambda: ops.bfs_euler(mask,H,W)))

@@ -192,9 +192,10 @@ def test_bfs_from_adjacency_mask_bit_exact(kind, B, D, H, W):
         deg[b] = torch.bincount(tree[b].reshape(-1).long(), minlength=V)
     pop = sum(((mask.cpu().long() >> k) & 1) for k in range(4))
     assert torch.equal(pop, deg)
-    gsi, gsp, gsc, gls, gnl = ops.bfs_grid(mask, H, W)
-    assert torch.equal(gsi.cpu(), si) and torch.equal(gsp.cpu(), sp) and torch.equal(gsc.cpu(), sc)
-    for b in range(B):
-        _, _, _, ls = tree_cpu.bfs_levels(tree[b])
-        n = int(gnl[b])
-        assert n == len(ls) - 1 and torch.equal(gls[b, :n + 1].cpu(), ls)
+    for fn in (ops.bfs_grid, ops.bfs_euler):   # level-by-level walk in shared memory; Euler tour + prefix sums
+        gsi, gsp, gsc, gls, gnl = fn(mask, H, W)
+        assert torch.equal(gsi.cpu(), si) and torch.equal(gsp.cpu(), sp) and torch.equal(gsc.cpu(), sc), fn.__name__
+        for b in range(B):
+            _, _, _, ls = tree_cpu.bfs_levels(tree[b])
+            n = int(gnl[b])
+            assert n == len(ls) - 1 and torch.equal(gls[b, :n + 1].cpu(), ls), fn.__name__
