@@ -192,89 +192,144 @@ __device__ __forceinline__ float prologue(const SweepArgs &a, int b, int c, int 
     }
 }
 
+constexpr int SWEEP_SLOTS = 64;  // positions of one level handled per pass; a sweep CTA has 64 threads per channel
+
 template <int MODE, bool INJECT, bool SMEM>
 __device__ void sweep_body(const TreeView &t, const SweepArgs &a, int b, int beta, int nb, int L0, int L1, int p0, int p1,
-                           int pcap, int slot_shift, char *smem) {
-    const int tid = threadIdx.x, V = t.V, NC = a.NC, P = p1 - p0;
+                           int pcap, char *smem) {
+    const int tid = threadIdx.x, nthr = blockDim.x, V = t.V, NC = a.NC, P = p1 - p0;
     const int *ls = t.ls + (size_t)b * (V + 1);
     const int *vtx = t.vtx + (size_t)b * V, *pp = t.ppos + (size_t)b * V;
     const int4 *child = t.child + (size_t)b * V;
     const float *w = t.w + (size_t)b * V;
     const size_t img = (size_t)b * NC * V;
-    // band state: val[c][i], and (shared-memory mode) copies of w / children / parent / vertex
+    // band state: val[c][i], and (shared-memory mode) copies of w / packed parent+children / vertex
     float *sval = reinterpret_cast<float *>(smem);            // [NC][pcap]
     float *sw = sval + (size_t)NC * pcap;                     // [pcap]
-    int *sch = reinterpret_cast<int *>(sw + pcap);            // [pcap] (first child position << 3 | count)
-    int *spp = sch + pcap;                                    // [pcap]
-    int *svx = spp + pcap;                                    // [pcap]
+    int *spk = reinterpret_cast<int *>(sw + pcap);            // [pcap] (parent - p0) << 15 | (first child - p0) << 3 | #children
+    int *svx = spk + pcap;                                    // [pcap] vertex of the position (staging only)
     int *sls = svx + pcap;                                    // [LSCAP+1]
     float *gval = a.slab + img;
     auto VAL = [&](int c, int i) -> float & { return SMEM ? sval[(size_t)c * pcap + (i - p0)] : gval[(size_t)c * V + i]; };
     auto Wat = [&](int i) -> float { return SMEM ? sw[i - p0] : ((i == 0) ? 0.f : w[i]); };
     const bool ls_cached = SMEM && (L1 - L0) <= LSCAP;
     auto LS = [&](int L) -> int { return ls_cached ? sls[L - L0] : ls[L]; };
-    // thread -> (channel, slot) without a division: SLOTS = NT >> slot_shift... channels beyond NC idle
-    const int SLOTS = 1 << slot_shift, ch_of_thread = tid >> slot_shift, slot = tid & (SLOTS - 1);
-    const bool ch_active = ch_of_thread < NC;
+    // thread -> (channel, slot): blockDim.x = 64 * NC, no division, no idle warp
+    const int c = tid / SWEEP_SLOTS, slot = tid % SWEEP_SLOTS;
 
     // ---- stage the band: topology first (coalesced), then the feature gather with the loads batched four deep
     if (ls_cached)
-        for (int L = L0 + tid; L <= L1; L += NT) sls[L - L0] = ls[L];
+        for (int L = L0 + tid; L <= L1; L += nthr) sls[L - L0] = ls[L];
     if (SMEM) {
-        for (int i = p0 + tid; i < p1; i += NT) {
+        for (int i = p0 + tid; i < p1; i += nthr) {
             const int4 ch = child[i];
+            const int cnt = child_count(ch), par = pp[i];
+            // parents above the band / children below it are never followed, so their (out of range) offsets are dropped
+            const int pl = (par >= p0) ? par - p0 : 0, cl = (cnt > 0 && ch.x < p1) ? ch.x - p0 : 0;
             sw[i - p0] = (i == 0) ? 0.f : w[i];
-            sch[i - p0] = (ch.x << 3) | child_count(ch);
-            spp[i - p0] = pp[i];
+            spk[i - p0] = (pl << 15) | (cl << 3) | cnt;
             svx[i - p0] = vtx[i];
         }
         __syncthreads();
     }
-    for (int c = 0; c < NC; ++c) {
+    for (int cc = 0; cc < NC; ++cc) {
         int i = p0 + tid;
-        for (; i + 3 * NT < p1; i += 4 * NT) {
-            float v0 = prologue<MODE>(a, b, c, i, SMEM ? svx[i - p0] : vtx[i], V);
-            float v1 = prologue<MODE>(a, b, c, i + NT, SMEM ? svx[i + NT - p0] : vtx[i + NT], V);
-            float v2 = prologue<MODE>(a, b, c, i + 2 * NT, SMEM ? svx[i + 2 * NT - p0] : vtx[i + 2 * NT], V);
-            float v3 = prologue<MODE>(a, b, c, i + 3 * NT, SMEM ? svx[i + 3 * NT - p0] : vtx[i + 3 * NT], V);
-            VAL(c, i) = v0; VAL(c, i + NT) = v1; VAL(c, i + 2 * NT) = v2; VAL(c, i + 3 * NT) = v3;
+        for (; i + 3 * nthr < p1; i += 4 * nthr) {
+            float v0 = prologue<MODE>(a, b, cc, i, SMEM ? svx[i - p0] : vtx[i], V);
+            float v1 = prologue<MODE>(a, b, cc, i + nthr, SMEM ? svx[i + nthr - p0] : vtx[i + nthr], V);
+            float v2 = prologue<MODE>(a, b, cc, i + 2 * nthr, SMEM ? svx[i + 2 * nthr - p0] : vtx[i + 2 * nthr], V);
+            float v3 = prologue<MODE>(a, b, cc, i + 3 * nthr, SMEM ? svx[i + 3 * nthr - p0] : vtx[i + 3 * nthr], V);
+            VAL(cc, i) = v0; VAL(cc, i + nthr) = v1; VAL(cc, i + 2 * nthr) = v2; VAL(cc, i + 3 * nthr) = v3;
         }
-        for (; i < p1; i += NT) VAL(c, i) = prologue<MODE>(a, b, c, i, SMEM ? svx[i - p0] : vtx[i], V);
+        for (; i < p1; i += nthr) VAL(cc, i) = prologue<MODE>(a, b, cc, i, SMEM ? svx[i - p0] : vtx[i], V);
     }
     __syncthreads();
 
-    // ---- local leaf -> root sweep
+    const bool inject = INJECT && beta < nb - 1;
+    if (SMEM) {
+        // ================= shared-memory band: tight loops on local indices =================
+        float *mv = sval + (size_t)c * pcap;  // this thread's channel row, indexed by position - p0
+        // ---- local leaf -> root sweep; the next level's bounds are fetched before the barrier
+        int lo = LS(L1 - 1) - p0, hi = P;
+        for (int L = L1 - 1; L >= L0; --L) {
+            const int nlo = (L > L0) ? LS(L - 1) - p0 : 0;
+            if (L == L1 - 1) {
+                if (inject)
+                    for (int il = lo + slot; il < hi; il += SWEEP_SLOTS) mv[il] += a.X[img + (size_t)c * V + p0 + il];
+            } else {
+                for (int il = lo + slot; il < hi; il += SWEEP_SLOTS) {
+                    const int pk = spk[il], cl = (pk >> 3) & 0xfff, cnt = pk & 7;
+                    float acc = mv[il];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (k < cnt) acc = fmaf(mv[cl + k], sw[cl + k], acc);
+                    mv[il] = acc;
+                }
+            }
+            __syncthreads();
+            hi = lo;
+            lo = nlo;
+        }
+        if (!INJECT) {  // U1: what this band's first level sends up, summed per parent = the base of X for the level above
+            if (beta > 0) {
+                const int q0 = ls[L0 - 1], nq = p0 - q0;
+                for (int s = slot; s < nq; s += SWEEP_SLOTS) {
+                    const int4 ch = child[q0 + s];
+                    const int cnt = child_count(ch), cl = ch.x - p0;
+                    float acc = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (k < cnt) acc = fmaf(mv[cl + k], sw[cl + k], acc);
+                    a.X[img + (size_t)c * V + q0 + s] = acc;
+                }
+            }
+            return;
+        }
+        // ---- U3: exact up leaves; D1: local root -> leaf pass, in place: val <- B
+        for (int cc = 0; cc < NC; ++cc)
+            for (int il = tid; il < P; il += nthr) a.up[img + (size_t)cc * V + p0 + il] = sval[(size_t)cc * pcap + il];
+        __syncthreads();
+        lo = 0;
+        hi = LS(L0 + 1) - p0;
+        for (int L = L0; L < L1; ++L) {
+            const int nhi = (L + 1 < L1) ? LS(L + 2) - p0 : hi;
+            for (int il = lo + slot; il < hi; il += SWEEP_SLOTS) {
+                const float wi = sw[il];
+                float bval = mv[il] * (1.f - wi * wi);
+                if (L > L0) bval = fmaf(wi, mv[spk[il] >> 15], bval);
+                mv[il] = bval;
+            }
+            __syncthreads();
+            lo = hi;
+            hi = nhi;
+        }
+        for (int cc = 0; cc < NC; ++cc)
+            for (int il = tid; il < P; il += nthr) a.Bv[img + (size_t)cc * V + p0 + il] = sval[(size_t)cc * pcap + il];
+        return;
+    }
+
+    // ================= oversized band: same recurrences on global memory =================
     for (int L = L1 - 1; L >= L0; --L) {
         const int lo = LS(L), n = LS(L + 1) - lo;
         const bool last = (L == L1 - 1);
-        if (ch_active) {
-            const int c = ch_of_thread;
-            for (int s = slot; s < n; s += SLOTS) {
-                const int i = lo + s;
-                float acc = VAL(c, i);
-                if (!last) {
-                    int cs, cnt;
-                    if (SMEM) {
-                        const int pk = sch[i - p0];
-                        cs = pk >> 3; cnt = pk & 7;
-                    } else {
-                        const int4 ch = child[i];
-                        cs = ch.x; cnt = child_count(ch);
-                    }
-                    for (int k = 0; k < cnt; ++k) acc += VAL(c, cs + k) * Wat(cs + k);
-                } else if (INJECT && beta < nb - 1) {
-                    acc += a.X[img + (size_t)c * V + i];
-                }
-                VAL(c, i) = acc;
+        for (int s = slot; s < n; s += SWEEP_SLOTS) {
+            const int i = lo + s;
+            float acc = VAL(c, i);
+            if (!last) {
+                const int4 ch = child[i];
+                const int cnt = child_count(ch);
+                for (int k = 0; k < cnt; ++k) acc += VAL(c, ch.x + k) * Wat(ch.x + k);
+            } else if (inject) {
+                acc += a.X[img + (size_t)c * V + i];
             }
+            VAL(c, i) = acc;
         }
         __syncthreads();
     }
-
-    if (!INJECT) {  // U1: what this band's first level sends up, summed per parent = the base of X for the level above
-        if (beta > 0 && ch_active) {
-            const int c = ch_of_thread, q0 = ls[L0 - 1], nq = LS(L0) - q0;
-            for (int s = slot; s < nq; s += SLOTS) {
+    if (!INJECT) {
+        if (beta > 0) {
+            const int q0 = ls[L0 - 1], nq = LS(L0) - q0;
+            for (int s = slot; s < nq; s += SWEEP_SLOTS) {
                 const int4 ch = child[q0 + s];
                 const int cnt = child_count(ch);
                 float acc = 0.f;
@@ -284,31 +339,26 @@ __device__ void sweep_body(const TreeView &t, const SweepArgs &a, int b, int bet
         }
         return;
     }
-
-    // ---- U3: exact up leaves; D1: local root -> leaf pass, in place: val <- B
-    for (int c = 0; c < NC; ++c)
-        for (int i = p0 + tid; i < p1; i += NT) a.up[img + (size_t)c * V + i] = VAL(c, i);
+    for (int cc = 0; cc < NC; ++cc)
+        for (int i = p0 + tid; i < p1; i += nthr) a.up[img + (size_t)cc * V + i] = VAL(cc, i);
     __syncthreads();
     for (int L = L0; L < L1; ++L) {
         const int lo = LS(L), n = LS(L + 1) - lo;
-        if (ch_active) {
-            const int c = ch_of_thread;
-            for (int s = slot; s < n; s += SLOTS) {
-                const int i = lo + s;
-                const float wi = Wat(i);
-                float bval = VAL(c, i) * (1.f - wi * wi);
-                if (L > L0) bval += wi * VAL(c, SMEM ? spp[i - p0] : pp[i]);
-                VAL(c, i) = bval;
-            }
+        for (int s = slot; s < n; s += SWEEP_SLOTS) {
+            const int i = lo + s;
+            const float wi = Wat(i);
+            float bval = VAL(c, i) * (1.f - wi * wi);
+            if (L > L0) bval += wi * VAL(c, pp[i]);
+            VAL(c, i) = bval;
         }
         __syncthreads();
     }
-    for (int c = 0; c < NC; ++c)
-        for (int i = p0 + tid; i < p1; i += NT) a.Bv[img + (size_t)c * V + i] = VAL(c, i);
+    for (int cc = 0; cc < NC; ++cc)
+        for (int i = p0 + tid; i < p1; i += nthr) a.Bv[img + (size_t)cc * V + i] = VAL(cc, i);
 }
 
 template <int MODE, bool INJECT>
-__global__ void __launch_bounds__(NT) sweep_kernel(TreeView t, SweepArgs a, int pcap, int slot_shift) {
+__global__ void __launch_bounds__(1024) sweep_kernel(TreeView t, SweepArgs a, int pcap) {
     extern __shared__ float4 smem4[];
     const int b = blockIdx.y, beta = blockIdx.x;
     int L0, L1, nb;
@@ -316,9 +366,9 @@ __global__ void __launch_bounds__(NT) sweep_kernel(TreeView t, SweepArgs a, int 
     const int *ls = t.ls + (size_t)b * (t.V + 1);
     const int p0 = ls[L0], p1 = ls[L1];
     if (p1 - p0 <= pcap)
-        sweep_body<MODE, INJECT, true>(t, a, b, beta, nb, L0, L1, p0, p1, pcap, slot_shift, reinterpret_cast<char *>(smem4));
+        sweep_body<MODE, INJECT, true>(t, a, b, beta, nb, L0, L1, p0, p1, pcap, reinterpret_cast<char *>(smem4));
     else
-        sweep_body<MODE, INJECT, false>(t, a, b, beta, nb, L0, L1, p0, p1, pcap, slot_shift, reinterpret_cast<char *>(smem4));
+        sweep_body<MODE, INJECT, false>(t, a, b, beta, nb, L0, L1, p0, p1, pcap, reinterpret_cast<char *>(smem4));
 }
 
 // ------------------------------------------------------------------------------------------------ async staging
@@ -585,7 +635,7 @@ __global__ void zero_root_weight_kernel(float *w, int V, int B) {
 
 // ------------------------------------------------------------------------------------------------ host side
 // Band limits (host side, functions of the image size only).
-int plan_pmax(int V) { return V <= (1 << 17) ? 2048 : 3072; }   // positions per band (shared-memory band state)
+int plan_pmax(int V) { return V <= (1 << 17) ? 1792 : 3072; }   // positions per band (shared-memory band state, < 4096)
 constexpr int PLAN_KDIV = 32;                                     // a band holds at most ceil(n_levels / 32) levels
 int plan_grid(int V) {                                            // upper bound of the number of bands
     const int pm = plan_pmax(V);
@@ -624,21 +674,22 @@ int set_smem(Kern kern, size_t bytes, const char *name) {
 template <int MODE>
 int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int B, cudaStream_t st) {
     const int V = t.V, nb = plan_grid(V), NC = a.NC;
-    const int per_pos = (NC + 4) * 4;
+    const int per_pos = (NC + 3) * 4;
     int ncp = 1, slot_shift = 8;  // NT = 256 threads = ncp channel groups x (256 >> log2 ncp) slots
     while (ncp < NC) { ncp <<= 1; --slot_shift; }
-    if (NC > NT) return fedicra_fail(-1, "tree filter: %d channels per sweep exceed %d", NC, NT);
+    if (NC * SWEEP_SLOTS > 1024) return fedicra_fail(-1, "tree filter: %d channels per sweep exceed %d", NC, 1024 / SWEEP_SLOTS);
+    const int nthr_sweep = NC * SWEEP_SLOTS;
     const int pcap = plan_pmax(V);
     const size_t smem = (size_t)pcap * per_pos + (LSCAP + 1) * sizeof(int) + 16;
     if (set_smem(sweep_kernel<MODE, false>, smem, "sweep_kernel") || set_smem(sweep_kernel<MODE, true>, smem, "sweep_kernel")) return -2;
     const size_t smem_u2 = (size_t)(NSTAGE * (NC + 4) + 3 * NC) * SCAPW * sizeof(float) + 16;
     const size_t smem_d2 = (size_t)(NSTAGE * (NC + 2) + 2 * NC) * SCAPW * sizeof(float) + 16;
     if (set_smem(stitch_up_kernel, smem_u2, "stitch_up_kernel") || set_smem(stitch_down_kernel, smem_d2, "stitch_down_kernel")) return -2;
-    sweep_kernel<MODE, false><<<dim3(nb, B), NT, smem, st>>>(t, a, pcap, slot_shift);
+    sweep_kernel<MODE, false><<<dim3(nb, B), nthr_sweep, smem, st>>>(t, a, pcap);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U1>");
     stitch_up_kernel<<<B, NT, smem_u2, st>>>(t, k, a, slot_shift);
     FEDICRA_CHECK_LAUNCH("stitch_up_kernel");
-    sweep_kernel<MODE, true><<<dim3(nb, B), NT, smem, st>>>(t, a, pcap, slot_shift);
+    sweep_kernel<MODE, true><<<dim3(nb, B), nthr_sweep, smem, st>>>(t, a, pcap);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U3D1>");
     stitch_down_kernel<<<B, NT, smem_d2, st>>>(t, k, a, outE, slot_shift);
     FEDICRA_CHECK_LAUNCH("stitch_down_kernel");
