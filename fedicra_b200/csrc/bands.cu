@@ -564,6 +564,98 @@ __global__ void __launch_bounds__(NT) stitch_down_kernel(TreeView t, Consts k, S
     }
 }
 
+// ------------------------------------------------------------------------------------------------ D2 by pointer jumping
+// The band-to-band recurrence out[j] = B[j] + A[j] * out[entry(j)] over the bands' last levels is a chain of affine maps
+// in which every value depends on ONE value of the band above.  Such maps compose into maps of the same shape, so the
+// ~40 sequential band steps collapse into ceil(log2 nb) rounds of "absorb the map of the vertex I point to":
+//   (a, p, b) <- (a * a[p], p[p], b + a * b[p])         band-0 vertices are terminal: a = 0, p = self.
+// All boundary vertices of an image (a few thousand) sit in shared memory; one CTA per image, one barrier per round.
+constexpr int JNT = 1024;
+
+__global__ void __launch_bounds__(JNT) stitch_down_jump_kernel(TreeView t, Consts k, SweepArgs a, float *outE, int cap) {
+    extern __shared__ float4 smem4[];
+    __shared__ int s_e0[MAXBANDS], s_eo[MAXBANDS + 1];  // first position / first node index of every band's last level
+    const int b = blockIdx.x, tid = threadIdx.x, V = t.V, NC = a.NC;
+    const int *ls = t.ls + (size_t)b * (V + 1);
+    const float *A = k.A + (size_t)b * V;
+    const int *ent = k.ent + (size_t)b * V;
+    const size_t img = (size_t)b * NC * V;
+    const float *Bv = a.Bv + img;
+    float *og = outE + img;
+    const int *plan = t.bands + (size_t)b * PLAN_STRIDE;
+    const int nb = plan[0];
+    for (int beta = tid; beta < nb; beta += JNT) {  // every band's last level: first position and width (parallel loads)
+        const int L1 = plan[2 + beta];
+        const int e0 = ls[L1 - 1];
+        s_e0[beta] = e0;
+        s_eo[beta + 1] = ls[L1] - e0;
+    }
+    __syncthreads();
+    if (tid == 0) {  // widths -> node offsets (nb <= 256 shared-memory adds)
+        int acc = 0;
+        s_eo[0] = 0;
+        for (int beta = 0; beta < nb; ++beta) {
+            acc += s_eo[beta + 1];
+            s_eo[beta + 1] = acc;
+        }
+    }
+    __syncthreads();
+    const int NE = s_eo[nb];
+    if (NE > cap) {  // does not fit: band-by-band walk straight on global memory (rare: very wide levels)
+        for (int beta = 0; beta < nb; ++beta) {
+            const int e0 = s_e0[beta], n = s_eo[beta + 1] - s_eo[beta];
+            for (int idx = tid; idx < n * NC; idx += JNT) {
+                const int c = idx / n, j = e0 + (idx - c * n);
+                float o = Bv[(size_t)c * V + j];
+                if (beta > 0) o += A[j] * og[(size_t)c * V + ent[j]];
+                og[(size_t)c * V + j] = o;
+            }
+            __syncthreads();
+        }
+        return;
+    }
+    // node state, double buffered: a[2][cap], p[2][cap], b[2][NC][cap]
+    float *sa = reinterpret_cast<float *>(smem4);
+    int *spn = reinterpret_cast<int *>(sa + 2 * cap);
+    float *sb = reinterpret_cast<float *>(spn + 2 * cap);
+    auto band_of = [&](int node) {  // largest beta with s_eo[beta] <= node
+        int lo = 0, hi = nb - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (s_eo[mid] <= node) lo = mid; else hi = mid - 1;
+        }
+        return lo;
+    };
+    for (int node = tid; node < NE; node += JNT) {
+        const int beta = band_of(node), j = s_e0[beta] + (node - s_eo[beta]);
+        sa[node] = (beta == 0) ? 0.f : A[j];
+        spn[node] = (beta == 0) ? node : s_eo[beta - 1] + (ent[j] - s_e0[beta - 1]);
+        for (int c = 0; c < NC; ++c) sb[(size_t)c * cap + node] = Bv[(size_t)c * V + j];
+    }
+    __syncthreads();
+    int cur = 0;
+    for (int hop = 1; hop < nb; hop <<= 1) {
+        const float *ra = sa + cur * cap, *rb = sb + (size_t)cur * NC * cap;
+        const int *rp = spn + cur * cap;
+        float *wa = sa + (cur ^ 1) * cap, *wb = sb + (size_t)(cur ^ 1) * NC * cap;
+        int *wp = spn + (cur ^ 1) * cap;
+        for (int node = tid; node < NE; node += JNT) {
+            const int p = rp[node];
+            const float an = ra[node];
+            wa[node] = an * ra[p];
+            wp[node] = rp[p];
+            for (int c = 0; c < NC; ++c) wb[(size_t)c * cap + node] = fmaf(an, rb[(size_t)c * cap + p], rb[(size_t)c * cap + node]);
+        }
+        __syncthreads();
+        cur ^= 1;
+    }
+    const float *rb = sb + (size_t)cur * NC * cap;
+    for (int node = tid; node < NE; node += JNT) {
+        const int beta = band_of(node), j = s_e0[beta] + (node - s_eo[beta]);
+        for (int c = 0; c < NC; ++c) og[(size_t)c * V + j] = rb[(size_t)c * cap + node];
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ D3 epilogues
 __device__ __forceinline__ float down_value(const float *A, const int *ent, const float *Bv, const float *og, int i) {
     const float a = A[i];
@@ -635,8 +727,13 @@ __global__ void zero_root_weight_kernel(float *w, int V, int B) {
 
 // ------------------------------------------------------------------------------------------------ host side
 // Band limits (host side, functions of the image size only).
-int plan_pmax(int V) { return V <= (1 << 17) ? 1792 : 3072; }   // positions per band (shared-memory band state, < 4096)
-constexpr int PLAN_KDIV = 32;                                     // a band holds at most ceil(n_levels / 32) levels
+#include <stdlib.h>
+int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+int plan_pmax(int V) { return env_int("FEDICRA_PLAN_PMAX", V <= (1 << 17) ? 2560 : 3072); }  // positions per band (< 4096)
+#define PLAN_KDIV env_int("FEDICRA_PLAN_KDIV", 32)               // a band holds at most ceil(n_levels / KDIV) levels
 int plan_grid(int V) {                                            // upper bound of the number of bands
     const int pm = plan_pmax(V);
     long long g = 2LL * ((V + pm - 1) / pm) + PLAN_KDIV + 2;
@@ -691,8 +788,15 @@ int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int
     FEDICRA_CHECK_LAUNCH("stitch_up_kernel");
     sweep_kernel<MODE, true><<<dim3(nb, B), nthr_sweep, smem, st>>>(t, a, pcap);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U3D1>");
-    stitch_down_kernel<<<B, NT, smem_d2, st>>>(t, k, a, outE, slot_shift);
-    FEDICRA_CHECK_LAUNCH("stitch_down_kernel");
+    {
+        // all boundary vertices of an image in shared memory: 2 buffers x (NC + 2) words each
+        const int cap = (int)((200 * 1024) / (2 * (NC + 2) * sizeof(float))) / 32 * 32;
+        const size_t smem_j = (size_t)cap * 2 * (NC + 2) * sizeof(float) + 16;
+        if (set_smem(stitch_down_jump_kernel, smem_j, "stitch_down_jump_kernel")) return -2;
+        stitch_down_jump_kernel<<<B, JNT, smem_j, st>>>(t, k, a, outE, cap);
+        FEDICRA_CHECK_LAUNCH("stitch_down_jump_kernel");
+    }
+    (void)smem_d2;
     return 0;
 }
 
