@@ -59,37 +59,43 @@ __device__ __forceinline__ bool band_geom(const TreeView &t, int b, int beta, in
 // Band plan: consecutive levels are grouped greedily so that a band holds at most `pmax` positions (it must fit the
 // shared-memory band state) and at most ceil(n_levels / kdiv) levels (the length of the parallel phases); if that needs
 // more than MAXBANDS bands both limits are doubled (oversized bands then run on global memory).  One warp per image.
-__global__ void band_plan_kernel(const int *__restrict__ level_start, const int *__restrict__ n_levels, int V, int pmax,
-                                 int kdiv, int *__restrict__ bands) {
-    const int b = blockIdx.x, lane = threadIdx.x;
-    const int *ls = level_start + (size_t)b * (V + 1);
+constexpr int PLAN_LSCAP = 8192;  // level starts cached in shared memory by the planner
+
+__global__ void __launch_bounds__(256)
+band_plan_kernel(const int *__restrict__ level_start, const int *__restrict__ n_levels, int V, int pmax, int kdiv,
+                 int *__restrict__ bands) {
+    __shared__ int s_ls[PLAN_LSCAP + 1];
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int *gls = level_start + (size_t)b * (V + 1);
     int *plan = bands + (size_t)b * PLAN_STRIDE;
     const int nl = n_levels[b];
+    const bool cached = nl <= PLAN_LSCAP;
+    if (cached)
+        for (int L = tid; L <= nl; L += 256) s_ls[L] = gls[L];
+    __syncthreads();
+    if (tid != 0) return;
+    const int *ls = cached ? s_ls : gls;
     int kmax = max(4, (nl + kdiv - 1) / kdiv);
     while (true) {
-        // The cut points are sequential, so every lane runs the same greedy walk; level ends are fetched 32 at a time
-        // (one coalesced load) and handed over by shuffle.  Only lane 0 writes.
-        int nb = 0, band_first = 0, band_pos0 = 0, prev_end = 0;
+        // the cut points are sequential, but each one is a binary search: the band starting at level L0 ends at the
+        // largest L1 with L1 - L0 <= kmax and ls[L1] - ls[L0] <= pmax (at least one level)
+        int nb = 0, L0 = 0;
         bool overflow = false;
-        if (lane == 0) plan[1] = 0;
-        for (int base = 0; base < nl && !overflow; base += 32) {
-            const int mine = (base + lane < nl) ? ls[base + lane + 1] : 0;  // end of level base+lane
-            const int kend = min(32, nl - base);
-            for (int k = 0; k < kend; ++k) {
-                const int end = __shfl_sync(0xffffffffu, mine, k), l = base + k;
-                if (l > band_first && ((end - band_pos0) > pmax || (l - band_first) >= kmax)) {  // close before level l
-                    ++nb;
-                    if (nb >= MAXBANDS) { overflow = true; break; }
-                    band_first = l;
-                    band_pos0 = prev_end;
-                    if (lane == 0) plan[1 + nb] = l;
-                }
-                prev_end = end;
+        while (L0 < nl) {
+            if (nb >= MAXBANDS) { overflow = true; break; }
+            plan[1 + nb] = L0;
+            const int p0 = ls[L0];
+            int lo = L0 + 1, hi = min(L0 + kmax, nl);
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (ls[mid] - p0 <= pmax) lo = mid; else hi = mid - 1;
             }
+            L0 = lo;
+            ++nb;
         }
         if (!overflow) {
-            ++nb;
-            if (lane == 0) { plan[0] = nb; plan[1 + nb] = nl; }
+            plan[0] = nb;
+            plan[1 + nb] = nl;
             return;
         }
         pmax *= 2;
@@ -788,15 +794,17 @@ int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int
     FEDICRA_CHECK_LAUNCH("stitch_up_kernel");
     sweep_kernel<MODE, true><<<dim3(nb, B), nthr_sweep, smem, st>>>(t, a, pcap);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U3D1>");
-    {
+    if (V <= (1 << 17)) {
         // all boundary vertices of an image in shared memory: 2 buffers x (NC + 2) words each
         const int cap = (int)((200 * 1024) / (2 * (NC + 2) * sizeof(float))) / 32 * 32;
         const size_t smem_j = (size_t)cap * 2 * (NC + 2) * sizeof(float) + 16;
         if (set_smem(stitch_down_jump_kernel, smem_j, "stitch_down_jump_kernel")) return -2;
         stitch_down_jump_kernel<<<B, JNT, smem_j, st>>>(t, k, a, outE, cap);
         FEDICRA_CHECK_LAUNCH("stitch_down_jump_kernel");
+    } else {  // larger images: the boundary does not fit; stream it band by band
+        stitch_down_kernel<<<B, NT, smem_d2, st>>>(t, k, a, outE, slot_shift);
+        FEDICRA_CHECK_LAUNCH("stitch_down_kernel");
     }
-    (void)smem_d2;
     return 0;
 }
 
@@ -807,7 +815,7 @@ extern "C" size_t fedicra_band_plan_ints(int B) { return B > 0 ? (size_t)B * PLA
 extern "C" int fedicra_band_plan(const int *level_start, const int *n_levels, int B, int V, int *bands, void *stream) {
     FEDICRA_REQUIRE(level_start && n_levels && bands, "band_plan: null pointer");
     FEDICRA_REQUIRE(B > 0 && V > 0, "band_plan: bad sizes B=%d V=%d", B, V);
-    band_plan_kernel<<<B, 32, 0, (cudaStream_t)stream>>>(level_start, n_levels, V, plan_pmax(V), PLAN_KDIV, bands);
+    band_plan_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(level_start, n_levels, V, plan_pmax(V), PLAN_KDIV, bands);
     FEDICRA_CHECK_LAUNCH("band_plan_kernel");
     return 0;
 }
