@@ -393,38 +393,37 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 constexpr int SCAPW = 512;    // level width staged in shared memory by the two stitch kernels
 constexpr int NSTAGE = 4;     // staging buffers: operands are fetched NSTAGE-1 bands ahead (one L2 round trip ~ 2 bands)
 
-// ------------------------------------------------------------------------------------------------ U2: stitch upward
-// One CTA per image walks the bands from the deepest to the shallowest.  Per band (two barriers):
-//   A  S = segmented inclusive scan over the band's last level E of A[j] * X[j], segments = runs of equal entry(j)
-//      (32 entries per warp pass, shuffles only)
-//   B  for every j' of the last level of the band above: X'[j'] = base[j'] + the run's total, read off S at the run's end
-//      inside every 32-entry chunk it overlaps.
-// Operands are contiguous slices of position-indexed arrays, fetched by cp.async NSTAGE-1 bands ahead.
-__global__ void __launch_bounds__(NT) stitch_up_kernel(TreeView t, Consts k, SweepArgs a, int slot_shift) {
+// ------------------------------------------------------------------------------------------------ U2 / D2: stitching
+// The band-to-band recurrences are sequential over the ~40 bands of an image but independent across channels, and a
+// band's last level is only ~50 vertices wide.  So ONE WARP owns one (image, channel): no block barrier, no other warp
+// to wait for, the per-band step is a few dozen instructions on shared memory.  Operands are contiguous slices of
+// position-indexed arrays, fetched by cp.async NSTAGE-1 bands ahead.
+//
+// U2 (deepest band first): X'[j'] = base[j'] + sum_{j in E(beta), entry(j) = j'} A[j] * X[j] for j' in E(beta-1): a warp
+// segmented inclusive scan of A*X over E(beta) keyed by entry(j), carried across 32-entry chunks, leaves every run's
+// total at the run's last entry, where j' picks it up (run bounds rs/re come from consts_kernel).  Fixed summation order.
+__global__ void __launch_bounds__(32) stitch_up_kernel(TreeView t, Consts k, SweepArgs a) {
     extern __shared__ float4 smem4[];
     __shared__ int s_e0[MAXBANDS], s_e1[MAXBANDS];  // last level of every band
-    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = t.V, NC = a.NC;
+    const int c = blockIdx.x, b = blockIdx.y, lane = threadIdx.x, V = t.V, NC = a.NC;
     const int *ls = t.ls + (size_t)b * (V + 1);
     const float *A = k.A + (size_t)b * V;
     const int *ent = k.ent + (size_t)b * V;
     const int *rs = k.run_s + (size_t)b * V, *re = k.run_e + (size_t)b * V;
-    const size_t img = (size_t)b * NC * V;
-    float *Xg = a.X + img;
+    float *Xg = a.X + ((size_t)b * NC + c) * V;
     const int *plan = t.bands + (size_t)b * PLAN_STRIDE;
     const int nb = plan[0];
-    for (int beta = tid; beta < nb; beta += NT) {
+    for (int beta = lane; beta < nb; beta += 32) {
         const int L1 = plan[2 + beta];
         s_e0[beta] = ls[L1 - 1];
         s_e1[beta] = ls[L1];
     }
-    // shared memory: NSTAGE staging buffers {A[E], ent[E], base X[NC][E'], rs[E'], re[E']} + X[2][NC] + S[NC], SCAPW each
+    // shared memory: NSTAGE staging buffers {A[E], ent[E], base X[E'], rs[E'], re[E']} + X[2] + S, SCAPW entries each
     float *base = reinterpret_cast<float *>(smem4);
-    const int stage_words = (NC + 4) * SCAPW;
-    float *sX[2] = {base + NSTAGE * stage_words, base + NSTAGE * stage_words + NC * SCAPW};
-    float *sS = base + NSTAGE * stage_words + 2 * NC * SCAPW;
-    const int SLOTS = 1 << slot_shift, c = tid >> slot_shift, slot = tid & (SLOTS - 1);
-    const bool ch_active = c < NC;
-    __syncthreads();
+    const int stage_words = 5 * SCAPW;
+    float *sX[2] = {base + NSTAGE * stage_words, base + NSTAGE * stage_words + SCAPW};
+    float *sS = base + NSTAGE * stage_words + 2 * SCAPW;
+    __syncwarp();
 
     // step `beta` consumes X of E(beta) and produces X of E(beta-1)
     auto fits = [&](int beta) { return (s_e1[beta] - s_e0[beta]) <= SCAPW && (s_e1[beta - 1] - s_e0[beta - 1]) <= SCAPW; };
@@ -432,14 +431,14 @@ __global__ void __launch_bounds__(NT) stitch_up_kernel(TreeView t, Consts k, Swe
         if (beta >= 1 && fits(beta)) {
             const int e0 = s_e0[beta], ne = s_e1[beta] - e0, q0 = s_e0[beta - 1], nq = s_e1[beta - 1] - q0;
             float *st = base + (beta % NSTAGE) * stage_words;
-            for (int i = tid; i < ne; i += NT) {
+            for (int i = lane; i < ne; i += 32) {
                 cp_async4(st + i, A + e0 + i);
                 cp_async4(st + SCAPW + i, ent + e0 + i);
             }
-            for (int i = tid; i < nq; i += NT) {
-                for (int cc = 0; cc < NC; ++cc) cp_async4(st + (2 + cc) * SCAPW + i, Xg + (size_t)cc * V + q0 + i);
-                cp_async4(st + (2 + NC) * SCAPW + i, rs + q0 + i);
-                cp_async4(st + (3 + NC) * SCAPW + i, re + q0 + i);
+            for (int i = lane; i < nq; i += 32) {
+                cp_async4(st + 2 * SCAPW + i, Xg + q0 + i);
+                cp_async4(st + 3 * SCAPW + i, rs + q0 + i);
+                cp_async4(st + 4 * SCAPW + i, re + q0 + i);
             }
         }
         cp_async_commit();
@@ -448,217 +447,120 @@ __global__ void __launch_bounds__(NT) stitch_up_kernel(TreeView t, Consts k, Swe
     int cur = 0;
     for (int d = 0; d < NSTAGE - 1; ++d) prefetch(nb - 1 - d);
     for (int beta = nb - 1; beta >= 1; --beta) {
-        cp_async_wait<NSTAGE - 2>();  // band beta's operands have landed (this thread's part) ...
-        __syncthreads();              // ... and everybody's; the previous step's X is complete
+        cp_async_wait<NSTAGE - 2>();
+        __syncwarp();
         prefetch(beta - (NSTAGE - 1));
         const int e0 = s_e0[beta], ne = s_e1[beta] - e0, q0 = s_e0[beta - 1], nq = s_e1[beta - 1] - q0;
         const bool sm = fits(beta), has_x = beta < nb - 1;
         const float *st = base + (beta % NSTAGE) * stage_words;
         const int *st_ent = reinterpret_cast<const int *>(st + SCAPW);
-        const int *st_rs = reinterpret_cast<const int *>(st + (2 + NC) * SCAPW);
-        const int *st_re = reinterpret_cast<const int *>(st + (3 + NC) * SCAPW);
-        // A: segmented scan, one (channel, 32-entry chunk) task per warp pass
-        if (has_x && ne <= SCAPW) {
-            const int nchunk = (ne + 31) >> 5;
-            for (int task = wid; task < NC * nchunk; task += NT / 32) {
-                const int cc = task / nchunk, jl = (task - cc * nchunk) * 32 + lane;
+        const int *st_rs = reinterpret_cast<const int *>(st + 3 * SCAPW);
+        const int *st_re = reinterpret_cast<const int *>(st + 4 * SCAPW);
+        if (has_x && sm) {
+            int carry_seg = -1;
+            float carry_val = 0.f;
+            for (int s0 = 0; s0 < ne; s0 += 32) {
+                const int jl = s0 + lane;
                 const bool ok = jl < ne;
-                const int seg = ok ? (sm ? st_ent[jl] : ent[e0 + jl]) : -1 - lane;
-                float v = ok ? (sm ? st[jl] : A[e0 + jl]) * sX[cur][cc * SCAPW + jl] : 0.f;
+                const int seg = ok ? st_ent[jl] : -2 - lane;
+                float v = ok ? st[jl] * sX[cur][jl] : 0.f;
+                if (lane == 0 && seg == carry_seg) v += carry_val;  // the run continues from the previous chunk
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
                     const float pv = __shfl_up_sync(0xffffffffu, v, o);
                     const int ps = __shfl_up_sync(0xffffffffu, seg, o);
                     if (lane >= o && ps == seg) v += pv;
                 }
-                if (ok) sS[cc * SCAPW + jl] = v;
+                if (ok) sS[jl] = v;
+                carry_seg = __shfl_sync(0xffffffffu, seg, 31);
+                carry_val = __shfl_sync(0xffffffffu, v, 31);
             }
+            __syncwarp();
         }
-        __syncthreads();
-        // B: complete X for the last level of the band above
-        if (ch_active) {
-            for (int jl = slot; jl < nq; jl += SLOTS) {
-                const int j = q0 + jl;
-                float acc = sm ? st[(2 + c) * SCAPW + jl] : Xg[(size_t)c * V + j];
-                if (has_x) {
-                    const int j0 = sm ? st_rs[jl] : rs[j], j1 = sm ? st_re[jl] : re[j];
-                    if (ne <= SCAPW) {
-                        for (int hi = j1; hi > j0;) {  // one partial per 32-entry chunk the run overlaps, from its end
-                            acc += sS[c * SCAPW + (hi - 1 - e0)];
-                            const int chunk_start = e0 + (((hi - 1 - e0) >> 5) << 5);
-                            hi = chunk_start;  // continue in the previous chunk (its last entry belongs to the run if > j0)
-                        }
-                    } else {  // oversized level: plain sequential run sum from global memory
-                        for (int jj = j0; jj < j1; ++jj) acc += A[jj] * Xg[(size_t)c * V + jj];
-                    }
+        for (int jl = lane; jl < nq; jl += 32) {
+            const int j = q0 + jl;
+            float acc = sm ? st[2 * SCAPW + jl] : Xg[j];
+            if (has_x) {
+                const int j0 = sm ? st_rs[jl] : rs[j], j1 = sm ? st_re[jl] : re[j];
+                if (sm) {
+                    if (j1 > j0) acc += sS[j1 - 1 - e0];
+                } else {  // oversized level: plain sequential run sum from global memory
+                    for (int jj = j0; jj < j1; ++jj) acc += A[jj] * Xg[jj];
                 }
-                Xg[(size_t)c * V + j] = acc;
-                if (nq <= SCAPW) sX[cur ^ 1][c * SCAPW + jl] = acc;
             }
+            Xg[j] = acc;
+            if (nq <= SCAPW) sX[cur ^ 1][jl] = acc;
         }
+        __syncwarp();
+        if (!sm) __threadfence_block();
         cur ^= 1;
     }
 }
 
-// ------------------------------------------------------------------------------------------------ D2: stitch downward
-__global__ void __launch_bounds__(NT) stitch_down_kernel(TreeView t, Consts k, SweepArgs a, float *outE, int slot_shift) {
+// D2 (shallowest band first): out[j] = B[j] + A[j] * out[entry(j)] for j in E(beta), entry(j) in E(beta-1).
+__global__ void __launch_bounds__(32) stitch_down_kernel(TreeView t, Consts k, SweepArgs a, float *outE) {
     extern __shared__ float4 smem4[];
     __shared__ int s_e0[MAXBANDS], s_e1[MAXBANDS];
-    const int b = blockIdx.x, tid = threadIdx.x, V = t.V, NC = a.NC;
+    const int c = blockIdx.x, b = blockIdx.y, lane = threadIdx.x, V = t.V, NC = a.NC;
     const int *ls = t.ls + (size_t)b * (V + 1);
     const float *A = k.A + (size_t)b * V;
     const int *ent = k.ent + (size_t)b * V;
-    const size_t img = (size_t)b * NC * V;
-    const float *Bv = a.Bv + img;
-    float *og = outE + img;
+    const float *Bv = a.Bv + ((size_t)b * NC + c) * V;
+    float *og = outE + ((size_t)b * NC + c) * V;
     const int *plan = t.bands + (size_t)b * PLAN_STRIDE;
     const int nb = plan[0];
-    for (int beta = tid; beta < nb; beta += NT) {
+    for (int beta = lane; beta < nb; beta += 32) {
         const int L1 = plan[2 + beta];
         s_e0[beta] = ls[L1 - 1];
         s_e1[beta] = ls[L1];
     }
-    // shared memory: NSTAGE staging buffers {Bv[NC], A, ent} + out[2][NC], SCAPW entries each
+    // shared memory: NSTAGE staging buffers {Bv, A, ent} + out[2], SCAPW entries each
     float *base = reinterpret_cast<float *>(smem4);
-    const int stage_words = (NC + 2) * SCAPW;
-    float *sO[2] = {base + NSTAGE * stage_words, base + NSTAGE * stage_words + NC * SCAPW};
-    __syncthreads();
+    const int stage_words = 3 * SCAPW;
+    float *sO[2] = {base + NSTAGE * stage_words, base + NSTAGE * stage_words + SCAPW};
+    __syncwarp();
 
     auto prefetch = [&](int beta) {
         if (beta < nb) {
             const int e0 = s_e0[beta], n = s_e1[beta] - e0;
             if (n <= SCAPW) {
                 float *st = base + (beta % NSTAGE) * stage_words;
-                for (int i = tid; i < n; i += NT) {
-                    for (int cc = 0; cc < NC; ++cc) cp_async4(st + cc * SCAPW + i, Bv + (size_t)cc * V + e0 + i);
-                    cp_async4(st + NC * SCAPW + i, A + e0 + i);
-                    cp_async4(st + (NC + 1) * SCAPW + i, ent + e0 + i);
+                for (int i = lane; i < n; i += 32) {
+                    cp_async4(st + i, Bv + e0 + i);
+                    cp_async4(st + SCAPW + i, A + e0 + i);
+                    cp_async4(st + 2 * SCAPW + i, ent + e0 + i);
                 }
             }
         }
         cp_async_commit();
     };
 
-    const int SLOTS = 1 << slot_shift, c = tid >> slot_shift, slot = tid & (SLOTS - 1);
-    const bool ch_active = c < NC;
     int cur = 0, pe0 = 0, pn = 0;
     for (int d = 0; d < NSTAGE - 1; ++d) prefetch(d);
     for (int beta = 0; beta < nb; ++beta) {
         cp_async_wait<NSTAGE - 2>();
-        __syncthreads();          // band beta's operands are in shared memory and the previous band's outputs complete
+        __syncwarp();
         prefetch(beta + NSTAGE - 1);
         const int e0 = s_e0[beta], n = s_e1[beta] - e0;
         const bool sm = n <= SCAPW;
         const float *st = base + (beta % NSTAGE) * stage_words;
-        const int *st_ent = reinterpret_cast<const int *>(st + (NC + 1) * SCAPW);
-        if (ch_active) {
-            for (int jl = slot; jl < n; jl += SLOTS) {
-                const int j = e0 + jl;
-                float o = sm ? st[c * SCAPW + jl] : Bv[(size_t)c * V + j];
-                if (beta > 0) {
-                    const int en = sm ? st_ent[jl] : ent[j];
-                    const float aj = sm ? st[NC * SCAPW + jl] : A[j];
-                    o += aj * (pn <= SCAPW ? sO[cur][c * SCAPW + (en - pe0)] : og[(size_t)c * V + en]);
-                }
-                og[(size_t)c * V + j] = o;
-                if (sm) sO[cur ^ 1][c * SCAPW + jl] = o;
+        const int *st_ent = reinterpret_cast<const int *>(st + 2 * SCAPW);
+        for (int jl = lane; jl < n; jl += 32) {
+            const int j = e0 + jl;
+            float o = sm ? st[jl] : Bv[j];
+            if (beta > 0) {
+                const int en = sm ? st_ent[jl] : ent[j];
+                const float aj = sm ? st[SCAPW + jl] : A[j];
+                o = fmaf(aj, (pn <= SCAPW ? sO[cur][en - pe0] : og[en]), o);
             }
+            og[j] = o;
+            if (sm) sO[cur ^ 1][jl] = o;
         }
+        __syncwarp();
+        if (!sm) __threadfence_block();
         cur ^= 1;
         pe0 = e0;
         pn = n;
-    }
-}
-
-// ------------------------------------------------------------------------------------------------ D2 by pointer jumping
-// The band-to-band recurrence out[j] = B[j] + A[j] * out[entry(j)] over the bands' last levels is a chain of affine maps
-// in which every value depends on ONE value of the band above.  Such maps compose into maps of the same shape, so the
-// ~40 sequential band steps collapse into ceil(log2 nb) rounds of "absorb the map of the vertex I point to":
-//   (a, p, b) <- (a * a[p], p[p], b + a * b[p])         band-0 vertices are terminal: a = 0, p = self.
-// All boundary vertices of an image (a few thousand) sit in shared memory; one CTA per image, one barrier per round.
-constexpr int JNT = 1024;
-
-__global__ void __launch_bounds__(JNT) stitch_down_jump_kernel(TreeView t, Consts k, SweepArgs a, float *outE, int cap) {
-    extern __shared__ float4 smem4[];
-    __shared__ int s_e0[MAXBANDS], s_eo[MAXBANDS + 1];  // first position / first node index of every band's last level
-    const int b = blockIdx.x, tid = threadIdx.x, V = t.V, NC = a.NC;
-    const int *ls = t.ls + (size_t)b * (V + 1);
-    const float *A = k.A + (size_t)b * V;
-    const int *ent = k.ent + (size_t)b * V;
-    const size_t img = (size_t)b * NC * V;
-    const float *Bv = a.Bv + img;
-    float *og = outE + img;
-    const int *plan = t.bands + (size_t)b * PLAN_STRIDE;
-    const int nb = plan[0];
-    for (int beta = tid; beta < nb; beta += JNT) {  // every band's last level: first position and width (parallel loads)
-        const int L1 = plan[2 + beta];
-        const int e0 = ls[L1 - 1];
-        s_e0[beta] = e0;
-        s_eo[beta + 1] = ls[L1] - e0;
-    }
-    __syncthreads();
-    if (tid == 0) {  // widths -> node offsets (nb <= 256 shared-memory adds)
-        int acc = 0;
-        s_eo[0] = 0;
-        for (int beta = 0; beta < nb; ++beta) {
-            acc += s_eo[beta + 1];
-            s_eo[beta + 1] = acc;
-        }
-    }
-    __syncthreads();
-    const int NE = s_eo[nb];
-    if (NE > cap) {  // does not fit: band-by-band walk straight on global memory (rare: very wide levels)
-        for (int beta = 0; beta < nb; ++beta) {
-            const int e0 = s_e0[beta], n = s_eo[beta + 1] - s_eo[beta];
-            for (int idx = tid; idx < n * NC; idx += JNT) {
-                const int c = idx / n, j = e0 + (idx - c * n);
-                float o = Bv[(size_t)c * V + j];
-                if (beta > 0) o += A[j] * og[(size_t)c * V + ent[j]];
-                og[(size_t)c * V + j] = o;
-            }
-            __syncthreads();
-        }
-        return;
-    }
-    // node state, double buffered: a[2][cap], p[2][cap], b[2][NC][cap]
-    float *sa = reinterpret_cast<float *>(smem4);
-    int *spn = reinterpret_cast<int *>(sa + 2 * cap);
-    float *sb = reinterpret_cast<float *>(spn + 2 * cap);
-    auto band_of = [&](int node) {  // largest beta with s_eo[beta] <= node
-        int lo = 0, hi = nb - 1;
-        while (lo < hi) {
-            const int mid = (lo + hi + 1) >> 1;
-            if (s_eo[mid] <= node) lo = mid; else hi = mid - 1;
-        }
-        return lo;
-    };
-    for (int node = tid; node < NE; node += JNT) {
-        const int beta = band_of(node), j = s_e0[beta] + (node - s_eo[beta]);
-        sa[node] = (beta == 0) ? 0.f : A[j];
-        spn[node] = (beta == 0) ? node : s_eo[beta - 1] + (ent[j] - s_e0[beta - 1]);
-        for (int c = 0; c < NC; ++c) sb[(size_t)c * cap + node] = Bv[(size_t)c * V + j];
-    }
-    __syncthreads();
-    int cur = 0;
-    for (int hop = 1; hop < nb; hop <<= 1) {
-        const float *ra = sa + cur * cap, *rb = sb + (size_t)cur * NC * cap;
-        const int *rp = spn + cur * cap;
-        float *wa = sa + (cur ^ 1) * cap, *wb = sb + (size_t)(cur ^ 1) * NC * cap;
-        int *wp = spn + (cur ^ 1) * cap;
-        for (int node = tid; node < NE; node += JNT) {
-            const int p = rp[node];
-            const float an = ra[node];
-            wa[node] = an * ra[p];
-            wp[node] = rp[p];
-            for (int c = 0; c < NC; ++c) wb[(size_t)c * cap + node] = fmaf(an, rb[(size_t)c * cap + p], rb[(size_t)c * cap + node]);
-        }
-        __syncthreads();
-        cur ^= 1;
-    }
-    const float *rb = sb + (size_t)cur * NC * cap;
-    for (int node = tid; node < NE; node += JNT) {
-        const int beta = band_of(node), j = s_e0[beta] + (node - s_eo[beta]);
-        for (int c = 0; c < NC; ++c) og[(size_t)c * V + j] = rb[(size_t)c * cap + node];
     }
 }
 
@@ -778,33 +680,22 @@ template <int MODE>
 int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int B, cudaStream_t st) {
     const int V = t.V, nb = plan_grid(V), NC = a.NC;
     const int per_pos = (NC + 3) * 4;
-    int ncp = 1, slot_shift = 8;  // NT = 256 threads = ncp channel groups x (256 >> log2 ncp) slots
-    while (ncp < NC) { ncp <<= 1; --slot_shift; }
     if (NC * SWEEP_SLOTS > 1024) return fedicra_fail(-1, "tree filter: %d channels per sweep exceed %d", NC, 1024 / SWEEP_SLOTS);
     const int nthr_sweep = NC * SWEEP_SLOTS;
     const int pcap = plan_pmax(V);
     const size_t smem = (size_t)pcap * per_pos + (LSCAP + 1) * sizeof(int) + 16;
     if (set_smem(sweep_kernel<MODE, false>, smem, "sweep_kernel") || set_smem(sweep_kernel<MODE, true>, smem, "sweep_kernel")) return -2;
-    const size_t smem_u2 = (size_t)(NSTAGE * (NC + 4) + 3 * NC) * SCAPW * sizeof(float) + 16;
-    const size_t smem_d2 = (size_t)(NSTAGE * (NC + 2) + 2 * NC) * SCAPW * sizeof(float) + 16;
+    const size_t smem_u2 = (size_t)(NSTAGE * 5 + 3) * SCAPW * sizeof(float) + 16;
+    const size_t smem_d2 = (size_t)(NSTAGE * 3 + 2) * SCAPW * sizeof(float) + 16;
     if (set_smem(stitch_up_kernel, smem_u2, "stitch_up_kernel") || set_smem(stitch_down_kernel, smem_d2, "stitch_down_kernel")) return -2;
     sweep_kernel<MODE, false><<<dim3(nb, B), nthr_sweep, smem, st>>>(t, a, pcap);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U1>");
-    stitch_up_kernel<<<B, NT, smem_u2, st>>>(t, k, a, slot_shift);
+    stitch_up_kernel<<<dim3(NC, B), 32, smem_u2, st>>>(t, k, a);
     FEDICRA_CHECK_LAUNCH("stitch_up_kernel");
     sweep_kernel<MODE, true><<<dim3(nb, B), nthr_sweep, smem, st>>>(t, a, pcap);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U3D1>");
-    if (V <= (1 << 17)) {
-        // all boundary vertices of an image in shared memory: 2 buffers x (NC + 2) words each
-        const int cap = (int)((200 * 1024) / (2 * (NC + 2) * sizeof(float))) / 32 * 32;
-        const size_t smem_j = (size_t)cap * 2 * (NC + 2) * sizeof(float) + 16;
-        if (set_smem(stitch_down_jump_kernel, smem_j, "stitch_down_jump_kernel")) return -2;
-        stitch_down_jump_kernel<<<B, JNT, smem_j, st>>>(t, k, a, outE, cap);
-        FEDICRA_CHECK_LAUNCH("stitch_down_jump_kernel");
-    } else {  // larger images: the boundary does not fit; stream it band by band
-        stitch_down_kernel<<<B, NT, smem_d2, st>>>(t, k, a, outE, slot_shift);
-        FEDICRA_CHECK_LAUNCH("stitch_down_kernel");
-    }
+    stitch_down_kernel<<<dim3(NC, B), 32, smem_d2, st>>>(t, k, a, outE);
+    FEDICRA_CHECK_LAUNCH("stitch_down_kernel");
     return 0;
 }
 
