@@ -265,7 +265,7 @@ def run_reference(args, wl):
     sample = (f"{sample_b} of the {B} images of one batch per step; Gated CRF = unfold formulation of gate_crf_loss.py in "
               f"torch CPU, MST = {'the reference boruvka.cpp (oracle/_ref)' if kind == 'reference' else 'C port of boruvka.cpp'}"
               f", BFS/refine = C restatement, {cores} threads")
-    print(json.dumps({
+    emit(json.dumps({
         "impl": "reference", "metric": "GatedCRF+TreeEnergy loss fwd+bwd images/s", "value": value, "unit": "images/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -296,7 +296,7 @@ def run_ours(args, wl):
     eager_step = GpuStep(C, H, W, world, B)
     step = eager_step
     graphed = False
-    if not args.no_graph and world == 1:  # (the 2-scalar all-reduce of N>1 stays eager: NCCL capture is not needed)
+    if not args.no_graph:  # N > 1: the 2-scalar NCCL all-reduce of the normaliser is captured with the rest
         try:
             step = GraphedStep(eager_step, data)
             data = step.static_in
@@ -358,13 +358,23 @@ def run_ours(args, wl):
     h2d = sum(v.numel() * v.element_size() for v in pinned.values())
     d2h = 4 + sum(g.numel() * g.element_size() for g in grads_host)
 
-    if rank != 0:
+    def teardown():
+        """All ranks together.  A captured graph keeps NCCL kernels of the communicator alive, so it is released first."""
         if world > 1:
+            dist.barrier()
+            if graphed:
+                step.graph.reset()
+            torch.cuda.synchronize()
             dist.destroy_process_group()
+
+    if rank != 0:
+        teardown()  # (waits for rank 0's attribution pass)
         return
 
     # ---- attribution + roofline of the dominant kernel group (rank 0, separate instrumented pass)
-    ops_prof = profile_ops(eager_step, data, min(args.steps, 10), flush_buf)
+    # (rank 0 alone from here on: the attribution pass uses a step WITHOUT the cross-rank all-reduce)
+    local_step = eager_step if world == 1 else GpuStep(C, H, W, 1, B)
+    ops_prof = profile_ops(local_step, data, min(args.steps, 10), flush_buf)
     ab = algorithmic_bytes(Cin, C, H, W)
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
@@ -417,7 +427,7 @@ def run_ours(args, wl):
                          f"C restatement of bfs/refine) on {cores} threads"}
 
     n_images = B * world * args.steps
-    print(json.dumps({
+    emit(json.dumps({
         "metric": "GatedCRF+TreeEnergy loss fwd+bwd images/s", "value": n_images / (total_ms * 1e-3), "unit": "images/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -436,11 +446,28 @@ def run_ours(args, wl):
         "kernel_groups": ops_prof,
         "cpu_baseline": cpu,
     }))
-    if world > 1:
-        dist.destroy_process_group()
+    teardown()
+
+
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The one JSON line goes to the real stdout; everything else written to fd 1 (NCCL's version banner, library
+    chatter) was redirected to stderr at start-up."""
+    data = (line + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line + "\n")
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
