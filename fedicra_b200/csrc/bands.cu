@@ -40,11 +40,13 @@ struct TreeView {
 
 constexpr int MAXBANDS = 256;
 constexpr int PLAN_STRIDE = MAXBANDS + 2;
+constexpr int NBCAP = 36;        // most bands per image the planner produces (the resident kernel's grid is NBCAP + 1 wide)
 
 struct Consts {  // per (tree, edge weights), all [B,V] in position order
     float *A;           // product of w from i up to and including its band's first-level ancestor
     int *ent;           // entry(i): position of the parent of that ancestor (in the last level of the band above)
     int *run_s, *run_e; // for j' in a band's last level: the run of positions j in the NEXT band's last level with entry(j) = j'
+    int *pk;            // packed band-local topology: parent << 16 | first child << 3 | #children (offsets from the band's p0)
 };
 
 __device__ __forceinline__ bool band_geom(const TreeView &t, int b, int beta, int &L0, int &L1, int &nb) {
@@ -57,13 +59,16 @@ __device__ __forceinline__ bool band_geom(const TreeView &t, int b, int beta, in
 }
 
 // Band plan: consecutive levels are grouped greedily so that a band holds at most `pmax` positions (it must fit the
-// shared-memory band state) and at most ceil(n_levels / kdiv) levels (the length of the parallel phases); if that needs
-// more than MAXBANDS bands both limits are doubled (oversized bands then run on global memory).  One warp per image.
+// shared-memory band state) and at most ceil(n_levels / kdiv) levels (the length of the parallel phases).  If that needs
+// more than `nbcap` bands the level limit grows by a quarter and the plan is redone; after six such rounds the position
+// limit grows too (oversized bands then run on global memory).  One thread per image, level starts cached in shared
+// memory.  (Cutting at locally narrow levels was tried: level widths vary too smoothly for it to shrink the stitched
+// state.)
 constexpr int PLAN_LSCAP = 8192;  // level starts cached in shared memory by the planner
 
 __global__ void __launch_bounds__(256)
 band_plan_kernel(const int *__restrict__ level_start, const int *__restrict__ n_levels, int V, int pmax, int kdiv,
-                 int *__restrict__ bands) {
+                 int nbcap, int *__restrict__ bands) {
     __shared__ int s_ls[PLAN_LSCAP + 1];
     const int b = blockIdx.x, tid = threadIdx.x;
     const int *gls = level_start + (size_t)b * (V + 1);
@@ -75,14 +80,14 @@ band_plan_kernel(const int *__restrict__ level_start, const int *__restrict__ n_
     __syncthreads();
     if (tid != 0) return;
     const int *ls = cached ? s_ls : gls;
-    int kmax = max(4, (nl + kdiv - 1) / kdiv);
+    int kmax = max(4, (nl + kdiv - 1) / kdiv), escalations = 0;
     while (true) {
         // the cut points are sequential, but each one is a binary search: the band starting at level L0 ends at the
         // largest L1 with L1 - L0 <= kmax and ls[L1] - ls[L0] <= pmax (at least one level)
         int nb = 0, L0 = 0;
         bool overflow = false;
         while (L0 < nl) {
-            if (nb >= MAXBANDS) { overflow = true; break; }
+            if (nb >= nbcap) { overflow = true; break; }
             plan[1 + nb] = L0;
             const int p0 = ls[L0];
             int lo = L0 + 1, hi = min(L0 + kmax, nl);
@@ -98,8 +103,8 @@ band_plan_kernel(const int *__restrict__ level_start, const int *__restrict__ n_
             plan[1 + nb] = nl;
             return;
         }
-        pmax *= 2;
-        kmax *= 2;
+        kmax += kmax / 4 + 1;
+        if (++escalations > 6) pmax += pmax / 4;
     }
 }
 
@@ -142,6 +147,16 @@ __device__ void consts_body(const TreeView &t, const Consts &k, int b, int beta,
     }
     if (SMEM)
         for (int i = p0 + tid; i < p1; i += NT) { gA[i] = sA[i - p0]; gE[i] = sE[i - p0]; }
+    {   // packed topology for the resident kernel (parents above / children below the band are never followed)
+        const int4 *child = t.child + (size_t)b * V;
+        int *gpk = k.pk + (size_t)b * V;
+        for (int i = p0 + tid; i < p1; i += NT) {
+            const int4 ch = child[i];
+            const int cnt = child_count(ch), par = SMEM ? sP[i - p0] : pp[i];
+            const int pl = (par >= p0) ? par - p0 : 0, cl = (cnt > 0 && ch.x < p1) ? ch.x - p0 : 0;
+            gpk[i] = (pl << 16) | ((cl & 0x1fff) << 3) | cnt;
+        }
+    }
     // runs of this band's last-level vertices under each vertex of the previous band's last level (contiguous in the
     // canonical order); written by this CTA for the level just above the band
     if (beta == 0) return;
@@ -636,23 +651,42 @@ __global__ void zero_root_weight_kernel(float *w, int V, int B) {
 // ------------------------------------------------------------------------------------------------ host side
 // Band limits (host side, functions of the image size only).
 #include <stdlib.h>
+#include <string.h>
 int env_int(const char *name, int dflt) {
     const char *v = getenv(name);
     return (v && *v) ? atoi(v) : dflt;
 }
-int plan_pmax(int V) { return env_int("FEDICRA_PLAN_PMAX", V <= (1 << 17) ? 2560 : 3072); }  // positions per band (< 4096)
-#define PLAN_KDIV env_int("FEDICRA_PLAN_KDIV", 32)               // a band holds at most ceil(n_levels / KDIV) levels
-int plan_grid(int V) {                                            // upper bound of the number of bands
+// most bands per image: 36 up to 2^17 pixels (37 CTAs per image x 12 images fill the GPU at three CTAs per SM), twice
+// that for larger images (their bands take a whole SM each)
+int plan_nbcap(int V) { return env_int("FEDICRA_PLAN_NBCAP", V <= (1 << 17) ? NBCAP : 2 * NBCAP); }
+// positions per band: what keeps three resident CTAs per SM at the 256^2 working size (3100 x 24 B + level cache;
+// 37 CTAs per image x 12 images = 444 = 3 x 148), and 1.35 x the mean band of an NBCAP-band plan for larger images
+// (the pk fields hold local offsets < 8192)
+int plan_pmax(int V) {
+    long long need = (long long)V * 135 / (100 * plan_nbcap(V)) + 1;
+    int pm = (int)(need < 3100 ? 3100 : (need > 8000 ? 8000 : need));
+    return env_int("FEDICRA_PLAN_PMAX", pm);
+}
+#define PLAN_KDIV env_int("FEDICRA_PLAN_KDIV", 30)               // a band holds at most ceil(n_levels / KDIV) levels
+int plan_grid(int V) { return plan_nbcap(V); }                    // upper bound of the number of bands
+constexpr size_t SMEM_MAX = 227 * 1024;
+// the multi-launch kernels keep (NC + 3) words per position; their shared-memory capacity may be below the plan's pmax
+int multi_pcap(int V, int NC) {
+    const long long fit = ((long long)SMEM_MAX - (LSCAP + 1) * 4 - 64) / ((NC + 3) * 4);
     const int pm = plan_pmax(V);
-    long long g = 2LL * ((V + pm - 1) / pm) + PLAN_KDIV + 2;
-    return (int)(g > MAXBANDS ? MAXBANDS : g);
+    const long long cap = fit < 4095 ? fit : 4095;   // 12-bit local offsets in the multi-launch kernels' packed topology
+    return (int)(cap < pm ? cap : pm);
 }
 
 struct Layout {
-    // saved (forward -> backward): A [V]; up, pos [(C+1),V]; ent, run_s, run_e [V]
-    static size_t saved_bytes(int B, int C, int V) { return (size_t)B * V * (1 + 2 * (C + 1) + 3) * 4; }
+    // saved (forward -> backward): A [V]; up, pos [(C+1),V]; ent, run_s, run_e, pk [V]
+    static size_t saved_bytes(int B, int C, int V) { return (size_t)B * V * (1 + 2 * (C + 1) + 4) * 4; }
     // work: upl, X, up, Bv, outE, slab  [NCmax,V] each
-    static size_t work_bytes(int B, int NCmax, int V) { return (size_t)B * V * 6 * NCmax * 4; }
+    // preceded by the resident kernel's sync words, 8 ints per image at a FIXED place (the head of the workspace, sized
+    // for the largest batch the API takes) so that no call's scratch ever lands on them: they must be zero before the
+    // first use and every launch leaves them at zero
+    static constexpr size_t SYNC_BYTES = (size_t)65536 * 8 * sizeof(int);
+    static size_t work_bytes(int B, int NCmax, int V) { return SYNC_BYTES + (size_t)B * V * 6 * NCmax * 4; }
 };
 
 Consts consts_view(void *saved, int B, int C, int V, float **up, float **pos) {
@@ -666,6 +700,7 @@ Consts consts_view(void *saved, int B, int C, int V, float **up, float **pos) {
     k.ent = ip;
     k.run_s = ip + n;
     k.run_e = ip + 2 * n;
+    k.pk = ip + 3 * n;
     return k;
 }
 
@@ -682,7 +717,7 @@ int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int
     const int per_pos = (NC + 3) * 4;
     if (NC * SWEEP_SLOTS > 1024) return fedicra_fail(-1, "tree filter: %d channels per sweep exceed %d", NC, 1024 / SWEEP_SLOTS);
     const int nthr_sweep = NC * SWEEP_SLOTS;
-    const int pcap = plan_pmax(V);
+    const int pcap = multi_pcap(V, NC);
     const size_t smem = (size_t)pcap * per_pos + (LSCAP + 1) * sizeof(int) + 16;
     if (set_smem(sweep_kernel<MODE, false>, smem, "sweep_kernel") || set_smem(sweep_kernel<MODE, true>, smem, "sweep_kernel")) return -2;
     const size_t smem_u2 = (size_t)(NSTAGE * 5 + 3) * SCAPW * sizeof(float) + 16;
@@ -699,14 +734,102 @@ int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int
     return 0;
 }
 
+#include "resident.cuh"
+
+// Which implementation serves fedicra_tree_filter_*: the resident kernel (default) or the multi-launch phases.
+bool use_resident() {
+    const char *v = getenv("FEDICRA_FILTER");
+    return !(v && strcmp(v, "multi") == 0);
+}
+
+// Shared memory of a resident CTA: band state (NC values + weight + packed topology per position) + level cache.
+size_t resident_smem(int pcap, int NC) { return (size_t)pcap * (NC + 2) * 4 + (LSCAP + 1) * sizeof(int) + 16; }
+
+__device__ long long g_prof[(NBMAX + 1) * PROF_SLOTS];   // phase timestamps of the last profiled launch (FEDICRA_PROF=1)
+
+template <int MODE, int NCT>
+int launch_resident(const TreeView &t, const Consts &k, ResidentArgs a, int B, cudaStream_t st) {
+    const int V = t.V, NC = a.NC, nthr = NC * RSLOTS, nbcap = plan_nbcap(V);
+    const int pcap = plan_pmax(V);
+    const size_t smem = resident_smem(pcap, NC);
+    if (nthr > 1024 || smem > SMEM_MAX || pcap > 8191 || nbcap > NBMAX) return 1;
+    static thread_local int cached_key[2] = {-1, -1}, cached_cap = 0;   // (device, nthr, smem) -> resident CTAs
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const int key0 = nthr * 64 + dev, key1 = (int)smem;
+    if (cached_key[0] != key0 || cached_key[1] != key1) {
+        if (set_smem(resident_kernel<MODE, NCT>, smem, "resident_kernel")) return -2;
+        int per_sm = 0, sms = 0;
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resident_kernel<MODE, NCT>, nthr, smem);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return fedicra_fail(-2, "resident_kernel: occupancy query failed: %s", cudaGetErrorString(e));
+        cached_key[0] = key0;
+        cached_key[1] = key1;
+        cached_cap = per_sm * sms;
+    }
+    const int chunk = cached_cap / (nbcap + 1);
+    if (chunk < 1) return 1;
+    a.pcap = pcap;
+    a.tcap = (int)((smem - 3 * (NBMAX + 2) * sizeof(int) - 64) / (8 + 4 * NC));
+    a.prof = nullptr;
+    if (env_int("FEDICRA_PROF", 0)) {
+        void *ptr = nullptr;
+        if (cudaGetSymbolAddress(&ptr, g_prof) == cudaSuccess) a.prof = (long long *)ptr;
+    }
+    const bool coop = env_int("FEDICRA_COOP", 1) != 0;
+    for (int b0 = 0; b0 < B; b0 += chunk) {
+        a.b0 = b0;
+        const int nbatch = (B - b0 < chunk) ? B - b0 : chunk;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(nbcap + 1, nbatch);
+        cfg.blockDim = dim3(nthr);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeCooperative;
+        attr[0].val.cooperative = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = coop ? 1 : 0;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, resident_kernel<MODE, NCT>, t, k, a);
+        fedicra_count_launches(1);
+        if (e != cudaSuccess) return fedicra_fail(-2, "resident_kernel: %s", cudaGetErrorString(e));
+        a.prof = nullptr;   // only the first chunk is profiled
+    }
+    return 0;
+}
+
+// Launches the resident kernel over the batch in chunks of as many images as fit on the GPU at once.
+// Returns 1 when the configuration cannot run resident (the caller then takes the multi-launch path).
+template <int MODE>
+int run_resident(const TreeView &t, const Consts &k, const ResidentArgs &a, int B, cudaStream_t st) {
+    switch (a.NC) {
+        case 1: return launch_resident<MODE, 1>(t, k, a, B, st);
+        case 2: return launch_resident<MODE, 2>(t, k, a, B, st);
+        case 3: return launch_resident<MODE, 3>(t, k, a, B, st);
+        case 4: return launch_resident<MODE, 4>(t, k, a, B, st);
+        case 5: return launch_resident<MODE, 5>(t, k, a, B, st);
+        case 6: return launch_resident<MODE, 6>(t, k, a, B, st);
+        case 8: return launch_resident<MODE, 8>(t, k, a, B, st);
+        default: return 1;   // other channel counts take the multi-launch phases
+    }
+}
+
 }  // namespace
+
+extern "C" int fedicra_debug_filter_profile(long long *h_out, int n) {
+    const int total = (NBMAX + 1) * PROF_SLOTS;
+    if (h_out == nullptr || n < total) return total;
+    cudaError_t e = cudaMemcpyFromSymbol(h_out, g_prof, sizeof(long long) * total);
+    if (e != cudaSuccess) return fedicra_fail(-2, "debug_filter_profile: %s", cudaGetErrorString(e));
+    return total;
+}
 
 extern "C" size_t fedicra_band_plan_ints(int B) { return B > 0 ? (size_t)B * PLAN_STRIDE : 0; }
 
 extern "C" int fedicra_band_plan(const int *level_start, const int *n_levels, int B, int V, int *bands, void *stream) {
     FEDICRA_REQUIRE(level_start && n_levels && bands, "band_plan: null pointer");
     FEDICRA_REQUIRE(B > 0 && V > 0, "band_plan: bad sizes B=%d V=%d", B, V);
-    band_plan_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(level_start, n_levels, V, plan_pmax(V), PLAN_KDIV, bands);
+    band_plan_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(level_start, n_levels, V, plan_pmax(V), PLAN_KDIV, plan_nbcap(V), bands);
     FEDICRA_CHECK_LAUNCH("band_plan_kernel");
     return 0;
 }
@@ -738,17 +861,24 @@ extern "C" int fedicra_tree_filter_forward(const float *feature_in, float *edge_
     float *fup, *fpos;
     Consts k = consts_view(saved, B, C, V, &fup, &fpos);
     const size_t n = (size_t)B * V * (2 * C > NC ? 2 * C : NC);
-    float *wk = (float *)workspace;
+    float *wk = (float *)((char *)workspace + Layout::SYNC_BYTES);
     SweepArgs a{feature_in, nullptr, C, NC, wk, wk + n, fup, wk + 2 * n, wk + 4 * n};
     float *outE = wk + 3 * n;
 
     zero_root_weight_kernel<<<(B + 127) / 128, 128, 0, st>>>(edge_weight, V, B);
     FEDICRA_CHECK_LAUNCH("zero_root_weight_kernel");
-    const int pcap_c = plan_pmax(V);
+    const int pcap_c = multi_pcap(V, 1);
     const size_t smem_c = (size_t)pcap_c * 16 + 16;
     if (set_smem(consts_kernel, smem_c, "consts_kernel")) return -2;
     consts_kernel<<<dim3(nb, B), NT, smem_c, st>>>(t, k, pcap_c);
     FEDICRA_CHECK_LAUNCH("consts_kernel");
+    if (use_resident()) {
+        int *sync = reinterpret_cast<int *>(workspace);
+        ResidentArgs ra{feature_in, fpos, fup, C, NC, wk + n, nullptr, wk + 2 * n, wk + 3 * n, wk + 4 * n, sync,
+                        feature_out, feature_aggr, weight_sum, 0, 0, 0, nullptr};
+        const int rc = run_resident<MODE_FWD>(t, k, ra, B, st);
+        if (rc <= 0) return rc;   // launched (0) or failed (<0); 1 = configuration not supported, take the phases below
+    }
     if (int rc = run_sweeps<MODE_FWD>(t, k, a, outE, B, st)) return rc;
     finish_forward_kernel<<<dim3((V + 255) / 256, B), 256, 0, st>>>(t, k, a.Bv, outE, C, fpos, feature_out, feature_aggr, weight_sum);
     FEDICRA_CHECK_LAUNCH("finish_forward_kernel");
@@ -770,9 +900,16 @@ extern "C" int fedicra_tree_filter_backward(const float *grad_out, const float *
     float *fup, *fpos;
     Consts k = consts_view(const_cast<void *>(saved), B, C, V, &fup, &fpos);
     const size_t n = (size_t)B * V * (2 * C > C + 1 ? 2 * C : C + 1);
-    float *wk = (float *)workspace;
+    float *wk = (float *)((char *)workspace + Layout::SYNC_BYTES);
     SweepArgs a{grad_out, fpos, C, NC, wk, wk + n, wk + 5 * n, wk + 2 * n, wk + 4 * n};
     float *outE = wk + 3 * n;
+    if (use_resident()) {
+        int *sync = reinterpret_cast<int *>(workspace);
+        ResidentArgs ra{grad_out, fpos, fup, C, NC, wk + n, wk + 5 * n, wk + 2 * n, wk + 3 * n, wk + 4 * n, sync,
+                        grad_feature, grad_weight, nullptr, 0, 0, 0, nullptr};
+        const int rc = run_resident<MODE_BWD>(t, k, ra, B, st);
+        if (rc <= 0) return rc;
+    }
     if (int rc = run_sweeps<MODE_BWD>(t, k, a, outE, B, st)) return rc;
     finish_backward_kernel<<<dim3((V + 255) / 256, B), 256, 0, st>>>(t, k, a.Bv, outE, a.up, fup, fpos, C, NC, grad_feature, grad_weight);
     FEDICRA_CHECK_LAUNCH("finish_backward_kernel");

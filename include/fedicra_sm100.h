@@ -175,6 +175,12 @@ int fedicra_tree_filter_backward(const float *grad_out, const float *edge_weight
                                  float *grad_feature, float *grad_weight, void *workspace, size_t workspace_bytes,
                                  void *stream);
 
+/* Telemetry of the resident filter kernel (no counterpart in the reference): with FEDICRA_PROF=1 in the environment the
+ * CTAs of the first image of a launch record %globaltimer at their phase boundaries.  Copies the last launch's
+ * [bands + 1][12] nanosecond stamps to the HOST buffer h_out (n = its capacity in elements; the required count is
+ * returned; synchronises the device). */
+int fedicra_debug_filter_profile(long long *h_out, int n);
+
 /* ------------------------------------------------------------------------------------------------ aggregation -- */
 /* Adaptive local aggregation, element-wise part of MyModel.set_weights (flower_common.py:590-602) over one flat
  * array: w <- clamp(w - eta*g*(s-p), 0, 1);  t <- p + (s-p)*w.   No fused multiply-add: bit-exact with torch.

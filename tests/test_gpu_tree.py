@@ -143,10 +143,18 @@ def test_filter_properties_at_512():
     ("uniform", 1, 2, 1, 1, 1, 1.0), ("uniform", 1, 2, 1, 1, 2, 1.0), ("quant8", 12, 2, 3, 256, 256, 50.0),
     ("uniform", 3, 3, 3, 256, 256, 0.3), ("quant8", 2, 3, 3, 512, 512, 1.0),
 ])
-def test_depth_banded_filter_vs_oracle(kind, B, C, D, H, W, inv_sigma):
-    """fedicra_tree_filter_forward/backward (csrc/bands.cu) against the sequential oracle, including degenerate trees:
-    paths (depth = V), combs, single vertices."""
+@pytest.mark.parametrize("impl", ["resident", "multi", "resident-global"])
+def test_depth_banded_filter_vs_oracle(kind, B, C, D, H, W, inv_sigma, impl, monkeypatch):
+    """fedicra_tree_filter_forward/backward (csrc/bands.cu, csrc/resident.cuh) against the sequential oracle, including
+    degenerate trees: paths (depth = V), combs, single vertices.  `resident` = one cooperative launch per filter,
+    `multi` = the phase-per-kernel version, `resident-global` = the resident kernel with a shared-memory budget so
+    small that every band and the stitcher take their global-memory code."""
     from fedicra_b200 import ops
+    monkeypatch.setenv("FEDICRA_FILTER", "multi" if impl == "multi" else "resident")
+    if impl == "resident-global":
+        if H * W > 70000:
+            pytest.skip("global-memory mode is exercised at the smaller sizes")
+        monkeypatch.setenv("FEDICRA_PLAN_PMAX", "48")
     emb, feat, gout, tree = _tree_case(kind, B, C, D, H, W, seed=5)
     V = H * W
     if V == 1:
