@@ -11,6 +11,7 @@
 // Also fuses MinimumSpanningTree._build_matrix_index / _build_feature_weight (LTF/modules/tree_filter.py:15-34): on the
 // implicit 4-connected grid the edge list is never materialised and the weights come straight from the embedding.
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -29,6 +30,9 @@ struct Ws {
     unsigned char *intree;  // [B,E]
     int *ncomp;      // [B]
     int *done;       // [B]
+    int *act;        // [B,2,V] active-vertex lists (vertices that still see another component), ping-pong
+    int *roots;      // [B,2,V] component-root lists, ping-pong
+    int *cnt;        // [B,4]   list lengths: act[0], act[1], roots[0], roots[1]
 };
 
 size_t ws_layout(int B, int V, int E, char *base, Ws *w) {
@@ -46,6 +50,9 @@ size_t ws_layout(int B, int V, int E, char *base, Ws *w) {
     t.intree = (unsigned char *)take((size_t)B * E);
     t.ncomp = (int *)take((size_t)B * sizeof(int));
     t.done = (int *)take((size_t)B * sizeof(int));
+    t.act = (int *)take((size_t)B * 2 * V * sizeof(int));
+    t.roots = (int *)take((size_t)B * 2 * V * sizeof(int));
+    t.cnt = (int *)take((size_t)B * 4 * sizeof(int));
     if (w) *w = t;
     return off;
 }
@@ -243,25 +250,37 @@ __global__ void grid_mask_kernel(Ws ws, unsigned char *__restrict__ mask, int H,
 
 // ---------------------------------------------------------------------------------------------------------------
 // Persistent variant for the implicit grid: ONE launch for the whole batch.  A thread-block cluster of CL CTAs owns an
-// image and runs every Boruvka round itself -- vertex-centric find (each vertex scans its <= 4 grid edges and issues at
-// most one atomicMin on its component), hook, pointer chase -- separated by cluster barriers instead of kernel
-// boundaries.  Same keys, same hooks, hence the same edge set as the multi-launch path (and as the reference).
+// image and runs every Boruvka round itself, separated by cluster barriers instead of kernel boundaries.  Same keys, same
+// hooks, hence the same edge set as the multi-launch path (and as the reference).
+//
+// The rounds work on two shrinking lists instead of on all V vertices:
+//   active vertices -- those that still have a neighbour in another component.  A vertex whose four neighbours are all in
+//                      its own component can never see an outgoing edge again (components only grow): it is dropped and
+//                      its label is set to DEAD, which its neighbours read as "same component as me" (they were, and
+//                      stay, in its component).  After a few rounds only the component boundaries are left.
+//   roots           -- the current components (one vertex id each); a third of them survive a round.
+// find  (active list): vertex-centric, each vertex scans its <= 4 grid edges and issues at most one 64-bit atomicMin on
+//                      its component; survivors are appended to the next active list (warp-aggregated atomicAdd).
+// hook  (root list):   every root follows its edge; of two roots that picked the same edge the larger one hooks.
+// chase (next active list): labels follow the hooks to the new roots; the cheapest-edge slots of the new roots are reset.
+// List order depends on atomics, the result does not: min is order-free and hooks depend on the minima only.
 constexpr int PNT = 512;
+constexpr int DEAD = -1;
 
 __global__ void __launch_bounds__(PNT)
 mst_grid_cluster_kernel(Ws ws, const float *__restrict__ embed, unsigned char *__restrict__ mask, int D, int H, int W,
                         int max_rounds) {
     cg::cluster_group cluster = cg::this_cluster();
     const int CL = (int)cluster.num_blocks(), rank = (int)cluster.block_rank();
-    const int b = blockIdx.x / CL, tid = threadIdx.x;
+    const int b = blockIdx.x / CL, tid = threadIdx.x, lane = tid & 31;
     const int V = H * W, E = 2 * H * W - H - W, nvert = (H - 1) * W;
     int *comp = ws.comp + (size_t)b * V, *parent = ws.parent + (size_t)b * V;
     u64 *best = ws.best + (size_t)b * V;
     float *wgt = ws.wgt + (size_t)b * E;
     unsigned char *intree = ws.intree + (size_t)b * E;
-    int *ncomp = ws.ncomp + b;
+    int *act = ws.act + (size_t)b * 2 * V, *roots = ws.roots + (size_t)b * 2 * V;
+    int *cnt = ws.cnt + (size_t)b * 4;
     const int stride = CL * PNT, first = rank * PNT + tid;
-    __shared__ int s_merges;
 
     // ---- init: weights (tree_filter.py:27-34, no fused multiply-add), union state
     const float *x = embed + (size_t)b * D * V;
@@ -281,60 +300,82 @@ mst_grid_cluster_kernel(Ws ws, const float *__restrict__ embed, unsigned char *_
         parent[v] = v;
         best[v] = KEY_INF;
     }
-    if (rank == 0 && tid == 0) *ncomp = V;
+    if (rank == 0 && tid < 4) cnt[tid] = 0;
     cluster.sync();
 
-    // Every loop below handles IL vertices per iteration with the loads of all of them issued before the first use: the
-    // phases are chains of dependent L2 round trips, and one cluster only has CL*512 threads to hide them with.
+    // Every loop below handles IL list entries per iteration with the loads of all of them issued before the first use:
+    // the phases are chains of dependent L2 round trips, and one cluster only has CL*512 threads to hide them with.
     constexpr int IL = 4;
-    for (int round = 0; round < max_rounds; ++round) {
+    int cur = 0;            // lists of this round: act + cur*V, roots + cur*V (round 0: the identity, not stored)
+    int nact = V, nroots = V;
+    for (int round = 0; round < max_rounds && nroots > 1; ++round) {
+        const int *alist = round ? act + (size_t)cur * V : nullptr, *rlist = round ? roots + (size_t)cur * V : nullptr;
+        int *anext = act + (size_t)(cur ^ 1) * V, *rnext = roots + (size_t)(cur ^ 1) * V;
+        int *cnt_anext = cnt + (cur ^ 1), *cnt_rnext = cnt + 2 + (cur ^ 1);
         // ---- find: cheapest outgoing edge per component
-        for (int v0 = first; v0 < V; v0 += stride * IL) {
+        for (int w0 = first - lane; w0 < nact; w0 += stride * IL) {   // warp-uniform trip count (ballots inside)
+            const int i0 = w0 + lane;
             int vv[IL], cv[IL], nb_[IL][4], ee[IL][4];
 #pragma unroll
             for (int k = 0; k < IL; ++k) {
-                const int v = v0 + k * stride;
-                vv[k] = v;
-                cv[k] = (v < V) ? comp[v] : -1;
+                const int i = i0 + k * stride;
+                vv[k] = (i < nact) ? (alist ? alist[i] : i) : -1;
             }
+#pragma unroll
+            for (int k = 0; k < IL; ++k) cv[k] = (vv[k] >= 0) ? comp[vv[k]] : DEAD;
 #pragma unroll
             for (int k = 0; k < IL; ++k) {
                 const int v = vv[k], h = v / W, w = v - h * W;
-                const bool ok = v < V;
+                const bool ok = v >= 0;
                 ee[k][0] = (ok && h > 0) ? v - W : -1;
                 ee[k][1] = (ok && w > 0) ? nvert + h * (W - 1) + w - 1 : -1;
                 ee[k][2] = (ok && w < W - 1) ? nvert + h * (W - 1) + w : -1;
                 ee[k][3] = (ok && h < H - 1) ? v : -1;
-                nb_[k][0] = ee[k][0] >= 0 ? comp[v - W] : cv[k];
-                nb_[k][1] = ee[k][1] >= 0 ? comp[v - 1] : cv[k];
-                nb_[k][2] = ee[k][2] >= 0 ? comp[v + 1] : cv[k];
-                nb_[k][3] = ee[k][3] >= 0 ? comp[v + W] : cv[k];
+                nb_[k][0] = ee[k][0] >= 0 ? comp[v - W] : DEAD;
+                nb_[k][1] = ee[k][1] >= 0 ? comp[v - 1] : DEAD;
+                nb_[k][2] = ee[k][2] >= 0 ? comp[v + 1] : DEAD;
+                nb_[k][3] = ee[k][3] >= 0 ? comp[v + W] : DEAD;
             }
             float wv[IL][4];
 #pragma unroll
             for (int k = 0; k < IL; ++k)
 #pragma unroll
-                for (int d = 0; d < 4; ++d) wv[k][d] = (nb_[k][d] != cv[k]) ? wgt[ee[k][d]] : 0.f;
+                for (int d = 0; d < 4; ++d) {
+                    // a DEAD neighbour is in this vertex's component (see above); so is one with the same label
+                    const bool out = nb_[k][d] != DEAD && nb_[k][d] != cv[k];
+                    wv[k][d] = out ? wgt[ee[k][d]] : 0.f;
+                    if (!out) ee[k][d] = -1;
+                }
 #pragma unroll
             for (int k = 0; k < IL; ++k) {
                 u64 key = KEY_INF;
 #pragma unroll
                 for (int d = 0; d < 4; ++d)
-                    if (nb_[k][d] != cv[k]) key = min(key, ((u64)orderable(wv[k][d]) << 32) | (unsigned)ee[k][d]);
-                if (key != KEY_INF) atomicMin(best + cv[k], key);
+                    if (ee[k][d] >= 0) key = min(key, ((u64)orderable(wv[k][d]) << 32) | (unsigned)ee[k][d]);
+                const bool alive = key != KEY_INF;
+                if (alive) atomicMin(best + cv[k], key);
+                else if (vv[k] >= 0) comp[vv[k]] = DEAD;
+                // survivors -> next active list
+                const unsigned m = __ballot_sync(0xffffffffu, alive);
+                if (m) {
+                    const int leader = __ffs(m) - 1;
+                    int base = 0;
+                    if (lane == leader) base = atomicAdd(cnt_anext, __popc(m));
+                    base = __shfl_sync(0xffffffffu, base, leader);
+                    if (alive) anext[base + __popc(m & ((1u << lane) - 1u))] = vv[k];
+                }
             }
         }
-        if (tid == 0) s_merges = 0;
         cluster.sync();
         // ---- hook: every root follows its edge; of two roots that picked the same edge the larger one hooks
-        int merges = 0;
-        for (int c0 = first; c0 < V; c0 += stride * IL) {
+        for (int w0 = first - lane; w0 < nroots; w0 += stride * IL) {
+            const int i0 = w0 + lane;
             int cc[IL];
             u64 key[IL];
 #pragma unroll
             for (int k = 0; k < IL; ++k) {
-                const int c = c0 + k * stride;
-                cc[k] = (c < V && comp[c] == c) ? c : -1;
+                const int i = i0 + k * stride;
+                cc[k] = (i < nroots) ? (rlist ? rlist[i] : i) : -1;
             }
 #pragma unroll
             for (int k = 0; k < IL; ++k) key[k] = (cc[k] >= 0) ? best[cc[k]] : KEY_INF;
@@ -347,29 +388,39 @@ mst_grid_cluster_kernel(Ws ws, const float *__restrict__ embed, unsigned char *_
                     const int e = (int)(unsigned)(key[k] & 0xffffffffull);
                     int u, v;
                     grid_endpoints(e, H, W, u, v);
-                    const int cu = comp[u], cvv = comp[v];
+                    const int cu = comp[u], cvv = comp[v];   // both endpoints of a cheapest edge are active: labels are fresh
                     other[k] = (cu == cc[k]) ? cvv : cu;
                     eid[k] = e;
                 }
             }
 #pragma unroll
             for (int k = 0; k < IL; ++k) {
-                if (other[k] < 0) continue;
-                if (best[other[k]] == key[k] && cc[k] < other[k]) continue;
-                parent[cc[k]] = other[k];
-                intree[eid[k]] = 1;
-                ++merges;
+                bool stays = cc[k] >= 0;   // a root without outgoing edge (finished tree) stays too
+                if (other[k] >= 0 && !(best[other[k]] == key[k] && cc[k] < other[k])) {
+                    parent[cc[k]] = other[k];
+                    intree[eid[k]] = 1;
+                    stays = false;
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, stays);
+                if (m) {
+                    const int leader = __ffs(m) - 1;
+                    int base = 0;
+                    if (lane == leader) base = atomicAdd(cnt_rnext, __popc(m));
+                    base = __shfl_sync(0xffffffffu, base, leader);
+                    if (stays) rnext[base + __popc(m & ((1u << lane) - 1u))] = cc[k];
+                }
             }
         }
-        if (merges) atomicAdd(&s_merges, merges);
-        __syncthreads();
-        if (tid == 0 && s_merges) atomicSub(ncomp, s_merges);
         cluster.sync();
-        // ---- compress: every vertex chases the hooks to its new root
-        for (int v0 = first; v0 < V; v0 += stride * IL) {
-            int r[IL], p[IL];
+        // ---- chase: the labels of the surviving vertices follow the hooks to their new roots
+        const int nact_next = *reinterpret_cast<volatile int *>(cnt_anext);
+        const int nroots_next = *reinterpret_cast<volatile int *>(cnt_rnext);
+        for (int i0 = first; i0 < nact_next; i0 += stride * IL) {
+            int vv[IL], r[IL], p[IL];
 #pragma unroll
-            for (int k = 0; k < IL; ++k) r[k] = (v0 + k * stride < V) ? comp[v0 + k * stride] : 0;
+            for (int k = 0; k < IL; ++k) vv[k] = (i0 + k * stride < nact_next) ? anext[i0 + k * stride] : -1;
+#pragma unroll
+            for (int k = 0; k < IL; ++k) r[k] = (vv[k] >= 0) ? comp[vv[k]] : 0;
 #pragma unroll
             for (int k = 0; k < IL; ++k) p[k] = parent[r[k]];
             bool moving = true;
@@ -388,16 +439,18 @@ mst_grid_cluster_kernel(Ws ws, const float *__restrict__ embed, unsigned char *_
                 }
             }
 #pragma unroll
-            for (int k = 0; k < IL; ++k) {
-                const int v = v0 + k * stride;
-                if (v < V) {
-                    comp[v] = r[k];
-                    best[v] = KEY_INF;
-                }
-            }
+            for (int k = 0; k < IL; ++k)
+                if (vv[k] >= 0) comp[vv[k]] = r[k];
+        }
+        for (int i = first; i < nroots_next; i += stride) best[rnext[i]] = KEY_INF;
+        if (rank == 0 && tid == 0) {   // the lists just consumed become the next round's output lists
+            cnt[cur] = 0;
+            cnt[2 + cur] = 0;
         }
         cluster.sync();
-        if (*reinterpret_cast<volatile int *>(ncomp) <= 1) break;
+        cur ^= 1;
+        nact = nact_next;
+        nroots = nroots_next;
     }
 
     // ---- 4-bit adjacency mask from the selected-edge flags
@@ -413,6 +466,12 @@ mst_grid_cluster_kernel(Ws ws, const float *__restrict__ embed, unsigned char *_
             m[v] = (unsigned char)bits;
         }
     }
+}
+
+int env_cl(int dflt) {
+    const char *v = getenv("FEDICRA_MST_CL");
+    const int x = (v && *v) ? atoi(v) : dflt;
+    return (x >= 1 && x <= 8) ? x : dflt;
 }
 
 int rounds_for(int V) {
@@ -477,8 +536,12 @@ extern "C" int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, 
     cudaStream_t st = (cudaStream_t)stream;
     if (E > 0) {
         // one persistent launch: a cluster of CL CTAs per image (as many as keep the whole batch in one wave)
+        // the largest cluster that keeps the whole batch in one wave.  63 registers x 512 threads = two CTAs per SM, 296
+        // slots, but clusters are placed GPC by GPC and do not pack perfectly: measured on B200 with 48 trees, clusters of
+        // 5 (240 CTAs) take 490 us, of 4 570 us, of 6 (288 CTAs, spills into a second wave) 680 us -- so leave 1/8 slack
         int CL = 8;
-        while (CL > 1 && (long long)B * CL > 2 * 148) CL >>= 1;  // 62 registers x 512 threads: two CTAs per SM
+        while (CL > 1 && (long long)B * CL > 2 * 148 - 37) --CL;
+        CL = env_cl(CL);
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)(B * CL));
         cfg.blockDim = dim3(PNT);
