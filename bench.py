@@ -191,8 +191,10 @@ def time_steps(fn, steps, flush_buf):
 def profile_ops(step, data, steps, flush_buf):
     """Second, instrumented pass: CUDA events around every C-ABI call, to attribute the step time to kernel groups."""
     from fedicra_b200 import ops
-    names = ["gcrf_fwd_bwd", "mst_grid", "bfs_forward", "bfs_grid", "bfs_euler", "edge_weight_fwd", "edge_weight_bwd", "refine_forward",
-             "refine_backward_feature", "refine_backward_weight", "tree_filter_forward", "tree_filter_backward"]
+    names = ["gcrf_fwd_bwd", "mst_grid", "mst_grid_multi", "bfs_forward", "bfs_grid", "bfs_euler", "edge_weight_fwd",
+             "edge_weight_bwd", "refine_forward", "refine_backward_feature", "refine_backward_weight", "tree_filter_forward",
+             "tree_filter_backward", "band_plan", "channel_softmax_fwd", "channel_softmax_bwd", "masked_l1_fwd",
+             "masked_l1_bwd"]
     records, originals = {n: [] for n in names}, {}
 
     def wrap(name, fn):
@@ -381,28 +383,39 @@ def run_ours(args, wl):
         peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs (of measured)"
     else:
         peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
-    group_bytes = {  # algorithmic bytes per CALL of each kernel group (all B images of the batch)
-        "mst_grid": lambda k: B * (ab["stages"][k]["mst_bfs"] - ab["u"]),
-        "bfs_forward": lambda k: B * ab["u"],
-        "bfs_grid": lambda k: B * ab["u"],
-        "bfs_euler": lambda k: B * ab["u"],
-        "refine_forward": lambda k: B * ab["stages"][k]["filter_fwd"],
-        "refine_backward_feature": lambda k: B * (2 * C + 3) * ab["u"],
-        "refine_backward_weight": lambda k: B * (2 * C + 2 * C) * ab["u"],
-        "tree_filter_forward": lambda k: B * ab["stages"][k]["filter_fwd"],
-        "tree_filter_backward": lambda k: B * ab["stages"][k]["filter_bwd"],
-        "gcrf_fwd_bwd": lambda k: B * ab["gcrf"],
-        "edge_weight_fwd": lambda k: B * (C + 3) * ab["u"],
-        "edge_weight_bwd": lambda k: B * (2 * C + 4) * ab["u"],
+    all_stages = lambda key: sum(st[key] for st in ab["stages"])
+    u = ab["u"]
+    group_bytes = {  # algorithmic bytes per CALL of each kernel group (all B images of the batch; SURVEY.md §8d)
+        "mst_grid": lambda: B * (ab["stages"][0]["mst_bfs"] - u),
+        "mst_grid_multi": lambda: B * (all_stages("mst_bfs") - 4 * u),          # one launch for the 4 embeddings
+        "bfs_forward": lambda: B * u,
+        "bfs_grid": lambda: B * u,
+        "bfs_euler": lambda: 4 * B * u,                                          # one call for the 4 trees
+        "refine_forward": lambda: B * ab["stages"][1]["filter_fwd"],
+        "refine_backward_feature": lambda: B * (2 * C + 3) * u,
+        "refine_backward_weight": lambda: B * (2 * C + 2 * C) * u,
+        "tree_filter_forward": lambda: B * all_stages("filter_fwd") / 4,        # mean over the 4 trees
+        "tree_filter_backward": lambda: B * all_stages("filter_bwd") / 4,
+        "gcrf_fwd_bwd": lambda: B * ab["gcrf"],
+        "edge_weight_fwd": lambda: B * (C + 3) * u,
+        "edge_weight_bwd": lambda: B * (2 * C + 4) * u,
+        "band_plan": lambda: 4 * B * u / 16,
+        "channel_softmax_fwd": lambda: B * 2 * C * u,
+        "channel_softmax_bwd": lambda: B * 3 * C * u,
+        "masked_l1_fwd": lambda: B * (2 * C + 0.25) * u,
+        "masked_l1_bwd": lambda: B * (4 * C + 0.25) * u,
     }
+    # DRAM bytes per launch of the kernel groups, from the committed `ncu --set full` captures (profiles/traffic.json)
+    traffic_path = os.path.join(ROOT, "profiles", "traffic.json")
+    traffic_tab = json.load(open(traffic_path)).get(args.workload, {}) if os.path.exists(traffic_path) else {}
     dominant = max(ops_prof, key=lambda n: ops_prof[n]["ms_per_step"]) if ops_prof else None
     roofline = None
     if dominant:
         p = ops_prof[dominant]
-        nbytes = group_bytes[dominant](1)
+        nbytes = group_bytes[dominant]()
         achieved = nbytes / (p["ms_per_call"] * 1e-3) / 1e9
         roofline = {"kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "frac": achieved / peak, "traffic": traffic_tab.get(dominant), "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": nbytes, "ms_per_launch": p["ms_per_call"],
                     "share_of_step": p["ms_per_step"] / (total_ms / args.steps)}
     step_bytes = B * (ab["tree"] + ab["gcrf"])

@@ -38,6 +38,8 @@ SIGNATURES = {
     "fedicra_mst_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "fedicra_mst_forward": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
     "fedicra_mst_grid": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "fedicra_mst_grid_multi": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                       c_size_t, c_void_p]),
     "fedicra_bfs_grid": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "fedicra_bfs_workspace_bytes": (c_size_t, [c_int, c_int]),
     "fedicra_bfs_forward": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
@@ -61,6 +63,13 @@ SIGNATURES = {
     "fedicra_tree_filter_forward": (c_int, [c_void_p] * 8 + [c_int, c_int, c_int] + [c_void_p] * 4 + [c_size_t, c_void_p,
                                                                                                     c_size_t, c_void_p]),
     "fedicra_tree_filter_backward": (c_int, [c_void_p] * 8 + [c_int, c_int, c_int] + [c_void_p] * 4 + [c_size_t, c_void_p]),
+    "fedicra_channel_softmax_fwd": (c_int, [c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p, c_void_p]),
+    "fedicra_channel_softmax_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p, c_void_p]),
+    "fedicra_masked_l1_workspace_bytes": (c_size_t, []),
+    "fedicra_masked_l1_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, ctypes.c_longlong, c_float, c_void_p,
+                                      c_void_p, c_void_p, c_size_t, c_void_p]),
+    "fedicra_masked_l1_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int, c_int,
+                                      ctypes.c_longlong, c_void_p, c_void_p, c_void_p]),
     "fedicra_debug_filter_profile": (c_int, [c_void_p, c_int]),
     "fedicra_ala_update_flat": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_void_p]),
     "fedicra_ala_update_multi": (c_int, [c_void_p] * 8 + [c_int, c_int, c_float, c_void_p]),

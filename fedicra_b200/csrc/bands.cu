@@ -176,6 +176,7 @@ __global__ void __launch_bounds__(NT) consts_kernel(TreeView t, Consts k, int pc
     const int b = blockIdx.y;
     int L0, L1, nb;
     if (!band_geom(t, b, blockIdx.x, L0, L1, nb)) return;
+    if (blockIdx.x == 0 && threadIdx.x == 0) const_cast<float *>(t.w)[(size_t)b * t.V] = 0.f;   // refine.cu:43-46
     const int *ls = t.ls + (size_t)b * (t.V + 1);
     const int p0 = ls[L0], p1 = ls[L1];
     if (p1 - p0 <= pcap)
@@ -656,17 +657,12 @@ int env_int(const char *name, int dflt) {
     const char *v = getenv(name);
     return (v && *v) ? atoi(v) : dflt;
 }
-// most bands per image: 36 up to 2^17 pixels (37 CTAs per image x 12 images fill the GPU at three CTAs per SM), twice
-// that for larger images (their bands take a whole SM each)
-int plan_nbcap(int V) { return env_int("FEDICRA_PLAN_NBCAP", V <= (1 << 17) ? NBCAP : 2 * NBCAP); }
-// positions per band: what keeps three resident CTAs per SM at the 256^2 working size (3100 x 24 B + level cache;
-// 37 CTAs per image x 12 images = 444 = 3 x 148), and 1.35 x the mean band of an NBCAP-band plan for larger images
-// (the pk fields hold local offsets < 8192)
-int plan_pmax(int V) {
-    long long need = (long long)V * 135 / (100 * plan_nbcap(V)) + 1;
-    int pm = (int)(need < 3100 ? 3100 : (need > 8000 ? 8000 : need));
-    return env_int("FEDICRA_PLAN_PMAX", pm);
-}
+// Plan limits.  Up to 2^17 pixels per image the resident kernel runs the filter: at most 36 bands (37 CTAs per image x 12
+// images fill the GPU at three CTAs per SM) of at most 3100 positions (3100 x 24 B + level cache = a third of an SM's
+// shared memory).  Larger images would need so many chunks of co-resident images that the multi-launch phases are
+// faster: they get that path's plan (bands of 3072 positions, up to 128 of them).
+int plan_nbcap(int V) { return env_int("FEDICRA_PLAN_NBCAP", V <= (1 << 17) ? NBCAP : 128); }
+int plan_pmax(int V) { return env_int("FEDICRA_PLAN_PMAX", V <= (1 << 17) ? 3100 : 3072); }
 #define PLAN_KDIV env_int("FEDICRA_PLAN_KDIV", 30)               // a band holds at most ceil(n_levels / KDIV) levels
 int plan_grid(int V) { return plan_nbcap(V); }                    // upper bound of the number of bands
 constexpr size_t SMEM_MAX = 227 * 1024;
@@ -753,7 +749,7 @@ int launch_resident(const TreeView &t, const Consts &k, ResidentArgs a, int B, c
     const int pcap = plan_pmax(V);
     const size_t smem = resident_smem(pcap, NC);
     if (nthr > 1024 || smem > SMEM_MAX || pcap > 8191 || nbcap > NBMAX) return 1;
-    static thread_local int cached_key[2] = {-1, -1}, cached_cap = 0;   // (device, nthr, smem) -> resident CTAs
+    static thread_local int cached_key[2] = {-1, -1}, cached_cap = 0, cached_per_sm = 0;   // (device, nthr, smem) -> resident CTAs
     int dev = 0;
     cudaGetDevice(&dev);
     const int key0 = nthr * 64 + dev, key1 = (int)smem;
@@ -766,11 +762,22 @@ int launch_resident(const TreeView &t, const Consts &k, ResidentArgs a, int B, c
         cached_key[0] = key0;
         cached_key[1] = key1;
         cached_cap = per_sm * sms;
+        cached_per_sm = per_sm;
+        // the launches below ask for the whole per-CTA share of the SM (see smem_all)
+        const size_t share = per_sm > 0 ? (size_t)233472 / per_sm - 1024 : smem;
+        if (set_smem(resident_kernel<MODE, NCT>, share > SMEM_MAX ? SMEM_MAX : (share < smem ? smem : share), "resident_kernel")) return -2;
     }
     const int chunk = cached_cap / (nbcap + 1);
     if (chunk < 1) return 1;
     a.pcap = pcap;
-    a.tcap = (int)((smem - 3 * (NBMAX + 2) * sizeof(int) - 64) / (8 + 4 * NC));
+    // the stitcher's capacity comes from the same allocation: take everything the occupancy leaves (it is free)
+    size_t smem_all = smem;
+    if (cached_per_sm > 0) {
+        const size_t share = (size_t)233472 / cached_per_sm - 1024;
+        smem_all = share > SMEM_MAX ? SMEM_MAX : share;
+        if (smem_all < smem) smem_all = smem;
+    }
+    a.tcap = (int)((smem_all - 3 * (NBMAX + 2) * sizeof(int) - 64) / (8 + 4 * NC));
     a.prof = nullptr;
     if (env_int("FEDICRA_PROF", 0)) {
         void *ptr = nullptr;
@@ -783,7 +790,7 @@ int launch_resident(const TreeView &t, const Consts &k, ResidentArgs a, int B, c
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(nbcap + 1, nbatch);
         cfg.blockDim = dim3(nthr);
-        cfg.dynamicSmemBytes = smem;
+        cfg.dynamicSmemBytes = smem_all;
         cfg.stream = st;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeCooperative;
@@ -865,8 +872,6 @@ extern "C" int fedicra_tree_filter_forward(const float *feature_in, float *edge_
     SweepArgs a{feature_in, nullptr, C, NC, wk, wk + n, fup, wk + 2 * n, wk + 4 * n};
     float *outE = wk + 3 * n;
 
-    zero_root_weight_kernel<<<(B + 127) / 128, 128, 0, st>>>(edge_weight, V, B);
-    FEDICRA_CHECK_LAUNCH("zero_root_weight_kernel");
     const int pcap_c = multi_pcap(V, 1);
     const size_t smem_c = (size_t)pcap_c * 16 + 16;
     if (set_smem(consts_kernel, smem_c, "consts_kernel")) return -2;

@@ -14,13 +14,20 @@
 //   4. BFS position = level_start[depth] + rank of the preorder index among the vertices of that depth (the BFS queue
 //      order equals "sort by depth, then preorder"): counted per level.
 // Integer-only, deterministic (atomics are used for counters whose order does not reach the result).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
 
 constexpr int NT = 256;
 constexpr int NIL = -1;
-constexpr int SPLIT_PER_CTA = 1024;  // splitters handed out dynamically inside one CTA of the tour walk
+// splitters handed out dynamically inside one CTA of the tour walk (FEDICRA_EULER_SPC overrides; see run time notes below)
+int split_per_cta() {
+    const char *v = getenv("FEDICRA_EULER_SPC");
+    const int x = (v && *v) ? atoi(v) : 512;   // measured on B200, 48 trees of 256^2: 1024 -> 476 us, 512 -> 462, 256 -> 464, 128 -> 499
+    return (x >= 32 && x <= 8192) ? x : 512;
+}
 
 __device__ __forceinline__ int dir_delta(int d, int W) { return d == 0 ? -W : (d == 1 ? -1 : (d == 2 ? 1 : W)); }
 
@@ -53,7 +60,7 @@ struct Ws {
 };
 
 struct Dims {
-    int B, V, H, W, SP, SPLOG, NS, T, NBLK;  // T = 2(V-1) arcs on the tour; NBLK = ceil(T / 1024)
+    int B, V, H, W, SP, SPLOG, NS, T, NBLK, SPC;  // T = 2(V-1) arcs on the tour; NBLK = ceil(T / 1024); SPC splitters per walk CTA
 };
 
 size_t ws_layout(const Dims &d, char *base, Ws *w) {
@@ -94,6 +101,7 @@ Dims make_dims(int B, int H, int W) {
     d.NS = (d.V + d.SP - 1) / d.SP;
     d.T = 2 * (d.V - 1);
     d.NBLK = (d.T + 1023) / 1024;
+    d.SPC = split_per_cta();
     return d;
 }
 
@@ -131,9 +139,9 @@ __global__ void __launch_bounds__(NT) walk_kernel(const unsigned char *__restric
         return m[v];
     };
     // Stretch lengths are geometric (mean ~2 SP, longest a few hundred), so a fixed splitter per thread leaves most lanes
-    // idle; instead every CTA owns SPLIT_PER_CTA consecutive splitters and its lanes pull the next one when they are done.
+    // idle; instead every CTA owns SPC consecutive splitters and its lanes pull the next one when they are done.
     __shared__ int s_next;
-    const int s_begin = blockIdx.x * SPLIT_PER_CTA, s_end = min(s_begin + SPLIT_PER_CTA, dm.NS);
+    const int s_begin = blockIdx.x * dm.SPC, s_end = min(s_begin + dm.SPC, dm.NS);
     if (threadIdx.x == 0) s_next = s_begin + NT;
     __syncthreads();
     unsigned *arc = ws.arc + (size_t)b * 4 * V;
@@ -480,9 +488,9 @@ extern "C" int fedicra_bfs_euler(const unsigned char *tree_mask, int B, int H, i
     if (smem_mask <= 200 * 1024) {
         e = cudaFuncSetAttribute(walk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_mask);
         if (e != cudaSuccess) return fedicra_fail(-2, "bfs_euler: shared memory: %s", cudaGetErrorString(e));
-        walk_kernel<true><<<dim3((dm.NS + SPLIT_PER_CTA - 1) / SPLIT_PER_CTA, B), NT, smem_mask, st>>>(tree_mask, ws, dm);
+        walk_kernel<true><<<dim3((dm.NS + dm.SPC - 1) / dm.SPC, B), NT, smem_mask, st>>>(tree_mask, ws, dm);
     } else {
-        walk_kernel<false><<<dim3((dm.NS + SPLIT_PER_CTA - 1) / SPLIT_PER_CTA, B), NT, 0, st>>>(tree_mask, ws, dm);
+        walk_kernel<false><<<dim3((dm.NS + dm.SPC - 1) / dm.SPC, B), NT, 0, st>>>(tree_mask, ws, dm);
     }
     FEDICRA_CHECK_LAUNCH("walk_kernel");
     const size_t smem_rank = (size_t)4 * dm.NS * sizeof(int);

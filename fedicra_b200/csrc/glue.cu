@@ -1,0 +1,191 @@
+// glue.cu -- the element-wise ends of the tree-energy loss, fused (sm_100a).
+//
+// What it replaces (reference = /root/reference/code/flower_common.py, class MScaleRecurveTreeEnergyLoss and siblings):
+//   :781            prob = torch.softmax(preds, dim=1)                      -> channel_softmax_{fwd,bwd}_kernel
+//   :777, :813-816  N = ROI.sum();  loss = (ROI * |prob - AS|).sum();  if N > 0: loss /= N;  weight * loss
+//                                                                           -> masked_l1_{fwd,bwd}_kernel
+// In PyTorch these are ~20 small kernels per step (sub, abs, mul, sum, clamp, div, sign, neg, ...), each a full HBM round
+// trip of a [B,C,H,W] tensor; here each direction is one pass at HBM rate.  The reductions are deterministic: per-CTA
+// partial sums in a fixed order, combined by the last CTA to arrive in CTA-index order.
+#include "common.cuh"
+
+namespace {
+
+constexpr int NT = 256;
+constexpr int MAXC = 16;
+
+// prob[b,c,p] = exp(x[b,c,p] - max_c) / sum_c exp(x[b,c,p] - max_c); one thread per pixel, channels strided by P.
+__global__ void __launch_bounds__(NT)
+channel_softmax_fwd_kernel(const float *__restrict__ x, float *__restrict__ y, int C, long long P, long long BP) {
+    const long long i = (long long)blockIdx.x * NT + threadIdx.x;
+    if (i >= BP) return;
+    const long long b = i / P, p = i - b * P;
+    const float *xi = x + b * C * P + p;
+    float *yi = y + b * C * P + p;
+    float v[MAXC];
+    float m = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c)
+        if (c < C) {
+            v[c] = xi[(long long)c * P];
+            m = fmaxf(m, v[c]);
+        }
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c)
+        if (c < C) {
+            v[c] = expf(v[c] - m);
+            s += v[c];
+        }
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c)
+        if (c < C) yi[(long long)c * P] = v[c] / s;
+}
+
+// gx[c] = y[c] * (gy[c] - sum_k gy[k] * y[k])
+__global__ void __launch_bounds__(NT)
+channel_softmax_bwd_kernel(const float *__restrict__ y, const float *__restrict__ gy, float *__restrict__ gx, int C,
+                           long long P, long long BP) {
+    const long long i = (long long)blockIdx.x * NT + threadIdx.x;
+    if (i >= BP) return;
+    const long long b = i / P, p = i - b * P, base = b * C * P + p;
+    float yv[MAXC], gv[MAXC];
+    float dot = 0.f;
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c)
+        if (c < C) {
+            yv[c] = y[base + (long long)c * P];
+            gv[c] = gy[base + (long long)c * P];
+            dot = fmaf(gv[c], yv[c], dot);
+        }
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c)
+        if (c < C) gx[base + (long long)c * P] = yv[c] * (gv[c] - dot);
+}
+
+__device__ __forceinline__ float block_sum(float v, float *s_red) {
+    v = warp_sum(v);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) s_red[wid] = v;
+    __syncthreads();
+    float t = 0.f;
+    if (wid == 0) {
+        t = (lane < NT / 32) ? s_red[lane] : 0.f;
+        t = warp_sum(t);
+    }
+    __syncthreads();
+    return t;  // valid in warp 0
+}
+
+// sums[0] = sum_{b,c,p} roi[b,p] * |prob - filt|, sums[1] = sum_{b,p} roi[b,p];
+// loss[0] = weight * sums[0] / max(sums[1], 1)      (flower_common.py:813-818; the `if N > 0` without its host sync)
+// scratch: [2*gridDim.x] partials + 1 counter word (zero before the first use, left at zero).
+__global__ void __launch_bounds__(NT)
+masked_l1_fwd_kernel(const float *__restrict__ prob, const float *__restrict__ filt, const unsigned char *__restrict__ roi,
+                     int C, long long P, long long BP, float weight, float *__restrict__ sums, float *__restrict__ loss,
+                     float *__restrict__ partial, unsigned *__restrict__ counter) {
+    __shared__ float s_red[NT / 32];
+    __shared__ bool s_last;
+    float acc = 0.f, cnt = 0.f;
+    for (long long i = (long long)blockIdx.x * NT + threadIdx.x; i < BP; i += (long long)gridDim.x * NT) {
+        if (!roi[i]) continue;
+        const long long b = i / P, p = i - b * P, base = b * C * P + p;
+        cnt += 1.f;
+        for (int c = 0; c < C; ++c) acc += fabsf(prob[base + (long long)c * P] - filt[base + (long long)c * P]);
+    }
+    const float a = block_sum(acc, s_red), n = block_sum(cnt, s_red);
+    if (threadIdx.x == 0) {
+        partial[2 * blockIdx.x] = a;
+        partial[2 * blockIdx.x + 1] = n;
+        __threadfence();
+        s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    float ta = 0.f, tn = 0.f;   // fixed order: thread t sums partials t, t+NT, ...; then the block tree
+    for (int k = threadIdx.x; k < (int)gridDim.x; k += NT) {
+        ta += __ldcg(partial + 2 * k);
+        tn += __ldcg(partial + 2 * k + 1);
+    }
+    ta = block_sum(ta, s_red);
+    tn = block_sum(tn, s_red);
+    if (threadIdx.x == 0) {
+        sums[0] = ta;
+        sums[1] = tn;
+        loss[0] = weight * ta / fmaxf(tn, 1.f);
+        *counter = 0u;
+    }
+}
+
+// g_prob = s * roi * sign(prob - filt), g_filt = -g_prob, with s = gout[0] * weight / max(n[0], 1)  (n == NULL: s = gout[0])
+__global__ void __launch_bounds__(NT)
+masked_l1_bwd_kernel(const float *__restrict__ prob, const float *__restrict__ filt, const unsigned char *__restrict__ roi,
+                     const float *__restrict__ gout, const float *__restrict__ n, float weight, int C, long long P,
+                     long long BP, float *__restrict__ g_prob, float *__restrict__ g_filt) {
+    const long long i = (long long)blockIdx.x * NT + threadIdx.x;
+    if (i >= BP) return;
+    const float s = gout[0] * (n ? weight / fmaxf(n[0], 1.f) : 1.f);
+    const long long b = i / P, p = i - b * P, base = b * C * P + p;
+    const bool on = roi[i] != 0;
+    for (int c = 0; c < C; ++c) {
+        const long long j = base + (long long)c * P;
+        const float d = prob[j] - filt[j];
+        const float g = on ? (d > 0.f ? s : (d < 0.f ? -s : 0.f)) : 0.f;   // torch.sign(0) = 0
+        if (g_prob) g_prob[j] = g;
+        if (g_filt) g_filt[j] = -g;
+    }
+}
+
+}  // namespace
+
+extern "C" int fedicra_channel_softmax_fwd(const float *x, int B, int C, long long P, float *y, void *stream) {
+    FEDICRA_REQUIRE(x && y, "channel_softmax_fwd: null pointer");
+    FEDICRA_REQUIRE(B > 0 && C > 0 && C <= MAXC && P > 0, "channel_softmax_fwd: bad sizes B=%d C=%d P=%lld (C <= %d)", B, C, P, MAXC);
+    const long long BP = (long long)B * P;
+    channel_softmax_fwd_kernel<<<(unsigned)((BP + NT - 1) / NT), NT, 0, (cudaStream_t)stream>>>(x, y, C, P, BP);
+    FEDICRA_CHECK_LAUNCH("channel_softmax_fwd_kernel");
+    return 0;
+}
+
+extern "C" int fedicra_channel_softmax_bwd(const float *y, const float *grad_y, int B, int C, long long P, float *grad_x,
+                                           void *stream) {
+    FEDICRA_REQUIRE(y && grad_y && grad_x, "channel_softmax_bwd: null pointer");
+    FEDICRA_REQUIRE(B > 0 && C > 0 && C <= MAXC && P > 0, "channel_softmax_bwd: bad sizes B=%d C=%d P=%lld (C <= %d)", B, C, P, MAXC);
+    const long long BP = (long long)B * P;
+    channel_softmax_bwd_kernel<<<(unsigned)((BP + NT - 1) / NT), NT, 0, (cudaStream_t)stream>>>(y, grad_y, grad_x, C, P, BP);
+    FEDICRA_CHECK_LAUNCH("channel_softmax_bwd_kernel");
+    return 0;
+}
+
+constexpr int L1_GRID = 592;   // 4 CTAs per SM
+
+extern "C" size_t fedicra_masked_l1_workspace_bytes(void) { return (2 * L1_GRID + 4) * sizeof(float); }
+
+extern "C" int fedicra_masked_l1_fwd(const float *prob, const float *filtered, const unsigned char *roi, int B, int C,
+                                     long long P, float weight, float *sums, float *loss, void *workspace,
+                                     size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(prob && filtered && roi && sums && loss && workspace, "masked_l1_fwd: null pointer");
+    FEDICRA_REQUIRE(B > 0 && C > 0 && P > 0, "masked_l1_fwd: bad sizes B=%d C=%d P=%lld", B, C, P);
+    FEDICRA_REQUIRE(workspace_bytes >= fedicra_masked_l1_workspace_bytes(), "masked_l1_fwd: workspace too small");
+    const long long BP = (long long)B * P;
+    const long long want = (BP + NT - 1) / NT;
+    const int grid = (int)(want < L1_GRID ? want : L1_GRID);
+    float *partial = (float *)workspace;
+    unsigned *counter = (unsigned *)(partial + 2 * L1_GRID);
+    masked_l1_fwd_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(prob, filtered, roi, C, P, BP, weight, sums, loss, partial, counter);
+    FEDICRA_CHECK_LAUNCH("masked_l1_fwd_kernel");
+    return 0;
+}
+
+extern "C" int fedicra_masked_l1_bwd(const float *prob, const float *filtered, const unsigned char *roi,
+                                     const float *grad_out, const float *n, float weight, int B, int C, long long P,
+                                     float *grad_prob, float *grad_filtered, void *stream) {
+    FEDICRA_REQUIRE(prob && filtered && roi && grad_out && (grad_prob || grad_filtered), "masked_l1_bwd: null pointer");
+    FEDICRA_REQUIRE(B > 0 && C > 0 && P > 0, "masked_l1_bwd: bad sizes B=%d C=%d P=%lld", B, C, P);
+    const long long BP = (long long)B * P;
+    masked_l1_bwd_kernel<<<(unsigned)((BP + NT - 1) / NT), NT, 0, (cudaStream_t)stream>>>(prob, filtered, roi, grad_out, n, weight, C,
+                                                                                       P, BP, grad_prob, grad_filtered);
+    FEDICRA_CHECK_LAUNCH("masked_l1_bwd_kernel");
+    return 0;
+}

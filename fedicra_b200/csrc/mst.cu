@@ -266,10 +266,18 @@ __global__ void grid_mask_kernel(Ws ws, unsigned char *__restrict__ mask, int H,
 // List order depends on atomics, the result does not: min is order-free and hooks depend on the minima only.
 constexpr int PNT = 512;
 constexpr int DEAD = -1;
+constexpr int MAX_EMBEDS = 8;
+
+// The trees of one launch may come from several embeddings of one batch (the image and the decoder heads of the
+// multiscale loss): tree t belongs to embedding t / per, image t % per.  No stacked copy is ever made.
+struct EmbedSet {
+    const float *ptr[MAX_EMBEDS];
+    int D[MAX_EMBEDS];
+    int per;   // images per embedding
+};
 
 __global__ void __launch_bounds__(PNT)
-mst_grid_cluster_kernel(Ws ws, const float *__restrict__ embed, unsigned char *__restrict__ mask, int D, int H, int W,
-                        int max_rounds) {
+mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, int H, int W, int max_rounds) {
     cg::cluster_group cluster = cg::this_cluster();
     const int CL = (int)cluster.num_blocks(), rank = (int)cluster.block_rank();
     const int b = blockIdx.x / CL, tid = threadIdx.x, lane = tid & 31;
@@ -283,7 +291,8 @@ mst_grid_cluster_kernel(Ws ws, const float *__restrict__ embed, unsigned char *_
     const int stride = CL * PNT, first = rank * PNT + tid;
 
     // ---- init: weights (tree_filter.py:27-34, no fused multiply-add), union state
-    const float *x = embed + (size_t)b * D * V;
+    const int D = es.D[b / es.per];
+    const float *x = es.ptr[b / es.per] + (size_t)(b % es.per) * D * V;
     for (int e = first; e < E; e += stride) {
         int u, v;
         grid_endpoints(e, H, W, u, v);
@@ -522,20 +531,16 @@ extern "C" int fedicra_mst_forward(const int *edge_index, const float *edge_weig
     return run_mst<false>(edge_index, edge_weight, B, E, V, 0, 0, edge_out, ws, (cudaStream_t)stream);
 }
 
-extern "C" int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out,
-                                unsigned char *tree_mask, void *workspace, size_t workspace_bytes, void *stream) {
-    FEDICRA_REQUIRE(embed && workspace && (edge_out || tree_mask || (long long)H * W <= 1),
-                    "mst_grid: null pointer (edge_out and tree_mask cannot both be NULL)");
-    FEDICRA_REQUIRE(B > 0 && B <= 65535 && D > 0 && H >= 1 && W >= 1 && (long long)H * W < (1ll << 30),
-                    "mst_grid: bad sizes B=%d D=%d H=%d W=%d", B, D, H, W);
+namespace {
+int mst_grid_launch(const EmbedSet &es, int B, int H, int W, int *edge_out, unsigned char *tree_mask, void *workspace,
+                    size_t workspace_bytes, cudaStream_t st) {
     const int V = H * W, E = 2 * H * W - H - W;
     FEDICRA_REQUIRE(workspace_bytes >= fedicra_mst_workspace_bytes(B, V, E), "mst_grid: workspace too small");
     FEDICRA_REQUIRE(((uintptr_t)edge_out & 7) == 0, "mst_grid: edge_out must be 8-byte aligned");  // (NULL passes)
     Ws ws;
     ws_layout(B, V, E, (char *)workspace, &ws);
-    cudaStream_t st = (cudaStream_t)stream;
     if (E > 0) {
-        // one persistent launch: a cluster of CL CTAs per image (as many as keep the whole batch in one wave)
+        // one persistent launch: a cluster of CL CTAs per image.
         // the largest cluster that keeps the whole batch in one wave.  63 registers x 512 threads = two CTAs per SM, 296
         // slots, but clusters are placed GPC by GPC and do not pack perfectly: measured on B200 with 48 trees, clusters of
         // 5 (240 CTAs) take 490 us, of 4 570 us, of 6 (288 CTAs, spills into a second wave) 680 us -- so leave 1/8 slack
@@ -554,7 +559,7 @@ extern "C" int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, 
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
-        cudaError_t e = cudaLaunchKernelEx(&cfg, mst_grid_cluster_kernel, ws, embed, tree_mask, D, H, W, rounds_for(V));
+        cudaError_t e = cudaLaunchKernelEx(&cfg, mst_grid_cluster_kernel, ws, es, tree_mask, H, W, rounds_for(V));
         fedicra_count_launches(1);
         if (e != cudaSuccess) return fedicra_fail(-2, "mst_grid_cluster_kernel: %s", cudaGetErrorString(e));
         if (edge_out != nullptr) {
@@ -563,14 +568,39 @@ extern "C" int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, 
         }
         return 0;
     }
-    if (int rc = run_mst<true>(nullptr, ws.wgt, B, E, V, H, W, edge_out, ws, st)) return rc;
-    if (tree_mask != nullptr) {
-        if (E > 0) {
-            grid_mask_kernel<<<dim3((V + 255) / 256, B), 256, 0, st>>>(ws, tree_mask, H, W, E);
-            FEDICRA_CHECK_LAUNCH("grid_mask_kernel");
-        } else {
-            cudaMemsetAsync(tree_mask, 0, (size_t)B * V, st);
-        }
-    }
+    // a single vertex: the empty tree
+    if (tree_mask != nullptr) cudaMemsetAsync(tree_mask, 0, (size_t)B * V, st);
     return 0;
+}
+}  // namespace
+
+extern "C" int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out,
+                                unsigned char *tree_mask, void *workspace, size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(embed && workspace && (edge_out || tree_mask || (long long)H * W <= 1),
+                    "mst_grid: null pointer (edge_out and tree_mask cannot both be NULL)");
+    FEDICRA_REQUIRE(B > 0 && B <= 65535 && D > 0 && H >= 1 && W >= 1 && (long long)H * W < (1ll << 30),
+                    "mst_grid: bad sizes B=%d D=%d H=%d W=%d", B, D, H, W);
+    EmbedSet es = {};
+    es.ptr[0] = embed;
+    es.D[0] = D;
+    es.per = B;
+    return mst_grid_launch(es, B, H, W, edge_out, tree_mask, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int fedicra_mst_grid_multi(const float *const *h_embeds, const int *h_D, int K, int B, int H, int W,
+                                      int *edge_out, unsigned char *tree_mask, void *workspace, size_t workspace_bytes,
+                                      void *stream) {
+    FEDICRA_REQUIRE(h_embeds && h_D && workspace && (edge_out || tree_mask || (long long)H * W <= 1),
+                    "mst_grid_multi: null pointer (edge_out and tree_mask cannot both be NULL)");
+    FEDICRA_REQUIRE(K >= 1 && K <= MAX_EMBEDS, "mst_grid_multi: %d embeddings (1..%d)", K, MAX_EMBEDS);
+    FEDICRA_REQUIRE(B > 0 && (long long)B * K <= 65535 && H >= 1 && W >= 1 && (long long)H * W < (1ll << 30),
+                    "mst_grid_multi: bad sizes B=%d K=%d H=%d W=%d", B, K, H, W);
+    EmbedSet es = {};
+    for (int k = 0; k < K; ++k) {
+        FEDICRA_REQUIRE(h_embeds[k] && h_D[k] > 0, "mst_grid_multi: embedding %d is null or has no channels", k);
+        es.ptr[k] = h_embeds[k];
+        es.D[k] = h_D[k];
+    }
+    es.per = B;
+    return mst_grid_launch(es, B * K, H, W, edge_out, tree_mask, workspace, workspace_bytes, (cudaStream_t)stream);
 }

@@ -83,6 +83,27 @@ def mst_grid(embed, want_mask=False, want_edges=True):
     return (out, mask) if want_mask else out
 
 
+def mst_grid_multi(embeds, want_mask=True, want_edges=False):
+    """MST of the grids of several embeddings of one batch ([B,D_k,H,W], same B/H/W) in one launch, no stacked copy.
+    Returns (edges [K*B,V-1,2] or None, mask [K*B,V] or None)."""
+    import ctypes
+    es = [_cuda(e, torch.float32, "guide_in") for e in embeds]
+    B, _, H, W = es[0].shape
+    K = len(es)
+    assert all(e.shape[0] == B and tuple(e.shape[2:]) == (H, W) for e in es)
+    V, E = H * W, 2 * H * W - H - W
+    dev = es[0].device
+    with torch.cuda.device(dev):
+        out = torch.empty(K * B, V - 1, 2, dtype=torch.int32, device=dev) if want_edges else None
+        mask = torch.empty(K * B, V, dtype=torch.uint8, device=dev) if want_mask else None
+        ws = workspace("mst", lib.fedicra_mst_workspace_bytes(K * B, V, E), dev)
+        ptrs = (ctypes.c_void_p * K)(*[e.data_ptr() for e in es])
+        dims = (ctypes.c_int * K)(*[e.shape[1] for e in es])
+        check(lib.fedicra_mst_grid_multi(ptrs, dims, K, B, H, W, _p(out), _p(mask), _p(ws), ws.numel(), _stream()),
+              "mst_grid_multi")
+    return out, mask
+
+
 BFS_GRID_MAX_V = 2 * (227 * 1024 - 4 * 4096 * 4 - 256)
 BFS_EULER_MAX_V = 1 << 18
 
@@ -259,6 +280,58 @@ def tree_filter_backward(grad_out, edge_weight, si, sp, sc, ls, nl, bands, saved
                                                _p(saved), _p(gf), _p(gw), _p(ws), ws.numel(), _stream()),
               "tree_filter_backward")
     return gf, gw
+
+
+# ------------------------------------------------------------------ loss glue
+
+
+def channel_softmax_fwd(x):
+    x = _cuda(x, torch.float32, "preds")
+    B, C = x.shape[0], x.shape[1]
+    P = x.numel() // (B * C)
+    with torch.cuda.device(x.device):
+        y = torch.empty_like(x)
+        check(lib.fedicra_channel_softmax_fwd(_p(x), B, C, P, _p(y), _stream()), "channel_softmax_fwd")
+    return y
+
+
+def channel_softmax_bwd(y, grad_y):
+    g = _cuda(grad_y, torch.float32, "grad_prob")
+    B, C = y.shape[0], y.shape[1]
+    P = y.numel() // (B * C)
+    with torch.cuda.device(y.device):
+        gx = torch.empty_like(y)
+        check(lib.fedicra_channel_softmax_bwd(_p(y), _p(g), B, C, P, _p(gx), _stream()), "channel_softmax_bwd")
+    return gx
+
+
+def masked_l1_fwd(prob, filtered, roi_u8, weight):
+    """-> sums [2] = (sum roi*|prob-filtered|, N), loss [1] = weight * sums[0] / max(N, 1)."""
+    prob = _cuda(prob, torch.float32, "prob")
+    filtered = _cuda(filtered, torch.float32, "filtered")
+    roi = _cuda(roi_u8, torch.uint8, "roi")
+    B, C = prob.shape[0], prob.shape[1]
+    P = prob.numel() // (B * C)
+    assert roi.numel() == B * P and filtered.shape == prob.shape
+    with torch.cuda.device(prob.device):
+        sums = torch.empty(2, dtype=torch.float32, device=prob.device)
+        loss = torch.empty(1, dtype=torch.float32, device=prob.device)
+        ws = workspace("masked_l1", lib.fedicra_masked_l1_workspace_bytes(), prob.device)
+        check(lib.fedicra_masked_l1_fwd(_p(prob), _p(filtered), _p(roi), B, C, P, float(weight), _p(sums), _p(loss),
+                                        _p(ws), ws.numel(), _stream()), "masked_l1_fwd")
+    return sums, loss
+
+
+def masked_l1_bwd(prob, filtered, roi_u8, grad_out, n, weight, want_prob=True, want_filtered=True):
+    B, C = prob.shape[0], prob.shape[1]
+    P = prob.numel() // (B * C)
+    g = _cuda(grad_out.reshape(-1), torch.float32, "grad_loss")
+    with torch.cuda.device(prob.device):
+        gp = torch.empty_like(prob) if want_prob else None
+        gf = torch.empty_like(prob) if want_filtered else None
+        check(lib.fedicra_masked_l1_bwd(_p(prob), _p(filtered), _p(roi_u8), _p(g), _p(n), float(weight), B, C, P, _p(gp),
+                                        _p(gf), _stream()), "masked_l1_bwd")
+    return gp, gf
 
 
 # ------------------------------------------------------------------ aggregation

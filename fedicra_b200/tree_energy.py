@@ -9,19 +9,26 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from . import ops
 from .tree_filter import MinimumSpanningTree, TreeFilter2D, batched_tree_orders
 
 
 def _prepare(preds, low_feats, unlabeled_ROIs):
-    """flower_common.py:770-777: bring the image embedding and the ROI mask to the prediction size."""
+    """flower_common.py:770-777: bring the image embedding and the ROI mask to the prediction size.  Returns the
+    embedding, the float ROI + its sum for the generic path, and (when the mask already has the prediction size and the
+    tensors are on the GPU) the mask as bytes for the fused masked-L1 kernel, in which case roi / N are not computed."""
     with torch.no_grad():
         h, w = preds.shape[2:]
         if low_feats.shape[2:] != (h, w):
             low_feats = F.interpolate(low_feats, size=(h, w), mode='bilinear', align_corners=False)
+        if preds.is_cuda and unlabeled_ROIs.shape[-2:] == (h, w) and unlabeled_ROIs.dtype in (torch.bool, torch.uint8):
+            roi_u8 = unlabeled_ROIs.contiguous().view(torch.uint8) if unlabeled_ROIs.dtype == torch.bool \
+                else unlabeled_ROIs.contiguous()
+            return low_feats, None, None, roi_u8
         roi = unlabeled_ROIs.unsqueeze(1).float()
         if roi.shape[2:] != (h, w):
             roi = F.interpolate(roi, size=(h, w), mode='nearest')
-        return low_feats, roi, roi.sum()
+        return low_feats, roi, roi.sum(), None
 
 
 def _resize(feats, h, w):
@@ -41,8 +48,66 @@ def _normalise(loss_sum, n, distributed):
     return loss_sum / torch.clamp(n, min=1.0)
 
 
-def _masked_l1(roi, prob, filtered, n, distributed=False):
-    return _normalise((roi * torch.abs(prob - filtered)).sum(), n, distributed)
+class _ChannelSoftmax(torch.autograd.Function):
+    """torch.softmax(preds, dim=1) (flower_common.py:781), one pass per direction (csrc/glue.cu)."""
+
+    @staticmethod
+    def forward(ctx, preds):
+        prob = ops.channel_softmax_fwd(preds)
+        ctx.save_for_backward(prob)
+        return prob
+
+    @staticmethod
+    def backward(ctx, grad_prob):
+        (prob,) = ctx.saved_tensors
+        return ops.channel_softmax_bwd(prob, grad_prob.contiguous())
+
+
+def _softmax(preds):
+    if preds.is_cuda and preds.dtype == torch.float32 and preds.shape[1] <= 16:
+        return _ChannelSoftmax.apply(preds.contiguous())
+    return torch.softmax(preds, dim=1)
+
+
+class _MaskedL1(torch.autograd.Function):
+    """(ROI * |prob - filtered|).sum(), N and weight * sum / max(N, 1) in one pass (flower_common.py:777, 813-818).
+    Returns (loss, sums): `loss` (0-d) is for the single-GPU path, `sums` = (sum, N) feeds the sharded normalisation
+    (only sums[0] carries a gradient)."""
+
+    @staticmethod
+    def forward(ctx, prob, filtered, roi_u8, weight):
+        sums, loss = ops.masked_l1_fwd(prob, filtered, roi_u8, weight)
+        ctx.save_for_backward(prob, filtered, roi_u8, sums)
+        ctx.weight = float(weight)
+        ctx.set_materialize_grads(False)
+        return loss.reshape(()), sums
+
+    @staticmethod
+    def backward(ctx, grad_loss, grad_sums):
+        prob, filtered, roi_u8, sums = ctx.saved_tensors
+        want_p, want_f = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        gp = gf = None
+        if want_p or want_f:
+            # whichever output the caller used: d loss (scaled by weight / max(N, 1) inside the kernel) or d sums[0]
+            for g, n in ((grad_loss, sums[1:2]), (None if grad_sums is None else grad_sums[0:1], None)):
+                if g is None:
+                    continue
+                a, b = ops.masked_l1_bwd(prob, filtered, roi_u8, g.contiguous(), n, ctx.weight, want_p, want_f)
+                gp = a if gp is None else (gp + a if a is not None else gp)
+                gf = b if gf is None else (gf + b if b is not None else gf)
+        return gp, gf, None, None
+
+
+def _masked_l1(roi, prob, filtered, n, distributed=False, weight=1.0, roi_u8=None):
+    """weight * (roi * |prob - filtered|).sum() / N   (N over the global batch when `distributed`)."""
+    if isinstance(weight, torch.Tensor):   # keep a tensor weight on the device: scale outside the kernel
+        return weight * _masked_l1(roi, prob, filtered, n, distributed, 1.0, roi_u8)
+    if roi_u8 is not None and prob.is_cuda and prob.dtype == torch.float32 and filtered.dtype == torch.float32:
+        loss, sums = _MaskedL1.apply(prob.contiguous(), filtered.contiguous(), roi_u8, weight)
+        if not distributed:
+            return loss
+        return weight * _normalise(sums[0], sums[1].detach(), True)
+    return weight * _normalise((roi * torch.abs(prob - filtered)).sum(), n, distributed)
 
 
 class _TreeLossBase(nn.Module):
@@ -71,35 +136,36 @@ class _TreeLossBase(nn.Module):
 
 class TreeEnergyLoss(_TreeLossBase):
     def forward(self, preds, low_feats, high_feats, unlabeled_ROIs, weight):
-        low_feats, roi, n = _prepare(preds, low_feats, unlabeled_ROIs)
+        low_feats, roi, n, roi_u8 = _prepare(preds, low_feats, unlabeled_ROIs)
         h, w = preds.shape[2:]
-        prob = torch.softmax(preds, dim=1)
+        prob = _softmax(preds)
         highs = [] if high_feats is None else [_resize(high_feats, h, w)]
         trees = self._trees([low_feats] + highs)
         AS = self._low(prob, low_feats, trees[0])
         if highs:
             AS = self._high(AS, highs[0], h, w, trees[1])
-        return weight * _masked_l1(roi, prob, AS, n, self.distributed), AS
+        return _masked_l1(roi, prob, AS, n, self.distributed, weight, roi_u8), AS
 
 
 class MScaleAddTreeEnergyLoss(_TreeLossBase):
     def forward(self, preds, low_feats, high_feats_1, high_feats_2, high_feats_3, unlabeled_ROIs, weight):
-        low_feats, roi, n = _prepare(preds, low_feats, unlabeled_ROIs)
+        low_feats, roi, n, roi_u8 = _prepare(preds, low_feats, unlabeled_ROIs)
         h, w = preds.shape[2:]
-        prob = torch.softmax(preds, dim=1)
+        prob = _softmax(preds)
         highs = [_resize(hf, h, w) for hf in (high_feats_1, high_feats_2, high_feats_3)]
         trees = self._trees([low_feats] + highs)
         AS = self._low(prob, low_feats, trees[0])
         outs = [self._high(AS, hf, h, w, t) for hf, t in zip(highs, trees[1:])]
-        loss = _normalise(sum((roi * torch.abs(prob - o)).sum() for o in outs), n, self.distributed)
-        return (weight * loss, *outs)
+        # flower_common.py:748-751: the three masked-L1 sums share one normaliser
+        loss = sum(_masked_l1(roi, prob, o, n, self.distributed, weight, roi_u8) for o in outs)
+        return (loss, *outs)
 
 
 class MScaleRecurveTreeEnergyLoss(_TreeLossBase):
     def forward(self, preds, low_feats, high_feats_1, high_feats_2, high_feats_3, unlabeled_ROIs, weight):
-        low_feats, roi, n = _prepare(preds, low_feats, unlabeled_ROIs)
+        low_feats, roi, n, roi_u8 = _prepare(preds, low_feats, unlabeled_ROIs)
         h, w = preds.shape[2:]
-        prob = torch.softmax(preds, dim=1)
+        prob = _softmax(preds)
         highs = [_resize(hf, h, w) for hf in (high_feats_1, high_feats_2, high_feats_3)]
         trees = self._trees([low_feats] + highs)
         cur = self._low(prob, low_feats, trees[0])
@@ -107,4 +173,4 @@ class MScaleRecurveTreeEnergyLoss(_TreeLossBase):
         for hf, t in zip(highs, trees[1:]):
             cur = self._high(cur, hf, h, w, t)
             outs.append(cur)
-        return (weight * _masked_l1(roi, prob, cur, n, self.distributed), *outs)
+        return (_masked_l1(roi, prob, cur, n, self.distributed, weight, roi_u8), *outs)

@@ -33,14 +33,17 @@ class _TreeOrder:
 
 def batched_tree_orders(embeds):
     """MST + BFS of several embeddings of one batch in ONE pass: the embeddings ([B,D_k,H,W], same B/H/W) are stacked
-    along the batch axis (channels zero-padded to the widest: adding 0*0 leaves every fp32 edge weight bit-identical) so
-    that each kernel of the topology stage is launched once for all of them.  Returns one _TreeOrder per embedding."""
+    along the batch axis -- by a pointer table, not by a copy -- so that each kernel of the topology stage is launched
+    once for all of them.  Returns one _TreeOrder per embedding."""
     B, _, H, W = embeds[0].shape
-    D = max(e.shape[1] for e in embeds)
     with torch.no_grad():
-        stacked = torch.cat([torch.nn.functional.pad(e.detach().float(), (0, 0, 0, 0, 0, D - e.shape[1])) for e in embeds], 0)
         fits = H * W <= max(ops.BFS_GRID_MAX_V, ops.BFS_EULER_MAX_V)
-        tree, mask = ops.mst_grid(stacked, want_mask=True, want_edges=not fits)  # the mask alone feeds the grid BFS
+        if len(embeds) <= 8:   # one launch straight from the K tensors (pointer table), nothing stacked
+            tree, mask = ops.mst_grid_multi([e.detach().float() for e in embeds], want_mask=True, want_edges=not fits)
+        else:
+            D = max(e.shape[1] for e in embeds)
+            stacked = torch.cat([torch.nn.functional.pad(e.detach().float(), (0, 0, 0, 0, 0, D - e.shape[1])) for e in embeds], 0)
+            tree, mask = ops.mst_grid(stacked, want_mask=True, want_edges=not fits)  # the mask alone feeds the grid BFS
         arrays = ops.bfs_from_mask(mask, H, W) if fits else ops.bfs_forward(tree)
         bands = ops.band_plan(arrays[3], arrays[4]).view(len(embeds) * B, -1)
     return [_TreeOrder(arrays=tuple(a[k * B:(k + 1) * B] for a in (*arrays, bands))) for k in range(len(embeds))]

@@ -91,6 +91,13 @@ int fedicra_mst_forward(const int *edge_index, const float *edge_weight, int B, 
 int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out, unsigned char *tree_mask,
                      void *workspace, size_t workspace_bytes, void *stream);
 
+/* The same for the trees of K embeddings of one batch in ONE launch (the image and the decoder heads of the multiscale
+ * loss, flower_common.py:784-803: four MinimumSpanningTree calls per step): h_embeds / h_D are HOST arrays of K device
+ * pointers [B,D_k,H,W] and channel counts (K <= 8).  Tree k*B + b is image b of embedding k; edge_out [K*B,H*W-1,2],
+ * tree_mask [K*B,H*W]; workspace for K*B images. */
+int fedicra_mst_grid_multi(const float *const *h_embeds, const int *h_D, int K, int B, int H, int W, int *edge_out,
+                           unsigned char *tree_mask, void *workspace, size_t workspace_bytes, void *stream);
+
 /* ------------------------------------------------------------------------------------------------ BFS ---------- */
 size_t fedicra_bfs_workspace_bytes(int B, int V);
 
@@ -174,6 +181,28 @@ int fedicra_tree_filter_backward(const float *grad_out, const float *edge_weight
                                  const int *n_levels, const int *bands, int B, int C, int V, const void *saved,
                                  float *grad_feature, float *grad_weight, void *workspace, size_t workspace_bytes,
                                  void *stream);
+
+/* ------------------------------------------------------------------------------------------------ loss glue ---- */
+/* prob = softmax over the channel axis of x [B,C,P]  (flower_common.py:781, torch.softmax(preds, dim=1)); C <= 16. */
+int fedicra_channel_softmax_fwd(const float *x, int B, int C, long long P, float *y, void *stream);
+/* Its backward: grad_x = y * (grad_y - sum_c grad_y * y). */
+int fedicra_channel_softmax_bwd(const float *y, const float *grad_y, int B, int C, long long P, float *grad_x,
+                                void *stream);
+
+/* Masked L1 tail of the tree-energy losses (flower_common.py:777, 813-818) in one pass:
+ *   sums[0] = sum_{b,c,p} roi[b,p] * |prob[b,c,p] - filtered[b,c,p]|,   sums[1] = N = sum roi,
+ *   loss[0] = weight * sums[0] / max(N, 1)      (equals the reference's `if N > 0: loss /= N` without its host sync).
+ * roi [B,P] bytes (0 / non-0).  The workspace (fedicra_masked_l1_workspace_bytes) must be zero before its first use;
+ * the call leaves it reusable.  Deterministic (fixed summation order). */
+size_t fedicra_masked_l1_workspace_bytes(void);
+int fedicra_masked_l1_fwd(const float *prob, const float *filtered, const unsigned char *roi, int B, int C, long long P,
+                          float weight, float *sums, float *loss, void *workspace, size_t workspace_bytes, void *stream);
+/* Backward: grad_prob = s * roi * sign(prob - filtered), grad_filtered = -grad_prob (either may be NULL), with
+ * s = grad_out[0] * weight / max(n[0], 1) when n is given (gradient of loss[0]), s = grad_out[0] when n is NULL
+ * (gradient of sums[0]; the sharded path divides after its all-reduce). */
+int fedicra_masked_l1_bwd(const float *prob, const float *filtered, const unsigned char *roi, const float *grad_out,
+                          const float *n, float weight, int B, int C, long long P, float *grad_prob,
+                          float *grad_filtered, void *stream);
 
 /* Telemetry of the resident filter kernel (no counterpart in the reference): with FEDICRA_PROF=1 in the environment the
  * CTAs of the first image of a launch record %globaltimer at their phase boundaries.  Copies the last launch's

@@ -1,0 +1,79 @@
+"""Fused element-wise ends of the tree-energy loss (csrc/glue.cu) and the multi-embedding MST launch, against PyTorch
+expressions of the reference lines they replace (flower_common.py:777-781, 813-818)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+def rel(a, b):
+    return float((a.double() - b.double()).abs().max() / b.double().abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("B,C,H,W", [(12, 2, 256, 256), (3, 3, 37, 41), (1, 1, 5, 7), (2, 16, 16, 16)])
+def test_channel_softmax_forward_backward(B, C, H, W):
+    from fedicra_b200.tree_energy import _ChannelSoftmax
+    g = torch.Generator().manual_seed(1)
+    x = (torch.randn(B, C, H, W, generator=g) * 3).cuda()
+    gy = torch.randn(B, C, H, W, generator=g).cuda()
+    x1, x2 = x.clone().requires_grad_(), x.clone().requires_grad_()
+    y1 = _ChannelSoftmax.apply(x1)
+    y2 = torch.softmax(x2, dim=1)
+    assert rel(y1, y2) < TOL
+    (y1 * gy).sum().backward()
+    (y2 * gy).sum().backward()
+    assert rel(x1.grad, x2.grad) < TOL
+
+
+@pytest.mark.parametrize("B,C,H,W,frac", [(12, 2, 256, 256, 0.97), (2, 3, 33, 65, 0.5), (1, 2, 8, 8, 0.0)])
+def test_masked_l1_matches_reference_expression(B, C, H, W, frac):
+    from fedicra_b200.tree_energy import _masked_l1
+    g = torch.Generator().manual_seed(2)
+    prob = torch.rand(B, C, H, W, generator=g).cuda()
+    filt = torch.rand(B, C, H, W, generator=g).cuda()
+    filt[:, :, 0, :] = prob[:, :, 0, :]                       # exact ties: sign(0) = 0
+    roi_b = (torch.rand(B, H, W, generator=g) < frac).cuda()
+    weight = 0.1
+    p1, f1 = prob.clone().requires_grad_(), filt.clone().requires_grad_()
+    p2, f2 = prob.clone().requires_grad_(), filt.clone().requires_grad_()
+    for _ in range(2):                                         # the scratch counter must be left reusable
+        got = _masked_l1(None, p1, f1, None, False, weight, roi_b.view(torch.uint8))
+    roi = roi_b.unsqueeze(1).float()                           # flower_common.py:776-777, 813-818
+    n = roi.sum()
+    want = (roi * torch.abs(p2 - f2)).sum()
+    want = weight * (want / n if float(n) > 0 else want)
+    assert abs(float(got) - float(want)) <= 1e-5 * max(1.0, abs(float(want)))
+    p1.grad = f1.grad = None
+    got.backward()
+    want.backward()
+    if float(n) > 0:
+        assert rel(p1.grad, p2.grad) < TOL and rel(f1.grad, f2.grad) < TOL
+    else:
+        assert float(p1.grad.abs().max()) == 0.0
+
+
+def test_masked_l1_sums_output_feeds_the_sharded_path():
+    from fedicra_b200.tree_energy import _MaskedL1
+    g = torch.Generator().manual_seed(3)
+    prob = torch.rand(2, 2, 16, 16, generator=g).cuda().requires_grad_()
+    filt = torch.rand(2, 2, 16, 16, generator=g).cuda().requires_grad_()
+    roi_b = (torch.rand(2, 16, 16, generator=g) < 0.5).cuda()
+    _, sums = _MaskedL1.apply(prob, filt, roi_b.view(torch.uint8), 1.0)
+    (3.0 * sums[0]).backward()
+    roi = roi_b.unsqueeze(1).float()
+    assert abs(float(sums[1]) - float(roi.sum())) < 0.5
+    want = 3.0 * roi * torch.sign(prob.detach() - filt.detach())
+    assert rel(prob.grad, want) < TOL and rel(filt.grad, -want) < TOL
+
+
+def test_mst_grid_multi_equals_separate_launches():
+    from fedicra_b200 import ops
+    g = torch.Generator().manual_seed(4)
+    B, H, W = 3, 40, 56
+    embs = [((torch.rand(B, 3, H, W, generator=g) * 255).round() / 255).cuda(), torch.randn(B, 2, H, W, generator=g).cuda(),
+            torch.randn(B, 1, H, W, generator=g).cuda()]
+    edges, mask = ops.mst_grid_multi(embs, want_mask=True, want_edges=True)
+    for k, e in enumerate(embs):
+        e1, m1 = ops.mst_grid(e, want_mask=True)
+        assert torch.equal(edges[k * B:(k + 1) * B], e1) and torch.equal(mask[k * B:(k + 1) * B], m1)
