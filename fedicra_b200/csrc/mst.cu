@@ -277,7 +277,7 @@ struct EmbedSet {
 };
 
 __global__ void __launch_bounds__(PNT)
-mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, int H, int W, int max_rounds) {
+mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, int H, int W, int max_rounds, int prepared) {
     cg::cluster_group cluster = cg::this_cluster();
     const int CL = (int)cluster.num_blocks(), rank = (int)cluster.block_rank();
     const int b = blockIdx.x / CL, tid = threadIdx.x, lane = tid & 31;
@@ -290,34 +290,37 @@ mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, in
     int *cnt = ws.cnt + (size_t)b * 4;
     const int stride = CL * PNT, first = rank * PNT + tid;
 
-    // ---- init: weights (tree_filter.py:27-34, no fused multiply-add), union state
-    const int D = es.D[b / es.per];
-    const float *x = es.ptr[b / es.per] + (size_t)(b % es.per) * D * V;
-    for (int e = first; e < E; e += stride) {
-        int u, v;
-        grid_endpoints(e, H, W, u, v);
-        float d = 0.f;
-        for (int c = 0; c < D; ++c) {
-            const float t = __fsub_rn(x[(size_t)c * V + u], x[(size_t)c * V + v]);
-            d = __fadd_rn(d, __fmul_rn(t, t));
+    // ---- init: weights (tree_filter.py:27-34, no fused multiply-add), union state.  `prepared`: mst_tile_kernel has
+    //      already run the rounds that stay inside 64x64 tiles and left weights, labels, flags and the two lists
+    if (!prepared) {
+        const int D = es.D[b / es.per];
+        const float *x = es.ptr[b / es.per] + (size_t)(b % es.per) * D * V;
+        for (int e = first; e < E; e += stride) {
+            int u, v;
+            grid_endpoints(e, H, W, u, v);
+            float d = 0.f;
+            for (int c = 0; c < D; ++c) {
+                const float t = __fsub_rn(x[(size_t)c * V + u], x[(size_t)c * V + v]);
+                d = __fadd_rn(d, __fmul_rn(t, t));
+            }
+            wgt[e] = __fadd_rn(d, 1.f);
+            intree[e] = 0;
         }
-        wgt[e] = __fadd_rn(d, 1.f);
-        intree[e] = 0;
+        for (int v = first; v < V; v += stride) {
+            comp[v] = v;
+            parent[v] = v;
+            best[v] = KEY_INF;
+        }
+        if (rank == 0 && tid < 4) cnt[tid] = 0;
+        cluster.sync();
     }
-    for (int v = first; v < V; v += stride) {
-        comp[v] = v;
-        parent[v] = v;
-        best[v] = KEY_INF;
-    }
-    if (rank == 0 && tid < 4) cnt[tid] = 0;
-    cluster.sync();
 
     // Every loop below handles IL list entries per iteration with the loads of all of them issued before the first use:
     // the phases are chains of dependent L2 round trips, and one cluster only has CL*512 threads to hide them with.
     constexpr int IL = 4;
     int cur = 0;            // lists of this round: act + cur*V, roots + cur*V (round 0: the identity, not stored)
-    int nact = V, nroots = V;
-    for (int round = 0; round < max_rounds && nroots > 1; ++round) {
+    int nact = prepared ? cnt[0] : V, nroots = prepared ? cnt[2] : V;
+    for (int round = prepared ? 1 : 0; round < max_rounds + 1 && nroots > 1; ++round) {
         const int *alist = round ? act + (size_t)cur * V : nullptr, *rlist = round ? roots + (size_t)cur * V : nullptr;
         int *anext = act + (size_t)(cur ^ 1) * V, *rnext = roots + (size_t)(cur ^ 1) * V;
         int *cnt_anext = cnt + (cur ^ 1), *cnt_rnext = cnt + 2 + (cur ^ 1);
@@ -477,6 +480,281 @@ mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, in
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Tile-local Boruvka rounds.  One CTA owns a 64x64 tile of an image and runs, entirely out of shared memory, every
+// round that can be decided inside the tile: a component takes the cheapest of ALL its outgoing edges -- those that
+// leave the tile included, their weights come from the embedding's halo -- and hooks when that edge lies inside the
+// tile; when it leaves the tile the component waits for the global rounds (it may still be hooked INTO by others, after
+// which its cheapest edge is looked at again).  A component's cheapest outgoing edge belongs to the MST whatever the
+// others do (cut property, keys are distinct), so the edges chosen here are exactly those the untiled rounds would
+// choose: same edge set, bit for bit.  The rounds stop after `max_rounds` or when a whole round hooks nothing.  What is left for the cluster
+// kernel is the tile boundaries: a few hundred components per tile instead of 4 096 vertices.
+// Output: edge weights and tree flags of the tile's own edges (down / right of each of its vertices), fresh labels
+// (DEAD for vertices whose neighbours all share their component), identity hooks, and the root / active lists.
+constexpr int TS = 64, TV = TS * TS, TNT = 512;
+constexpr unsigned short T_OUT = 0xFFFFu;   // label of "the other side of the tile boundary"
+constexpr size_t TILE_SMEM = (size_t)TV * 8 + 2 * (size_t)(TS + 1) * TS * 4 + 2 * (size_t)TV * 2;
+
+__global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, int H, int W, int tiles_x, int max_rounds) {
+    // cheapest outgoing edge per component as two 32-bit words (orderable weight, edge code): shared memory has native
+    // 32-bit atomicMin.  min weight first, then min code among the edges of that weight.  The code of an edge that
+    // touches the tile is type << 14 | row << 7 | column (see s_wv / s_wh); among such edges it orders like the global
+    // edge id (vertical edges first, then row-major), so (weight, code) picks the edge (weight, edge id) would.
+    extern __shared__ unsigned s_bw[];                                // [TV] orderable weight
+    unsigned *s_be = s_bw + TV;                                       // [TV] edge code
+    float *s_wv = reinterpret_cast<float *>(s_be + TV);              // [TS+1][TS] edge (row r-1, row r) of column c; 0 = none
+    float *s_wh = s_wv + (TS + 1) * TS;                               // [TS][TS+1] edge (col c-1, col c) of row r;    0 = none
+    unsigned short *s_lab = reinterpret_cast<unsigned short *>(s_wh + TS * (TS + 1));   // [TV]
+    unsigned short *s_par = s_lab + TV;                               // [TV]
+    float *s_x = reinterpret_cast<float *>(s_bw);                     // [(TS+2)][(TS+2)] one channel of the tile + halo (init only)
+    constexpr int XS = TS + 2;
+    const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
+    const int ty = blockIdx.x / tiles_x, tx = blockIdx.x - ty * tiles_x, h0 = ty * TS, w0 = tx * TS;
+    const int th = min(TS, H - h0), tw = min(TS, W - w0);
+    const int V = H * W, E = 2 * H * W - H - W, nvert = (H - 1) * W;
+    int *comp = ws.comp + (size_t)b * V, *parent = ws.parent + (size_t)b * V;
+    u64 *best = ws.best + (size_t)b * V;
+    float *wgt = ws.wgt + (size_t)b * E;
+    unsigned char *intree = ws.intree + (size_t)b * E;
+    int *act = ws.act + (size_t)b * 2 * V, *roots = ws.roots + (size_t)b * 2 * V;
+    int *cnt = ws.cnt + (size_t)b * 4;
+    const int D = es.D[b / es.per];
+    const float *x = es.ptr[b / es.per] + (size_t)(b % es.per) * D * V;
+    auto v_valid = [&](int r, int c) { return c < tw && r <= th && h0 + r >= 1 && h0 + r < H; };      // s_wv[r][c]
+    auto h_valid = [&](int r, int c) { return r < th && c <= tw && w0 + c >= 1 && w0 + c < W; };      // s_wh[r][c]
+    // ---- weights of every edge that touches the tile: sum_c (delta)^2 + 1, channels in order, no fused multiply-add
+    //      (tree_filter.py:27-34); the embedding is staged one channel at a time (tile + one pixel of halo)
+    for (int i = tid; i < (TS + 1) * TS; i += TNT) s_wv[i] = 0.f;
+    for (int i = tid; i < TS * (TS + 1); i += TNT) s_wh[i] = 0.f;
+    for (int ch = 0; ch < D; ++ch) {
+        __syncthreads();
+        {   // all of a thread's loads first (one round trip), then the stores
+            constexpr int NX = (XS * XS + TNT - 1) / TNT;
+            float xv[NX];
+#pragma unroll
+            for (int k = 0; k < NX; ++k) {
+                const int i = tid + k * TNT, r = i / XS, c = i - r * XS, hh = h0 + r - 1, ww = w0 + c - 1;
+                xv[k] = (i < XS * XS && hh >= 0 && hh < H && ww >= 0 && ww < W) ? x[(size_t)ch * V + (size_t)hh * W + ww] : 0.f;
+            }
+#pragma unroll
+            for (int k = 0; k < NX; ++k)
+                if (tid + k * TNT < XS * XS) s_x[tid + k * TNT] = xv[k];
+        }
+        __syncthreads();
+        for (int i = tid; i < (TS + 1) * TS; i += TNT) {
+            const int r = i / TS, c = i - r * TS;   // pixels (r-1, c) and (r, c) of the tile = s_x rows r, r+1, column c+1
+            const float t = __fsub_rn(s_x[r * XS + c + 1], s_x[(r + 1) * XS + c + 1]);
+            s_wv[i] = __fadd_rn(s_wv[i], __fmul_rn(t, t));
+        }
+        for (int i = tid; i < TS * (TS + 1); i += TNT) {
+            const int r = i / (TS + 1), c = i - r * (TS + 1);   // pixels (r, c-1) and (r, c) = s_x row r+1, columns c, c+1
+            const float t = __fsub_rn(s_x[(r + 1) * XS + c], s_x[(r + 1) * XS + c + 1]);
+            s_wh[i] = __fadd_rn(s_wh[i], __fmul_rn(t, t));
+        }
+    }
+    __syncthreads();
+    // finish (+1, or 0 for "no such edge") and publish the edges the tile owns (below / right of its vertices)
+    for (int i = tid; i < (TS + 1) * TS; i += TNT) {
+        const int r = i / TS, c = i - r * TS;
+        float wt = 0.f;
+        if (v_valid(r, c)) {
+            wt = __fadd_rn(s_wv[i], 1.f);
+            if (r >= 1) {
+                const int e = (h0 + r - 1) * W + w0 + c;
+                wgt[e] = wt;
+                intree[e] = 0;
+            }
+        }
+        s_wv[i] = wt;
+    }
+    for (int i = tid; i < TS * (TS + 1); i += TNT) {
+        const int r = i / (TS + 1), c = i - r * (TS + 1);
+        float wt = 0.f;
+        if (h_valid(r, c)) {
+            wt = __fadd_rn(s_wh[i], 1.f);
+            if (c >= 1) {
+                const int e = nvert + (h0 + r) * (W - 1) + w0 + c - 1;
+                wgt[e] = wt;
+                intree[e] = 0;
+            }
+        }
+        s_wh[i] = wt;
+    }
+    for (int l = tid; l < TV; l += TNT) {
+        s_lab[l] = (unsigned short)l;
+        s_par[l] = (unsigned short)l;
+        s_bw[l] = 0xffffffffu;
+        s_be[l] = 0xffffffffu;
+    }
+    __syncthreads();
+    // ---- rounds.  Thread t owns vertices (row (t >> 6) + 8q, column t & 63), q = 0..7.
+    constexpr int PER = TV / TNT;
+    const int c = tid & (TS - 1), rbase = tid >> 6;
+    unsigned interior = 0;   // bit q: all four neighbours share the vertex's component -- for good (components only grow)
+#pragma unroll
+    for (int q = 0; q < PER; ++q)
+        if (rbase + q * (TNT / TS) >= th || c >= tw) interior |= 1u << q;   // outside the image: never looked at
+    for (int round = 0; round < max_rounds; ++round) {
+        // find: cheapest outgoing edge per component (outgoing = other label, or the other side of the tile boundary)
+        unsigned kw[PER], ke[PER];
+        unsigned short kc[PER];
+#pragma unroll
+        for (int q = 0; q < PER; ++q) {
+            kw[q] = ke[q] = 0xffffffffu;
+            kc[q] = 0;
+            if (interior & (1u << q)) continue;
+            const int r = rbase + q * (TNT / TS), l = r * TS + c;
+            const unsigned short cl = s_lab[l];
+            kc[q] = cl;
+            const float wu = s_wv[l], wd = s_wv[l + TS], wl = s_wh[l + r], wr = s_wh[l + r + 1];
+            // candidates in increasing code order (up, down are vertical: codes r<<7|c and (r+1)<<7|c; then left, right)
+            unsigned bw = 0xffffffffu, be = 0xffffffffu;
+            auto take = [&](float wt, unsigned code) {
+                const unsigned o = orderable(wt);
+                if (o < bw) { bw = o; be = code; }   // strict: on equal weight the earlier (smaller) code stays
+            };
+            if (wu > 0.f && (r == 0 || s_lab[l - TS] != cl)) take(wu, (unsigned)(r << 7 | c));
+            if (wd > 0.f && (r + 1 >= th || s_lab[l + TS] != cl)) take(wd, (unsigned)((r + 1) << 7 | c));
+            if (wl > 0.f && (c == 0 || s_lab[l - 1] != cl)) take(wl, (unsigned)(1 << 14 | r << 7 | c));
+            if (wr > 0.f && (c + 1 >= tw || s_lab[l + 1] != cl)) take(wr, (unsigned)(1 << 14 | r << 7 | (c + 1)));
+            kw[q] = bw;
+            ke[q] = be;
+            if (be == 0xffffffffu) interior |= 1u << q;
+        }
+        // one atomic per warp when all its candidates belong to one component (the usual case once components are
+        // large: a warp is 32 consecutive pixels of a row), else one per lane -- and only when it can lower the slot
+#pragma unroll
+        for (int q = 0; q < PER; ++q) {
+            const bool has = ke[q] != 0xffffffffu;
+            const unsigned m = __ballot_sync(0xffffffffu, has);
+            if (m == 0) continue;
+            const int first = __ffs(m) - 1;
+            const unsigned c0l = __shfl_sync(0xffffffffu, (unsigned)kc[q], first);
+            if (__all_sync(0xffffffffu, !has || kc[q] == c0l)) {
+                const unsigned wmin = __reduce_min_sync(0xffffffffu, kw[q]);
+                if (lane == first && wmin < s_bw[c0l]) atomicMin(s_bw + c0l, wmin);
+            } else if (has && kw[q] < s_bw[kc[q]]) {
+                atomicMin(s_bw + kc[q], kw[q]);
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < PER; ++q) {
+            const bool has = ke[q] != 0xffffffffu && s_bw[kc[q]] == kw[q];
+            const unsigned m = __ballot_sync(0xffffffffu, has);
+            if (m == 0) continue;
+            const int first = __ffs(m) - 1;
+            const unsigned c0l = __shfl_sync(0xffffffffu, (unsigned)kc[q], first);
+            if (__all_sync(0xffffffffu, !has || kc[q] == c0l)) {
+                const unsigned emin = __reduce_min_sync(0xffffffffu, has ? ke[q] : 0xffffffffu);
+                if (lane == first && emin < s_be[c0l]) atomicMin(s_be + c0l, emin);
+            } else if (has && ke[q] < s_be[kc[q]]) {
+                atomicMin(s_be + kc[q], ke[q]);
+            }
+        }
+        __syncthreads();
+
+        // hook: a root whose cheapest edge lies inside the tile follows it (of a mutual pair the larger root hooks)
+        int merged = 0;
+#pragma unroll
+        for (int q = 0; q < PER; ++q) {
+            const int r = rbase + q * (TNT / TS), l = r * TS + c;
+            if (r >= th || c >= tw || s_lab[l] != l) continue;
+            const unsigned code = s_be[l];
+            if (code == 0xffffffffu) continue;
+            const int horiz = code >> 14, er = (code >> 7) & 127, ec = code & 127;
+            int la, lb;   // local endpoints
+            if (!horiz) {
+                if (er < 1 || er >= th) continue;   // leaves the tile
+                la = (er - 1) * TS + ec;
+                lb = er * TS + ec;
+            } else {
+                if (ec < 1 || ec >= tw) continue;
+                la = er * TS + ec - 1;
+                lb = er * TS + ec;
+            }
+            const int ca = s_lab[la], cb = s_lab[lb];
+            const int other = (ca == l) ? cb : ca;
+            if (s_be[other] == code && l < other) continue;   // same edge from both sides (codes are unique)
+            s_par[l] = (unsigned short)other;
+            intree[horiz ? nvert + (h0 + er) * (W - 1) + w0 + ec - 1 : (h0 + er - 1) * W + w0 + ec] = 1;
+            merged = 1;
+        }
+        merged = __syncthreads_or(merged);
+        // chase: labels follow the hooks; cheapest-edge slots are cleared for the next round
+#pragma unroll
+        for (int q = 0; q < PER; ++q) {
+            const int l = (rbase + q * (TNT / TS)) * TS + c;
+            int r = s_lab[l], p = s_par[r];
+            while (p != r) { r = p; p = s_par[r]; }
+            s_lab[l] = (unsigned short)r;
+            s_bw[l] = 0xffffffffu;
+            s_be[l] = 0xffffffffu;
+        }
+        __syncthreads();
+        if (!merged) break;
+    }
+    // ---- hand over to the cluster kernel: global labels, identity hooks, root and active lists.  The two lists are
+    //      collected in shared memory (the cheapest-edge slots are free now) and appended with ONE reservation each.
+    int *s_act = reinterpret_cast<int *>(s_bw), *s_root = reinterpret_cast<int *>(s_be);
+    __shared__ int s_nact, s_nroot, s_abase, s_rbase;
+    if (tid == 0) { s_nact = 0; s_nroot = 0; }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < PER; ++q) {
+        const int r = rbase + q * (TNT / TS), l = r * TS + c;
+        const bool valid = r < th && c < tw;
+        bool is_root = false, is_act = false;
+        int gv = 0;
+        if (valid) {
+            gv = (h0 + r) * W + w0 + c;
+            const int cl = s_lab[l];
+            is_root = cl == l;
+            is_act = !(interior & (1u << q));
+            comp[gv] = is_act ? (h0 + (cl >> 6)) * W + w0 + (cl & (TS - 1)) : DEAD;
+            parent[gv] = gv;
+            best[gv] = KEY_INF;
+        }
+        unsigned m = __ballot_sync(0xffffffffu, is_act);
+        if (m) {
+            const int leader = __ffs(m) - 1;
+            int base = 0;
+            if (lane == leader) base = atomicAdd(&s_nact, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (is_act) s_act[base + __popc(m & ((1u << lane) - 1u))] = gv;
+        }
+        m = __ballot_sync(0xffffffffu, is_root);
+        if (m) {
+            const int leader = __ffs(m) - 1;
+            int base = 0;
+            if (lane == leader) base = atomicAdd(&s_nroot, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (is_root) s_root[base + __popc(m & ((1u << lane) - 1u))] = gv;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) s_abase = atomicAdd(cnt + 0, s_nact);
+    if (tid == 32) s_rbase = atomicAdd(cnt + 2, s_nroot);
+    __syncthreads();
+    for (int i = tid; i < s_nact; i += TNT) act[s_abase + i] = s_act[i];
+    for (int i = tid; i < s_nroot; i += TNT) roots[s_rbase + i] = s_root[i];
+}
+
+// Tile-local rounds before the cluster kernel takes over.  The tile kernel is issue-bound (~9 us per round and CTA, 2.6
+// waves of CTAs for 48 trees of 256^2) and its late rounds hook little; measured on B200, 48 trees, total MST time:
+// 3 rounds 381 us, 4 rounds 367 us, 5 rounds 377 us, 6 rounds 393 us, until nothing hooks (7-8 rounds) 420 us, no tile
+// kernel at all 490 us.
+int env_tile_rounds() {
+    const char *v = getenv("FEDICRA_MST_TILE_ROUNDS");
+    const int x = (v && *v) ? atoi(v) : 4;
+    return x >= 1 ? x : 4;
+}
+
+int env_tiles() {
+    const char *v = getenv("FEDICRA_MST_TILES");
+    return !(v && *v == '0');
+}
+
 int env_cl(int dflt) {
     const char *v = getenv("FEDICRA_MST_CL");
     const int x = (v && *v) ? atoi(v) : dflt;
@@ -559,7 +837,17 @@ int mst_grid_launch(const EmbedSet &es, int B, int H, int W, int *edge_out, unsi
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
-        cudaError_t e = cudaLaunchKernelEx(&cfg, mst_grid_cluster_kernel, ws, es, tree_mask, H, W, rounds_for(V));
+        int prepared = 0;
+        if (env_tiles()) {   // rounds that stay inside 64x64 tiles first, out of shared memory
+            cudaError_t e0 = cudaFuncSetAttribute(mst_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_SMEM);
+            if (e0 != cudaSuccess) return fedicra_fail(-2, "mst_tile_kernel: %s", cudaGetErrorString(e0));
+            cudaMemsetAsync(ws.cnt, 0, (size_t)B * 4 * sizeof(int), st);
+            const int tiles_x = (W + TS - 1) / TS, tiles_y = (H + TS - 1) / TS;
+            mst_tile_kernel<<<dim3(tiles_x * tiles_y, B), TNT, TILE_SMEM, st>>>(ws, es, H, W, tiles_x, env_tile_rounds());
+            FEDICRA_CHECK_LAUNCH("mst_tile_kernel");
+            prepared = 1;
+        }
+        cudaError_t e = cudaLaunchKernelEx(&cfg, mst_grid_cluster_kernel, ws, es, tree_mask, H, W, rounds_for(V), prepared);
         fedicra_count_launches(1);
         if (e != cudaSuccess) return fedicra_fail(-2, "mst_grid_cluster_kernel: %s", cudaGetErrorString(e));
         if (edge_out != nullptr) {
