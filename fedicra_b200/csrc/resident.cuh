@@ -105,6 +105,11 @@ __device__ __forceinline__ void resident_inputs(const ResidentArgs &a, int b, in
             }
     }
 }
+// The sweeps of different channels never read each other's rows: inside a sweep the two warps of a channel meet at their
+// own named barrier (ids 1..NC) instead of stopping the whole CTA at every level.
+__device__ __forceinline__ void channel_barrier(int c) {
+    asm volatile("bar.sync %0, %1;" ::"r"(c + 1), "n"(RSLOTS) : "memory");
+}
 __device__ __forceinline__ int sls_or(bool cached, const int *sls, const int *ls, int L, int L0) {
     return cached ? sls[L - L0] : ls[L];
 }
@@ -123,15 +128,18 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
     const int4 *child = t.child + (size_t)b * V;
     const float *w = t.w + (size_t)b * V;
     const size_t img = (size_t)b * NC * V;
-    float *sval = reinterpret_cast<float *>(smem);       // [NC][pcap]
-    float *sw = sval + (size_t)NC * pcap;                // [pcap]
-    int *spk = reinterpret_cast<int *>(sw + pcap);       // [pcap]; after D1: the stitched values of the level above
-    int *sls = spk + pcap;                               // [LSCAP+1]
+    // rows of ps = pcap + 1 entries: the last one is the "zero slot" (value 0, weight 0) that a missing child points to,
+    // so that the sweeps load four children unconditionally instead of branching on the child count
+    const int ps = pcap + 1;
+    float *sval = reinterpret_cast<float *>(smem);       // [NC][ps]
+    float *sw = sval + (size_t)NC * ps;                  // [ps]
+    int *spk = reinterpret_cast<int *>(sw + ps);         // [ps]; after D1: the stitched values of the level above
+    int *sls = spk + ps;                                 // [LSCAP+1] level starts (a shared-memory band has <= LSCAP levels)
     float *gval = a.slab + img + p0;                     // oversized band: its state; otherwise: cache of the inputs
     int *sync = a.sync + (size_t)b * SYNC_INTS;
     const bool ls_cached = (L1 - L0) <= LSCAP;
     auto LSl = [&](int L) -> int { return (ls_cached ? sls[L - L0] : ls[L]) - p0; };   // level start, band-local
-    auto VAL = [&](int c, int il) -> float & { return SMEM ? sval[c * pcap + il] : gval[(size_t)c * V + il]; };
+    auto VAL = [&](int c, int il) -> float & { return SMEM ? sval[c * ps + il] : gval[(size_t)c * V + il]; };
     auto Wl = [&](int il) -> float { return SMEM ? sw[il] : ((p0 + il == 0) ? 0.f : w[p0 + il]); };
     auto kids = [&](int il, int &cl, int &cnt) {
         if (SMEM) {
@@ -159,6 +167,8 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
             spk[il] = gpk[il];
             sw[il] = (p0 + il == 0) ? 0.f : gw[il];
         }
+        if (tid < NC) sval[tid * ps + pcap] = 0.f;
+        if (tid == NC) sw[pcap] = 0.f;
     }
     // inputs: computed once (vertex-order gathers, one reciprocal per position); a shared-memory band also leaves them
     // in the slab, position order, from where the second sweep re-reads them with coalesced loads
@@ -196,7 +206,7 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
             for (int u = 0; u < 2 * U; ++u)
                 if (base + u * nthr < P) {
 #pragma unroll
-                    for (int cc = 0; cc < NCT; ++cc) sval[cc * pcap + base + u * nthr] = x[u][cc];
+                    for (int cc = 0; cc < NCT; ++cc) sval[cc * ps + base + u * nthr] = x[u][cc];
                 }
         }
     };
@@ -206,32 +216,31 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
         if (inject)
             for (int il = lo + slot; il < hi; il += RSLOTS) VAL(c, il) += __ldcg(a.X + img + (size_t)c * V + p0 + il);
         if (SMEM) {
-            // Software-pipelined: a level step is a chain of dependent shared-memory loads (level start -> packed
-            // topology -> child weights -> child values) and only the last link depends on the sweep itself.  The
-            // others are fetched one level (level starts: two levels) ahead, so that between two barriers a thread
-            // waits for one load of child values, four FMAs and a store.
-            float *mv = sval + c * pcap;   // this thread's channel row
-            const int Pm1 = P - 1;
-            auto start_of = [&](int L) -> int { return (L > L0) ? sls_or(ls_cached, sls, ls, L, L0) - p0 : 0; };
-            int L = L1 - 2;
-            hi = lo;                                   // level L = [lo, hi)
-            lo = (L >= L0) ? start_of(L) : 0;
-            int nlo = (L - 1 >= L0) ? start_of(L - 1) : 0;
+            // Software-pipelined and branch-free: a level step is a chain of dependent shared-memory loads (level start
+            // -> packed topology -> child weights -> child values) of which only the last link depends on the sweep.
+            // The others are fetched one level (level starts: two levels) ahead; a missing child is the zero slot.
+            // Between two barriers a thread then waits for one batch of value loads, four FMAs and a store.
+            float *mv = sval + c * ps;         // this thread's channel row
+            const int Z = pcap;                // zero slot
+            auto S = [&](int q) -> int { return sls[max(q, 0)] - p0; };   // start of level L0 + q, band-local (S(0) = 0)
+            auto kid = [&](int pk, int q) -> int { return ((pk & 7) > q) ? ((pk >> 3) & 0x1fff) + q : Z; };
+            int q = L1 - 2 - L0;               // level being processed = L0 + q = [lo, hi)
+            hi = lo;
+            lo = S(q);
+            int nlo = S(q - 1);
             int il = lo + slot;
-            bool act = (L >= L0) && il < hi;
+            bool act = q >= 0 && il < hi;
             int pk = act ? spk[il] : 0;
-            int cl = (pk >> 3) & 0x1fff, cnt = pk & 7;
-            float w0 = (cnt > 0) ? sw[cl] : 0.f, w1 = (cnt > 1) ? sw[min(cl + 1, Pm1)] : 0.f,
-                  w2 = (cnt > 2) ? sw[min(cl + 2, Pm1)] : 0.f, w3 = (cnt > 3) ? sw[min(cl + 3, Pm1)] : 0.f;
-            for (; L >= L0; --L) {
-                // next level [nlo, lo): its topology does not depend on the values
-                const int nnlo = (L - 2 >= L0) ? start_of(L - 2) : 0;
+            int i0 = kid(pk, 0), i1 = kid(pk, 1), i2 = kid(pk, 2), i3 = kid(pk, 3);
+            float w0 = sw[i0], w1 = sw[i1], w2 = sw[i2], w3 = sw[i3];
+            for (; q >= 0; --q) {
+                const int nnlo = S(q - 2);
                 const int nil = nlo + slot;
-                const bool nact = (L - 1 >= L0) && nil < lo;
-                const int npk = nact ? spk[nil] : 0;
-                __syncthreads();                       // the children of level L are final
+                const bool nact = q >= 1 && nil < lo;
+                const int npk = nact ? spk[nil] : 0;    // next level [nlo, lo): its topology does not depend on the values
+                channel_barrier(c);                    // the children of this level are final (this channel's 64 threads)
                 if (act) {
-                    const float v0 = mv[cl], v1 = mv[min(cl + 1, Pm1)], v2 = mv[min(cl + 2, Pm1)], v3 = mv[min(cl + 3, Pm1)];
+                    const float v0 = mv[i0], v1 = mv[i1], v2 = mv[i2], v3 = mv[i3];
                     float acc = mv[il];
                     acc = fmaf(v0, w0, acc);
                     acc = fmaf(v1, w1, acc);
@@ -239,21 +248,18 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
                     acc = fmaf(v3, w3, acc);
                     mv[il] = acc;
                     for (int j = il + RSLOTS; j < hi; j += RSLOTS) {   // levels wider than the slots
-                        const int pj = spk[j], cj = (pj >> 3) & 0x1fff, nj = pj & 7;
+                        const int pj = spk[j];
+                        const int j0 = kid(pj, 0), j1 = kid(pj, 1), j2 = kid(pj, 2), j3 = kid(pj, 3);
                         float aj = mv[j];
-                        if (nj > 0) aj = fmaf(mv[cj], sw[cj], aj);
-                        if (nj > 1) aj = fmaf(mv[cj + 1], sw[cj + 1], aj);
-                        if (nj > 2) aj = fmaf(mv[cj + 2], sw[cj + 2], aj);
-                        if (nj > 3) aj = fmaf(mv[cj + 3], sw[cj + 3], aj);
+                        aj = fmaf(mv[j0], sw[j0], aj);
+                        aj = fmaf(mv[j1], sw[j1], aj);
+                        aj = fmaf(mv[j2], sw[j2], aj);
+                        aj = fmaf(mv[j3], sw[j3], aj);
                         mv[j] = aj;
                     }
                 }
-                cl = (npk >> 3) & 0x1fff;
-                cnt = npk & 7;
-                w0 = (cnt > 0) ? sw[cl] : 0.f;
-                w1 = (cnt > 1) ? sw[min(cl + 1, Pm1)] : 0.f;
-                w2 = (cnt > 2) ? sw[min(cl + 2, Pm1)] : 0.f;
-                w3 = (cnt > 3) ? sw[min(cl + 3, Pm1)] : 0.f;
+                i0 = kid(npk, 0); i1 = kid(npk, 1); i2 = kid(npk, 2); i3 = kid(npk, 3);
+                w0 = sw[i0]; w1 = sw[i1]; w2 = sw[i2]; w3 = sw[i3];
                 hi = lo;
                 lo = nlo;
                 nlo = nnlo;
@@ -323,23 +329,24 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
         }
         if (SMEM) {
             // pipelined like the up sweep: weight and parent of the next level are fetched a level ahead
-            float *mv = sval + c * pcap;
-            auto end_of = [&](int L) -> int { return (L + 1 < L1) ? sls_or(ls_cached, sls, ls, L + 1, L0) - p0 : P; };
-            int L = L0 + 1;
-            lo = hi;                                   // level L = [lo, hi)
-            hi = (L < L1) ? end_of(L) : P;
-            int nhi = (L + 1 < L1) ? end_of(L + 1) : P;
+            float *mv = sval + c * ps;
+            const int nlev = L1 - L0;
+            auto Eq = [&](int q) -> int { return sls[min(q + 1, nlev)] - p0; };   // end of level L0 + q, band-local
+            int q = 1;                                 // level being processed = L0 + q = [lo, hi)
+            lo = hi;
+            hi = Eq(q);
+            int nhi = Eq(q + 1);
             int il = lo + slot;
-            bool act = (L < L1) && il < hi;
+            bool act = q < nlev && il < hi;
             float wi = act ? sw[il] : 0.f;
             int par = act ? (spk[il] >> 16) : 0;
-            for (; L < L1; ++L) {
-                const int nnhi = (L + 2 < L1) ? end_of(L + 2) : P;
+            for (; q < nlev; ++q) {
+                const int nnhi = Eq(q + 2);
                 const int nil = hi + slot;
-                const bool nact = (L + 1 < L1) && nil < nhi;
+                const bool nact = q + 1 < nlev && nil < nhi;
                 const float nwi = nact ? sw[nil] : 0.f;
                 const int npar = nact ? (spk[nil] >> 16) : 0;
-                __syncthreads();                       // level L-1 is final
+                channel_barrier(c);                    // the level above is final (this channel's 64 threads)
                 if (act) {
                     mv[il] = fmaf(wi, mv[par], mv[il] * (1.f - wi * wi));
                     for (int j = il + RSLOTS; j < hi; j += RSLOTS) {
@@ -762,6 +769,6 @@ resident_kernel(TreeView t, Consts k, ResidentArgs a) {
     if (!band_geom(t, b, beta, L0, L1, nb)) return;
     const int *ls = t.ls + (size_t)b * (t.V + 1);
     const int p0 = ls[L0], p1 = ls[L1];
-    if (p1 - p0 <= a.pcap) resident_band<MODE, true, NCT>(t, k, a, b, beta, nb, L0, L1, p0, p1, smem);
+    if (p1 - p0 <= a.pcap && L1 - L0 <= LSCAP) resident_band<MODE, true, NCT>(t, k, a, b, beta, nb, L0, L1, p0, p1, smem);
     else resident_band<MODE, false, NCT>(t, k, a, b, beta, nb, L0, L1, p0, p1, smem);
 }
