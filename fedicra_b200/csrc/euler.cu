@@ -5,7 +5,7 @@
 // walk needs one dependent step per tree depth (1 100 - 2 200 at 256^2); here the depth of the dependency chain is
 // logarithmic:
 //   1. Euler tour of the tree (each tree edge = two arcs; successor of the arc into u = next tree edge around u)
-//      ranked with a splitter walk: one thread per 16 vertices walks its stretch of the tour (~32 arcs), the ~4 096
+//      ranked with a splitter walk: one thread per 8 vertices walks its stretch of the tour (~16 arcs), the ~8 192
 //      stretches are ranked by pointer jumping in shared memory.
 //   2. From the ranks: the parent of u is where the tour first enters u; subtree size = half the span between entering
 //      and leaving u.
@@ -25,8 +25,8 @@ constexpr int NIL = -1;
 // splitters handed out dynamically inside one CTA of the tour walk (FEDICRA_EULER_SPC overrides; see run time notes below)
 int split_per_cta() {
     const char *v = getenv("FEDICRA_EULER_SPC");
-    const int x = (v && *v) ? atoi(v) : 512;   // measured on B200, 48 trees of 256^2: 1024 -> 476 us, 512 -> 462, 256 -> 464, 128 -> 499
-    return (x >= 32 && x <= 8192) ? x : 512;
+    const int x = (v && *v) ? atoi(v) : 1024;
+    return (x >= 32 && x <= 8192) ? x : 1024;
 }
 
 __device__ __forceinline__ int dir_delta(int d, int W) { return d == 0 ? -W : (d == 1 ? -1 : (d == 2 ? 1 : W)); }
@@ -95,8 +95,13 @@ size_t ws_layout(const Dims &d, char *base, Ws *w) {
 Dims make_dims(int B, int H, int W) {
     Dims d;
     d.B = B; d.H = H; d.W = W; d.V = H * W;
-    d.SP = 16;
-    d.SPLOG = 4;
+    {   // splitter spacing: FEDICRA_EULER_SPLOG overrides (2^k vertices per splitter)
+        const char *v = getenv("FEDICRA_EULER_SPLOG");
+        // measured on B200, 48 trees of 256^2 (whole BFS): 8 vertices per splitter 444 us, 16 -> 460 us, 32 -> 570 us
+        const int k = (v && *v) ? atoi(v) : 3;
+        d.SPLOG = (k >= 1 && k <= 10) ? k : 3;
+        d.SP = 1 << d.SPLOG;
+    }
     while ((d.V + d.SP - 1) / d.SP > 8192) { d.SP <<= 1; ++d.SPLOG; }  // at most 8 192 splitters per image (shared-memory ranking)
     d.NS = (d.V + d.SP - 1) / d.SP;
     d.T = 2 * (d.V - 1);

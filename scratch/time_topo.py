@@ -17,4 +17,4 @@ def run(tag, fn, reps=10):
     print(f"{tag}: median {ts[len(ts)//2]*1e3:.1f} us  min {ts[0]*1e3:.1f} us")
 tree, mask = ops.mst_grid(emb, want_mask=True, want_edges=False)
 run("mst_grid CL=" + os.environ.get("FEDICRA_MST_CL", "auto"), lambda: ops.mst_grid(emb, want_mask=True, want_edges=False))
-run("bfs_euler", lambda: ops.bfs_euler(mask, H, W))
+run("bfs_euler", lambda: ops.bfs_euler(mask, H, W)); sys.stdout.flush()
