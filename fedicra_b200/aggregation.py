@@ -74,7 +74,13 @@ def fused_ala_update(params_p, server_params_p, temp_params_p, fedaa_weights, et
                 raise RuntimeError("fused_ala_update: gradients must be contiguous")
     else:
         gptrs = [0] * tab.n
-    g_table = torch.tensor(gptrs, dtype=torch.int64, device=dev)
+    # gradient pointers usually do not move between batches (optimizer.zero_grad(set_to_none=False), or the caching
+    # allocator handing back the same blocks): upload the table only when they did
+    gkey = tuple(gptrs)
+    if getattr(tab, "g_key", None) != gkey:
+        tab.g_table = torch.tensor(gptrs, dtype=torch.int64, device=dev)
+        tab.g_key = gkey
+    g_table = tab.g_table
     with torch.cuda.device(dev):
         check(lib.fedicra_ala_update_multi(tab.p.data_ptr(), tab.s.data_ptr(), g_table.data_ptr(), tab.w.data_ptr(),
                                            tab.t.data_ptr(), tab.sizes.data_ptr(), tab.chunk_tensor.data_ptr(),
