@@ -51,7 +51,7 @@ struct Ws {
                                     //        (packed so that the whole table stays L2-resident: its writes are random)
     int *snext, *slen, *sbase;      // [B,NS] next splitter on the tour, stretch length, tour rank of the splitter arc
     int *rin, *rout, *pdir, *size;  // [B,V]  tour rank entering / leaving u, direction of the parent (4 = root), subtree size
-    int4 *S;                        // [B,2V] tour-ordered (d depth, d preorder, vertex entered or -1, 0)
+    int2 *S;                        // [B,2V] tour-ordered (d preorder = +-o, vertex entered or -1); d depth = sign(d preorder), o >= 1
     int2 *bsum;                     // [B,NBLK] per-block sums of S
     int *depth, *pre;               // [B,V]
     int *cnt, *cursor;              // [B,V+1] vertices per depth; bucket fill cursors   (zeroed per call)
@@ -82,7 +82,7 @@ size_t ws_layout(const Dims &d, char *base, Ws *w) {
     t.rout = (int *)take(B * V * 4);
     t.pdir = (int *)take(B * V * 4);
     t.size = (int *)take(B * V * 4);
-    t.S = (int4 *)take(B * 2 * V * 16);
+    t.S = (int2 *)take(B * 2 * V * 8);
     t.bsum = (int2 *)take(B * (size_t)(d.NBLK > 0 ? d.NBLK : 1) * 8);
     t.depth = (int *)take(B * V * 4);
     t.pre = (int *)take(B * V * 4);
@@ -252,9 +252,9 @@ __global__ void __launch_bounds__(NT) increments_kernel(const unsigned char *__r
 #pragma unroll
     for (int d = 0; d < 3; ++d)
         if (d < du && (mp & (1u << d)) && d != ppd) offs += ws.size[o + p + dir_delta(d, W)];
-    int4 *S = ws.S + (size_t)b * 2 * V;
-    S[ws.rin[o + u]] = make_int4(1, offs, u, 0);
-    S[ws.rout[o + u]] = make_int4(-1, -offs, -1, 0);
+    int2 *S = ws.S + (size_t)b * 2 * V;
+    S[ws.rin[o + u]] = make_int2(offs, u);
+    S[ws.rout[o + u]] = make_int2(-offs, -1);
 }
 
 // ---- 3b. prefix sums along the tour (block sums, scan of block sums, apply)
@@ -263,8 +263,8 @@ __global__ void __launch_bounds__(1024) tour_block_sum_kernel(Ws ws, Dims dm) {
     const int r = blk * 1024 + tid;
     int2 v = make_int2(0, 0);
     if (r < dm.T) {
-        const int4 s = ws.S[(size_t)b * 2 * dm.V + r];
-        v = make_int2(s.x, s.y);
+        const int2 s = ws.S[(size_t)b * 2 * dm.V + r];
+        v = make_int2((s.x > 0) - (s.x < 0), s.x);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -324,8 +324,9 @@ __global__ void __launch_bounds__(1024) tour_scan_sums_kernel(Ws ws, Dims dm) { 
 __global__ void __launch_bounds__(1024) tour_apply_kernel(Ws ws, Dims dm) {
     const int b = blockIdx.y, blk = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = dm.V;
     const int r = blk * 1024 + tid;
-    int4 s = make_int4(0, 0, -1, 0);
-    if (r < dm.T) s = ws.S[(size_t)b * 2 * V + r];
+    int2 sp = make_int2(0, -1);
+    if (r < dm.T) sp = ws.S[(size_t)b * 2 * V + r];
+    const int3 s = make_int3((sp.x > 0) - (sp.x < 0), sp.x, sp.y);   // (d depth, d preorder, vertex entered or -1)
     int2 x = make_int2(s.x, s.y);
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -435,6 +436,25 @@ __global__ void __launch_bounds__(NT) level_rank_kernel(Ws ws, Dims dm, const in
     int *pos = ws.pos + (size_t)b * V, *order = sorted_index + (size_t)b * V;
     for (int L = warp; L < nl; L += warps_per_image) {
         const int lo = ls[L], n = ls[L + 1] - lo;
+        if (n <= 64) {   // the usual case: two entries per lane, keys exchanged by shuffles (one memory round trip in all)
+            const bool h0 = lane < n, h1 = lane + 32 < n;
+            const int2 m0 = h0 ? tmp[lo + lane] : make_int2(0x7fffffff, 0), m1 = h1 ? tmp[lo + 32 + lane] : make_int2(0x7fffffff, 0);
+            int r0 = 0, r1 = 0;
+            const int na = min(n, 32), nb2 = n - na;
+            for (int j = 0; j < na; ++j) {
+                const int kj = __shfl_sync(0xffffffffu, m0.x, j);
+                r0 += kj < m0.x;
+                r1 += kj < m1.x;
+            }
+            for (int j = 0; j < nb2; ++j) {
+                const int kj = __shfl_sync(0xffffffffu, m1.x, j);
+                r0 += kj < m0.x;
+                r1 += kj < m1.x;
+            }
+            if (h0) { order[lo + r0] = m0.y; pos[m0.y] = lo + r0; }
+            if (h1) { order[lo + r1] = m1.y; pos[m1.y] = lo + r1; }
+            continue;
+        }
         for (int i = lane; i < n; i += 32) {
             const int2 me = tmp[lo + i];
             int rank = 0;

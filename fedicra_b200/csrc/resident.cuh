@@ -20,6 +20,9 @@
 // The sync words start at zero (caller-zeroed workspace, like the Gated CRF scratch) and every launch leaves them at zero.
 
 constexpr int RSLOTS = 64;       // threads per swept channel
+#ifndef RES_MINB
+#define RES_MINB 3                // resident CTAs per SM the kernel is compiled for (channel counts up to 4)
+#endif
 constexpr int SYNC_INTS = 8;     // per image: cnt_up, flag_up, cnt_down, flag_down, cnt_fin, (3 spare)
 
 struct ResidentArgs {
@@ -756,7 +759,7 @@ __device__ void resident_stitch(const TreeView &t, const Consts &k, const Reside
 }
 
 template <int MODE, int NCT>
-__global__ void __launch_bounds__(NCT * RSLOTS, NCT <= 4 ? 3 : (NCT <= 6 ? 2 : 1))
+__global__ void __launch_bounds__(NCT * RSLOTS, NCT <= 4 ? RES_MINB : (NCT <= 6 ? 2 : 1))
 resident_kernel(TreeView t, Consts k, ResidentArgs a) {
     extern __shared__ float4 smem4[];
     char *smem = reinterpret_cast<char *>(smem4);
