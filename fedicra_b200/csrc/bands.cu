@@ -644,11 +644,6 @@ finish_backward_kernel(TreeView t, Consts k, const float *__restrict__ Bv, const
     if (grad_weight != nullptr) grad_weight[(size_t)b * V + i] = gw;
 }
 
-__global__ void zero_root_weight_kernel(float *w, int V, int B) {
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b < B) w[(size_t)b * V] = 0.f;  // refine.cu:43-46
-}
-
 // ------------------------------------------------------------------------------------------------ host side
 // Band limits (host side, functions of the image size only).
 #include <stdlib.h>

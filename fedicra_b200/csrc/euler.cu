@@ -147,11 +147,13 @@ __global__ void __launch_bounds__(NT) walk_kernel(const unsigned char *__restric
     // idle; instead every CTA owns SPC consecutive splitters and its lanes pull the next one when they are done.
     __shared__ int s_next;
     const int s_begin = blockIdx.x * dm.SPC, s_end = min(s_begin + dm.SPC, dm.NS);
-    if (threadIdx.x == 0) s_next = s_begin + NT;
+    if (threadIdx.x == 0) s_next = s_begin + 2 * NT;
     __syncthreads();
     unsigned *arc = ws.arc + (size_t)b * 4 * V;
     const int limit = 2 * V;  // a consistent tree mask closes the tour after 2(V-1) arcs; guard against a bad one
-    int s = s_begin + threadIdx.x, v = 0, d = 0, steps = 0;
+    // A lane's next splitter is fetched when it STARTS a stretch, not when it ends one: with ~16 arcs per stretch some lane
+    // of a warp finishes on almost every iteration, and the shared-memory atomic's latency would sit on every one of them.
+    int s = s_begin + threadIdx.x, sn = s_begin + NT + threadIdx.x, v = 0, d = 0, steps = 0;
     bool walking = false;
     while (true) {
         if (!walking) {
@@ -161,7 +163,8 @@ __global__ void __launch_bounds__(NT) walk_kernel(const unsigned char *__restric
             if (mv0 == 0) {  // single-vertex tree
                 ws.snext[(size_t)b * dm.NS + s] = s;
                 ws.slen[(size_t)b * dm.NS + s] = 0;
-                s = atomicAdd(&s_next, 1);
+                s = sn;
+                sn = atomicAdd(&s_next, 1);
                 continue;
             }
             d = __ffs(mv0) - 1;
@@ -177,7 +180,8 @@ __global__ void __launch_bounds__(NT) walk_kernel(const unsigned char *__restric
             ws.snext[(size_t)b * dm.NS + s] = v >> spl;
             ws.slen[(size_t)b * dm.NS + s] = steps;
             walking = false;
-            s = atomicAdd(&s_next, 1);
+            s = sn;
+            sn = atomicAdd(&s_next, 1);
         }
     }
 }

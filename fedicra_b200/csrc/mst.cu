@@ -90,23 +90,6 @@ __global__ void mst_init_kernel(Ws ws, int V, int E) {
     }
 }
 
-// weight = sum_c (x_u - x_v)^2 + 1, channels in order, no fused multiply-add (bits equal to torch's, tree_filter.py:27-34)
-__global__ void grid_weight_kernel(const float *__restrict__ embed, float *__restrict__ wgt, int D, int H, int W, int E) {
-    const int b = blockIdx.y;
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= E) return;
-    int u, v;
-    grid_endpoints(e, H, W, u, v);
-    const size_t V = (size_t)H * W;
-    const float *x = embed + (size_t)b * D * V;
-    float d = 0.f;
-    for (int c = 0; c < D; ++c) {
-        const float t = __fsub_rn(x[c * V + u], x[c * V + v]);
-        d = __fadd_rn(d, __fmul_rn(t, t));
-    }
-    wgt[(size_t)b * E + e] = __fadd_rn(d, 1.f);
-}
-
 template <bool GRID>
 __global__ void mst_find_kernel(Ws ws, const int *__restrict__ edge_index, const float *__restrict__ edge_weight, int V,
                                 int E, int H, int W) {
@@ -177,11 +160,6 @@ __global__ void mst_compress_kernel(Ws ws, int V) {
     if (i == 0 && ws.ncomp[b] <= 1) ws.done[b] = 1;
 }
 
-__global__ void mst_finish_round_kernel(Ws ws, int B) {
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b < B && ws.ncomp[b] <= 1) ws.done[b] = 1;
-}
-
 // One CTA per image: stable compaction of the selected edges, in increasing edge index.  Unused slots (disconnected
 // input) are filled with -1.
 template <bool GRID>
@@ -229,23 +207,6 @@ mst_compact_kernel(Ws ws, const int *__restrict__ edge_index, int *__restrict__ 
         __syncthreads();
     }
     for (int i = s_base + tid; i < V - 1; i += 1024) out[i] = make_int2(-1, -1);
-}
-
-// 4-bit tree adjacency per vertex: bit 0 = up (v-W), 1 = left (v-1), 2 = right (v+1), 3 = down (v+W).  Gathered from the
-// selected-edge flags, no atomics.
-__global__ void grid_mask_kernel(Ws ws, unsigned char *__restrict__ mask, int H, int W, int E) {
-    const int b = blockIdx.y;
-    const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    const int V = H * W;
-    if (v >= V) return;
-    const unsigned char *f = ws.intree + (size_t)b * E;
-    const int h = v / W, w = v - h * W, nvert = (H - 1) * W;
-    unsigned m = 0;
-    if (h > 0 && f[v - W]) m |= 1u;                                   // vertical edge (h-1,w)-(h,w) has id (h-1)*W+w
-    if (w > 0 && f[nvert + h * (W - 1) + w - 1]) m |= 2u;             // horizontal edge (h,w-1)-(h,w)
-    if (w < W - 1 && f[nvert + h * (W - 1) + w]) m |= 4u;             // horizontal edge (h,w)-(h,w+1)
-    if (h < H - 1 && f[v]) m |= 8u;                                   // vertical edge (h,w)-(h+1,w)
-    mask[(size_t)b * V + v] = (unsigned char)m;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -390,7 +351,7 @@ mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, in
                 cc[k] = (i < nroots) ? (rlist ? rlist[i] : i) : -1;
             }
 #pragma unroll
-            for (int k = 0; k < IL; ++k) key[k] = (cc[k] >= 0) ? best[cc[k]] : KEY_INF;
+            for (int k = 0; k < IL; ++k) key[k] = (cc[k] >= 0) ? __ldcg(best + cc[k]) : KEY_INF;   // written by atomics: read at L2
             int other[IL], eid[IL];
 #pragma unroll
             for (int k = 0; k < IL; ++k) {
@@ -408,7 +369,7 @@ mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, in
 #pragma unroll
             for (int k = 0; k < IL; ++k) {
                 bool stays = cc[k] >= 0;   // a root without outgoing edge (finished tree) stays too
-                if (other[k] >= 0 && !(best[other[k]] == key[k] && cc[k] < other[k])) {
+                if (other[k] >= 0 && !(__ldcg(best + other[k]) == key[k] && cc[k] < other[k])) {
                     parent[cc[k]] = other[k];
                     intree[eid[k]] = 1;
                     stays = false;
@@ -492,7 +453,6 @@ mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, in
 // Output: edge weights and tree flags of the tile's own edges (down / right of each of its vertices), fresh labels
 // (DEAD for vertices whose neighbours all share their component), identity hooks, and the root / active lists.
 constexpr int TS = 64, TV = TS * TS, TNT = 512;
-constexpr unsigned short T_OUT = 0xFFFFu;   // label of "the other side of the tile boundary"
 constexpr size_t TILE_SMEM = (size_t)TV * 8 + 2 * (size_t)(TS + 1) * TS * 4 + 2 * (size_t)TV * 2;
 
 __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, int H, int W, int tiles_x, int max_rounds) {
