@@ -734,7 +734,7 @@ bool use_resident() {
 }
 
 // Shared memory of a resident CTA: band state (NC values + weight + packed topology per position) + level cache.
-size_t resident_smem(int pcap, int NC) { return (size_t)(pcap + 1) * (NC + 2) * 4 + (LSCAP + 1) * sizeof(int) + 16; }
+size_t resident_smem(int pcap, int NC) { return (size_t)(pcap + 4) * (NC + 2) * 4 + (LSCAP + 1) * sizeof(int) + 16; }
 
 __device__ long long g_prof[(NBMAX + 1) * PROF_SLOTS];   // phase timestamps of the last profiled launch (FEDICRA_PROF=1)
 

@@ -131,9 +131,10 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
     const int4 *child = t.child + (size_t)b * V;
     const float *w = t.w + (size_t)b * V;
     const size_t img = (size_t)b * NC * V;
-    // rows of ps = pcap + 1 entries: the last one is the "zero slot" (value 0, weight 0) that a missing child points to,
-    // so that the sweeps load four children unconditionally instead of branching on the child count
-    const int ps = pcap + 1;
+    // rows of ps = pcap + 4 entries: children are contiguous, so a sweep loads the four slots from its first child on with
+    // ONE address and constant offsets and masks the missing ones by their weight; the three slots past the end (zeroed)
+    // keep those loads inside the row for the last positions of a band
+    const int ps = pcap + 4;
     float *sval = reinterpret_cast<float *>(smem);       // [NC][ps]
     float *sw = sval + (size_t)NC * ps;                  // [ps]
     int *spk = reinterpret_cast<int *>(sw + ps);         // [ps]; after D1: the stitched values of the level above
@@ -158,6 +159,7 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
     auto parent_l = [&](int il) -> int { return SMEM ? (spk[il] >> 16) : (pp[il] - p0); };
     const int c = tid / RSLOTS, slot = tid % RSLOTS;   // blockDim.x = 64 * NC
     constexpr int U = 4;                               // elements per thread whose loads are issued together
+    constexpr int UG = (MODE == MODE_FWD && NCT <= 3) ? 8 : 4;   // ... in the first gather (registers permitting)
 
     // ---- stage the band: level starts, weights, packed topology (two coalesced streams)
     if (ls_cached)
@@ -170,22 +172,23 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
             spk[il] = gpk[il];
             sw[il] = (p0 + il == 0) ? 0.f : gw[il];
         }
-        if (tid < NC) sval[tid * ps + pcap] = 0.f;
-        if (tid == NC) sw[pcap] = 0.f;
+        // the four slots after the band's last position (never written otherwise; 0 * garbage could be NaN)
+        if (tid < 4 * NC) sval[(tid >> 2) * ps + P + (tid & 3)] = 0.f;
+        if (tid < 4) sw[P + tid] = 0.f;
     }
     // inputs: computed once (vertex-order gathers, one reciprocal per position); a shared-memory band also leaves them
     // in the slab, position order, from where the second sweep re-reads them with coalesced loads
     auto gather = [&]() {
-        for (int base = tid; base < P; base += U * nthr) {
-            int v[U];
-            float x[U][NCT];
+        for (int base = tid; base < P; base += UG * nthr) {
+            int v[UG];
+            float x[UG][NCT];
 #pragma unroll
-            for (int u = 0; u < U; ++u) v[u] = (base + u * nthr < P) ? vtx[base + u * nthr] : -1;
+            for (int u = 0; u < UG; ++u) v[u] = (base + u * nthr < P) ? vtx[base + u * nthr] : -1;
 #pragma unroll
-            for (int u = 0; u < U; ++u)
+            for (int u = 0; u < UG; ++u)
                 if (v[u] >= 0) resident_inputs<MODE, NCT>(a, b, p0 + base + u * nthr, v[u], V, x[u]);
 #pragma unroll
-            for (int u = 0; u < U; ++u)
+            for (int u = 0; u < UG; ++u)
                 if (v[u] >= 0) {
 #pragma unroll
                     for (int cc = 0; cc < NCT; ++cc) {
@@ -221,12 +224,12 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
         if (SMEM) {
             // Software-pipelined and branch-free: a level step is a chain of dependent shared-memory loads (level start
             // -> packed topology -> child weights -> child values) of which only the last link depends on the sweep.
-            // The others are fetched one level (level starts: two levels) ahead; a missing child is the zero slot.
-            // Between two barriers a thread then waits for one batch of value loads, four FMAs and a store.
+            // The others are fetched one level (level starts: two levels) ahead, the weights of missing children as 0.
+            // Between two barriers a thread then computes one address, waits for one batch of five value loads, does
+            // four FMAs and a store.  (The loops are issue-bound: three CTAs per SM run them at the same time, so
+            // every instruction taken out of the level step shortens it.)
             float *mv = sval + c * ps;         // this thread's channel row
-            const int Z = pcap;                // zero slot
             auto S = [&](int q) -> int { return sls[max(q, 0)] - p0; };   // start of level L0 + q, band-local (S(0) = 0)
-            auto kid = [&](int pk, int q) -> int { return ((pk & 7) > q) ? ((pk >> 3) & 0x1fff) + q : Z; };
             int q = L1 - 2 - L0;               // level being processed = L0 + q = [lo, hi)
             hi = lo;
             lo = S(q);
@@ -234,8 +237,9 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
             int il = lo + slot;
             bool act = q >= 0 && il < hi;
             int pk = act ? spk[il] : 0;
-            int i0 = kid(pk, 0), i1 = kid(pk, 1), i2 = kid(pk, 2), i3 = kid(pk, 3);
-            float w0 = sw[i0], w1 = sw[i1], w2 = sw[i2], w3 = sw[i3];
+            int cl = (pk >> 3) & 0x1fff, cnt = pk & 7;
+            const float *pw = sw + cl;
+            float w0 = pw[0], w1 = pw[1], w2 = pw[2], w3 = pw[3];
             for (; q >= 0; --q) {
                 const int nnlo = S(q - 2);
                 const int nil = nlo + slot;
@@ -243,26 +247,29 @@ __device__ void resident_band(const TreeView &t, const Consts &k, const Resident
                 const int npk = nact ? spk[nil] : 0;    // next level [nlo, lo): its topology does not depend on the values
                 channel_barrier(c);                    // the children of this level are final (this channel's 64 threads)
                 if (act) {
-                    const float v0 = mv[i0], v1 = mv[i1], v2 = mv[i2], v3 = mv[i3];
+                    const float *pv = mv + cl;
+                    const float v0 = pv[0], v1 = pv[1], v2 = pv[2], v3 = pv[3];
                     float acc = mv[il];
-                    acc = fmaf(v0, w0, acc);
-                    acc = fmaf(v1, w1, acc);
-                    acc = fmaf(v2, w2, acc);
-                    acc = fmaf(v3, w3, acc);
+                    acc = fmaf(v0, cnt > 0 ? w0 : 0.f, acc);
+                    acc = fmaf(v1, cnt > 1 ? w1 : 0.f, acc);
+                    acc = fmaf(v2, cnt > 2 ? w2 : 0.f, acc);
+                    acc = fmaf(v3, cnt > 3 ? w3 : 0.f, acc);
                     mv[il] = acc;
                     for (int j = il + RSLOTS; j < hi; j += RSLOTS) {   // levels wider than the slots
-                        const int pj = spk[j];
-                        const int j0 = kid(pj, 0), j1 = kid(pj, 1), j2 = kid(pj, 2), j3 = kid(pj, 3);
+                        const int pj = spk[j], cj = (pj >> 3) & 0x1fff, nj = pj & 7;
+                        const float *qv = mv + cj, *qw = sw + cj;
                         float aj = mv[j];
-                        aj = fmaf(mv[j0], sw[j0], aj);
-                        aj = fmaf(mv[j1], sw[j1], aj);
-                        aj = fmaf(mv[j2], sw[j2], aj);
-                        aj = fmaf(mv[j3], sw[j3], aj);
+                        aj = fmaf(qv[0], nj > 0 ? qw[0] : 0.f, aj);
+                        aj = fmaf(qv[1], nj > 1 ? qw[1] : 0.f, aj);
+                        aj = fmaf(qv[2], nj > 2 ? qw[2] : 0.f, aj);
+                        aj = fmaf(qv[3], nj > 3 ? qw[3] : 0.f, aj);
                         mv[j] = aj;
                     }
                 }
-                i0 = kid(npk, 0); i1 = kid(npk, 1); i2 = kid(npk, 2); i3 = kid(npk, 3);
-                w0 = sw[i0]; w1 = sw[i1]; w2 = sw[i2]; w3 = sw[i3];
+                cl = (npk >> 3) & 0x1fff;
+                cnt = npk & 7;
+                pw = sw + cl;
+                w0 = pw[0]; w1 = pw[1]; w2 = pw[2]; w3 = pw[3];
                 hi = lo;
                 lo = nlo;
                 nlo = nnlo;
