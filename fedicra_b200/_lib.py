@@ -47,6 +47,8 @@ SIGNATURES = {
     "fedicra_bfs_euler_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "fedicra_bfs_euler": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_size_t, c_void_p]),
+    "fedicra_bfs_euler_rooted": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                         c_void_p, c_void_p, c_size_t, c_void_p]),
     "fedicra_edge_weight_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p]),
     "fedicra_edge_weight_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                         c_float, c_void_p, c_void_p]),

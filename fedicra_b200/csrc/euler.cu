@@ -60,6 +60,7 @@ struct Ws {
 };
 
 struct Dims {
+    int root;  // the vertex the order starts from (0 = the reference's, bfs.cu:69-74)
     int B, V, H, W, SP, SPLOG, NS, T, NBLK, SPC;  // T = 2(V-1) arcs on the tour; NBLK = ceil(T / 1024); SPC splitters per walk CTA
 };
 
@@ -92,8 +93,9 @@ size_t ws_layout(const Dims &d, char *base, Ws *w) {
     return offb;
 }
 
-Dims make_dims(int B, int H, int W) {
+Dims make_dims(int B, int H, int W, int root = 0) {
     Dims d;
+    d.root = root;
     d.B = B; d.H = H; d.W = W; d.V = H * W;
     {   // splitter spacing: FEDICRA_EULER_SPLOG overrides (2^k vertices per splitter)
         const char *v = getenv("FEDICRA_EULER_SPLOG");
@@ -212,9 +214,20 @@ __global__ void __launch_bounds__(1024) rank_splitters_kernel(Ws ws, Dims dm) {
     for (int s = tid; s < NS; s += 1024) ws.sbase[(size_t)b * NS + s] = total - val[cur][s];
 }
 
-__device__ __forceinline__ int arc_rank(const unsigned *arc, const int *sbase, int a) {
+__device__ __forceinline__ int arc_rank_raw(const unsigned *arc, const int *sbase, int a) {
     const unsigned r = arc[a];
     return sbase[r >> 19] + (int)(r & 0x7ffffu);
+}
+// The splitter ranking cuts the (cyclic) tour at vertex 0.  A tour that starts at another root is the same cycle rotated:
+// rank' = rank - rank(first arc out of the root) mod T.
+__device__ __forceinline__ int root_shift(const unsigned char *mask_b, const unsigned *arc, const int *sbase, int root) {
+    if (root == 0) return 0;
+    const unsigned m = mask_b[root];
+    return m ? arc_rank_raw(arc, sbase, 4 * root + __ffs(m) - 1) : 0;
+}
+__device__ __forceinline__ int arc_rank(const unsigned *arc, const int *sbase, int a, int shift, int T) {
+    const int r = arc_rank_raw(arc, sbase, a) - shift;
+    return r < 0 ? r + T : r;
 }
 
 // ---- 2. where the tour enters and leaves every vertex
@@ -225,20 +238,21 @@ __global__ void __launch_bounds__(NT) enter_leave_kernel(const unsigned char *__
     const unsigned *arc = ws.arc + (size_t)b * 4 * V;
     const int *sbase = ws.sbase + (size_t)b * dm.NS;
     const size_t o = (size_t)b * V + u;
-    if (u == 0) {
+    if (u == dm.root) {
         ws.rin[o] = -1; ws.rout[o] = dm.T; ws.pdir[o] = 4; ws.size[o] = V;
         return;
     }
+    const int shift = root_shift(mask + (size_t)b * V, arc, sbase, dm.root), T = dm.T;
     const unsigned m = mask[o];
     int best = 0x7fffffff, pd = 0;
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
         if (m & (1u << d)) {
-            const int r = arc_rank(arc, sbase, 4 * (u + dir_delta(d, W)) + (3 - d));  // the arc neighbour -> u
+            const int r = arc_rank(arc, sbase, 4 * (u + dir_delta(d, W)) + (3 - d), shift, T);  // the arc neighbour -> u
             if (r < best) { best = r; pd = d; }
         }
     }
-    const int out = arc_rank(arc, sbase, 4 * u + pd);
+    const int out = arc_rank(arc, sbase, 4 * u + pd, shift, T);
     ws.rin[o] = best; ws.rout[o] = out; ws.pdir[o] = pd; ws.size[o] = (out - best + 1) >> 1;
 }
 
@@ -247,7 +261,7 @@ __global__ void __launch_bounds__(NT) increments_kernel(const unsigned char *__r
     const long long idx = (long long)blockIdx.x * NT + threadIdx.x;
     if (idx >= (long long)dm.B * dm.V) return;
     const int b = (int)(idx / dm.V), u = (int)(idx - (long long)b * dm.V), V = dm.V, W = dm.W;
-    if (u == 0) return;
+    if (u == dm.root) return;
     const size_t o = (size_t)b * V;
     const int pd = ws.pdir[o + u], p = u + dir_delta(pd, W), du = 3 - pd;  // u is p's child in direction du
     const unsigned mp = mask[o + p];
@@ -352,8 +366,8 @@ __global__ void __launch_bounds__(1024) tour_apply_kernel(Ws ws, Dims dm) {
     __syncthreads();
     const size_t o = (size_t)b * V;
     if (blk == 0 && tid == 0) {  // the root is never entered
-        ws.depth[o] = 0;
-        ws.pre[o] = 0;
+        ws.depth[o + dm.root] = 0;
+        ws.pre[o + dm.root] = 0;
         atomicAdd(ws.cnt + (size_t)b * (V + 1), 1);
     }
     if (s.z >= 0) {  // the tour enters vertex s.z here: inclusive sums = its depth and preorder index
@@ -479,7 +493,7 @@ __global__ void __launch_bounds__(NT) finalize_kernel(const unsigned char *__res
     const int *pos = ws.pos + o;
     const int i = pos[u], pd = ws.pdir[o + u];
     const unsigned m = mask[o + u];
-    sorted_parent[o + i] = (u == 0) ? 0 : pos[u + dir_delta(pd, W)];
+    sorted_parent[o + i] = (u == dm.root) ? 0 : pos[u + dir_delta(pd, W)];
     int c[4] = {0, 0, 0, 0}, k = 0;
 #pragma unroll
     for (int d = 0; d < 4; ++d)
@@ -494,15 +508,27 @@ extern "C" size_t fedicra_bfs_euler_workspace_bytes(int B, int H, int W) {
     return ws_layout(make_dims(B, H, W), nullptr, nullptr);
 }
 
+extern "C" int fedicra_bfs_euler_rooted(const unsigned char *tree_mask, int B, int H, int W, int root, int *sorted_index,
+                                        int *sorted_parent, int *sorted_child, int *level_start, int *n_levels,
+                                        void *workspace, size_t workspace_bytes, void *stream);
+
 extern "C" int fedicra_bfs_euler(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index,
                                  int *sorted_parent, int *sorted_child, int *level_start, int *n_levels,
                                  void *workspace, size_t workspace_bytes, void *stream) {
+    return fedicra_bfs_euler_rooted(tree_mask, B, H, W, 0, sorted_index, sorted_parent, sorted_child, level_start, n_levels,
+                                    workspace, workspace_bytes, stream);
+}
+
+extern "C" int fedicra_bfs_euler_rooted(const unsigned char *tree_mask, int B, int H, int W, int root, int *sorted_index,
+                                        int *sorted_parent, int *sorted_child, int *level_start, int *n_levels,
+                                        void *workspace, size_t workspace_bytes, void *stream) {
     FEDICRA_REQUIRE(tree_mask && sorted_index && sorted_parent && sorted_child && level_start && n_levels && workspace,
                     "bfs_euler: null pointer");
     FEDICRA_REQUIRE(B > 0 && B <= 65535 && H >= 1 && W >= 1 && (long long)H * W <= (1ll << 18),
                     "bfs_euler: bad sizes B=%d H=%d W=%d (at most 262144 pixels per image)", B, H, W);
     FEDICRA_REQUIRE(((uintptr_t)sorted_child & 15) == 0, "bfs_euler: sorted_child must be 16-byte aligned");
-    const Dims dm = make_dims(B, H, W);
+    FEDICRA_REQUIRE(root >= 0 && root < H * W, "bfs_euler: root %d outside the %d x %d image", root, H, W);
+    const Dims dm = make_dims(B, H, W, root);
     FEDICRA_REQUIRE(workspace_bytes >= ws_layout(dm, nullptr, nullptr), "bfs_euler: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
     Ws ws;

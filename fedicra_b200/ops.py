@@ -108,11 +108,12 @@ BFS_GRID_MAX_V = 2 * (227 * 1024 - 4 * 4096 * 4 - 256)
 BFS_EULER_MAX_V = 1 << 18
 
 
-def bfs_from_mask(mask, H, W):
+def bfs_from_mask(mask, H, W, root=0):
     """Fastest BFS ordering available for an H x W grid tree given as adjacency mask (all three give identical arrays):
-    Euler tour + prefix sums up to 262 144 pixels, else the shared-memory depth walk; None when neither applies."""
+    Euler tour + prefix sums up to 262 144 pixels, else the shared-memory depth walk; None when neither applies.
+    `root`: vertex the order starts from (Euler path only; the others always start from vertex 0)."""
     if H * W <= BFS_EULER_MAX_V:
-        return bfs_euler(mask, H, W)
+        return bfs_euler(mask, H, W, root)
     if H * W <= BFS_GRID_MAX_V:
         return bfs_grid(mask, H, W)
     return None
@@ -153,8 +154,23 @@ def bfs_forward(tree):
     return si, sp, sc, ls, nl
 
 
-def bfs_euler(mask, H, W):
-    """BFS arrays from the adjacency mask via Euler tour + prefix sums (no per-depth step); same outputs as bfs_grid."""
+def centre_root(H, W):
+    """The centre pixel as BFS root.  The filter's result does not depend on the root, the tree's shape does:
+    centre-rooted trees are 15-40 % shallower than corner-rooted ones -- and as much wider."""
+    return (H // 2) * W + W // 2 if H * W <= BFS_EULER_MAX_V else 0
+
+
+def default_root(H, W):
+    """Root TreeFilter2D orders its trees from.  Vertex 0, like the reference: measured on B200 (faz256) the centre root
+    is a loss -- levels of ~80 instead of ~50 vertices need two passes of the 64 slots per channel and overflow the
+    stitcher's shared memory, which costs more than the 30 % fewer levels save (FEDICRA_ROOT=centre to try it)."""
+    import os
+    return centre_root(H, W) if os.environ.get("FEDICRA_ROOT") == "centre" else 0
+
+
+def bfs_euler(mask, H, W, root=0):
+    """BFS arrays from the adjacency mask via Euler tour + prefix sums (no per-depth step); same outputs as bfs_grid
+    (for root 0)."""
     m = _cuda(mask, torch.uint8, "tree_mask")
     B, V = m.shape
     dev = m.device
@@ -165,8 +181,8 @@ def bfs_euler(mask, H, W):
         ls = torch.empty(B, V + 1, dtype=torch.int32, device=dev)
         nl = torch.empty(B, dtype=torch.int32, device=dev)
         ws = workspace("bfs_euler", lib.fedicra_bfs_euler_workspace_bytes(B, H, W), dev)
-        check(lib.fedicra_bfs_euler(_p(m), B, H, W, _p(si), _p(sp), _p(sc), _p(ls), _p(nl), _p(ws), ws.numel(), _stream()),
-              "bfs_euler")
+        check(lib.fedicra_bfs_euler_rooted(_p(m), B, H, W, int(root), _p(si), _p(sp), _p(sc), _p(ls), _p(nl), _p(ws),
+                                           ws.numel(), _stream()), "bfs_euler")
     return si, sp, sc, ls, nl
 
 

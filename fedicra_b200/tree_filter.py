@@ -26,7 +26,7 @@ class _TreeOrder:
             self.si, self.sp, self.sc, self.ls, self.nl, self.bands = arrays
             return
         mask, hw = getattr(tree, "_fedicra_mask", None), getattr(tree, "_fedicra_hw", None)
-        arrays = ops.bfs_from_mask(mask, *hw) if mask is not None else None
+        arrays = ops.bfs_from_mask(mask, *hw, root=ops.default_root(*hw)) if mask is not None else None
         self.si, self.sp, self.sc, self.ls, self.nl = arrays if arrays is not None else ops.bfs_forward(tree)
         self.bands = ops.band_plan(self.ls, self.nl)
 
@@ -44,7 +44,7 @@ def batched_tree_orders(embeds):
             D = max(e.shape[1] for e in embeds)
             stacked = torch.cat([torch.nn.functional.pad(e.detach().float(), (0, 0, 0, 0, 0, D - e.shape[1])) for e in embeds], 0)
             tree, mask = ops.mst_grid(stacked, want_mask=True, want_edges=not fits)  # the mask alone feeds the grid BFS
-        arrays = ops.bfs_from_mask(mask, H, W) if fits else ops.bfs_forward(tree)
+        arrays = ops.bfs_from_mask(mask, H, W, root=ops.default_root(H, W)) if fits else ops.bfs_forward(tree)
         bands = ops.band_plan(arrays[3], arrays[4]).view(len(embeds) * B, -1)
     return [_TreeOrder(arrays=tuple(a[k * B:(k + 1) * B] for a in (*arrays, bands))) for k in range(len(embeds))]
 

@@ -121,6 +121,14 @@ size_t fedicra_bfs_euler_workspace_bytes(int B, int H, int W);
 int fedicra_bfs_euler(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index, int *sorted_parent,
                       int *sorted_child, int *level_start, int *n_levels, void *workspace, size_t workspace_bytes,
                       void *stream);
+/* The same order started from another root vertex (the reference always starts from vertex 0, bfs.cu:69-74).  The tree
+ * filter (refine.cu) does not depend on the root -- out[i] = sum_j S(i,j) f_j / sum_j S(i,j) with S the product of edge
+ * weights along the tree path -- but the tree's shape does: rooted at the centre of the image it is 15-40 % shallower
+ * than rooted at the corner, and as much wider.  (TreeFilter2D keeps vertex 0: with this library's band sizes the wider
+ * levels cost more than the missing ones save; see DESIGN.md.) */
+int fedicra_bfs_euler_rooted(const unsigned char *tree_mask, int B, int H, int W, int root, int *sorted_index,
+                             int *sorted_parent, int *sorted_child, int *level_start, int *n_levels, void *workspace,
+                             size_t workspace_bytes, void *stream);
 
 /* ------------------------------------------------------------------------------------------------ tree filter -- */
 /* TreeFilter2D.build_edge_weight (LTF/modules/tree_filter.py:91-108): ew[b,i] = exp(-|e[v(i)] - e[v(par i)]|^2 *

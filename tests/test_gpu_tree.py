@@ -207,3 +207,43 @@ def test_bfs_from_adjacency_mask_bit_exact(kind, B, D, H, W):
             _, _, _, ls = tree_cpu.bfs_levels(tree[b])
             n = int(gnl[b])
             assert n == len(ls) - 1 and torch.equal(gls[b, :n + 1].cpu(), ls), fn.__name__
+
+
+@pytest.mark.parametrize("kind,B,C,H,W", [("quant8", 2, 2, 96, 80), ("uniform", 1, 3, 33, 47), ("constant", 1, 1, 40, 24)])
+def test_rooted_order_is_a_level_order_and_the_filter_does_not_depend_on_the_root(kind, B, C, H, W):
+    """fedicra_bfs_euler_rooted: started from the centre pixel the arrays are still a breadth-first order (levels,
+    parents one level up, children contiguous and increasing), and the filter -- forward, feature gradient, edge-weight
+    gradient mapped back to the embedding -- equals the one on the reference's vertex-0 order."""
+    from fedicra_b200 import ops
+    g = torch.Generator().manual_seed(11)
+    emb = make_image(kind, B, 3, H, W, g).cuda()
+    feat = torch.rand(B, C, H * W, generator=g).cuda()
+    gout = torch.randn(B, C, H * W, generator=g).cuda()
+    V = H * W
+    _, mask = ops.mst_grid(emb, want_mask=True)
+    results = []
+    for root in (0, ops.centre_root(H, W)):
+        si, sp, sc, ls, nl = ops.bfs_euler(mask, H, W, root)
+        for b in range(B):
+            s, p, c = si[b].cpu().long(), sp[b].cpu().long(), sc[b].cpu().long()
+            n = int(nl[b]); starts = ls[b, :n + 1].cpu().long()
+            assert int(s[0]) == root and int(p[0]) == 0 and sorted(s.tolist()) == list(range(V))
+            level = torch.bucketize(torch.arange(V), starts[1:], right=True)
+            assert int(starts[0]) == 0 and int(starts[n]) == V and int(starts[1]) == 1
+            assert bool((level[p[1:]] == level[1:] - 1).all())                     # parents sit one level up
+            kids = c[c > 0]
+            assert sorted(kids.tolist()) == list(range(1, V))                      # every non-root is someone's child once
+            for k in range(4):
+                has = c[:, k] > 0
+                assert bool((p[c[has, k]] == torch.arange(V)[has]).all())
+            two = (c[:, 0] > 0) & (c[:, 1] > 0)
+            assert bool((c[two, 1] == c[two, 0] + 1).all())                        # contiguous, increasing
+        ew = ops.edge_weight_fwd(emb.reshape(B, 3, V), si, sp, 1.0)
+        ew0 = ew.clone()
+        bands = ops.band_plan(ls, nl)
+        out, saved = ops.tree_filter_forward(feat, ew, si, sp, sc, ls, nl, bands)
+        gf, gw = ops.tree_filter_backward(gout, ew, si, sp, sc, ls, nl, bands, saved, True)
+        ge = ops.edge_weight_bwd(emb.reshape(B, 3, V), si, sp, sc, ew0, gw, 1.0)
+        results.append((out, gf, ge))
+    for a, b_ in zip(results[0], results[1]):
+        assert rel_err(b_.cpu(), a.cpu()) < 2e-5
