@@ -702,6 +702,8 @@ int set_smem(Kern kern, size_t bytes, const char *name) {
     return 0;
 }
 
+#include "stitch2.cuh"
+
 template <int MODE>
 int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int B, cudaStream_t st) {
     const int V = t.V, nb = plan_grid(V), NC = a.NC;
@@ -714,14 +716,24 @@ int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int
     const size_t smem_u2 = (size_t)(NSTAGE * 5 + 3) * SCAPW * sizeof(float) + 16;
     const size_t smem_d2 = (size_t)(NSTAGE * 3 + 2) * SCAPW * sizeof(float) + 16;
     if (set_smem(stitch_up_kernel, smem_u2, "stitch_up_kernel") || set_smem(stitch_down_kernel, smem_d2, "stitch_down_kernel")) return -2;
+    // band-to-band recurrences: all last levels of a channel in shared memory (stitch2.cuh); FEDICRA_STITCH=ring selects
+    // the older cp.async-ring kernels
+    const char *sv = getenv("FEDICRA_STITCH");
+    const bool ring = sv && strcmp(sv, "ring") == 0;
+    const size_t smem_s2 = SMEM_MAX;
+    const int tcap2 = (int)((smem_s2 - 3 * (MAXBANDS + 2) * sizeof(int) - 64) / 12);
+    if (!ring && (set_smem(stitch2_kernel<true>, smem_s2, "stitch2_kernel") || set_smem(stitch2_kernel<false>, smem_s2, "stitch2_kernel")))
+        return -2;
     sweep_kernel<MODE, false><<<dim3(nb, B), nthr_sweep, smem, st>>>(t, a, pcap);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U1>");
-    stitch_up_kernel<<<dim3(NC, B), 32, smem_u2, st>>>(t, k, a);
-    FEDICRA_CHECK_LAUNCH("stitch_up_kernel");
+    if (ring) stitch_up_kernel<<<dim3(NC, B), 32, smem_u2, st>>>(t, k, a);
+    else stitch2_kernel<true><<<dim3(NC, B), ST2_NT, smem_s2, st>>>(t, k, a.X, nullptr, nullptr, NC, tcap2);
+    FEDICRA_CHECK_LAUNCH("stitch_up");
     sweep_kernel<MODE, true><<<dim3(nb, B), nthr_sweep, smem, st>>>(t, a, pcap);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U3D1>");
-    stitch_down_kernel<<<dim3(NC, B), 32, smem_d2, st>>>(t, k, a, outE);
-    FEDICRA_CHECK_LAUNCH("stitch_down_kernel");
+    if (ring) stitch_down_kernel<<<dim3(NC, B), 32, smem_d2, st>>>(t, k, a, outE);
+    else stitch2_kernel<false><<<dim3(NC, B), ST2_NT, smem_s2, st>>>(t, k, nullptr, a.Bv, outE, NC, tcap2);
+    FEDICRA_CHECK_LAUNCH("stitch_down");
     return 0;
 }
 
