@@ -47,7 +47,7 @@ __device__ __forceinline__ int next_dir(unsigned m, int r) {
 }
 
 struct Ws {
-    unsigned *arc;                  // [B,4V] splitter owning the arc << 19 | offset of the arc inside the splitter's stretch
+    unsigned *arc;                  // [B,4V] splitter owning the arc << 18 | offset of the arc inside the splitter's stretch
                                     //        (packed so that the whole table stays L2-resident: its writes are random)
     int *snext, *slen, *sbase;      // [B,NS] next splitter on the tour, stretch length, tour rank of the splitter arc
     int *rin, *rout, *pdir, *size;  // [B,V]  tour rank entering / leaving u, direction of the parent (4 = root), subtree size
@@ -104,7 +104,7 @@ Dims make_dims(int B, int H, int W, int root = 0) {
         d.SPLOG = (k >= 1 && k <= 10) ? k : 3;
         d.SP = 1 << d.SPLOG;
     }
-    while ((d.V + d.SP - 1) / d.SP > 8192) { d.SP <<= 1; ++d.SPLOG; }  // at most 8 192 splitters per image (shared-memory ranking)
+    while ((d.V + d.SP - 1) / d.SP > 16384) { d.SP <<= 1; ++d.SPLOG; }  // at most 16 384 splitters per image (shared-memory ranking: 12 bytes each)
     d.NS = (d.V + d.SP - 1) / d.SP;
     d.T = 2 * (d.V - 1);
     d.NBLK = (d.T + 1023) / 1024;
@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(NT) walk_kernel(const unsigned char *__restric
             steps = 0;
             walking = true;
         }
-        arc[4 * v + d] = ((unsigned)s << 19) | (unsigned)steps;
+        arc[4 * v + d] = ((unsigned)s << 18) | ((unsigned)steps & 0x3ffffu);
         ++steps;
         v += dir_delta(d, W);
         const unsigned mv = mask_of(v);
@@ -192,12 +192,13 @@ __global__ void __launch_bounds__(NT) walk_kernel(const unsigned char *__restric
 __global__ void __launch_bounds__(1024) rank_splitters_kernel(Ws ws, Dims dm) {
     extern __shared__ int s_mem[];
     const int b = blockIdx.x, tid = threadIdx.x, NS = dm.NS;
-    int *val[2] = {s_mem, s_mem + NS}, *nxt[2] = {s_mem + 2 * NS, s_mem + 3 * NS};
+    int *val[2] = {s_mem, s_mem + NS};
+    short *nxt[2] = {reinterpret_cast<short *>(s_mem + 2 * NS), reinterpret_cast<short *>(s_mem + 2 * NS) + NS};   // NS <= 16 384
     const int *snext = ws.snext + (size_t)b * NS, *slen = ws.slen + (size_t)b * NS;
     for (int s = tid; s < NS; s += 1024) {
         const int n = snext[s];
         val[0][s] = slen[s];
-        nxt[0][s] = (n == 0) ? NIL : n;  // the tour is a cycle through splitter 0 (vertex 0, the root): cut it there
+        nxt[0][s] = (short)((n == 0) ? NIL : n);  // the tour is a cycle through splitter 0 (vertex 0, the root): cut it there
     }
     __syncthreads();
     int cur = 0;
@@ -205,7 +206,7 @@ __global__ void __launch_bounds__(1024) rank_splitters_kernel(Ws ws, Dims dm) {
         for (int s = tid; s < NS; s += 1024) {
             const int n = nxt[cur][s];
             val[cur ^ 1][s] = val[cur][s] + (n >= 0 ? val[cur][n] : 0);
-            nxt[cur ^ 1][s] = (n >= 0) ? nxt[cur][n] : NIL;
+            nxt[cur ^ 1][s] = (short)((n >= 0) ? nxt[cur][n] : NIL);
         }
         __syncthreads();
         cur ^= 1;
@@ -216,7 +217,7 @@ __global__ void __launch_bounds__(1024) rank_splitters_kernel(Ws ws, Dims dm) {
 
 __device__ __forceinline__ int arc_rank_raw(const unsigned *arc, const int *sbase, int a) {
     const unsigned r = arc[a];
-    return sbase[r >> 19] + (int)(r & 0x7ffffu);
+    return sbase[r >> 18] + (int)(r & 0x3ffffu);
 }
 // The splitter ranking cuts the (cyclic) tour at vertex 0.  A tour that starts at another root is the same cycle rotated:
 // rank' = rank - rank(first arc out of the root) mod T.
@@ -454,23 +455,27 @@ __global__ void __launch_bounds__(NT) level_rank_kernel(Ws ws, Dims dm, const in
     int *pos = ws.pos + (size_t)b * V, *order = sorted_index + (size_t)b * V;
     for (int L = warp; L < nl; L += warps_per_image) {
         const int lo = ls[L], n = ls[L + 1] - lo;
-        if (n <= 64) {   // the usual case: two entries per lane, keys exchanged by shuffles (one memory round trip in all)
-            const bool h0 = lane < n, h1 = lane + 32 < n;
-            const int2 m0 = h0 ? tmp[lo + lane] : make_int2(0x7fffffff, 0), m1 = h1 ? tmp[lo + 32 + lane] : make_int2(0x7fffffff, 0);
-            int r0 = 0, r1 = 0;
-            const int na = min(n, 32), nb2 = n - na;
-            for (int j = 0; j < na; ++j) {
-                const int kj = __shfl_sync(0xffffffffu, m0.x, j);
-                r0 += kj < m0.x;
-                r1 += kj < m1.x;
+        if (n <= 128) {   // the usual case: up to four entries per lane, keys exchanged by shuffles (one memory round trip)
+            constexpr int R = 4;
+            int2 m[R];
+            int rk[R];
+#pragma unroll
+            for (int q = 0; q < R; ++q) {
+                m[q] = (q * 32 + lane < n) ? tmp[lo + q * 32 + lane] : make_int2(0x7fffffff, 0);
+                rk[q] = 0;
             }
-            for (int j = 0; j < nb2; ++j) {
-                const int kj = __shfl_sync(0xffffffffu, m1.x, j);
-                r0 += kj < m0.x;
-                r1 += kj < m1.x;
+#pragma unroll
+            for (int q = 0; q < R; ++q) {
+                const int cnt = min(n - q * 32, 32);   // entries held in register q across the warp (warp-uniform)
+                for (int j = 0; j < cnt; ++j) {
+                    const int kj = __shfl_sync(0xffffffffu, m[q].x, j);
+#pragma unroll
+                    for (int p = 0; p < R; ++p) rk[p] += kj < m[p].x;
+                }
             }
-            if (h0) { order[lo + r0] = m0.y; pos[m0.y] = lo + r0; }
-            if (h1) { order[lo + r1] = m1.y; pos[m1.y] = lo + r1; }
+#pragma unroll
+            for (int q = 0; q < R; ++q)
+                if (q * 32 + lane < n) { order[lo + rk[q]] = m[q].y; pos[m[q].y] = lo + rk[q]; }
             continue;
         }
         for (int i = lane; i < n; i += 32) {
@@ -548,7 +553,7 @@ extern "C" int fedicra_bfs_euler_rooted(const unsigned char *tree_mask, int B, i
         walk_kernel<false><<<dim3((dm.NS + dm.SPC - 1) / dm.SPC, B), NT, 0, st>>>(tree_mask, ws, dm);
     }
     FEDICRA_CHECK_LAUNCH("walk_kernel");
-    const size_t smem_rank = (size_t)4 * dm.NS * sizeof(int);
+    const size_t smem_rank = (size_t)3 * dm.NS * sizeof(int);
     e = cudaFuncSetAttribute(rank_splitters_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rank);
     if (e != cudaSuccess) return fedicra_fail(-2, "bfs_euler: shared memory: %s", cudaGetErrorString(e));
     rank_splitters_kernel<<<B, 1024, smem_rank, st>>>(ws, dm);
