@@ -76,10 +76,21 @@ __device__ __forceinline__ void cta_arrive(int *counter) {
         red_release_add(counter, 1);
     }
 }
-// Block the CTA until *word == want.
+// Block the CTA until *word == want.  A wait that lasts two seconds can only mean corrupted sync words (a workspace that
+// was not zeroed, or shared by overlapping calls): trap -- the launch fails with an error instead of hanging the GPU.
 __device__ __forceinline__ void cta_wait(const int *word, int want) {
     if (threadIdx.x == 0) {
-        while (ld_acquire(word) != want) __nanosleep(20);
+        unsigned long long t0 = 0;
+        unsigned spins = 0;
+        while (ld_acquire(word) != want) {
+            __nanosleep(20);
+            if ((++spins & 0xfffu) == 0) {   // look at the clock every 4096 polls
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > 2000000000ull) __trap();
+            }
+        }
         __threadfence();
     }
     __syncthreads();

@@ -247,3 +247,37 @@ def test_rooted_order_is_a_level_order_and_the_filter_does_not_depend_on_the_roo
         results.append((out, gf, ge))
     for a, b_ in zip(results[0], results[1]):
         assert rel_err(b_.cpu(), a.cpu()) < 2e-5
+
+
+def test_corrupted_sync_words_fail_the_launch_instead_of_hanging():
+    """The resident filter's CTAs wait on counters in the workspace head.  Garbage there (a workspace that was not
+    zeroed) must end in a CUDA error within seconds -- the kernel traps after a two-second wait -- not in a hung GPU.
+    Runs in a child process: the trap poisons the CUDA context."""
+    import subprocess
+    import sys
+    code = r"""
+import sys, torch
+sys.path.insert(0, %r)
+from fedicra_b200 import ops
+g = torch.Generator().manual_seed(0)
+B, C, H, W = 2, 2, 64, 64
+emb = torch.rand(B, 3, H, W, generator=g).cuda()
+feat = torch.rand(B, C, H * W, generator=g).cuda()
+_, mask = ops.mst_grid(emb, want_mask=True)
+order = ops.bfs_euler(mask, H, W)
+bands = ops.band_plan(order[3], order[4])
+ew = ops.edge_weight_fwd(emb.reshape(B, 3, -1), order[0], order[1], 1.0)
+ops.tree_filter_forward(feat, ew, *order, bands)          # creates (and zeroes) the cached workspace
+torch.cuda.synchronize()
+ws = [v for k, v in ops._WORKSPACES.items() if k[0] == "tree_filter"][0]
+ws[:64].fill_(0x7f)                                       # corrupt the sync words of image 0 and 1
+try:
+    ops.tree_filter_forward(feat, ew, *order, bands)
+    torch.cuda.synchronize()
+except RuntimeError as exc:
+    print("CUDA-ERROR", type(exc).__name__)
+    sys.exit(0)
+print("NO-ERROR")
+""" % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    assert "CUDA-ERROR" in r.stdout, (r.stdout[-500:], r.stderr[-500:])
