@@ -255,6 +255,8 @@ def test_corrupted_sync_words_fail_the_launch_instead_of_hanging():
     Runs in a child process: the trap poisons the CUDA context."""
     import subprocess
     import sys
+    if os.environ.get("FEDICRA_FILTER") == "multi":
+        pytest.skip("the phase kernels have no inter-CTA waits")
     code = r"""
 import sys, torch
 sys.path.insert(0, %r)
