@@ -52,10 +52,8 @@ def _stub(name, **attrs):
     return m
 
 
-def install(tree_module=None):
-    """Register the stand-ins and put the reference's code/ directory on sys.path.  Idempotent."""
-    if not available():
-        raise RuntimeError("the reference tree is not mounted at /root/reference")
+def install_stubs():
+    """Empty stand-ins for the third-party modules the reference imports and this image lacks.  Idempotent."""
     if "flwr" not in sys.modules:
         for name in ("flwr", "flwr.common", "flwr.common.logger", "flwr.client", "flwr.server", "flwr.server.server",
                      "flwr.server.history", "flwr.server.client_manager", "flwr.server.strategy",
@@ -68,6 +66,13 @@ def install(tree_module=None):
         sys.modules["flwr"].server = sys.modules["flwr.server"]
         sys.modules["flwr.common.logger"].log = lambda *a, **k: None
         _stub("efficientnet_pytorch.utils", url_map=_AnyDict(), url_map_advprop=_AnyDict())
+
+
+def install(tree_module=None):
+    """Register the stand-ins and put the reference's code/ directory on sys.path.  Idempotent."""
+    if not available():
+        raise RuntimeError("the reference tree is not mounted at /root/reference")
+    install_stubs()
     if tree_module is None:
         from oracle import tree_cpu as tree_module
     sys.modules["tree_filter_cuda"] = tree_module
