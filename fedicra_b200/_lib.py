@@ -49,6 +49,15 @@ SIGNATURES = {
                                   c_size_t, c_void_p]),
     "fedicra_bfs_euler_rooted": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                          c_void_p, c_void_p, c_size_t, c_void_p]),
+    "fedicra_chain_order": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                    c_void_p]),
+    "fedicra_chain_filter_max_channels": (c_int, []),
+    "fedicra_chain_filter_saved_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "fedicra_chain_filter_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "fedicra_chain_filter_forward": (c_int, [c_void_p] * 6 + [c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p,
+                                                               c_size_t, c_void_p]),
+    "fedicra_chain_filter_backward": (c_int, [c_void_p] * 6 + [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                                                c_size_t, c_void_p]),
     "fedicra_edge_weight_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p]),
     "fedicra_edge_weight_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                         c_float, c_void_p, c_void_p]),
@@ -73,6 +82,7 @@ SIGNATURES = {
     "fedicra_masked_l1_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int, c_int,
                                       ctypes.c_longlong, c_void_p, c_void_p, c_void_p]),
     "fedicra_debug_filter_profile": (c_int, [c_void_p, c_int]),
+    "fedicra_debug_chain_profile": (c_int, [c_void_p, c_int]),
     "fedicra_ala_update_flat": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_void_p]),
     "fedicra_ala_update_multi": (c_int, [c_void_p] * 8 + [c_int, c_int, c_float, c_void_p]),
     "fedicra_scale_inplace": (c_int, [c_void_p, c_int64, c_float, c_void_p]),

@@ -1,0 +1,667 @@
+// chains.cu -- the two-pass tree filter as scans of affine maps along heavy chains (sm_100a).
+//
+// Replaces refine.cu:19-370 of the reference (leaf_root_aggr / root_leaf_prop / root_leaf_grad: one dependent step per
+// tree depth, ~1 500 at 256^2) for trees given in CHAIN ORDER (fedicra_chain_order, csrc/euler.cu): vertices sorted by
+// light depth, every heavy chain on consecutive positions top -> bottom.  In that order
+//
+//   leaf -> root:  x_q = b_q + a_q x_{q+1},   a_q = w_{q+1} if q has a heavy child else 0,
+//                                             b_q = f(vertex q) + sum over light children c of w_c x_c   (next group)
+//   root -> leaf:  y_q = c_q + a_q y_{q-1},   a_q = w_q unless q is a chain top, then 0,
+//                                             c_q = x_q (1 - w_q^2) [+ w_q y_parent for a chain top]   (previous group)
+//
+// i.e. per group one scan of affine maps x -> a x + b (|a| <= 1: no log domain, no overflow), and the only sequential
+// dimension left is the number of groups (8 - 11) instead of the tree depth.
+//
+// ONE launch per filter call.  Work items = (image, group, 512-position tile), handed out by an atomic ticket in an order
+// in which every item only depends on items with smaller tickets (leaf -> root: groups deepest first, tiles by
+// decreasing position; then root -> leaf: groups from 0, tiles increasing) -- so a waiting CTA always waits for a CTA
+// that is already running, whatever the grid size.  Items publish a flag (release) after their results are in global
+// memory; consumers poll the flags of exactly the tiles they read (acquire) and read them at L2.
+// All channels of an image ride in one item (C feature channels + the all-ones channel whose result is the
+// normaliser), so the topology is read once.
+#include <stdlib.h>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int CT = 128;          // threads per CTA
+constexpr int PPT = 4;           // positions per thread
+constexpr int TILE = CT * PPT;   // positions per item
+constexpr int NW = CT / 32;
+constexpr int SYNC_HEAD = 16;    // ints ahead of the flags: [0] ticket, [1] watchdog trips
+
+struct ChainArgs {
+    const int *vtx, *par;        // [B,V] vertex at position, position of the parent
+    const int4 *child;           // [B,V] positions of (heavy child, light children...), 0 = none
+    const int *gstart;           // [B,33] first position of every group; V past the last one
+    float *w;                    // [B,V] edge weight to the parent, position order (w of the root counts as 0)
+    const float *src;            // [B,C,V] vertex order: features (forward) / grad_out (backward)
+    float *up, *agg;             // [B,NC,V] position order: leaf->root and root->leaf results (forward: saved; backward: scratch)
+    float *out;                  // [B,C,V] vertex order: filter output (forward) / feature gradient (backward)
+    const float *up_f, *agg_f;   // backward: what forward saved
+    float *gw;                   // backward: [B,V] edge-weight gradient, position order (may be null)
+    int *sync;                   // [SYNC_HEAD + 4 B Kmax] ticket + flags (zero at launch), then the hand-over values
+    float *hand;                 // [2,B,Kmax,8] value a tile hands to its neighbour in the same group
+    int B, V, Kmax, vec;         // vec: 16-byte vector access allowed (V % 4 == 0, aligned bases)
+    int prof;
+};
+
+__device__ __forceinline__ void st_release(int *p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire(const int *p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ int ld_relaxed(const int *p) {
+    int v;
+    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void fence_acquire() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+
+// Wait until the N items behind flags[idx[k]] (idx < 0: nothing to wait for) have all published.  The flags are polled
+// together with relaxed loads (they pipeline; an acquire load per flag would cost one L2 round trip EACH) and one fence
+// afterwards makes it an acquire.  Every item waits only for items with smaller tickets, which are running, so this
+// ends; the bound (about a second) turns corrupted sync words into a counted error instead of a hang.
+template <int N>
+__device__ __forceinline__ void wait_flags(const int *flags, int (&idx)[N], int *sync) {
+    long long t0 = 0;
+    while (true) {
+        int got[N];
+#pragma unroll
+        for (int k = 0; k < N; ++k) got[k] = idx[k] >= 0 ? ld_relaxed(flags + idx[k]) : 1;
+        bool all = true;
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+            if (got[k] != 0) idx[k] = -1;
+            else all = false;
+        }
+        if (all) break;
+        __nanosleep(20);
+        if (t0 == 0) t0 = clock64();
+        else if (clock64() - t0 > 2000000000ll) {
+            atomicAdd(sync + 1, 1);
+            break;
+        }
+    }
+    fence_acquire();
+}
+
+template <typename T>
+__device__ __forceinline__ void load4(const T *base, int q, int V, bool vec, T (&v)[PPT], T fill) {
+    if (vec) {
+        if (q < V) {
+            const int4 t = *reinterpret_cast<const int4 *>(base + q);
+            v[0] = *reinterpret_cast<const T *>(&t.x); v[1] = *reinterpret_cast<const T *>(&t.y);
+            v[2] = *reinterpret_cast<const T *>(&t.z); v[3] = *reinterpret_cast<const T *>(&t.w);
+        } else {
+            v[0] = v[1] = v[2] = v[3] = fill;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < PPT; ++j) v[j] = (q + j < V) ? base[q + j] : fill;
+    }
+}
+// same, for data another CTA of this launch has written: read at L2
+__device__ __forceinline__ void load4_cg(const float *base, int q, int V, bool vec, float (&v)[PPT]) {
+    if (vec) {
+        if (q < V) {
+            const float4 t = __ldcg(reinterpret_cast<const float4 *>(base + q));
+            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+        } else {
+            v[0] = v[1] = v[2] = v[3] = 0.f;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < PPT; ++j) v[j] = (q + j < V) ? __ldcg(base + q + j) : 0.f;
+    }
+}
+__device__ __forceinline__ void store4(float *base, int q, bool vec, const float (&v)[PPT], const bool (&ok)[PPT]) {
+    if (vec && ok[0] && ok[1] && ok[2] && ok[3]) {
+        *reinterpret_cast<float4 *>(base + q) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+#pragma unroll
+        for (int j = 0; j < PPT; ++j)
+            if (ok[j]) base[q + j] = v[j];
+    }
+}
+
+struct Item {
+    int b, r, T, id, lo, hi, gs, ge;
+};
+
+// FEDICRA_PROF=1: %globaltimer stamps of every item of the first images (claimed, inputs loaded, dependencies met,
+// published) -- read back with fedicra_debug_chain_profile
+constexpr int PROF_B = 2, PROF_K = 768;
+__device__ long long g_chain_prof[2 * PROF_B * PROF_K * 4];
+__device__ __forceinline__ long long globaltimer() {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void stamp(const ChainArgs &a, int phase, const Item &it, int slot) {
+    if (a.prof && threadIdx.x == 0 && it.b < PROF_B && it.id < PROF_K)
+        g_chain_prof[((phase * PROF_B + it.b) * PROF_K + it.id) * 4 + slot] = globaltimer();
+}
+
+// all threads' results are in global memory -> one release store of the item's flag
+__device__ __forceinline__ void publish(int *flag) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        st_release(flag, 1);
+    }
+}
+
+template <int MODE, int NC>
+__device__ __forceinline__ void up_item(const ChainArgs &a, const Item &it, const int *s_gs, const int *s_cum,
+                                        float (*s_agg)[NC + 1]) {
+    constexpr int C = NC - 1;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = a.V, b = it.b;
+    const bool vec = a.vec != 0;
+    const size_t ob = (size_t)b * V;
+    const int q0 = it.T * TILE + tid * PPT;
+    const int *flags_up = a.sync + SYNC_HEAD + (size_t)b * a.Kmax;
+    bool ok[PPT];
+    int vt[PPT];
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) ok[j] = q0 + j >= it.lo && q0 + j < it.hi;
+    load4(a.vtx + ob, q0, V, vec, vt, 0);
+    float av[PPT], bq[PPT][NC];
+    int4 ch[PPT];
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        ch[j] = ok[j] ? a.child[ob + q0 + j] : make_int4(0, 0, 0, 0);
+        av[j] = ok[j] ? ((ch[j].x != 0) ? a.w[ob + q0 + j + 1] : 0.f) : 1.f;   // outside the item: identity map
+        if (!ok[j]) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) bq[j][c] = 0.f;
+        } else if (MODE == 0) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) bq[j][c] = a.src[((size_t)b * C + c) * V + vt[j]];
+            bq[j][C] = 1.f;
+        } else {   // grad_out / Z per channel, and sum_c (grad_out_c / Z) out_c  (refine.cu:347-348, summed over c)
+            const float z = a.agg_f[((size_t)b * NC + C) * V + q0 + j], rz = 1.f / z;
+            float s = 0.f;
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                const float gn = a.src[((size_t)b * C + c) * V + vt[j]] * rz;
+                bq[j][c] = gn;
+                s += gn * (a.agg_f[((size_t)b * NC + c) * V + q0 + j] * rz);
+            }
+            bq[j][C] = s;
+        }
+    }
+    // light children live in the next group; a chain that runs on into the next tile of this group hands its value in.
+    // Everything this item depends on is waited for at once, then fetched at once.
+    const int next_base = s_cum[it.r + 1] - s_gs[it.r + 1] / TILE;
+    const bool cross = it.hi == (it.T + 1) * TILE && it.hi < it.ge && a.child[ob + it.hi - 1].x != 0;
+    int lc[PPT][3], need[PPT * 3 + 1];
+    float wl[PPT][3];
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        lc[j][0] = ch[j].y; lc[j][1] = ch[j].z; lc[j][2] = ch[j].w;
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+            need[j * 3 + s] = lc[j][s] > 0 ? next_base + lc[j][s] / TILE : -1;
+            wl[j][s] = lc[j][s] > 0 ? a.w[ob + lc[j][s]] : 0.f;
+        }
+    }
+    need[PPT * 3] = -1;
+    stamp(a, 0, it, 1);
+    wait_flags(flags_up, need, a.sync);
+    stamp(a, 0, it, 2);
+    {
+        float xv[PPT][3][NC];
+#pragma unroll
+        for (int j = 0; j < PPT; ++j)
+#pragma unroll
+            for (int s = 0; s < 3; ++s)
+#pragma unroll
+                for (int c = 0; c < NC; ++c)
+                    xv[j][s][c] = lc[j][s] > 0 ? __ldcg(a.up + ((size_t)b * NC + c) * V + lc[j][s]) : 0.f;
+#pragma unroll
+        for (int j = 0; j < PPT; ++j)
+#pragma unroll
+            for (int s = 0; s < 3; ++s)
+#pragma unroll
+                for (int c = 0; c < NC; ++c) bq[j][c] = fmaf(wl[j][s], xv[j][s][c], bq[j][c]);
+    }
+    // this thread's four positions as one map x_{q0} = X + P x_{q0+4}
+    float P = 1.f, X[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) X[c] = 0.f;
+#pragma unroll
+    for (int j = PPT - 1; j >= 0; --j) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) X[c] = fmaf(av[j], X[c], bq[j][c]);
+        P *= av[j];
+    }
+    // suffix scan over the warp, then over the warps
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const float Pn = __shfl_down_sync(0xffffffffu, P, o);
+        float Xn[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) Xn[c] = __shfl_down_sync(0xffffffffu, X[c], o);
+        if (lane + o < 32) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) X[c] = fmaf(P, Xn[c], X[c]);
+            P *= Pn;
+        }
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) s_agg[wid][c] = X[c];
+        s_agg[wid][NC] = P;
+    }
+    __syncthreads();
+    // The tile as one map: value at its first position = Xt + Pt * (value handed in at its end).  Pt is 0 unless one
+    // chain spans the whole tile, so the value the PREVIOUS tile of this group waits for is usually known right here,
+    // before this tile has heard from its own neighbour: tiles of a group do not queue up behind each other.
+    float cw[NC], Pt = 1.f, Xt[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) Xt[c] = 0.f;
+    for (int w2 = NW - 1; w2 >= 0; --w2) {
+        const float Pw = s_agg[w2][NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) Xt[c] = fmaf(Pw, Xt[c], s_agg[w2][c]);
+        Pt *= Pw;
+    }
+    int *head_flag = a.sync + SYNC_HEAD + (size_t)(2 * a.B + b) * a.Kmax + it.id;
+    float *head_val = a.hand + ((size_t)b * a.Kmax + it.id) * 8;
+    const bool early = Pt == 0.f || !cross;
+    if (early && tid == 0) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) head_val[c] = Xt[c];
+        __threadfence();
+        st_release(head_flag, 1);
+    }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) cw[c] = 0.f;
+    if (cross) {
+        int nb[1] = {2 * a.B * a.Kmax + it.id + 1};   // the next tile's hand-over flag
+        wait_flags(flags_up, nb, a.sync);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) cw[c] = __ldcg(head_val + 8 + c);
+        if (!early && tid == 0) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) head_val[c] = fmaf(Pt, cw[c], Xt[c]);
+            __threadfence();
+            st_release(head_flag, 1);
+        }
+    }
+    for (int w2 = NW - 1; w2 > wid; --w2) {
+        const float Pw = s_agg[w2][NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) cw[c] = fmaf(Pw, cw[c], s_agg[w2][c]);
+    }
+    {
+        const float Pn = __shfl_down_sync(0xffffffffu, P, 1);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            const float Xn = __shfl_down_sync(0xffffffffu, X[c], 1);
+            if (lane < 31) cw[c] = fmaf(Pn, cw[c], Xn);
+        }
+    }
+    float res[NC][PPT];
+#pragma unroll
+    for (int j = PPT - 1; j >= 0; --j) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            cw[c] = fmaf(av[j], cw[c], bq[j][c]);
+            res[c][j] = cw[c];
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) store4(a.up + ((size_t)b * NC + c) * V, q0, vec, res[c], ok);
+    publish(a.sync + SYNC_HEAD + (size_t)b * a.Kmax + it.id);
+    stamp(a, 0, it, 3);
+}
+
+template <int MODE, int NC>
+__device__ __forceinline__ void down_item(const ChainArgs &a, const Item &it, const int *s_gs, const int *s_cum,
+                                          float (*s_agg)[NC + 1]) {
+    constexpr int C = NC - 1;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = a.V, b = it.b;
+    const bool vec = a.vec != 0;
+    const size_t ob = (size_t)b * V;
+    const int q0 = it.T * TILE + tid * PPT;
+    const int *flags_up = a.sync + SYNC_HEAD + (size_t)b * a.Kmax;
+    const int *flags_dn = a.sync + SYNC_HEAD + (size_t)(a.B + b) * a.Kmax;
+    bool ok[PPT], top[PPT];
+    int vt[PPT], pr[PPT];
+    float wq[PPT];
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) ok[j] = q0 + j >= it.lo && q0 + j < it.hi;
+    load4(a.vtx + ob, q0, V, vec, vt, 0);
+    load4(a.par + ob, q0, V, vec, pr, 0);
+    load4(a.w + ob, q0, V, vec, wq, 0.f);
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        if (q0 + j == 0) wq[j] = 0.f;                          // the root has no parent edge (refine.cu:43-46)
+        top[j] = q0 + j == 0 || pr[j] != q0 + j - 1;
+    }
+    if (it.lo == 0 && tid == 0) a.w[ob] = 0.f;                 // and the reference says so in place
+    // waits: this tile's leaf->root values, the parents of chain tops (previous group), the previous tile of a chain
+    // that started there
+    const int prev_base = it.r > 0 ? s_cum[it.r - 1] - s_gs[it.r - 1] / TILE : 0;
+    const bool cross = it.lo == it.T * TILE && it.lo > it.gs && a.par[ob + it.lo] == it.lo - 1;
+    bool far[PPT];
+    {
+        int need[PPT + 1];
+#pragma unroll
+        for (int j = 0; j < PPT; ++j) {
+            far[j] = ok[j] && top[j] && q0 + j != 0;
+            need[j] = far[j] ? a.B * a.Kmax + prev_base + pr[j] / TILE : -1;   // flags_dn = flags_up + B Kmax
+        }
+        need[PPT] = -1;
+        int mine[1] = {it.id};
+        stamp(a, 1, it, 1);
+        wait_flags(flags_up, mine, a.sync);
+        wait_flags(flags_up, need, a.sync);
+        stamp(a, 1, it, 2);
+    }
+    float u[NC][PPT];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) load4_cg(a.up + ((size_t)b * NC + c) * V, q0, V, vec, u[c]);
+    float av[PPT], cq[PPT][NC];
+#pragma unroll
+    for (int j = 0; j < PPT; ++j)
+#pragma unroll
+        for (int c = 0; c < NC; ++c) cq[j][c] = far[j] ? __ldcg(a.agg + ((size_t)b * NC + c) * V + pr[j]) : 0.f;
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        const float w = wq[j], k = 1.f - w * w;
+        av[j] = ok[j] ? (top[j] ? 0.f : w) : 1.f;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) cq[j][c] = ok[j] ? fmaf(w, cq[j][c], u[c][j] * k) : 0.f;
+    }
+    float P = 1.f, X[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) X[c] = 0.f;
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) X[c] = fmaf(av[j], X[c], cq[j][c]);
+        P *= av[j];
+    }
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const float Pn = __shfl_up_sync(0xffffffffu, P, o);
+        float Xn[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) Xn[c] = __shfl_up_sync(0xffffffffu, X[c], o);
+        if (lane >= o) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) X[c] = fmaf(P, Xn[c], X[c]);
+            P *= Pn;
+        }
+    }
+    if (lane == 31) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) s_agg[wid][c] = X[c];
+        s_agg[wid][NC] = P;
+    }
+    __syncthreads();
+    // as in up_item: the value at this tile's last position = Xt + Pt * (value handed in from the previous tile)
+    float cw[NC], Pt = 1.f, Xt[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) Xt[c] = 0.f;
+    for (int w2 = 0; w2 < NW; ++w2) {
+        const float Pw = s_agg[w2][NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) Xt[c] = fmaf(Pw, Xt[c], s_agg[w2][c]);
+        Pt *= Pw;
+    }
+    int *tail_flag = a.sync + SYNC_HEAD + (size_t)(3 * a.B + b) * a.Kmax + it.id;
+    float *tail_val = a.hand + ((size_t)(a.B + b) * a.Kmax + it.id) * 8;
+    const bool early = Pt == 0.f || !cross;
+    if (early && tid == 0) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) tail_val[c] = Xt[c];
+        __threadfence();
+        st_release(tail_flag, 1);
+    }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) cw[c] = 0.f;
+    if (cross) {
+        int nb[1] = {3 * a.B * a.Kmax + it.id - 1};   // the previous tile's hand-over flag
+        wait_flags(flags_up, nb, a.sync);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) cw[c] = __ldcg(tail_val - 8 + c);
+        if (!early && tid == 0) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) tail_val[c] = fmaf(Pt, cw[c], Xt[c]);
+            __threadfence();
+            st_release(tail_flag, 1);
+        }
+    }
+    for (int w2 = 0; w2 < wid; ++w2) {
+        const float Pw = s_agg[w2][NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) cw[c] = fmaf(Pw, cw[c], s_agg[w2][c]);
+    }
+    {
+        const float Pn = __shfl_up_sync(0xffffffffu, P, 1);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            const float Xn = __shfl_up_sync(0xffffffffu, X[c], 1);
+            if (lane > 0) cw[c] = fmaf(Pn, cw[c], Xn);
+        }
+    }
+    float res[NC][PPT], cw0[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) cw0[c] = cw[c];
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            cw[c] = fmaf(av[j], cw[c], cq[j][c]);
+            res[c][j] = cw[c];
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) store4(a.agg + ((size_t)b * NC + c) * V, q0, vec, res[c], ok);
+    publish(a.sync + SYNC_HEAD + (size_t)(a.B + b) * a.Kmax + it.id);
+    stamp(a, 1, it, 3);
+    // nobody inside this launch waits for what follows
+    if (MODE == 1 && a.gw != nullptr) {
+        // refine.cu:136-199 with both passes folded: U = leaf->root of this call, G = its root->leaf form at the
+        // parent, (upf, A) = what forward saved here and at the parent
+        float gwv[PPT];
+#pragma unroll
+        for (int j = 0; j < PPT; ++j) {
+            float acc = 0.f;
+            if (ok[j] && q0 + j != 0) {
+                const float w = wq[j];
+#pragma unroll
+                for (int c = 0; c < NC; ++c) {
+                    const float gpar = top[j] ? __ldcg(a.agg + ((size_t)b * NC + c) * V + pr[j]) : (j > 0 ? res[c][j > 0 ? j - 1 : 0] : cw0[c]);
+                    const float upf = a.up_f[((size_t)b * NC + c) * V + q0 + j];
+                    const float apar = a.agg_f[((size_t)b * NC + c) * V + pr[j]];
+                    const float t = u[c][j] * (apar - w * upf) + upf * (gpar - w * u[c][j]);
+                    acc += (c < C) ? t : -t;
+                }
+            }
+            gwv[j] = acc;
+        }
+        store4(a.gw + ob, q0, vec, gwv, ok);
+    }
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        if (!ok[j]) continue;
+        if (MODE == 0) {
+            const float rz = 1.f / res[C][j];
+#pragma unroll
+            for (int c = 0; c < C; ++c) a.out[((size_t)b * C + c) * V + vt[j]] = res[c][j] * rz;
+        } else {
+#pragma unroll
+            for (int c = 0; c < C; ++c) a.out[((size_t)b * C + c) * V + vt[j]] = res[c][j];
+        }
+    }
+}
+
+template <int MODE, int NC>
+__global__ void __launch_bounds__(CT) chain_filter_kernel(ChainArgs a) {
+    __shared__ int s_gs[33], s_cum[33], s_ticket;
+    __shared__ float s_agg[NW][NC + 1];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int per_phase = a.B * a.Kmax;
+    while (true) {
+        __syncthreads();
+        if (tid == 0) s_ticket = atomicAdd(a.sync, 1);
+        __syncthreads();
+        const int t = s_ticket;
+        if (t >= 2 * per_phase) break;
+        const int phase = t / per_phase, rem = t - phase * per_phase, k = rem / a.B;
+        Item it;
+        it.b = rem - k * a.B;
+        if (tid < 32) {   // tiles per group and their running count: the dense numbering of this image's items
+            const int g0 = a.gstart[it.b * 33 + lane], g1 = a.gstart[it.b * 33 + lane + 1];
+            const int n = g1 > g0 ? (g1 - 1) / TILE - g0 / TILE + 1 : 0;
+            int x = n;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, x, o);
+                if (lane >= o) x += y;
+            }
+            s_gs[lane] = g0;
+            s_cum[lane] = x - n;
+            if (lane == 31) { s_gs[32] = g1; s_cum[32] = x; }
+        }
+        __syncthreads();
+        const int total = s_cum[32];
+        if (k >= total) continue;
+        it.id = phase == 0 ? total - 1 - k : k;
+        it.r = 0;
+        for (int g = 1; g < 32; ++g)
+            if (s_cum[g] <= it.id) it.r = g;
+        it.gs = s_gs[it.r];
+        it.ge = s_gs[it.r + 1];
+        it.T = it.gs / TILE + (it.id - s_cum[it.r]);
+        it.lo = max(it.gs, it.T * TILE);
+        it.hi = min(it.ge, (it.T + 1) * TILE);
+        stamp(a, phase, it, 0);
+        if (phase == 0) up_item<MODE, NC>(a, it, s_gs, s_cum, s_agg);
+        else down_item<MODE, NC>(a, it, s_gs, s_cum, s_agg);
+    }
+}
+
+int items_bound(int V) { return (V + TILE - 1) / TILE + 33; }
+
+size_t flag_bytes(int B, int V) { return align_up((size_t)(SYNC_HEAD + 4 * (size_t)B * items_bound(V)) * sizeof(int), 256); }
+size_t sync_bytes(int B, int V) { return flag_bytes(B, V) + align_up((size_t)2 * B * items_bound(V) * 8 * sizeof(float), 256); }
+
+template <int MODE, int NC>
+int launch(const ChainArgs &a, cudaStream_t st) {
+    static int ctas_per_sm = 0, sms = 0;   // per process; all devices of a box are the same chip
+    if (ctas_per_sm == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, chain_filter_kernel<MODE, NC>, CT, 0);
+        if (ctas_per_sm < 1) ctas_per_sm = 1;
+    }
+    const long long items = 2ll * a.B * a.Kmax;
+    const int grid = (int)(items < (long long)sms * ctas_per_sm ? items : (long long)sms * ctas_per_sm);
+    chain_filter_kernel<MODE, NC><<<grid, CT, 0, st>>>(a);
+    FEDICRA_CHECK_LAUNCH(MODE == 0 ? "chain_filter_kernel<forward>" : "chain_filter_kernel<backward>");
+    return 0;
+}
+
+template <int MODE>
+int dispatch(const ChainArgs &a, int C, cudaStream_t st) {
+    switch (C) {
+        case 1: return launch<MODE, 2>(a, st);
+        case 2: return launch<MODE, 3>(a, st);
+        case 3: return launch<MODE, 4>(a, st);
+        case 4: return launch<MODE, 5>(a, st);
+    }
+    return fedicra_fail(-1, "chain_filter: %d channels (1..4 are built)", C);
+}
+
+bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
+
+int prof_enabled() {
+    const char *v = getenv("FEDICRA_PROF");
+    return (v && *v && *v != '0') ? 1 : 0;
+}
+
+}  // namespace
+
+extern "C" int fedicra_chain_filter_max_channels(void) { return 4; }
+
+extern "C" size_t fedicra_chain_filter_saved_bytes(int B, int C, int V) {
+    if (B <= 0 || C <= 0 || V <= 0) return 0;
+    return (size_t)2 * B * (C + 1) * V * sizeof(float);
+}
+
+extern "C" size_t fedicra_chain_filter_workspace_bytes(int B, int C, int V) {
+    if (B <= 0 || C <= 0 || V <= 0) return 0;
+    return sync_bytes(B, V) + (size_t)2 * B * (C + 1) * V * sizeof(float);
+}
+
+extern "C" int fedicra_chain_filter_forward(const float *feature_in, float *edge_weight, const int *sorted_index,
+                                            const int *sorted_parent, const int *sorted_child, const int *group_start,
+                                            int B, int C, int V, float *feature_out, void *saved, size_t saved_bytes,
+                                            void *workspace, size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(feature_in && edge_weight && sorted_index && sorted_parent && sorted_child && group_start &&
+                        feature_out && saved && workspace, "chain_filter_forward: null pointer");
+    FEDICRA_REQUIRE(B > 0 && C >= 1 && C <= 4 && V >= 1, "chain_filter_forward: bad sizes B=%d C=%d V=%d (1..4 channels)", B, C, V);
+    FEDICRA_REQUIRE(saved_bytes >= fedicra_chain_filter_saved_bytes(B, C, V), "chain_filter_forward: saved buffer too small");
+    FEDICRA_REQUIRE(workspace_bytes >= sync_bytes(B, V), "chain_filter_forward: workspace too small");
+    FEDICRA_REQUIRE(aligned16(sorted_child), "chain_filter_forward: sorted_child must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    ChainArgs a{};
+    a.vtx = sorted_index; a.par = sorted_parent; a.child = reinterpret_cast<const int4 *>(sorted_child);
+    a.gstart = group_start; a.w = edge_weight; a.src = feature_in;
+    a.up = (float *)saved; a.agg = a.up + (size_t)B * (C + 1) * V;
+    a.out = feature_out; a.sync = (int *)workspace;
+    a.B = B; a.V = V; a.Kmax = items_bound(V); a.prof = prof_enabled();
+    a.vec = (V % 4 == 0) && aligned16(sorted_index) && aligned16(sorted_parent) && aligned16(edge_weight) && aligned16(saved);
+    a.hand = (float *)((char *)workspace + flag_bytes(B, V));
+    cudaError_t e = cudaMemsetAsync(a.sync, 0, flag_bytes(B, V), st);
+    if (e != cudaSuccess) return fedicra_fail(-2, "chain_filter_forward: memset: %s", cudaGetErrorString(e));
+    return dispatch<0>(a, C, st);
+}
+
+extern "C" int fedicra_chain_filter_backward(const float *grad_out, float *edge_weight, const int *sorted_index,
+                                             const int *sorted_parent, const int *sorted_child, const int *group_start,
+                                             int B, int C, int V, const void *saved, float *grad_feature,
+                                             float *grad_weight, void *workspace, size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(grad_out && edge_weight && sorted_index && sorted_parent && sorted_child && group_start && saved &&
+                        grad_feature && workspace, "chain_filter_backward: null pointer");
+    FEDICRA_REQUIRE(B > 0 && C >= 1 && C <= 4 && V >= 1, "chain_filter_backward: bad sizes B=%d C=%d V=%d (1..4 channels)", B, C, V);
+    FEDICRA_REQUIRE(workspace_bytes >= fedicra_chain_filter_workspace_bytes(B, C, V), "chain_filter_backward: workspace too small");
+    FEDICRA_REQUIRE(aligned16(sorted_child), "chain_filter_backward: sorted_child must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    ChainArgs a{};
+    a.vtx = sorted_index; a.par = sorted_parent; a.child = reinterpret_cast<const int4 *>(sorted_child);
+    a.gstart = group_start; a.w = edge_weight; a.src = grad_out;
+    a.up_f = (const float *)saved; a.agg_f = a.up_f + (size_t)B * (C + 1) * V;
+    a.sync = (int *)workspace;
+    a.up = (float *)((char *)workspace + sync_bytes(B, V)); a.agg = a.up + (size_t)B * (C + 1) * V;
+    a.out = grad_feature; a.gw = grad_weight;
+    a.B = B; a.V = V; a.Kmax = items_bound(V); a.prof = prof_enabled();
+    a.vec = (V % 4 == 0) && aligned16(sorted_index) && aligned16(sorted_parent) && aligned16(edge_weight) &&
+            aligned16(saved) && aligned16(a.up) && (grad_weight == nullptr || aligned16(grad_weight));
+    a.hand = (float *)((char *)workspace + flag_bytes(B, V));
+    cudaError_t e = cudaMemsetAsync(a.sync, 0, flag_bytes(B, V), st);
+    if (e != cudaSuccess) return fedicra_fail(-2, "chain_filter_backward: memset: %s", cudaGetErrorString(e));
+    return dispatch<1>(a, C, st);
+}
+
+/* Debug: %globaltimer stamps of the last profiled chain-filter launch (FEDICRA_PROF=1), [2 phases][2 images][768 items][4]:
+ * claimed, inputs loaded, dependencies met, published.  Synchronises the device. */
+extern "C" int fedicra_debug_chain_profile(long long *h_out, int n) {
+    const int total = 2 * PROF_B * PROF_K * 4;
+    if (!h_out || n < total) return fedicra_fail(-1, "debug_chain_profile: need room for %d values", total);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(h_out, g_chain_prof, sizeof(long long) * total);
+    if (e != cudaSuccess) return fedicra_fail(-2, "debug_chain_profile: %s", cudaGetErrorString(e));
+    return total;
+}

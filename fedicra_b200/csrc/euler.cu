@@ -57,11 +57,13 @@ struct Ws {
     int *cnt, *cursor;              // [B,V+1] vertices per depth; bucket fill cursors   (zeroed per call)
     int2 *tmp;                      // [B,V]  per level, unordered: (preorder, vertex)
     int *pos;                       // [B,V]  BFS position of a vertex
+    int *hist;                      // [B,NTILE,32] chain order: vertices per (1024-wide preorder tile, light depth)   (zeroed per call)
 };
 
 struct Dims {
     int root;  // the vertex the order starts from (0 = the reference's, bfs.cu:69-74)
     int B, V, H, W, SP, SPLOG, NS, T, NBLK, SPC;  // T = 2(V-1) arcs on the tour; NBLK = ceil(T / 1024); SPC splitters per walk CTA
+    int NTILE;                                    // ceil(V / 1024)
 };
 
 size_t ws_layout(const Dims &d, char *base, Ws *w) {
@@ -75,6 +77,7 @@ size_t ws_layout(const Dims &d, char *base, Ws *w) {
     Ws t;
     t.cnt = (int *)take(B * (V + 1) * 4);      // cnt and cursor first and adjacent: one memset clears both
     t.cursor = (int *)take(B * (V + 1) * 4);
+    t.hist = (int *)take(B * (size_t)d.NTILE * 32 * 4);   // directly ahead of arc: the chain order clears hist + arc at once
     t.arc = (unsigned *)take(B * 4 * V * 4);
     t.snext = (int *)take(B * d.NS * 4);
     t.slen = (int *)take(B * d.NS * 4);
@@ -108,6 +111,7 @@ Dims make_dims(int B, int H, int W, int root = 0) {
     d.NS = (d.V + d.SP - 1) / d.SP;
     d.T = 2 * (d.V - 1);
     d.NBLK = (d.T + 1023) / 1024;
+    d.NTILE = (d.V + 1023) / 1024;
     d.SPC = split_per_cta();
     return d;
 }
@@ -506,6 +510,238 @@ __global__ void __launch_bounds__(NT) finalize_kernel(const unsigned char *__res
     reinterpret_cast<int4 *>(sorted_child)[o + i] = make_int4(c[0], c[1], c[2], c[3]);
 }
 
+
+// =====================================================================================================================
+// Chain order: heavy-path decomposition of the rooted tree, laid out for the scan-based filter (csrc/chains.cu).
+//
+//   heavy child of p  = the child with the largest subtree (smallest vertex id on ties); every other child is light;
+//   chain             = maximal path of heavy edges (top = the root or a light child; bottom = a leaf);
+//   light depth ld(u) = number of light edges between the root and u  (<= log2 V: a light subtree is at most half
+//                       its parent's);
+//   position          = vertices sorted by (ld, preorder index of the traversal that visits the heavy child first).
+//
+// In that order a chain occupies consecutive positions top -> bottom, all chains of one light depth form one contiguous
+// GROUP, the root sits at position 0, every parent precedes its children (so sorted_index / sorted_parent /
+// sorted_child are valid arrays in the reference's sense, bfs.cu:46-98, with child slot 0 = the heavy child at
+// position + 1), and the filter's recurrences become, per group, scans of affine maps along the chains: the depth of
+// the dependency chain is the number of groups (8 - 11 for 256^2 .. 512^2 images) instead of the tree depth (~1 500).
+// =====================================================================================================================
+
+// direction of the heavy child of p (-1: leaf); sz[d] = subtree size of the child in direction d (0: no child there)
+__device__ __forceinline__ int heavy_dir(unsigned m, int pd, const int *__restrict__ size_b, int p, int W, int sz[4]) {
+    int best = -1, bsz = 0;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        sz[d] = ((m >> d) & 1u) && d != pd ? size_b[p + dir_delta(d, W)] : 0;
+        if (sz[d] > bsz) { bsz = sz[d]; best = d; }
+    }
+    return best;
+}
+
+// tour-ordered increments: x = +-o with o(u) = 1 + sizes of the siblings visited before u when the heavy child goes
+// first and the light ones follow by increasing id;  y = (u << 1 | light(u)) where the tour enters u, -(1 + light(u))
+// where it leaves
+__global__ void __launch_bounds__(NT) chain_increments_kernel(const unsigned char *__restrict__ mask, Ws ws, Dims dm) {
+    const long long idx = (long long)blockIdx.x * NT + threadIdx.x;
+    if (idx >= (long long)dm.B * dm.V) return;
+    const int b = (int)(idx / dm.V), u = (int)(idx - (long long)b * dm.V), V = dm.V, W = dm.W;
+    if (u == dm.root) return;
+    const size_t o = (size_t)b * V;
+    const int pd = ws.pdir[o + u], p = u + dir_delta(pd, W), du = 3 - pd;  // u is p's child in direction du
+    int sz[4];
+    const int hd = heavy_dir(mask[o + p], ws.pdir[o + p], ws.size + o, p, W, sz);
+    int offs = 1, light = 0;
+    if (hd != du) {
+        light = 1;
+        offs += sz[hd];
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+            if (d < du && d != hd) offs += sz[d];
+    }
+    int2 *S = ws.S + (size_t)b * 2 * V;
+    S[ws.rin[o + u]] = make_int2(offs, (u << 1) | light);
+    S[ws.rout[o + u]] = make_int2(-offs, -(1 + light));
+}
+
+__device__ __forceinline__ int2 chain_delta(int2 s) {   // (d light depth, d preorder) of one tour entry
+    return make_int2(s.y >= 0 ? (s.y & 1) : (s.y + 1), s.x);
+}
+
+__global__ void __launch_bounds__(1024) chain_block_sum_kernel(Ws ws, Dims dm) {
+    const int b = blockIdx.y, blk = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int r = blk * 1024 + tid;
+    int2 v = make_int2(0, 0);
+    if (r < dm.T) v = chain_delta(ws.S[(size_t)b * 2 * dm.V + r]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+        v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+    }
+    __shared__ int2 s_w[32];
+    if (lane == 0) s_w[wid] = v;
+    __syncthreads();
+    if (wid == 0) {
+        int2 t = s_w[lane];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            t.x += __shfl_xor_sync(0xffffffffu, t.x, o);
+            t.y += __shfl_xor_sync(0xffffffffu, t.y, o);
+        }
+        if (lane == 0) ws.bsum[(size_t)b * dm.NBLK + blk] = t;
+    }
+}
+
+// prefix sums along the tour: where it enters u the inclusive sums are (ld(u), heavy-first preorder index of u);
+// key[preorder] = u << 5 | ld, and the (preorder tile, ld) histogram that the placement needs
+__global__ void __launch_bounds__(1024) chain_apply_kernel(Ws ws, Dims dm) {
+    const int b = blockIdx.y, blk = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = dm.V;
+    const int r = blk * 1024 + tid;
+    int2 sp = make_int2(0, -1);
+    bool enter = false;
+    if (r < dm.T) { sp = ws.S[(size_t)b * 2 * V + r]; enter = sp.y >= 0; }
+    int2 x = (r < dm.T) ? chain_delta(sp) : make_int2(0, 0);
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int tx = __shfl_up_sync(0xffffffffu, x.x, o), ty = __shfl_up_sync(0xffffffffu, x.y, o);
+        if (lane >= o) { x.x += tx; x.y += ty; }
+    }
+    __shared__ int2 s_w[32];
+    if (lane == 31) s_w[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+        int2 t = s_w[lane], y = t;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int tx = __shfl_up_sync(0xffffffffu, y.x, o), ty = __shfl_up_sync(0xffffffffu, y.y, o);
+            if (lane >= o) { y.x += tx; y.y += ty; }
+        }
+        s_w[lane] = make_int2(y.x - t.x, y.y - t.y);
+    }
+    __syncthreads();
+    int *key = ws.depth + (size_t)b * V;                     // reused: [B,V] keys in preorder
+    int *hist = ws.hist + (size_t)b * dm.NTILE * 32;
+    if (blk == 0 && tid == 0) {  // the root is never entered
+        key[0] = dm.root << 5;
+        atomicAdd(hist, 1);
+    }
+    if (enter) {
+        const int2 base = (dm.NBLK > 0) ? ws.bsum[(size_t)b * dm.NBLK + blk] : make_int2(0, 0), wo = s_w[wid];
+        const int ld = min(base.x + wo.x + x.x, 31), pre = base.y + wo.y + x.y;
+        if (pre >= 0 && pre < V) {               // always, for a consistent tree mask
+            key[pre] = ((sp.y >> 1) << 5) | ld;
+            atomicAdd(hist + (pre >> 10) * 32 + ld, 1);
+        }
+    }
+}
+
+// one CTA per image, one warp per light depth: exclusive scan of the histogram over the tiles (in place), then the
+// group starts = exclusive scan of the group sizes; group_start[g] = V for every g past the last group
+__global__ void __launch_bounds__(1024) chain_offsets_kernel(Ws ws, Dims dm, int *__restrict__ group_start) {
+    const int b = blockIdx.x, lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+    int *hist = ws.hist + (size_t)b * dm.NTILE * 32;
+    __shared__ int s_tot[32];
+    int carry = 0;
+    for (int base = 0; base < dm.NTILE; base += 32) {
+        const int t = base + lane;
+        const int c = (t < dm.NTILE) ? hist[t * 32 + g] : 0;
+        int x = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (t < dm.NTILE) hist[t * 32 + g] = carry + x - c;
+        carry += __shfl_sync(0xffffffffu, x, 31);
+    }
+    if (lane == 0) s_tot[g] = carry;
+    __syncthreads();
+    if (g == 0) {
+        const int c = s_tot[lane];
+        int x = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        group_start[(size_t)b * 33 + lane] = x - c;
+        if (lane == 31) group_start[(size_t)b * 33 + 32] = x;   // = V
+    }
+}
+
+// position of every vertex: group start + vertices of the same light depth in earlier tiles + in earlier warps of this
+// tile + in earlier lanes of this warp
+__global__ void __launch_bounds__(1024) chain_place_kernel(Ws ws, Dims dm, const int *__restrict__ group_start,
+                                                           int *__restrict__ sorted_index) {
+    const int b = blockIdx.y, tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = dm.V;
+    const int i = tile * 1024 + tid;
+    const bool valid = i < V;
+    const int key = valid ? ws.depth[(size_t)b * V + i] : 0;
+    const int bin = valid ? (key & 31) : 32 + lane;   // idle lanes match nobody
+    const unsigned same = __match_any_sync(0xffffffffu, bin);
+    const int rank = __popc(same & ((1u << lane) - 1u));
+    __shared__ int s_cnt[32][33];
+    for (int k = tid; k < 32 * 33; k += 1024) (&s_cnt[0][0])[k] = 0;
+    __syncthreads();
+    if (valid && rank == 0) s_cnt[wid][bin] = __popc(same);
+    __syncthreads();
+    {   // exclusive prefix over the warps, one thread per (warp, bin)
+        int acc = 0;
+        for (int w2 = 0; w2 < wid; ++w2) acc += s_cnt[w2][lane];
+        __syncthreads();
+        s_cnt[wid][lane] = acc;
+    }
+    __syncthreads();
+    if (!valid) return;
+    const int pos = group_start[(size_t)b * 33 + bin] + ws.hist[((size_t)b * dm.NTILE + tile) * 32 + bin] + s_cnt[wid][bin] + rank;
+    const int u = key >> 5;
+    ws.pos[(size_t)b * V + u] = pos;
+    sorted_index[(size_t)b * V + pos] = u;
+}
+
+// parent position; children positions: slot 0 = heavy child (always position + 1), then the light ones by increasing id
+__global__ void __launch_bounds__(NT) chain_finalize_kernel(const unsigned char *__restrict__ mask, Ws ws, Dims dm,
+                                                            int *__restrict__ sorted_parent, int *__restrict__ sorted_child) {
+    const long long idx = (long long)blockIdx.x * NT + threadIdx.x;
+    if (idx >= (long long)dm.B * dm.V) return;
+    const int b = (int)(idx / dm.V), u = (int)(idx - (long long)b * dm.V), V = dm.V, W = dm.W;
+    const size_t o = (size_t)b * V;
+    const int *pos = ws.pos + o;
+    const int i = pos[u], pd = ws.pdir[o + u];
+    sorted_parent[o + i] = (u == dm.root) ? 0 : pos[u + dir_delta(pd, W)];
+    int sz[4];
+    const int hd = heavy_dir(mask[o + u], pd, ws.size + o, u, W, sz);
+    int c[4] = {0, 0, 0, 0}, k = 1;
+    if (hd >= 0) c[0] = pos[u + dir_delta(hd, W)];
+#pragma unroll
+    for (int d = 0; d < 4; ++d)
+        if (sz[d] > 0 && d != hd) c[k++] = pos[u + dir_delta(d, W)];
+    reinterpret_cast<int4 *>(sorted_child)[o + i] = make_int4(c[0], c[1], c[2], c[3]);
+}
+
+// Euler tour of every tree ranked, entering / leaving ranks, parent direction and subtree size of every vertex
+int run_tour(const unsigned char *tree_mask, const Ws &ws, const Dims &dm, cudaStream_t st, const char *who) {
+    const int B = dm.B, V = dm.V;
+    const unsigned vb = (unsigned)(((long long)B * V + NT - 1) / NT);
+    const size_t smem_mask = (size_t)(V + 1) / 2;
+    cudaError_t e;
+    if (smem_mask <= 200 * 1024) {
+        e = cudaFuncSetAttribute(walk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_mask);
+        if (e != cudaSuccess) return fedicra_fail(-2, "%s: shared memory: %s", who, cudaGetErrorString(e));
+        walk_kernel<true><<<dim3((dm.NS + dm.SPC - 1) / dm.SPC, B), NT, smem_mask, st>>>(tree_mask, ws, dm);
+    } else {
+        walk_kernel<false><<<dim3((dm.NS + dm.SPC - 1) / dm.SPC, B), NT, 0, st>>>(tree_mask, ws, dm);
+    }
+    FEDICRA_CHECK_LAUNCH("walk_kernel");
+    const size_t smem_rank = (size_t)3 * dm.NS * sizeof(int);
+    e = cudaFuncSetAttribute(rank_splitters_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rank);
+    if (e != cudaSuccess) return fedicra_fail(-2, "%s: shared memory: %s", who, cudaGetErrorString(e));
+    rank_splitters_kernel<<<B, 1024, smem_rank, st>>>(ws, dm);
+    FEDICRA_CHECK_LAUNCH("rank_splitters_kernel");
+    enter_leave_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm);
+    FEDICRA_CHECK_LAUNCH("enter_leave_kernel");
+    return 0;
+}
+
 }  // namespace
 
 extern "C" size_t fedicra_bfs_euler_workspace_bytes(int B, int H, int W) {
@@ -544,22 +780,7 @@ extern "C" int fedicra_bfs_euler_rooted(const unsigned char *tree_mask, int B, i
     cudaError_t e = cudaMemsetAsync(ws.cnt, 0, (size_t)((char *)ws.snext - (char *)ws.cnt), st);
     if (e != cudaSuccess) return fedicra_fail(-2, "bfs_euler: memset: %s", cudaGetErrorString(e));
     const unsigned vb = (unsigned)(((long long)B * V + NT - 1) / NT);
-    const size_t smem_mask = (size_t)(V + 1) / 2;
-    if (smem_mask <= 200 * 1024) {
-        e = cudaFuncSetAttribute(walk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_mask);
-        if (e != cudaSuccess) return fedicra_fail(-2, "bfs_euler: shared memory: %s", cudaGetErrorString(e));
-        walk_kernel<true><<<dim3((dm.NS + dm.SPC - 1) / dm.SPC, B), NT, smem_mask, st>>>(tree_mask, ws, dm);
-    } else {
-        walk_kernel<false><<<dim3((dm.NS + dm.SPC - 1) / dm.SPC, B), NT, 0, st>>>(tree_mask, ws, dm);
-    }
-    FEDICRA_CHECK_LAUNCH("walk_kernel");
-    const size_t smem_rank = (size_t)3 * dm.NS * sizeof(int);
-    e = cudaFuncSetAttribute(rank_splitters_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rank);
-    if (e != cudaSuccess) return fedicra_fail(-2, "bfs_euler: shared memory: %s", cudaGetErrorString(e));
-    rank_splitters_kernel<<<B, 1024, smem_rank, st>>>(ws, dm);
-    FEDICRA_CHECK_LAUNCH("rank_splitters_kernel");
-    enter_leave_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm);
-    FEDICRA_CHECK_LAUNCH("enter_leave_kernel");
+    if (int rc = run_tour(tree_mask, ws, dm, st, "bfs_euler")) return rc;
     if (dm.T > 0) {
         increments_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm);
         FEDICRA_CHECK_LAUNCH("increments_kernel");
@@ -580,5 +801,45 @@ extern "C" int fedicra_bfs_euler_rooted(const unsigned char *tree_mask, int B, i
     FEDICRA_CHECK_LAUNCH("level_rank_kernel");
     finalize_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm, sorted_parent, sorted_child);
     FEDICRA_CHECK_LAUNCH("finalize_kernel");
+    return 0;
+}
+
+
+extern "C" int fedicra_chain_order(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index,
+                                   int *sorted_parent, int *sorted_child, int *group_start, void *workspace,
+                                   size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(tree_mask && sorted_index && sorted_parent && sorted_child && group_start && workspace,
+                    "chain_order: null pointer");
+    FEDICRA_REQUIRE(B > 0 && B <= 65535 && H >= 1 && W >= 1 && (long long)H * W <= (1ll << 18),
+                    "chain_order: bad sizes B=%d H=%d W=%d (at most 262144 pixels per image)", B, H, W);
+    FEDICRA_REQUIRE(((uintptr_t)sorted_child & 15) == 0, "chain_order: sorted_child must be 16-byte aligned");
+    const Dims dm = make_dims(B, H, W, 0);
+    FEDICRA_REQUIRE(workspace_bytes >= ws_layout(dm, nullptr, nullptr), "chain_order: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    Ws ws;
+    ws_layout(dm, (char *)workspace, &ws);
+    const int V = dm.V;
+    // the histogram must start at zero; the arc table is cleared with it so that its lines are L2-resident when the
+    // walk scatters 4-byte records into them
+    cudaError_t e = cudaMemsetAsync(ws.hist, 0, (size_t)((char *)ws.snext - (char *)ws.hist), st);
+    if (e != cudaSuccess) return fedicra_fail(-2, "chain_order: memset: %s", cudaGetErrorString(e));
+    const unsigned vb = (unsigned)(((long long)B * V + NT - 1) / NT);
+    if (int rc = run_tour(tree_mask, ws, dm, st, "chain_order")) return rc;
+    if (dm.T > 0) {
+        chain_increments_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm);
+        FEDICRA_CHECK_LAUNCH("chain_increments_kernel");
+        chain_block_sum_kernel<<<dim3(dm.NBLK, B), 1024, 0, st>>>(ws, dm);
+        FEDICRA_CHECK_LAUNCH("chain_block_sum_kernel");
+        tour_scan_sums_kernel<<<B, 1024, 0, st>>>(ws, dm);
+        FEDICRA_CHECK_LAUNCH("tour_scan_sums_kernel");
+    }
+    chain_apply_kernel<<<dim3(dm.NBLK > 0 ? dm.NBLK : 1, B), 1024, 0, st>>>(ws, dm);
+    FEDICRA_CHECK_LAUNCH("chain_apply_kernel");
+    chain_offsets_kernel<<<B, 1024, 0, st>>>(ws, dm, group_start);
+    FEDICRA_CHECK_LAUNCH("chain_offsets_kernel");
+    chain_place_kernel<<<dim3(dm.NTILE, B), 1024, 0, st>>>(ws, dm, group_start, sorted_index);
+    FEDICRA_CHECK_LAUNCH("chain_place_kernel");
+    chain_finalize_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm, sorted_parent, sorted_child);
+    FEDICRA_CHECK_LAUNCH("chain_finalize_kernel");
     return 0;
 }

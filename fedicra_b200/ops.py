@@ -186,6 +186,59 @@ def bfs_euler(mask, H, W, root=0):
     return si, sp, sc, ls, nl
 
 
+def chain_order(mask, H, W):
+    """Chain (heavy-path) order of grid trees given as adjacency masks: sorted_index, sorted_parent, sorted_child in the
+    reference's sense plus group_start [B,33] (first position of every light depth).  Feeds chain_filter_*."""
+    m = _cuda(mask, torch.uint8, "tree_mask")
+    B, V = m.shape
+    dev = m.device
+    with torch.cuda.device(dev):
+        si = torch.empty(B, V, dtype=torch.int32, device=dev)
+        sp = torch.empty(B, V, dtype=torch.int32, device=dev)
+        sc = torch.empty(B, V, 4, dtype=torch.int32, device=dev)
+        gs = torch.empty(B, 33, dtype=torch.int32, device=dev)
+        ws = workspace("bfs_euler", lib.fedicra_bfs_euler_workspace_bytes(B, H, W), dev)
+        check(lib.fedicra_chain_order(_p(m), B, H, W, _p(si), _p(sp), _p(sc), _p(gs), _p(ws), ws.numel(), _stream()),
+              "chain_order")
+    return si, sp, sc, gs
+
+
+CHAIN_MAX_V = 1 << 18
+CHAIN_MAX_C = lib.fedicra_chain_filter_max_channels()
+
+
+def chain_filter_forward(feature_in, edge_weight, si, sp, sc, gs):
+    """Tree filter on chain-ordered trees.  Returns (feature_out [B,C,V] vertex order, saved) with saved =
+    [2,B,C+1,V] float32: leaf->root values and root->leaf aggregates in chain order (channel C = weight sums)."""
+    f = _cuda(feature_in, torch.float32, "feature_in")
+    if not (edge_weight.is_cuda and edge_weight.dtype == torch.float32 and edge_weight.is_contiguous()):
+        raise RuntimeError("edge_weight must be a contiguous float32 CUDA tensor (it is written in place)")
+    B, C, V = f.shape
+    dev = f.device
+    with torch.cuda.device(dev):
+        out = torch.empty_like(f)
+        saved = torch.empty(2, B, C + 1, V, dtype=torch.float32, device=dev)
+        ws = workspace("chain_filter", lib.fedicra_chain_filter_workspace_bytes(B, C, V), dev)
+        check(lib.fedicra_chain_filter_forward(_p(f), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(gs), B, C, V, _p(out),
+                                               _p(saved), saved.numel() * 4, _p(ws), ws.numel(), _stream()),
+              "chain_filter_forward")
+    return out, saved
+
+
+def chain_filter_backward(grad_out, edge_weight, si, sp, sc, gs, saved, want_weight_grad):
+    """Returns (grad_feature [B,C,V] vertex order, grad_weight [B,V] chain order or None)."""
+    g = _cuda(grad_out, torch.float32, "grad_output")
+    B, C, V = g.shape
+    dev = g.device
+    with torch.cuda.device(dev):
+        gf = torch.empty_like(g)
+        gw = torch.empty(B, V, dtype=torch.float32, device=dev) if want_weight_grad else None
+        ws = workspace("chain_filter", lib.fedicra_chain_filter_workspace_bytes(B, C, V), dev)
+        check(lib.fedicra_chain_filter_backward(_p(g), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(gs), B, C, V, _p(saved),
+                                                _p(gf), _p(gw), _p(ws), ws.numel(), _stream()), "chain_filter_backward")
+    return gf, gw
+
+
 # ------------------------------------------------------------------ edge weights
 
 

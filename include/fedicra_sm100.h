@@ -130,6 +130,16 @@ int fedicra_bfs_euler_rooted(const unsigned char *tree_mask, int B, int H, int W
                              int *sorted_parent, int *sorted_child, int *level_start, int *n_levels, void *workspace,
                              size_t workspace_bytes, void *stream);
 
+/* Chain order: a second valid ordering of the same rooted tree (root = vertex 0; bfs.cu:46-98 semantics hold: parents
+ * precede children, sorted_parent[0] = 0, child slot value 0 = none), built for fedicra_chain_filter_*: vertices sorted
+ * by LIGHT DEPTH (number of non-heaviest-child edges above them), every heavy chain on consecutive positions top to
+ * bottom; sorted_child[i] = (heavy child = i + 1 or 0, light children by increasing vertex id, 0...).
+ *   group_start [B,33]: first position of every light depth; entries past the last group = V.
+ * The reference has one order (its BFS); the filter result does not depend on which valid order is used
+ * (refine.cu:19-199 only follow parent / child links).  Same size limit and workspace as fedicra_bfs_euler. */
+int fedicra_chain_order(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index, int *sorted_parent,
+                        int *sorted_child, int *group_start, void *workspace, size_t workspace_bytes, void *stream);
+
 /* ------------------------------------------------------------------------------------------------ tree filter -- */
 /* TreeFilter2D.build_edge_weight (LTF/modules/tree_filter.py:91-108): ew[b,i] = exp(-|e[v(i)] - e[v(par i)]|^2 *
  * inv_sigma) in BFS order; embed [B,D,V] in vertex order. */
@@ -190,6 +200,27 @@ int fedicra_tree_filter_backward(const float *grad_out, const float *edge_weight
                                  float *grad_feature, float *grad_weight, void *workspace, size_t workspace_bytes,
                                  void *stream);
 
+/* The same filter (refine_forward / refine_backward_feature / refine_backward_weight, LTF/src/refine/refine.cu:201-370)
+ * for trees in CHAIN ORDER (fedicra_chain_order): per light depth one scan of affine maps x -> a x + b along the heavy
+ * chains, so the sequential dimension is the number of light depths (8-11 at 256^2..512^2) instead of the tree depth
+ * (~1 500).  One launch per call (csrc/chains.cu); 1..4 feature channels.
+ *   feature_in / grad_out / feature_out / grad_feature [B,C,V] vertex order; edge_weight, grad_weight [B,V] chain order
+ *   (edge_weight[b,0] is set to 0 in place like refine.cu:43-46; grad_weight may be NULL);
+ *   saved = leaf->root values then root->leaf aggregates, each [B,C+1,V] in chain order, channel C = the all-ones
+ *   channel (weight_sum_up / weight_sum of the reference), i.e. feature_aggr_up, weight_sum_up, feature_aggr, weight_sum;
+ *   workspace: zeroed by the call itself; forward needs the first 64 KiB-ish sync part only. */
+int fedicra_chain_filter_max_channels(void);
+size_t fedicra_chain_filter_saved_bytes(int B, int C, int V);
+size_t fedicra_chain_filter_workspace_bytes(int B, int C, int V);
+int fedicra_chain_filter_forward(const float *feature_in, float *edge_weight, const int *sorted_index,
+                                 const int *sorted_parent, const int *sorted_child, const int *group_start, int B, int C,
+                                 int V, float *feature_out, void *saved, size_t saved_bytes, void *workspace,
+                                 size_t workspace_bytes, void *stream);
+int fedicra_chain_filter_backward(const float *grad_out, float *edge_weight, const int *sorted_index,
+                                  const int *sorted_parent, const int *sorted_child, const int *group_start, int B, int C,
+                                  int V, const void *saved, float *grad_feature, float *grad_weight, void *workspace,
+                                  size_t workspace_bytes, void *stream);
+
 /* ------------------------------------------------------------------------------------------------ loss glue ---- */
 /* prob = softmax over the channel axis of x [B,C,P]  (flower_common.py:781, torch.softmax(preds, dim=1)); C <= 16. */
 int fedicra_channel_softmax_fwd(const float *x, int B, int C, long long P, float *y, void *stream);
@@ -217,6 +248,7 @@ int fedicra_masked_l1_bwd(const float *prob, const float *filtered, const unsign
  * [bands + 1][12] nanosecond stamps to the HOST buffer h_out (n = its capacity in elements; the required count is
  * returned; synchronises the device). */
 int fedicra_debug_filter_profile(long long *h_out, int n);
+int fedicra_debug_chain_profile(long long *h_out, int n);   /* same for csrc/chains.cu: returns the value count */
 
 /* ------------------------------------------------------------------------------------------------ aggregation -- */
 /* Adaptive local aggregation, element-wise part of MyModel.set_weights (flower_common.py:590-602) over one flat
