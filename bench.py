@@ -143,7 +143,7 @@ class GpuStep:
 class GraphedStep:
     """The same step captured once into a CUDA graph and replayed: static input buffers, outputs in the graph's pool.
     Every kernel of the library launches on the capturing stream and none of them synchronises or allocates outside
-    torch's allocator, so the step is capture-safe.  Removes the host launch cost (~350 launches per step)."""
+    torch's allocator, so the step is capture-safe.  Removes the host launch cost (a few dozen library launches + ~20 ATen launches per step)."""
 
     def __init__(self, step, example):
         self.static_in = {k: v.clone() for k, v in example.items()}
@@ -193,7 +193,7 @@ def profile_ops(step, data, steps, flush_buf):
     from fedicra_b200 import ops
     names = ["gcrf_fwd_bwd", "mst_grid", "mst_grid_multi", "bfs_forward", "bfs_grid", "bfs_euler", "edge_weight_fwd",
              "edge_weight_bwd", "refine_forward", "refine_backward_feature", "refine_backward_weight", "tree_filter_forward",
-             "tree_filter_backward", "band_plan", "channel_softmax_fwd", "channel_softmax_bwd", "masked_l1_fwd",
+             "tree_filter_backward", "band_plan", "chain_order", "chain_filter_forward", "chain_filter_backward", "channel_softmax_fwd", "channel_softmax_bwd", "masked_l1_fwd",
              "masked_l1_bwd"]
     records, originals = {n: [] for n in names}, {}
 
@@ -394,6 +394,9 @@ def run_ours(args, wl):
         "refine_forward": lambda: B * ab["stages"][1]["filter_fwd"],
         "refine_backward_feature": lambda: B * (2 * C + 3) * u,
         "refine_backward_weight": lambda: B * (2 * C + 2 * C) * u,
+        "chain_order": lambda: 4 * B * u,                                        # one call for the 4 trees
+        "chain_filter_forward": lambda: B * all_stages("filter_fwd") / 4,       # mean over the 4 trees
+        "chain_filter_backward": lambda: B * all_stages("filter_bwd") / 4,
         "tree_filter_forward": lambda: B * all_stages("filter_fwd") / 4,        # mean over the 4 trees
         "tree_filter_backward": lambda: B * all_stages("filter_bwd") / 4,
         "gcrf_fwd_bwd": lambda: B * ab["gcrf"],

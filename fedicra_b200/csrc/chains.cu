@@ -15,8 +15,15 @@
 // ONE launch per filter call.  Work items = (image, group, 512-position tile), handed out by an atomic ticket in an order
 // in which every item only depends on items with smaller tickets (leaf -> root: groups deepest first, tiles by
 // decreasing position; then root -> leaf: groups from 0, tiles increasing) -- so a waiting CTA always waits for a CTA
-// that is already running, whatever the grid size.  Items publish a flag (release) after their results are in global
-// memory; consumers poll the flags of exactly the tiles they read (acquire) and read them at L2.
+// that is already running, whatever the grid size.
+//
+// Hand-over between items costs one L2 round trip and no fence: every intermediate word is SELF-VALIDATING.  The
+// intermediate arrays start as 0xFFFFFFFF (a NaN no arithmetic produces; the call memsets them), producers store
+// results with relaxed gpu-scope stores, and a consumer simply re-reads the words it needs (relaxed gpu-scope loads,
+// served by L2) until none of them is the start pattern.  No flags, no release / acquire pairs, no __threadfence.
+// A tile also hands its boundary value to the neighbouring tile of the same group as soon as it is known -- which is
+// before the tile has heard from its OTHER neighbour unless one chain spans the whole tile -- so the tiles of a group
+// do not queue up behind each other.
 // All channels of an image ride in one item (C feature channels + the all-ones channel whose result is the
 // normaliser), so the topology is read once.
 #include <stdlib.h>
@@ -29,7 +36,8 @@ constexpr int CT = 128;          // threads per CTA
 constexpr int PPT = 4;           // positions per thread
 constexpr int TILE = CT * PPT;   // positions per item
 constexpr int NW = CT / 32;
-constexpr int SYNC_HEAD = 16;    // ints ahead of the flags: [0] ticket, [1] watchdog trips
+constexpr int SYNC_HEAD = 64;    // ints ahead of the hand-over values: [0] ticket - 1, [1] watchdog trips - 1
+constexpr unsigned PENDING = 0xffffffffu;
 
 struct ChainArgs {
     const int *vtx, *par;        // [B,V] vertex at position, position of the parent
@@ -41,54 +49,43 @@ struct ChainArgs {
     float *out;                  // [B,C,V] vertex order: filter output (forward) / feature gradient (backward)
     const float *up_f, *agg_f;   // backward: what forward saved
     float *gw;                   // backward: [B,V] edge-weight gradient, position order (may be null)
-    int *sync;                   // [SYNC_HEAD + 4 B Kmax] ticket + flags (zero at launch), then the hand-over values
-    float *hand;                 // [2,B,Kmax,8] value a tile hands to its neighbour in the same group
+    int *sync;                   // [SYNC_HEAD] counters, all bits set at launch
+    float *hand;                 // [2,B,Kmax,8] value a tile hands to its neighbour in the same group (PENDING at launch)
     int B, V, Kmax, vec;         // vec: 16-byte vector access allowed (V % 4 == 0, aligned bases)
     int prof;
 };
 
-__device__ __forceinline__ void st_release(int *p, int v) {
-    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ int ld_acquire(const int *p) {
-    int v;
-    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+// relaxed gpu-scope accesses: "strong" operations in the PTX memory model (a relaxed load that polls a location
+// written by a relaxed store of another CTA is not a data race), served by L2
+__device__ __forceinline__ float ld_strong(const float *p) {
+    float v;
+    asm volatile("ld.relaxed.gpu.global.f32 %0, [%1];" : "=f"(v) : "l"(p));
     return v;
 }
-__device__ __forceinline__ int ld_relaxed(const int *p) {
-    int v;
-    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p));
+__device__ __forceinline__ float4 ld_strong4(const float *p) {
+    float4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
     return v;
 }
-__device__ __forceinline__ void fence_acquire() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+__device__ __forceinline__ void st_strong(float *p, float v) {
+    asm volatile("st.relaxed.gpu.global.f32 [%0], %1;" ::"l"(p), "f"(v));
+}
+__device__ __forceinline__ void st_strong4(float *p, float4 v) {
+    asm volatile("st.relaxed.gpu.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w));
+}
+__device__ __forceinline__ bool pending(float v) { return __float_as_uint(v) == PENDING; }
 
-// Wait until the N items behind flags[idx[k]] (idx < 0: nothing to wait for) have all published.  The flags are polled
-// together with relaxed loads (they pipeline; an acquire load per flag would cost one L2 round trip EACH) and one fence
-// afterwards makes it an acquire.  Every item waits only for items with smaller tickets, which are running, so this
-// ends; the bound (about a second) turns corrupted sync words into a counted error instead of a hang.
-template <int N>
-__device__ __forceinline__ void wait_flags(const int *flags, int (&idx)[N], int *sync) {
+// Spin control: every item waits only for items with smaller tickets, which are running, so a wait ends; the bound
+// (about a second) turns a corrupted buffer into a counted error instead of a hang.
+struct Spin {
     long long t0 = 0;
-    while (true) {
-        int got[N];
-#pragma unroll
-        for (int k = 0; k < N; ++k) got[k] = idx[k] >= 0 ? ld_relaxed(flags + idx[k]) : 1;
-        bool all = true;
-#pragma unroll
-        for (int k = 0; k < N; ++k) {
-            if (got[k] != 0) idx[k] = -1;
-            else all = false;
-        }
-        if (all) break;
+    __device__ __forceinline__ bool again(int *sync) {
         __nanosleep(20);
-        if (t0 == 0) t0 = clock64();
-        else if (clock64() - t0 > 2000000000ll) {
-            atomicAdd(sync + 1, 1);
-            break;
-        }
+        if (t0 == 0) { t0 = clock64(); return true; }
+        if (clock64() - t0 > 2000000000ll) { atomicAdd(sync + 1, 1); return false; }
+        return true;
     }
-    fence_acquire();
-}
+};
 
 template <typename T>
 __device__ __forceinline__ void load4(const T *base, int q, int V, bool vec, T (&v)[PPT], T fill) {
@@ -105,18 +102,14 @@ __device__ __forceinline__ void load4(const T *base, int q, int V, bool vec, T (
         for (int j = 0; j < PPT; ++j) v[j] = (q + j < V) ? base[q + j] : fill;
     }
 }
-// same, for data another CTA of this launch has written: read at L2
-__device__ __forceinline__ void load4_cg(const float *base, int q, int V, bool vec, float (&v)[PPT]) {
-    if (vec) {
-        if (q < V) {
-            const float4 t = __ldcg(reinterpret_cast<const float4 *>(base + q));
-            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-        } else {
-            v[0] = v[1] = v[2] = v[3] = 0.f;
-        }
+// intermediate results: strong stores (other CTAs of this launch poll them)
+__device__ __forceinline__ void store4_strong(float *base, int q, bool vec, const float (&v)[PPT], const bool (&ok)[PPT]) {
+    if (vec && ok[0] && ok[1] && ok[2] && ok[3]) {
+        st_strong4(base + q, make_float4(v[0], v[1], v[2], v[3]));
     } else {
 #pragma unroll
-        for (int j = 0; j < PPT; ++j) v[j] = (q + j < V) ? __ldcg(base + q + j) : 0.f;
+        for (int j = 0; j < PPT; ++j)
+            if (ok[j]) st_strong(base + q + j, v[j]);
     }
 }
 __device__ __forceinline__ void store4(float *base, int q, bool vec, const float (&v)[PPT], const bool (&ok)[PPT]) {
@@ -134,7 +127,7 @@ struct Item {
 };
 
 // FEDICRA_PROF=1: %globaltimer stamps of every item of the first images (claimed, inputs loaded, dependencies met,
-// published) -- read back with fedicra_debug_chain_profile
+// results stored) -- read back with fedicra_debug_chain_profile
 constexpr int PROF_B = 2, PROF_K = 768;
 __device__ long long g_chain_prof[2 * PROF_B * PROF_K * 4];
 __device__ __forceinline__ long long globaltimer() {
@@ -147,35 +140,44 @@ __device__ __forceinline__ void stamp(const ChainArgs &a, int phase, const Item 
         g_chain_prof[((phase * PROF_B + it.b) * PROF_K + it.id) * 4 + slot] = globaltimer();
 }
 
-// all threads' results are in global memory -> one release store of the item's flag
-__device__ __forceinline__ void publish(int *flag) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        st_release(flag, 1);
+// NC self-validating words p[0], p[stride], ...: re-read until all of them have arrived
+template <int NC>
+__device__ __forceinline__ void poll_words(const float *p, size_t stride, float (&v)[NC], int *sync) {
+    Spin spin;
+    while (true) {
+        bool all = true;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            v[c] = ld_strong(p + c * stride);
+            all = all && !pending(v[c]);
+        }
+        if (all || !spin.again(sync)) return;
     }
 }
 
 template <int MODE, int NC>
-__device__ __forceinline__ void up_item(const ChainArgs &a, const Item &it, const int *s_gs, const int *s_cum,
-                                        float (*s_agg)[NC + 1]) {
+__device__ __forceinline__ void up_item(const ChainArgs &a, const Item &it, float (*s_agg)[NC + 1]) {
     constexpr int C = NC - 1;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = a.V, b = it.b;
     const bool vec = a.vec != 0;
     const size_t ob = (size_t)b * V;
     const int q0 = it.T * TILE + tid * PPT;
-    const int *flags_up = a.sync + SYNC_HEAD + (size_t)b * a.Kmax;
+    float *upb = a.up + (size_t)b * NC * V;
     bool ok[PPT];
     int vt[PPT];
 #pragma unroll
     for (int j = 0; j < PPT; ++j) ok[j] = q0 + j >= it.lo && q0 + j < it.hi;
     load4(a.vtx + ob, q0, V, vec, vt, 0);
     float av[PPT], bq[PPT][NC];
-    int4 ch[PPT];
+    int lc[PPT][3];
+    float wl[PPT][3];
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
-        ch[j] = ok[j] ? a.child[ob + q0 + j] : make_int4(0, 0, 0, 0);
-        av[j] = ok[j] ? ((ch[j].x != 0) ? a.w[ob + q0 + j + 1] : 0.f) : 1.f;   // outside the item: identity map
+        const int4 ch = ok[j] ? a.child[ob + q0 + j] : make_int4(0, 0, 0, 0);
+        lc[j][0] = ch.y; lc[j][1] = ch.z; lc[j][2] = ch.w;
+        av[j] = ok[j] ? ((ch.x != 0) ? a.w[ob + q0 + j + 1] : 0.f) : 1.f;   // outside the item: identity map
+#pragma unroll
+        for (int s = 0; s < 3; ++s) wl[j][s] = lc[j][s] > 0 ? a.w[ob + lc[j][s]] : 0.f;
         if (!ok[j]) {
 #pragma unroll
             for (int c = 0; c < NC; ++c) bq[j][c] = 0.f;
@@ -195,41 +197,43 @@ __device__ __forceinline__ void up_item(const ChainArgs &a, const Item &it, cons
             bq[j][C] = s;
         }
     }
-    // light children live in the next group; a chain that runs on into the next tile of this group hands its value in.
-    // Everything this item depends on is waited for at once, then fetched at once.
-    const int next_base = s_cum[it.r + 1] - s_gs[it.r + 1] / TILE;
     const bool cross = it.hi == (it.T + 1) * TILE && it.hi < it.ge && a.child[ob + it.hi - 1].x != 0;
-    int lc[PPT][3], need[PPT * 3 + 1];
-    float wl[PPT][3];
-#pragma unroll
-    for (int j = 0; j < PPT; ++j) {
-        lc[j][0] = ch[j].y; lc[j][1] = ch[j].z; lc[j][2] = ch[j].w;
-#pragma unroll
-        for (int s = 0; s < 3; ++s) {
-            need[j * 3 + s] = lc[j][s] > 0 ? next_base + lc[j][s] / TILE : -1;
-            wl[j][s] = lc[j][s] > 0 ? a.w[ob + lc[j][s]] : 0.f;
-        }
-    }
-    need[PPT * 3] = -1;
     stamp(a, 0, it, 1);
-    wait_flags(flags_up, need, a.sync);
-    stamp(a, 0, it, 2);
+    // light children (chain tops of the next group): re-read their values until all have arrived, then add w_c x_c in
+    // a fixed order.  Two child slots cover every vertex but a root with four neighbours; the third is a rare path.
     {
-        float xv[PPT][3][NC];
+        float xv[PPT][2][NC];
+        Spin spin;
+        while (true) {
+            bool all = true;
+#pragma unroll
+            for (int j = 0; j < PPT; ++j)
+#pragma unroll
+                for (int s = 0; s < 2; ++s)
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) {
+                        xv[j][s][c] = lc[j][s] > 0 ? ld_strong(upb + (size_t)c * V + lc[j][s]) : 0.f;
+                        all = all && !pending(xv[j][s][c]);
+                    }
+            if (all || !spin.again(a.sync)) break;
+        }
 #pragma unroll
         for (int j = 0; j < PPT; ++j)
 #pragma unroll
-            for (int s = 0; s < 3; ++s)
-#pragma unroll
-                for (int c = 0; c < NC; ++c)
-                    xv[j][s][c] = lc[j][s] > 0 ? __ldcg(a.up + ((size_t)b * NC + c) * V + lc[j][s]) : 0.f;
-#pragma unroll
-        for (int j = 0; j < PPT; ++j)
-#pragma unroll
-            for (int s = 0; s < 3; ++s)
+            for (int s = 0; s < 2; ++s)
 #pragma unroll
                 for (int c = 0; c < NC; ++c) bq[j][c] = fmaf(wl[j][s], xv[j][s][c], bq[j][c]);
     }
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        if (lc[j][2] > 0) {
+            float xv[NC];
+            poll_words<NC>(upb + lc[j][2], (size_t)V, xv, a.sync);
+#pragma unroll
+            for (int c = 0; c < NC; ++c) bq[j][c] = fmaf(wl[j][2], xv[c], bq[j][c]);
+        }
+    }
+    stamp(a, 0, it, 2);
     // this thread's four positions as one map x_{q0} = X + P x_{q0+4}
     float P = 1.f, X[NC];
 #pragma unroll
@@ -260,8 +264,7 @@ __device__ __forceinline__ void up_item(const ChainArgs &a, const Item &it, cons
     }
     __syncthreads();
     // The tile as one map: value at its first position = Xt + Pt * (value handed in at its end).  Pt is 0 unless one
-    // chain spans the whole tile, so the value the PREVIOUS tile of this group waits for is usually known right here,
-    // before this tile has heard from its own neighbour: tiles of a group do not queue up behind each other.
+    // chain spans the whole tile, so the value the PREVIOUS tile of this group waits for is usually known right here.
     float cw[NC], Pt = 1.f, Xt[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) Xt[c] = 0.f;
@@ -271,33 +274,22 @@ __device__ __forceinline__ void up_item(const ChainArgs &a, const Item &it, cons
         for (int c = 0; c < NC; ++c) Xt[c] = fmaf(Pw, Xt[c], s_agg[w2][c]);
         Pt *= Pw;
     }
-    int *head_flag = a.sync + SYNC_HEAD + (size_t)(2 * a.B + b) * a.Kmax + it.id;
     float *head_val = a.hand + ((size_t)b * a.Kmax + it.id) * 8;
     const bool early = Pt == 0.f || !cross;
     if (early && tid == 0) {
 #pragma unroll
-        for (int c = 0; c < NC; ++c) head_val[c] = Xt[c];
-        __threadfence();
-        st_release(head_flag, 1);
+        for (int c = 0; c < NC; ++c) st_strong(head_val + c, Xt[c]);
     }
+    // What flows into this lane's last position is base + coef * (value handed in at the tile's end); coef is 0 for
+    // every lane behind the first chain bottom, i.e. for most: those store at once, the others wait for the hand-over.
+    float coef = 1.f;
 #pragma unroll
     for (int c = 0; c < NC; ++c) cw[c] = 0.f;
-    if (cross) {
-        int nb[1] = {2 * a.B * a.Kmax + it.id + 1};   // the next tile's hand-over flag
-        wait_flags(flags_up, nb, a.sync);
-#pragma unroll
-        for (int c = 0; c < NC; ++c) cw[c] = __ldcg(head_val + 8 + c);
-        if (!early && tid == 0) {
-#pragma unroll
-            for (int c = 0; c < NC; ++c) head_val[c] = fmaf(Pt, cw[c], Xt[c]);
-            __threadfence();
-            st_release(head_flag, 1);
-        }
-    }
     for (int w2 = NW - 1; w2 > wid; --w2) {
         const float Pw = s_agg[w2][NC];
 #pragma unroll
         for (int c = 0; c < NC; ++c) cw[c] = fmaf(Pw, cw[c], s_agg[w2][c]);
+        coef *= Pw;
     }
     {
         const float Pn = __shfl_down_sync(0xffffffffu, P, 1);
@@ -306,33 +298,46 @@ __device__ __forceinline__ void up_item(const ChainArgs &a, const Item &it, cons
             const float Xn = __shfl_down_sync(0xffffffffu, X[c], 1);
             if (lane < 31) cw[c] = fmaf(Pn, cw[c], Xn);
         }
+        if (lane < 31) coef *= Pn;
     }
-    float res[NC][PPT];
+    auto finish = [&](float (&x)[NC]) {
+        float res[NC][PPT];
 #pragma unroll
-    for (int j = PPT - 1; j >= 0; --j) {
+        for (int j = PPT - 1; j >= 0; --j) {
 #pragma unroll
-        for (int c = 0; c < NC; ++c) {
-            cw[c] = fmaf(av[j], cw[c], bq[j][c]);
-            res[c][j] = cw[c];
+            for (int c = 0; c < NC; ++c) {
+                x[c] = fmaf(av[j], x[c], bq[j][c]);
+                res[c][j] = x[c];
+            }
         }
-    }
 #pragma unroll
-    for (int c = 0; c < NC; ++c) store4(a.up + ((size_t)b * NC + c) * V, q0, vec, res[c], ok);
-    publish(a.sync + SYNC_HEAD + (size_t)b * a.Kmax + it.id);
+        for (int c = 0; c < NC; ++c) store4_strong(upb + (size_t)c * V, q0, vec, res[c], ok);
+    };
+    const bool waits = cross && coef != 0.f;
+    if (!waits) finish(cw);
+    if (waits) {
+        float tc[NC];
+        poll_words<NC>(head_val + 8, 1, tc, a.sync);      // from the next tile of this group
+        if (!early && tid == 0) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) st_strong(head_val + c, fmaf(Pt, tc[c], Xt[c]));
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c) cw[c] = fmaf(coef, tc[c], cw[c]);
+        finish(cw);
+    }
     stamp(a, 0, it, 3);
 }
 
 template <int MODE, int NC>
-__device__ __forceinline__ void down_item(const ChainArgs &a, const Item &it, const int *s_gs, const int *s_cum,
-                                          float (*s_agg)[NC + 1]) {
+__device__ __forceinline__ void down_item(const ChainArgs &a, const Item &it, float (*s_agg)[NC + 1]) {
     constexpr int C = NC - 1;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = a.V, b = it.b;
     const bool vec = a.vec != 0;
     const size_t ob = (size_t)b * V;
     const int q0 = it.T * TILE + tid * PPT;
-    const int *flags_up = a.sync + SYNC_HEAD + (size_t)b * a.Kmax;
-    const int *flags_dn = a.sync + SYNC_HEAD + (size_t)(a.B + b) * a.Kmax;
-    bool ok[PPT], top[PPT];
+    float *upb = a.up + (size_t)b * NC * V, *aggb = a.agg + (size_t)b * NC * V;
+    bool ok[PPT], top[PPT], far[PPT];
     int vt[PPT], pr[PPT];
     float wq[PPT];
 #pragma unroll
@@ -344,35 +349,41 @@ __device__ __forceinline__ void down_item(const ChainArgs &a, const Item &it, co
     for (int j = 0; j < PPT; ++j) {
         if (q0 + j == 0) wq[j] = 0.f;                          // the root has no parent edge (refine.cu:43-46)
         top[j] = q0 + j == 0 || pr[j] != q0 + j - 1;
+        far[j] = ok[j] && top[j] && q0 + j != 0;               // its parent sits in the previous group
     }
     if (it.lo == 0 && tid == 0) a.w[ob] = 0.f;                 // and the reference says so in place
-    // waits: this tile's leaf->root values, the parents of chain tops (previous group), the previous tile of a chain
-    // that started there
-    const int prev_base = it.r > 0 ? s_cum[it.r - 1] - s_gs[it.r - 1] / TILE : 0;
     const bool cross = it.lo == it.T * TILE && it.lo > it.gs && a.par[ob + it.lo] == it.lo - 1;
-    bool far[PPT];
+    stamp(a, 1, it, 1);
+    // this tile's leaf->root values and the root->leaf values of the parents of chain tops: re-read until all arrived
+    float u[NC][PPT], cq[PPT][NC];
     {
-        int need[PPT + 1];
+        Spin spin;
+        while (true) {
+            bool all = true;
+            if (vec) {
 #pragma unroll
-        for (int j = 0; j < PPT; ++j) {
-            far[j] = ok[j] && top[j] && q0 + j != 0;
-            need[j] = far[j] ? a.B * a.Kmax + prev_base + pr[j] / TILE : -1;   // flags_dn = flags_up + B Kmax
+                for (int c = 0; c < NC; ++c) {
+                    const float4 t = q0 < V ? ld_strong4(upb + (size_t)c * V + q0) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    u[c][0] = t.x; u[c][1] = t.y; u[c][2] = t.z; u[c][3] = t.w;
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < NC; ++c)
+#pragma unroll
+                    for (int j = 0; j < PPT; ++j) u[c][j] = ok[j] ? ld_strong(upb + (size_t)c * V + q0 + j) : 0.f;
+            }
+#pragma unroll
+            for (int j = 0; j < PPT; ++j)
+#pragma unroll
+                for (int c = 0; c < NC; ++c) {
+                    cq[j][c] = far[j] ? ld_strong(aggb + (size_t)c * V + pr[j]) : 0.f;
+                    all = all && !pending(cq[j][c]) && !(ok[j] && pending(u[c][j]));
+                }
+            if (all || !spin.again(a.sync)) break;
         }
-        need[PPT] = -1;
-        int mine[1] = {it.id};
-        stamp(a, 1, it, 1);
-        wait_flags(flags_up, mine, a.sync);
-        wait_flags(flags_up, need, a.sync);
-        stamp(a, 1, it, 2);
     }
-    float u[NC][PPT];
-#pragma unroll
-    for (int c = 0; c < NC; ++c) load4_cg(a.up + ((size_t)b * NC + c) * V, q0, V, vec, u[c]);
-    float av[PPT], cq[PPT][NC];
-#pragma unroll
-    for (int j = 0; j < PPT; ++j)
-#pragma unroll
-        for (int c = 0; c < NC; ++c) cq[j][c] = far[j] ? __ldcg(a.agg + ((size_t)b * NC + c) * V + pr[j]) : 0.f;
+    stamp(a, 1, it, 2);
+    float av[PPT];
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
         const float w = wq[j], k = 1.f - w * w;
@@ -417,33 +428,20 @@ __device__ __forceinline__ void down_item(const ChainArgs &a, const Item &it, co
         for (int c = 0; c < NC; ++c) Xt[c] = fmaf(Pw, Xt[c], s_agg[w2][c]);
         Pt *= Pw;
     }
-    int *tail_flag = a.sync + SYNC_HEAD + (size_t)(3 * a.B + b) * a.Kmax + it.id;
     float *tail_val = a.hand + ((size_t)(a.B + b) * a.Kmax + it.id) * 8;
     const bool early = Pt == 0.f || !cross;
     if (early && tid == 0) {
 #pragma unroll
-        for (int c = 0; c < NC; ++c) tail_val[c] = Xt[c];
-        __threadfence();
-        st_release(tail_flag, 1);
+        for (int c = 0; c < NC; ++c) st_strong(tail_val + c, Xt[c]);
     }
+    float coef = 1.f;
 #pragma unroll
     for (int c = 0; c < NC; ++c) cw[c] = 0.f;
-    if (cross) {
-        int nb[1] = {3 * a.B * a.Kmax + it.id - 1};   // the previous tile's hand-over flag
-        wait_flags(flags_up, nb, a.sync);
-#pragma unroll
-        for (int c = 0; c < NC; ++c) cw[c] = __ldcg(tail_val - 8 + c);
-        if (!early && tid == 0) {
-#pragma unroll
-            for (int c = 0; c < NC; ++c) tail_val[c] = fmaf(Pt, cw[c], Xt[c]);
-            __threadfence();
-            st_release(tail_flag, 1);
-        }
-    }
     for (int w2 = 0; w2 < wid; ++w2) {
         const float Pw = s_agg[w2][NC];
 #pragma unroll
         for (int c = 0; c < NC; ++c) cw[c] = fmaf(Pw, cw[c], s_agg[w2][c]);
+        coef *= Pw;
     }
     {
         const float Pn = __shfl_up_sync(0xffffffffu, P, 1);
@@ -452,21 +450,36 @@ __device__ __forceinline__ void down_item(const ChainArgs &a, const Item &it, co
             const float Xn = __shfl_up_sync(0xffffffffu, X[c], 1);
             if (lane > 0) cw[c] = fmaf(Pn, cw[c], Xn);
         }
+        if (lane > 0) coef *= Pn;
     }
     float res[NC][PPT], cw0[NC];
+    auto finish = [&](float (&x)[NC]) {
 #pragma unroll
-    for (int c = 0; c < NC; ++c) cw0[c] = cw[c];
+        for (int c = 0; c < NC; ++c) cw0[c] = x[c];
 #pragma unroll
-    for (int j = 0; j < PPT; ++j) {
+        for (int j = 0; j < PPT; ++j) {
 #pragma unroll
-        for (int c = 0; c < NC; ++c) {
-            cw[c] = fmaf(av[j], cw[c], cq[j][c]);
-            res[c][j] = cw[c];
+            for (int c = 0; c < NC; ++c) {
+                x[c] = fmaf(av[j], x[c], cq[j][c]);
+                res[c][j] = x[c];
+            }
         }
-    }
 #pragma unroll
-    for (int c = 0; c < NC; ++c) store4(a.agg + ((size_t)b * NC + c) * V, q0, vec, res[c], ok);
-    publish(a.sync + SYNC_HEAD + (size_t)(a.B + b) * a.Kmax + it.id);
+        for (int c = 0; c < NC; ++c) store4_strong(aggb + (size_t)c * V, q0, vec, res[c], ok);
+    };
+    const bool waits = cross && coef != 0.f;
+    if (!waits) finish(cw);
+    if (waits) {
+        float tc[NC];
+        poll_words<NC>(tail_val - 8, 1, tc, a.sync);       // from the previous tile of this group
+        if (!early && tid == NW * 32 - 1) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) st_strong(tail_val + c, fmaf(Pt, tc[c], Xt[c]));
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c) cw[c] = fmaf(coef, tc[c], cw[c]);
+        finish(cw);
+    }
     stamp(a, 1, it, 3);
     // nobody inside this launch waits for what follows
     if (MODE == 1 && a.gw != nullptr) {
@@ -480,7 +493,7 @@ __device__ __forceinline__ void down_item(const ChainArgs &a, const Item &it, co
                 const float w = wq[j];
 #pragma unroll
                 for (int c = 0; c < NC; ++c) {
-                    const float gpar = top[j] ? __ldcg(a.agg + ((size_t)b * NC + c) * V + pr[j]) : (j > 0 ? res[c][j > 0 ? j - 1 : 0] : cw0[c]);
+                    const float gpar = top[j] ? ld_strong(aggb + (size_t)c * V + pr[j]) : (j > 0 ? res[c][j > 0 ? j - 1 : 0] : cw0[c]);
                     const float upf = a.up_f[((size_t)b * NC + c) * V + q0 + j];
                     const float apar = a.agg_f[((size_t)b * NC + c) * V + pr[j]];
                     const float t = u[c][j] * (apar - w * upf) + upf * (gpar - w * u[c][j]);
@@ -513,7 +526,7 @@ __global__ void __launch_bounds__(CT) chain_filter_kernel(ChainArgs a) {
     const int per_phase = a.B * a.Kmax;
     while (true) {
         __syncthreads();
-        if (tid == 0) s_ticket = atomicAdd(a.sync, 1);
+        if (tid == 0) s_ticket = atomicAdd(a.sync, 1) + 1;     // the counter starts at -1
         __syncthreads();
         const int t = s_ticket;
         if (t >= 2 * per_phase) break;
@@ -546,15 +559,15 @@ __global__ void __launch_bounds__(CT) chain_filter_kernel(ChainArgs a) {
         it.lo = max(it.gs, it.T * TILE);
         it.hi = min(it.ge, (it.T + 1) * TILE);
         stamp(a, phase, it, 0);
-        if (phase == 0) up_item<MODE, NC>(a, it, s_gs, s_cum, s_agg);
-        else down_item<MODE, NC>(a, it, s_gs, s_cum, s_agg);
+        if (phase == 0) up_item<MODE, NC>(a, it, s_agg);
+        else down_item<MODE, NC>(a, it, s_agg);
     }
 }
 
 int items_bound(int V) { return (V + TILE - 1) / TILE + 33; }
 
-size_t flag_bytes(int B, int V) { return align_up((size_t)(SYNC_HEAD + 4 * (size_t)B * items_bound(V)) * sizeof(int), 256); }
-size_t sync_bytes(int B, int V) { return flag_bytes(B, V) + align_up((size_t)2 * B * items_bound(V) * 8 * sizeof(float), 256); }
+// counters + hand-over values: everything that must read "all bits set" when the kernel starts
+size_t sync_bytes(int B, int V) { return align_up((size_t)(SYNC_HEAD + 2 * (size_t)B * items_bound(V) * 8) * sizeof(int), 256); }
 
 template <int MODE, int NC>
 int launch(const ChainArgs &a, cudaStream_t st) {
@@ -620,11 +633,12 @@ extern "C" int fedicra_chain_filter_forward(const float *feature_in, float *edge
     a.vtx = sorted_index; a.par = sorted_parent; a.child = reinterpret_cast<const int4 *>(sorted_child);
     a.gstart = group_start; a.w = edge_weight; a.src = feature_in;
     a.up = (float *)saved; a.agg = a.up + (size_t)B * (C + 1) * V;
-    a.out = feature_out; a.sync = (int *)workspace;
+    a.out = feature_out; a.sync = (int *)workspace; a.hand = (float *)workspace + SYNC_HEAD;
     a.B = B; a.V = V; a.Kmax = items_bound(V); a.prof = prof_enabled();
     a.vec = (V % 4 == 0) && aligned16(sorted_index) && aligned16(sorted_parent) && aligned16(edge_weight) && aligned16(saved);
-    a.hand = (float *)((char *)workspace + flag_bytes(B, V));
-    cudaError_t e = cudaMemsetAsync(a.sync, 0, flag_bytes(B, V), st);
+    // every intermediate word starts as "pending" (all bits set): counters, hand-over values, and both saved arrays
+    cudaError_t e = cudaMemsetAsync(workspace, 0xff, sync_bytes(B, V), st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(saved, 0xff, fedicra_chain_filter_saved_bytes(B, C, V), st);
     if (e != cudaSuccess) return fedicra_fail(-2, "chain_filter_forward: memset: %s", cudaGetErrorString(e));
     return dispatch<0>(a, C, st);
 }
@@ -643,20 +657,20 @@ extern "C" int fedicra_chain_filter_backward(const float *grad_out, float *edge_
     a.vtx = sorted_index; a.par = sorted_parent; a.child = reinterpret_cast<const int4 *>(sorted_child);
     a.gstart = group_start; a.w = edge_weight; a.src = grad_out;
     a.up_f = (const float *)saved; a.agg_f = a.up_f + (size_t)B * (C + 1) * V;
-    a.sync = (int *)workspace;
+    a.sync = (int *)workspace; a.hand = (float *)workspace + SYNC_HEAD;
     a.up = (float *)((char *)workspace + sync_bytes(B, V)); a.agg = a.up + (size_t)B * (C + 1) * V;
     a.out = grad_feature; a.gw = grad_weight;
     a.B = B; a.V = V; a.Kmax = items_bound(V); a.prof = prof_enabled();
     a.vec = (V % 4 == 0) && aligned16(sorted_index) && aligned16(sorted_parent) && aligned16(edge_weight) &&
             aligned16(saved) && aligned16(a.up) && (grad_weight == nullptr || aligned16(grad_weight));
-    a.hand = (float *)((char *)workspace + flag_bytes(B, V));
-    cudaError_t e = cudaMemsetAsync(a.sync, 0, flag_bytes(B, V), st);
+    // counters, hand-over values and both scratch arrays are one range: one memset marks them all "pending"
+    cudaError_t e = cudaMemsetAsync(workspace, 0xff, fedicra_chain_filter_workspace_bytes(B, C, V), st);
     if (e != cudaSuccess) return fedicra_fail(-2, "chain_filter_backward: memset: %s", cudaGetErrorString(e));
     return dispatch<1>(a, C, st);
 }
 
 /* Debug: %globaltimer stamps of the last profiled chain-filter launch (FEDICRA_PROF=1), [2 phases][2 images][768 items][4]:
- * claimed, inputs loaded, dependencies met, published.  Synchronises the device. */
+ * claimed, inputs loaded, dependencies met, results stored.  Synchronises the device. */
 extern "C" int fedicra_debug_chain_profile(long long *h_out, int n) {
     const int total = 2 * PROF_B * PROF_K * 4;
     if (!h_out || n < total) return fedicra_fail(-1, "debug_chain_profile: need room for %d values", total);

@@ -6,6 +6,8 @@ kernels of libfedicra_sm100.so.
 is computed once per tree and remembered on that tensor object, so the four filters of the multiscale loss do not
 re-derive it.
 """
+import os
+
 import torch
 from torch import nn
 
@@ -13,40 +15,80 @@ from . import ops
 
 
 def _is_norm2(fn):
-    return fn is None or getattr(fn, "__name__", "") == "norm2_distance"
+    """True when `fn` is this module's squared-L2 distance (or absent): only then may the fused weight + MST and
+    edge-weight kernels stand in for it.  Identity, not name: a user function that happens to be called
+    norm2_distance takes the generic path."""
+    return fn is None or fn is TreeFilter2D.norm2_distance
+
+
+class _Arrays:
+    """One valid ordering of a batch of rooted trees in the reference's format (sorted_index, sorted_parent,
+    sorted_child; bfs.cu:46-98) plus what this library's filter kernels need on top of it:
+      kind "chain": group_start (heavy-chain order, csrc/chains.cu);  kind "bfs": level_start, n_levels, band plan."""
+
+    __slots__ = ("kind", "si", "sp", "sc", "gs", "ls", "nl", "bands")
+
+    def __init__(self, kind, si, sp, sc, gs=None, ls=None, nl=None, bands=None):
+        self.kind, self.si, self.sp, self.sc, self.gs, self.ls, self.nl, self.bands = kind, si, sp, sc, gs, ls, nl, bands
+
+
+def _want_chain(V):
+    """The scan-based chain filter is the default; FEDICRA_FILTER=resident|multi selects the depth-banded one."""
+    return os.environ.get("FEDICRA_FILTER", "chain") == "chain" and V <= ops.CHAIN_MAX_V
 
 
 class _TreeOrder:
-    """BFS arrays of a batch of trees (sorted_index, sorted_parent, sorted_child, level_start, n_levels)."""
+    """Topology record of a batch of trees: the adjacency mask (or edge list) and, built on first use, the orderings the
+    filters run on.  `for_channels(C)` picks the one the filter for C feature channels takes."""
 
-    __slots__ = ("si", "sp", "sc", "ls", "nl", "bands")
+    def __init__(self, tree=None, mask=None, hw=None, chain=None, bfs=None):
+        self.tree, self.mask, self.hw = tree, mask, hw
+        if tree is not None and mask is None:
+            self.mask, self.hw = getattr(tree, "_fedicra_mask", None), getattr(tree, "_fedicra_hw", None)
+        self._chain, self._bfs = chain, bfs
 
-    def __init__(self, tree=None, arrays=None):
-        if arrays is not None:
-            self.si, self.sp, self.sc, self.ls, self.nl, self.bands = arrays
-            return
-        mask, hw = getattr(tree, "_fedicra_mask", None), getattr(tree, "_fedicra_hw", None)
-        arrays = ops.bfs_from_mask(mask, *hw, root=ops.default_root(*hw)) if mask is not None else None
-        self.si, self.sp, self.sc, self.ls, self.nl = arrays if arrays is not None else ops.bfs_forward(tree)
-        self.bands = ops.band_plan(self.ls, self.nl)
+    def chain(self):
+        if self._chain is None:
+            self._chain = _Arrays("chain", *ops.chain_order(self.mask, *self.hw))
+        return self._chain
+
+    def bfs(self):
+        if self._bfs is None:
+            arrays = ops.bfs_from_mask(self.mask, *self.hw, root=ops.default_root(*self.hw)) if self.mask is not None else None
+            si, sp, sc, ls, nl = arrays if arrays is not None else ops.bfs_forward(self.tree)
+            self._bfs = _Arrays("bfs", si, sp, sc, ls=ls, nl=nl, bands=ops.band_plan(ls, nl))
+        return self._bfs
+
+    def for_channels(self, C):
+        if self.mask is not None and C <= ops.CHAIN_MAX_C and _want_chain(self.hw[0] * self.hw[1]):
+            return self.chain()
+        return self.bfs()
 
 
 def batched_tree_orders(embeds):
-    """MST + BFS of several embeddings of one batch in ONE pass: the embeddings ([B,D_k,H,W], same B/H/W) are stacked
-    along the batch axis -- by a pointer table, not by a copy -- so that each kernel of the topology stage is launched
-    once for all of them.  Returns one _TreeOrder per embedding."""
+    """MST + ordering of several embeddings of one batch in ONE pass: the embeddings ([B,D_k,H,W], same B/H/W) are
+    stacked along the batch axis -- by a pointer table, not by a copy -- so that each kernel of the topology stage is
+    launched once for all of them.  Returns one _TreeOrder per embedding."""
     B, _, H, W = embeds[0].shape
+    K = len(embeds)
     with torch.no_grad():
         fits = H * W <= max(ops.BFS_GRID_MAX_V, ops.BFS_EULER_MAX_V)
-        if len(embeds) <= 8:   # one launch straight from the K tensors (pointer table), nothing stacked
+        if K <= 8:   # one launch straight from the K tensors (pointer table), nothing stacked
             tree, mask = ops.mst_grid_multi([e.detach().float() for e in embeds], want_mask=True, want_edges=not fits)
         else:
             D = max(e.shape[1] for e in embeds)
             stacked = torch.cat([torch.nn.functional.pad(e.detach().float(), (0, 0, 0, 0, 0, D - e.shape[1])) for e in embeds], 0)
-            tree, mask = ops.mst_grid(stacked, want_mask=True, want_edges=not fits)  # the mask alone feeds the grid BFS
-        arrays = ops.bfs_from_mask(mask, H, W, root=ops.default_root(H, W)) if fits else ops.bfs_forward(tree)
-        bands = ops.band_plan(arrays[3], arrays[4]).view(len(embeds) * B, -1)
-    return [_TreeOrder(arrays=tuple(a[k * B:(k + 1) * B] for a in (*arrays, bands))) for k in range(len(embeds))]
+            tree, mask = ops.mst_grid(stacked, want_mask=True, want_edges=not fits)  # the mask alone feeds the ordering
+        cut = lambda a, k: a[k * B:(k + 1) * B]
+        if _want_chain(H * W):
+            arrays = ops.chain_order(mask, H, W)
+            return [_TreeOrder(mask=cut(mask, k), hw=(H, W), chain=_Arrays("chain", *(cut(a, k) for a in arrays)))
+                    for k in range(K)]
+        si, sp, sc, ls, nl = ops.bfs_from_mask(mask, H, W, root=ops.default_root(H, W)) if fits else ops.bfs_forward(tree)
+        bands = ops.band_plan(ls, nl).view(K * B, -1)
+    return [_TreeOrder(tree=None if tree is None else cut(tree, k), mask=cut(mask, k), hw=(H, W),
+                       bfs=_Arrays("bfs", cut(si, k), cut(sp, k), cut(sc, k), ls=cut(ls, k), nl=cut(nl, k),
+                                   bands=cut(bands, k))) for k in range(K)]
 
 
 def tree_order(tree):
@@ -115,13 +157,17 @@ class _EdgeWeight(torch.autograd.Function):
 
 
 class _Refine(torch.autograd.Function):
-    """Two-pass tree filter (depth-banded kernels, csrc/bands.cu); same gradient policy as functions/refine.py:23-40
-    (weight gradient for the high-level trees only, and only when the edge weights need one)."""
+    """Two-pass tree filter (affine scans along heavy chains, csrc/chains.cu; or the depth-banded kernels,
+    csrc/bands.cu); same gradient policy as functions/refine.py:23-40 (weight gradient for the high-level trees only,
+    and only when the edge weights need one)."""
 
     @staticmethod
     def forward(ctx, feature_in, edge_weight, order, low_tree):
-        out, saved = ops.tree_filter_forward(feature_in, edge_weight, order.si, order.sp, order.sc, order.ls, order.nl,
-                                             order.bands)
+        if order.kind == "chain":
+            out, saved = ops.chain_filter_forward(feature_in, edge_weight, order.si, order.sp, order.sc, order.gs)
+        else:
+            out, saved = ops.tree_filter_forward(feature_in, edge_weight, order.si, order.sp, order.sc, order.ls,
+                                                 order.nl, order.bands)
         ctx.order, ctx.low_tree = order, low_tree
         ctx.save_for_backward(edge_weight, saved)
         return out
@@ -131,8 +177,12 @@ class _Refine(torch.autograd.Function):
         edge_weight, saved = ctx.saved_tensors
         o = ctx.order
         want_w = (not ctx.low_tree) and ctx.needs_input_grad[1]
-        grad_feature, grad_weight = ops.tree_filter_backward(grad_out.contiguous(), edge_weight, o.si, o.sp, o.sc, o.ls,
-                                                             o.nl, o.bands, saved, want_w)
+        if o.kind == "chain":
+            grad_feature, grad_weight = ops.chain_filter_backward(grad_out.contiguous(), edge_weight, o.si, o.sp, o.sc,
+                                                                  o.gs, saved, want_w)
+        else:
+            grad_feature, grad_weight = ops.tree_filter_backward(grad_out.contiguous(), edge_weight, o.si, o.sp, o.sc,
+                                                                 o.ls, o.nl, o.bands, saved, want_w)
         return grad_feature, grad_weight, None, None
 
 
@@ -165,7 +215,7 @@ class TreeFilter2D(nn.Module):
         if self.groups != 1:
             raise NotImplementedError("fedicra_b200 TreeFilter2D: groups != 1 is not implemented (FedICRA uses 1)")
         ori_shape = feature_in.shape
-        order = tree_order(tree)
+        order = tree_order(tree).for_channels(ori_shape[1])
         edge_weight = self.build_edge_weight(embed_in, order, low_tree)
         self.enable_log = False
         feature = feature_in.reshape(ori_shape[0], ori_shape[1], -1).float()
