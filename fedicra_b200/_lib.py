@@ -54,8 +54,8 @@ SIGNATURES = {
     "fedicra_chain_filter_max_channels": (c_int, []),
     "fedicra_chain_filter_saved_bytes": (c_size_t, [c_int, c_int, c_int]),
     "fedicra_chain_filter_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
-    "fedicra_chain_filter_forward": (c_int, [c_void_p] * 6 + [c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p,
-                                                               c_size_t, c_void_p]),
+    "fedicra_chain_filter_saved_offset": (c_size_t, [c_int, c_int, c_int]),
+    "fedicra_chain_filter_forward": (c_int, [c_void_p] * 6 + [c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
     "fedicra_chain_filter_backward": (c_int, [c_void_p] * 6 + [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                                                 c_size_t, c_void_p]),
     "fedicra_edge_weight_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p]),

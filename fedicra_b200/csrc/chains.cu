@@ -74,6 +74,11 @@ __device__ __forceinline__ void st_strong4(float *p, float4 v) {
     asm volatile("st.relaxed.gpu.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w));
 }
 __device__ __forceinline__ bool pending(float v) { return __float_as_uint(v) == PENDING; }
+// The polling loads are volatile asm statements without a memory clobber, so the compiler may sink an ordinary load
+// whose value is first used after a polling loop to below that loop -- and its latency would then sit on the critical
+// path.  keep(x) pins the load that defines x ahead of the next volatile asm (no instruction is emitted).
+__device__ __forceinline__ void keep(float x) { asm volatile("" ::"f"(x)); }
+__device__ __forceinline__ void keep(int x) { asm volatile("" ::"r"(x)); }
 
 // Spin control: every item waits only for items with smaller tickets, which are running, so a wait ends; the bound
 // (about a second) turns a corrupted buffer into a counted error instead of a hang.
@@ -136,6 +141,8 @@ __device__ __forceinline__ long long globaltimer() {
     return t;
 }
 __device__ __forceinline__ void stamp(const ChainArgs &a, int phase, const Item &it, int slot) {
+    // thread 0 only: coarse, and the divergent branch perturbs the warp it sits in (sub-microsecond figures taken with
+    // FEDICRA_PROF=1 are upper bounds); with profiling off the branch is uniform and free
     if (a.prof && threadIdx.x == 0 && it.b < PROF_B && it.id < PROF_K)
         g_chain_prof[((phase * PROF_B + it.b) * PROF_K + it.id) * 4 + slot] = globaltimer();
 }
@@ -169,15 +176,14 @@ __device__ __forceinline__ void up_item(const ChainArgs &a, const Item &it, floa
     for (int j = 0; j < PPT; ++j) ok[j] = q0 + j >= it.lo && q0 + j < it.hi;
     load4(a.vtx + ob, q0, V, vec, vt, 0);
     float av[PPT], bq[PPT][NC];
-    int lc[PPT][3];
-    float wl[PPT][3];
+    int lc[PPT][2];          // first two light children; a third exists only below a root with four neighbours
+    bool more = false;
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
         const int4 ch = ok[j] ? a.child[ob + q0 + j] : make_int4(0, 0, 0, 0);
-        lc[j][0] = ch.y; lc[j][1] = ch.z; lc[j][2] = ch.w;
+        lc[j][0] = ch.y; lc[j][1] = ch.z;
+        more = more || ch.w > 0;
         av[j] = ok[j] ? ((ch.x != 0) ? a.w[ob + q0 + j + 1] : 0.f) : 1.f;   // outside the item: identity map
-#pragma unroll
-        for (int s = 0; s < 3; ++s) wl[j][s] = lc[j][s] > 0 ? a.w[ob + lc[j][s]] : 0.f;
         if (!ok[j]) {
 #pragma unroll
             for (int c = 0; c < NC; ++c) bq[j][c] = 0.f;
@@ -198,39 +204,56 @@ __device__ __forceinline__ void up_item(const ChainArgs &a, const Item &it, floa
         }
     }
     const bool cross = it.hi == (it.T + 1) * TILE && it.hi < it.ge && a.child[ob + it.hi - 1].x != 0;
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        keep(av[j]);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) keep(bq[j][c]);
+    }
+    keep((int)cross);
     stamp(a, 0, it, 1);
     // light children (chain tops of the next group): re-read their values until all have arrived, then add w_c x_c in
-    // a fixed order.  Two child slots cover every vertex but a root with four neighbours; the third is a rare path.
-    {
-        float xv[PPT][2][NC];
+    // a fixed order: slot by slot, the four positions of a slot together.
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+        bool any = false;
+#pragma unroll
+        for (int j = 0; j < PPT; ++j) any = any || lc[j][s] > 0;
+        if (s > 0 && !__any_sync(0xffffffffu, any)) break;
+        float wl[PPT], xv[PPT][NC];
+#pragma unroll
+        for (int j = 0; j < PPT; ++j) {
+            wl[j] = lc[j][s] > 0 ? a.w[ob + lc[j][s]] : 0.f;
+            keep(wl[j]);
+        }
         Spin spin;
         while (true) {
             bool all = true;
 #pragma unroll
             for (int j = 0; j < PPT; ++j)
 #pragma unroll
-                for (int s = 0; s < 2; ++s)
-#pragma unroll
-                    for (int c = 0; c < NC; ++c) {
-                        xv[j][s][c] = lc[j][s] > 0 ? ld_strong(upb + (size_t)c * V + lc[j][s]) : 0.f;
-                        all = all && !pending(xv[j][s][c]);
-                    }
+                for (int c = 0; c < NC; ++c) {
+                    xv[j][c] = lc[j][s] > 0 ? ld_strong(upb + (size_t)c * V + lc[j][s]) : 0.f;
+                    all = all && !pending(xv[j][c]);
+                }
             if (all || !spin.again(a.sync)) break;
         }
 #pragma unroll
         for (int j = 0; j < PPT; ++j)
 #pragma unroll
-            for (int s = 0; s < 2; ++s)
-#pragma unroll
-                for (int c = 0; c < NC; ++c) bq[j][c] = fmaf(wl[j][s], xv[j][s][c], bq[j][c]);
+            for (int c = 0; c < NC; ++c) bq[j][c] = fmaf(wl[j], xv[j][c], bq[j][c]);
     }
+    if (more) {
 #pragma unroll
-    for (int j = 0; j < PPT; ++j) {
-        if (lc[j][2] > 0) {
-            float xv[NC];
-            poll_words<NC>(upb + lc[j][2], (size_t)V, xv, a.sync);
+        for (int j = 0; j < PPT; ++j) {
+            const int l3 = ok[j] ? a.child[ob + q0 + j].w : 0;
+            if (l3 > 0) {
+                float xv[NC];
+                poll_words<NC>(upb + l3, (size_t)V, xv, a.sync);
+                const float wl = a.w[ob + l3];
 #pragma unroll
-            for (int c = 0; c < NC; ++c) bq[j][c] = fmaf(wl[j][2], xv[c], bq[j][c]);
+                for (int c = 0; c < NC; ++c) bq[j][c] = fmaf(wl, xv[c], bq[j][c]);
+            }
         }
     }
     stamp(a, 0, it, 2);
@@ -353,8 +376,15 @@ __device__ __forceinline__ void down_item(const ChainArgs &a, const Item &it, fl
     }
     if (it.lo == 0 && tid == 0) a.w[ob] = 0.f;                 // and the reference says so in place
     const bool cross = it.lo == it.T * TILE && it.lo > it.gs && a.par[ob + it.lo] == it.lo - 1;
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        keep(wq[j]);
+        keep(vt[j]);
+        keep(pr[j]);
+    }
+    keep((int)cross);
     stamp(a, 1, it, 1);
-    // this tile's leaf->root values and the root->leaf values of the parents of chain tops: re-read until all arrived
+    // this tile's leaf->root values (written long ago, as a rule) ...
     float u[NC][PPT], cq[PPT][NC];
     {
         Spin spin;
@@ -375,9 +405,21 @@ __device__ __forceinline__ void down_item(const ChainArgs &a, const Item &it, fl
 #pragma unroll
             for (int j = 0; j < PPT; ++j)
 #pragma unroll
+                for (int c = 0; c < NC; ++c) all = all && !(ok[j] && pending(u[c][j]));
+            if (all || !spin.again(a.sync)) break;
+        }
+    }
+    // ... and the root->leaf values of the parents of chain tops (previous group): re-read until all have arrived
+    {
+        Spin spin;
+        while (true) {
+            bool all = true;
+#pragma unroll
+            for (int j = 0; j < PPT; ++j)
+#pragma unroll
                 for (int c = 0; c < NC; ++c) {
                     cq[j][c] = far[j] ? ld_strong(aggb + (size_t)c * V + pr[j]) : 0.f;
-                    all = all && !pending(cq[j][c]) && !(ok[j] && pending(u[c][j]));
+                    all = all && !pending(cq[j][c]);
                 }
             if (all || !spin.again(a.sync)) break;
         }
@@ -608,9 +650,14 @@ int prof_enabled() {
 
 extern "C" int fedicra_chain_filter_max_channels(void) { return 4; }
 
+extern "C" size_t fedicra_chain_filter_saved_offset(int B, int C, int V) {
+    if (B <= 0 || C <= 0 || V <= 0) return 0;
+    return sync_bytes(B, V);
+}
+
 extern "C" size_t fedicra_chain_filter_saved_bytes(int B, int C, int V) {
     if (B <= 0 || C <= 0 || V <= 0) return 0;
-    return (size_t)2 * B * (C + 1) * V * sizeof(float);
+    return sync_bytes(B, V) + (size_t)2 * B * (C + 1) * V * sizeof(float);
 }
 
 extern "C" size_t fedicra_chain_filter_workspace_bytes(int B, int C, int V) {
@@ -621,24 +668,24 @@ extern "C" size_t fedicra_chain_filter_workspace_bytes(int B, int C, int V) {
 extern "C" int fedicra_chain_filter_forward(const float *feature_in, float *edge_weight, const int *sorted_index,
                                             const int *sorted_parent, const int *sorted_child, const int *group_start,
                                             int B, int C, int V, float *feature_out, void *saved, size_t saved_bytes,
-                                            void *workspace, size_t workspace_bytes, void *stream) {
+                                            void *stream) {
     FEDICRA_REQUIRE(feature_in && edge_weight && sorted_index && sorted_parent && sorted_child && group_start &&
-                        feature_out && saved && workspace, "chain_filter_forward: null pointer");
+                        feature_out && saved, "chain_filter_forward: null pointer");
     FEDICRA_REQUIRE(B > 0 && C >= 1 && C <= 4 && V >= 1, "chain_filter_forward: bad sizes B=%d C=%d V=%d (1..4 channels)", B, C, V);
     FEDICRA_REQUIRE(saved_bytes >= fedicra_chain_filter_saved_bytes(B, C, V), "chain_filter_forward: saved buffer too small");
-    FEDICRA_REQUIRE(workspace_bytes >= sync_bytes(B, V), "chain_filter_forward: workspace too small");
-    FEDICRA_REQUIRE(aligned16(sorted_child), "chain_filter_forward: sorted_child must be 16-byte aligned");
+    FEDICRA_REQUIRE(aligned16(sorted_child) && aligned16(saved), "chain_filter_forward: sorted_child and saved must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
     ChainArgs a{};
     a.vtx = sorted_index; a.par = sorted_parent; a.child = reinterpret_cast<const int4 *>(sorted_child);
     a.gstart = group_start; a.w = edge_weight; a.src = feature_in;
-    a.up = (float *)saved; a.agg = a.up + (size_t)B * (C + 1) * V;
-    a.out = feature_out; a.sync = (int *)workspace; a.hand = (float *)workspace + SYNC_HEAD;
+    a.sync = (int *)saved; a.hand = (float *)saved + SYNC_HEAD;
+    a.up = (float *)((char *)saved + sync_bytes(B, V)); a.agg = a.up + (size_t)B * (C + 1) * V;
+    a.out = feature_out;
     a.B = B; a.V = V; a.Kmax = items_bound(V); a.prof = prof_enabled();
-    a.vec = (V % 4 == 0) && aligned16(sorted_index) && aligned16(sorted_parent) && aligned16(edge_weight) && aligned16(saved);
-    // every intermediate word starts as "pending" (all bits set): counters, hand-over values, and both saved arrays
-    cudaError_t e = cudaMemsetAsync(workspace, 0xff, sync_bytes(B, V), st);
-    if (e == cudaSuccess) e = cudaMemsetAsync(saved, 0xff, fedicra_chain_filter_saved_bytes(B, C, V), st);
+    a.vec = (V % 4 == 0) && aligned16(sorted_index) && aligned16(sorted_parent) && aligned16(edge_weight);
+    // every intermediate word starts as "pending" (all bits set): the counters and hand-over values at the head of
+    // `saved`, and the two result arrays behind them -- one range, one memset
+    cudaError_t e = cudaMemsetAsync(saved, 0xff, fedicra_chain_filter_saved_bytes(B, C, V), st);
     if (e != cudaSuccess) return fedicra_fail(-2, "chain_filter_forward: memset: %s", cudaGetErrorString(e));
     return dispatch<0>(a, C, st);
 }
@@ -656,7 +703,7 @@ extern "C" int fedicra_chain_filter_backward(const float *grad_out, float *edge_
     ChainArgs a{};
     a.vtx = sorted_index; a.par = sorted_parent; a.child = reinterpret_cast<const int4 *>(sorted_child);
     a.gstart = group_start; a.w = edge_weight; a.src = grad_out;
-    a.up_f = (const float *)saved; a.agg_f = a.up_f + (size_t)B * (C + 1) * V;
+    a.up_f = (const float *)((const char *)saved + sync_bytes(B, V)); a.agg_f = a.up_f + (size_t)B * (C + 1) * V;
     a.sync = (int *)workspace; a.hand = (float *)workspace + SYNC_HEAD;
     a.up = (float *)((char *)workspace + sync_bytes(B, V)); a.agg = a.up + (size_t)B * (C + 1) * V;
     a.out = grad_feature; a.gw = grad_weight;

@@ -208,8 +208,8 @@ CHAIN_MAX_C = lib.fedicra_chain_filter_max_channels()
 
 
 def chain_filter_forward(feature_in, edge_weight, si, sp, sc, gs):
-    """Tree filter on chain-ordered trees.  Returns (feature_out [B,C,V] vertex order, saved) with saved =
-    [2,B,C+1,V] float32: leaf->root values and root->leaf aggregates in chain order (channel C = weight sums)."""
+    """Tree filter on chain-ordered trees.  Returns (feature_out [B,C,V] vertex order, saved); `saved` is an opaque
+    byte buffer for chain_filter_backward, chain_saved_arrays(saved, B, C, V) views its two [B,C+1,V] arrays."""
     f = _cuda(feature_in, torch.float32, "feature_in")
     if not (edge_weight.is_cuda and edge_weight.dtype == torch.float32 and edge_weight.is_contiguous()):
         raise RuntimeError("edge_weight must be a contiguous float32 CUDA tensor (it is written in place)")
@@ -217,12 +217,21 @@ def chain_filter_forward(feature_in, edge_weight, si, sp, sc, gs):
     dev = f.device
     with torch.cuda.device(dev):
         out = torch.empty_like(f)
-        saved = torch.empty(2, B, C + 1, V, dtype=torch.float32, device=dev)
-        ws = workspace("chain_filter", lib.fedicra_chain_filter_workspace_bytes(B, C, V), dev)
+        saved = torch.empty(lib.fedicra_chain_filter_saved_bytes(B, C, V), dtype=torch.uint8, device=dev)
         check(lib.fedicra_chain_filter_forward(_p(f), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(gs), B, C, V, _p(out),
-                                               _p(saved), saved.numel() * 4, _p(ws), ws.numel(), _stream()),
-              "chain_filter_forward")
+                                               _p(saved), saved.numel(), _stream()), "chain_filter_forward")
     return out, saved
+
+
+def chain_saved_arrays(saved, B, C, V):
+    """(leaf->root values, root->leaf aggregates), each [B,C+1,V] float32 in chain order (channel C = weight sums)."""
+    off = lib.fedicra_chain_filter_saved_offset(B, C, V)
+    return saved[off:].view(torch.float32).view(2, B, C + 1, V)
+
+
+def chain_watchdog_trips(saved):
+    """How many waits inside the last chain-filter launch that used this buffer ran into their time bound (0 = none)."""
+    return int(saved[:8].view(torch.int32)[1]) + 1
 
 
 def chain_filter_backward(grad_out, edge_weight, si, sp, sc, gs, saved, want_weight_grad):

@@ -206,16 +206,17 @@ int fedicra_tree_filter_backward(const float *grad_out, const float *edge_weight
  * (~1 500).  One launch per call (csrc/chains.cu); 1..4 feature channels.
  *   feature_in / grad_out / feature_out / grad_feature [B,C,V] vertex order; edge_weight, grad_weight [B,V] chain order
  *   (edge_weight[b,0] is set to 0 in place like refine.cu:43-46; grad_weight may be NULL);
- *   saved = leaf->root values then root->leaf aggregates, each [B,C+1,V] in chain order, channel C = the all-ones
- *   channel (weight_sum_up / weight_sum of the reference), i.e. feature_aggr_up, weight_sum_up, feature_aggr, weight_sum;
- *   workspace: zeroed by the call itself; forward needs the first 64 KiB-ish sync part only. */
+ *   saved = fedicra_chain_filter_saved_offset bytes of call-private counters, then the leaf->root values and the
+ *   root->leaf aggregates, each [B,C+1,V] float in chain order, channel C = the all-ones channel -- i.e.
+ *   feature_aggr_up | weight_sum_up and feature_aggr | weight_sum of the reference (refine.cu:201-249);
+ *   workspace (backward only): scratch, initialised by the call itself. */
 int fedicra_chain_filter_max_channels(void);
 size_t fedicra_chain_filter_saved_bytes(int B, int C, int V);
+size_t fedicra_chain_filter_saved_offset(int B, int C, int V);
 size_t fedicra_chain_filter_workspace_bytes(int B, int C, int V);
 int fedicra_chain_filter_forward(const float *feature_in, float *edge_weight, const int *sorted_index,
                                  const int *sorted_parent, const int *sorted_child, const int *group_start, int B, int C,
-                                 int V, float *feature_out, void *saved, size_t saved_bytes, void *workspace,
-                                 size_t workspace_bytes, void *stream);
+                                 int V, float *feature_out, void *saved, size_t saved_bytes, void *stream);
 int fedicra_chain_filter_backward(const float *grad_out, float *edge_weight, const int *sorted_index,
                                   const int *sorted_parent, const int *sorted_child, const int *group_start, int B, int C,
                                   int V, const void *saved, float *grad_feature, float *grad_weight, void *workspace,
