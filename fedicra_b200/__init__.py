@@ -16,12 +16,13 @@ from . import _lib  # noqa: F401  (fails loudly when the library is missing)
 from .gate_crf_loss import ModelLossSemsegGatedCRF
 from .tree_filter import MinimumSpanningTree, TreeFilter2D
 from .tree_energy import MScaleAddTreeEnergyLoss, MScaleRecurveTreeEnergyLoss, TreeEnergyLoss
-from .aggregation import AdaptiveAggregation, fedavg_allreduce, fused_ala_update
+from .aggregation import AdaptiveAggregation, FlatModelState, fedavg_allreduce, fused_ala_update
+from .runner import GraphedLossStack, LossStackStep, PipelinedLossStack
 from . import tree_filter_cuda
 from .dropin import install as install_dropin
 
 __all__ = [
     "ModelLossSemsegGatedCRF", "MinimumSpanningTree", "TreeFilter2D", "TreeEnergyLoss", "MScaleAddTreeEnergyLoss",
-    "MScaleRecurveTreeEnergyLoss", "AdaptiveAggregation", "fedavg_allreduce", "fused_ala_update", "tree_filter_cuda",
-    "install_dropin",
+    "MScaleRecurveTreeEnergyLoss", "AdaptiveAggregation", "FlatModelState", "fedavg_allreduce", "fused_ala_update",
+    "tree_filter_cuda", "install_dropin", "LossStackStep", "GraphedLossStack", "PipelinedLossStack",
 ]

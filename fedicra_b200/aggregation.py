@@ -112,20 +112,77 @@ class AdaptiveAggregation:
 
 
 def fedavg_allreduce(flat_state, num_examples, group=None):
-    """FedAvg over the ranks of ``group``: flat_state <- sum_i n_i * flat_state_i / sum_i n_i, in place.
+    """FedAvg over the ranks of ``group``: flat_state <- sum_i n_i * flat_state_i / sum_i n_i, in place, in flwr's order
+    of operations (aggregate.py::aggregate: every client's arrays times its n_i, summed, divided by the total).
 
-    One pre-scale kernel + one all-reduce of the flat fp32 state (NCCL over NVLink on the box) + one tiny all-reduce of
-    the example counts.  Mirrors flwr's aggregate() fed with (get_weights(), len(trainloader)) pairs
-    (flower_common.py:70-72, 488-489).
+    One scale kernel, one all-reduce of the flat fp32 state (NCCL over NVLink on the box), one tiny all-reduce of the
+    example counts, one scale by the reciprocal total -- no host synchronisation.  Mirrors flwr's aggregate() fed with
+    (get_weights(), len(trainloader)) pairs (flower_common.py:70-72, 488-489).
     """
     import torch.distributed as dist
 
-    n = torch.tensor([float(num_examples)], dtype=torch.float64, device=flat_state.device)
+    n = torch.tensor([float(num_examples)], dtype=torch.float32, device=flat_state.device)
     dist.all_reduce(n, op=dist.ReduceOp.SUM, group=group)
-    alpha = float(num_examples) / float(n.item())
     if flat_state.is_cuda:
-        ops.scale_inplace(flat_state, alpha)
+        ops.scale_inplace(flat_state, float(num_examples))
     else:  # gloo tests of the host logic only; the product path is CUDA + NCCL
-        flat_state.mul_(alpha)
+        flat_state.mul_(float(num_examples))
     dist.all_reduce(flat_state, op=dist.ReduceOp.SUM, group=group)
+    flat_state.div_(n)
     return flat_state
+
+
+class FlatModelState:
+    """The whole state_dict of a module in two persistent flat buffers, the module's own tensors re-pointed to views of
+    them -- what `get_weights` / `set_weights` / `load_state_dict` move tensor by tensor through numpy in the reference
+    (flower_common.py:488-489, 499-502):
+
+      flat  float32: every floating entry (parameters and BatchNorm running statistics), in state_dict order
+      ints  int64:   every integer entry (BatchNorm ``num_batches_tracked``)
+
+    so that FedAvg is ONE in-place all-reduce of ``flat`` (plus a 21-element one for the counters) and loading the
+    global model is no copy at all: the module already looks at the reduced buffer.
+    """
+
+    def __init__(self, module):
+        entries = list(module.state_dict(keep_vars=True).items())
+        self.names = [k for k, _ in entries]
+        dev = entries[0][1].device
+        fl = [(k, t) for k, t in entries if t.is_floating_point()]
+        it = [(k, t) for k, t in entries if not t.is_floating_point()]
+        self.flat = torch.empty(sum(t.numel() for _, t in fl), dtype=torch.float32, device=dev)
+        self.ints = torch.empty(sum(t.numel() for _, t in it), dtype=torch.int64, device=dev)
+        self.views, self.slices = {}, {}
+        for buf, group in ((self.flat, fl), (self.ints, it)):
+            off = 0
+            for k, t in group:
+                n = t.numel()
+                view = buf[off:off + n].view(t.shape)
+                view.copy_(t.detach())
+                t.data = view                 # the module's parameter / buffer now lives inside the flat buffer
+                self.views[k], self.slices[k] = view, (buf is self.flat, off, n)
+                off += n
+
+    def numel(self):
+        return self.flat.numel() + self.ints.numel()
+
+    def get_weights(self):
+        """The reference's wire format (flower_common.py:488-489): one numpy array per state_dict entry."""
+        return [self.views[k].detach().cpu().numpy() for k in self.names]
+
+    def set_weights(self, arrays):
+        """Inverse of get_weights: flwr's aggregate turns integer counters into floats, torch casts them back."""
+        for k, a in zip(self.names, arrays):
+            self.views[k].copy_(torch.as_tensor(a).to(self.views[k].dtype))
+
+    def fedavg_(self, num_examples, group=None):
+        """In-place FedAvg of the whole state over the ranks (one client per rank).  The integer counters go through
+        the same weighted mean in float64 and are truncated on the way back, as numpy + load_state_dict do."""
+        import torch.distributed as dist
+        fedavg_allreduce(self.flat, num_examples, group)
+        if self.ints.numel():
+            c = torch.cat([self.ints.double() * float(num_examples),
+                           torch.tensor([float(num_examples)], dtype=torch.float64, device=self.ints.device)])
+            dist.all_reduce(c, op=dist.ReduceOp.SUM, group=group)
+            self.ints.copy_((c[:-1] / c[-1]).to(torch.int64))
+        return self

@@ -72,6 +72,51 @@ def test_fedavg_and_sharded_normaliser_over_gloo_world_size_2():
     assert [r[2] for r in res] == [(0, 3), (3, 5)]
 
 
+def _flat_state_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from fedicra_b200.aggregation import FlatModelState
+    torch.manual_seed(rank)
+    net = torch.nn.Sequential(torch.nn.Conv2d(2, 3, 3), torch.nn.BatchNorm2d(3), torch.nn.Conv2d(3, 1, 1))
+    net[1].num_batches_tracked.fill_(10 * (rank + 1) + 1)
+    before = [v.clone() for v in net.state_dict().values()]
+    st = FlatModelState(net)
+    same = all(torch.equal(a, b) for a, b in zip(before, net.state_dict().values()))   # re-pointing keeps the values
+    shared = net[0].weight.data_ptr() == st.flat.data_ptr()                             # ... and the module lives in `flat`
+    wire = st.get_weights()
+    st.fedavg_(num_examples=[21, 13][rank])
+    x = torch.ones(1, 2, 5, 5)
+    q.put((rank, [a.tolist() for a in wire], [v.tolist() for v in net.state_dict().values()], same, shared,
+           net.eval()(x).flatten().tolist()))
+    dist.destroy_process_group()
+
+
+def test_flat_model_state_fedavg_equals_the_oracle_over_gloo_world_size_2():
+    """FlatModelState: 160-tensor state_dicts as one buffer (flower_common.py:488-489, 499-502); FedAvg in place, integer
+    counters averaged in float64 and truncated like numpy + load_state_dict; result == oracle.ala_cpu.fedavg."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_flat_state_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    wires = [[np.asarray(a) for a in r[1]] for r in res]
+    want = ala_cpu.fedavg([[a.astype(np.float32) if a.dtype.kind == "f" else a for a in w] for w in wires], [21, 13])
+    for rank, _, after, same, shared, out in res:
+        assert same and shared
+        for got, w, src in zip(after, want, wires[0]):
+            if np.asarray(src).dtype.kind == "f":
+                assert np.allclose(np.asarray(got, dtype=np.float32), np.asarray(w, dtype=np.float32), rtol=1e-6, atol=1e-7)
+            else:
+                assert int(np.asarray(got)) == int((11 * 21 + 21 * 13) / 34.0)      # truncation of the float mean
+    assert res[0][5] == res[1][5]                                                    # both clients hold the same model now
+
+
 def test_dropin_registers_reference_module_names():
     import fedicra_b200
     saved = {k: sys.modules.get(k) for k in list(sys.modules) if k.startswith("utils") or k == "tree_filter_cuda"}
