@@ -58,7 +58,8 @@ def fused_ala_update(params_p, server_params_p, temp_params_p, fedaa_weights, et
         for x in group:
             if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()):
                 raise RuntimeError("fused_ala_update: all tensors must be contiguous float32 CUDA tensors")
-    key = tuple(x.data_ptr() for group in datas for x in group)
+    # addresses AND sizes: the caching allocator may hand the same addresses to tensors of another shape
+    key = tuple((x.data_ptr(), x.numel()) for group in datas for x in group)
     tab = _TABLE_CACHE.get(key)
     if tab is None:
         if len(_TABLE_CACHE) > 16:

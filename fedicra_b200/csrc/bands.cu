@@ -759,6 +759,15 @@ int launch_resident(const TreeView &t, const Consts &k, ResidentArgs a, int B, c
     static thread_local int cached_key[2] = {-1, -1}, cached_cap = 0, cached_per_sm = 0;   // (device, nthr, smem) -> resident CTAs
     int dev = 0;
     cudaGetDevice(&dev);
+    {   // FEDICRA_WATCHDOG_MS: bound of the inter-CTA waits (0 = none), uploaded once per device
+        static thread_local unsigned long long uploaded = 0;
+        const char *v = getenv("FEDICRA_WATCHDOG_MS");
+        if (v && *v && !(uploaded & (1ull << (dev & 63)))) {
+            const unsigned long long ns = (unsigned long long)atoll(v) * 1000000ull;
+            cudaMemcpyToSymbolAsync(g_resident_watchdog_ns, &ns, sizeof(ns), 0, cudaMemcpyHostToDevice, st);
+            uploaded |= 1ull << (dev & 63);
+        }
+    }
     const int key0 = nthr * 64 + dev, key1 = (int)smem;
     if (cached_key[0] != key0 || cached_key[1] != key1) {
         if (set_smem(resident_kernel<MODE, NCT>, smem, "resident_kernel")) return -2;

@@ -352,10 +352,12 @@ extern "C" int fedicra_gcrf_fwd_bwd(const float *y, const float *image, int N, i
 // For them the scratch lives inside the library: one fixed array in device memory, created when the library is loaded
 // on a GPU and kept until the process exits.  Every GPU that loads the library pays for it, so it is kept small.
 //
-// Limit: the array is sized like the workspace fedicra_gcrf_workspace_bytes() asks for, one float per thread block of
-// the widest kernel, for at most FEDICRA_GCRF_NOALLOC_MAX_CTAS = 32768 blocks.  That covers N*H*W <= 4 194 304 pixels
-// (16 x 512 x 512, 64 x 256 x 256).  The array is 64 + 4*32768 = 131136 bytes.  Larger problems are refused with an
-// error; use fedicra_gcrf_fwd_bwd with a caller-owned workspace for those.
+// Limit: the array is sized like the workspace fedicra_gcrf_workspace_bytes() asks for -- one float per thread block of
+// the kernel that launches the most blocks -- for at most FEDICRA_GCRF_NOALLOC_MAX_CTAS = 32768 blocks, i.e.
+//     max(N * ceil(H/16) * ceil(W/32), ceil(N*H*W / 128)) <= 32768.
+// For ordinary images that is N*H*W <= 4 194 304 pixels (16 x 512 x 512, 64 x 256 x 256); very thin or very small
+// images reach the tile term first (20 000 images of 1 x 33 are 40 000 tiles).  The array is 64 + 4*32768 = 131136
+// bytes.  Larger problems are refused with an error; use fedicra_gcrf_fwd_bwd with a caller-owned workspace for those.
 //
 // The array is shared by all calls on a device and keeps whatever the previous call left in it.  The only part that
 // must start from zero is the 4-byte block counter at its front; each call clears it on `stream` before launching.
@@ -364,7 +366,8 @@ extern "C" int fedicra_gcrf_fwd_bwd(const float *y, const float *image, int N, i
 //
 // The first call on each device looks up the array's device address (the name `g_gcrf_noalloc_scratch` below is only a
 // host-side handle, not something a kernel can be given).  That lookup is a one-off set-up step: make the first call
-// on a device before starting any stream capture on it.
+// on a device before starting any stream capture on it.  The address is remembered per device ordinal for the life of
+// the process: it assumes the primary context and no cudaDeviceReset in between.
 #include <mutex>
 
 namespace {
@@ -412,10 +415,10 @@ extern "C" int fedicra_gcrf_fwd_bwd_noalloc(const float *y, const float *image, 
     FEDICRA_REQUIRE(N > 0 && H > 0 && W > 0, "gcrf_fwd_bwd_noalloc: bad shape N=%d H=%d W=%d", N, H, W);
     const size_t need = fedicra_gcrf_workspace_bytes(N, H, W);
     FEDICRA_REQUIRE(need <= FEDICRA_GCRF_NOALLOC_BYTES,
-                    "gcrf_fwd_bwd_noalloc: problem N=%d H=%d W=%d needs %zu scratch bytes, the built-in array holds %zu "
-                    "(at most %d thread blocks = %d pixels); call fedicra_gcrf_fwd_bwd with your own workspace instead",
-                    N, H, W, need, FEDICRA_GCRF_NOALLOC_BYTES, FEDICRA_GCRF_NOALLOC_MAX_CTAS,
-                    FEDICRA_GCRF_NOALLOC_MAX_CTAS * 128);
+                    "gcrf_fwd_bwd_noalloc: problem N=%d H=%d W=%d launches up to %zu thread blocks (%zu scratch bytes), the "
+                    "built-in array holds %zu bytes = %d thread blocks [max(tiles of 16x32, pixels/128)]; call "
+                    "fedicra_gcrf_fwd_bwd with your own workspace instead",
+                    N, H, W, (need - 64) / sizeof(float), need, FEDICRA_GCRF_NOALLOC_BYTES, FEDICRA_GCRF_NOALLOC_MAX_CTAS);
     void *scratch = gcrf_noalloc_scratch_ptr();
     if (scratch == nullptr) return -2;
     // the block counter must start at zero whatever an earlier (possibly failed) call left behind

@@ -76,8 +76,15 @@ __device__ __forceinline__ void cta_arrive(int *counter) {
         red_release_add(counter, 1);
     }
 }
-// Block the CTA until *word == want.  A wait that lasts two seconds can only mean corrupted sync words (a workspace that
-// was not zeroed, or shared by overlapping calls): trap -- the launch fails with an error instead of hanging the GPU.
+// Longest time a CTA may wait for a counter before the launch is given up (FEDICRA_WATCHDOG_MS, default 10 s, 0 = wait
+// for ever).  Wall-clock time also passes while the context is stopped under a debugger, slowed by compute-sanitizer or
+// time-sliced with other processes, and a non-cooperative launch (FEDICRA_COOP=0) may legitimately wait for CTAs that
+// are not resident yet -- raise or disable the bound there.
+__device__ unsigned long long g_resident_watchdog_ns = 10000000000ull;
+
+// Block the CTA until *word == want.  With sound sync words a wait ends within microseconds; one that outlasts the bound
+// above means they are corrupted (a workspace that was not zeroed, or shared by overlapping calls): the kernel traps, so
+// the launch fails with a (sticky) CUDA error instead of hanging the GPU.
 __device__ __forceinline__ void cta_wait(const int *word, int want) {
     if (threadIdx.x == 0) {
         unsigned long long t0 = 0;
@@ -87,8 +94,9 @@ __device__ __forceinline__ void cta_wait(const int *word, int want) {
             if ((++spins & 0xfffu) == 0) {   // look at the clock every 4096 polls
                 unsigned long long now;
                 asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+                const unsigned long long limit = g_resident_watchdog_ns;
                 if (t0 == 0) t0 = now;
-                else if (now - t0 > 2000000000ull) __trap();
+                else if (limit != 0 && now - t0 > limit) __trap();
             }
         }
         __threadfence();

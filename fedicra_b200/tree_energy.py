@@ -120,7 +120,7 @@ class _TreeLossBase(nn.Module):
 
     def _trees(self, embeds):
         """Topology of all the embeddings of this step at once (they do not depend on the filter chain)."""
-        if all(e.is_cuda for e in embeds) and len({(e.shape[0],) + tuple(e.shape[2:]) for e in embeds}) == 1:
+        if all(e.is_cuda and e.shape[1] <= 4 for e in embeds) and len({(e.shape[0],) + tuple(e.shape[2:]) for e in embeds}) == 1:
             return batched_tree_orders(embeds)
         return [self.mst_layers(e) for e in embeds]
 

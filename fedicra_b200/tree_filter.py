@@ -128,8 +128,10 @@ class MinimumSpanningTree(nn.Module):
         if label is not None:
             raise NotImplementedError("fedicra_b200 MinimumSpanningTree: the `label` branch is not implemented")
         with torch.no_grad():
-            if _is_norm2(self.distance_func):
-                # weights + MST fused, edge list never materialised; the adjacency mask rides along for the BFS
+            if _is_norm2(self.distance_func) and guide_in.shape[1] <= 4:
+                # weights + MST fused, edge list never materialised; the adjacency mask rides along for the ordering.
+                # Up to 4 channels the kernel's in-order channel sum has the bits of torch's reduction (the MST is
+                # decided on those bits); wider embeddings take the path below, on torch's own weights.
                 tree, mask = ops.mst_grid(guide_in.detach().float(), want_mask=True)
                 tree._fedicra_mask, tree._fedicra_hw = mask, tuple(guide_in.shape[2:])
             else:

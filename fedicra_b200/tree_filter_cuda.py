@@ -11,31 +11,24 @@ Differences a caller can observe:
   * ``bfs_forward`` returns the canonical level order (the reference: an atomic-dependent topological order) and only
     supports ``max_adj_per_vertex == 4`` (the only value the reference ever passes, tree_filter.py:135);
   * the refine operators need the sorted_* arrays of this module's ``bfs_forward`` (they rely on its level structure,
-    remembered per ``sorted_index`` storage) and raise on foreign arrays.
+    remembered on the ``sorted_index`` tensor object) and raise on foreign arrays.
 """
-import collections
-
 import torch
 
 from . import ops
 
-_LEVELS = collections.OrderedDict()  # sorted_index.data_ptr() -> (B, V, level_start, n_levels)
-_LEVELS_MAX = 256
-
-
 def _remember_levels(si, ls, nl):
-    _LEVELS[si.data_ptr()] = (si.shape[0], si.shape[1], ls, nl)
-    _LEVELS.move_to_end(si.data_ptr())
-    while len(_LEVELS) > _LEVELS_MAX:
-        _LEVELS.popitem(last=False)
+    """The level structure rides on the sorted_index tensor OBJECT the caller gets back (not on its address: a freed and
+    re-used block must not inherit another tree's levels)."""
+    si._fedicra_levels = (ls, nl)
 
 
 def _levels_of(si):
-    hit = _LEVELS.get(si.data_ptr())
-    if hit is None or hit[0] * hit[1] != si.numel():
+    hit = getattr(si, "_fedicra_levels", None)
+    if hit is None:
         raise RuntimeError("tree_filter_cuda.refine_*: sorted_index was not produced by this module's bfs_forward "
-                           "(the kernels need its level structure)")
-    return hit[2], hit[3]
+                           "(the kernels need its level structure); pass the tensor bfs_forward returned, not a copy")
+    return hit
 
 
 def mst_forward(edge_index, edge_weight, vertex_count):

@@ -62,7 +62,8 @@ int fedicra_gcrf_fwd_bwd(const float *y, const float *image, int N, int C, int C
 /* Allocation-free variant of fedicra_gcrf_fwd_bwd.  It has no counterpart in the reference.
  * For callers that cannot create device memory themselves (their host framework owns all of it, or they run where a
  * cudaMalloc -- which synchronises the device -- is not acceptable): the scratch is a fixed array inside the library,
- * fedicra_gcrf_noalloc_max_bytes() = 131136 bytes per GPU, enough for N*H*W <= 4 194 304 pixels (16 x 512 x 512).
+ * fedicra_gcrf_noalloc_max_bytes() = 131136 bytes per GPU, enough for 32 768 thread blocks: max(N*ceil(H/16)*ceil(W/32), ceil(N*H*W/128)) <= 32768, i.e. N*H*W <= 4 194 304
+ * pixels (16 x 512 x 512) for ordinary image shapes.
  * Same arguments and results as fedicra_gcrf_fwd_bwd minus the workspace; problems beyond the limit are refused with an
  * error.  The array is shared: calls that can overlap on the GPU race, serialise them.  The first call on a device
  * performs a one-off address lookup and should be made before any stream capture on that device. */
@@ -84,7 +85,8 @@ int fedicra_mst_forward(const int *edge_index, const float *edge_weight, int B, 
 
 /* MinimumSpanningTree.forward on the implicit 4-connected grid (LTF/modules/tree_filter.py:15-34, 53-62 fused with
  * mst_forward): edge e<(H-1)*W joins (h,w)-(h+1,w), the rest join (h,w)-(h,w+1); weight = sum_c (delta)^2 + 1 summed in
- * channel order without fused multiply-add, so the fp32 bits equal torch's.
+ * channel order without fused multiply-add, so the fp32 bits equal torch's for D <= 4 (what FedICRA uses: 2..3; torch's
+ * CUDA reduction interleaves four accumulators beyond that -- the Python modules take torch's own weights for D > 4).
  *   embed [B,D,H,W]  ->  edge_out [B,H*W-1,2] int32 (increasing edge index; may be NULL when only the mask is wanted);
  *   tree_mask [B,H*W] uint8 (may be NULL): per vertex, bit 0/1/2/3 set when the tree holds the edge to the pixel
  *   above / left / right / below -- the compact form fedicra_bfs_grid consumes. */

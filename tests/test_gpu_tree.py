@@ -251,7 +251,7 @@ def test_rooted_order_is_a_level_order_and_the_filter_does_not_depend_on_the_roo
 
 def test_corrupted_sync_words_fail_the_launch_instead_of_hanging():
     """The resident filter's CTAs wait on counters in the workspace head.  Garbage there (a workspace that was not
-    zeroed) must end in a CUDA error within seconds -- the kernel traps after a two-second wait -- not in a hung GPU.
+    zeroed) must end in a CUDA error within seconds -- the kernel traps once a wait outlasts FEDICRA_WATCHDOG_MS -- not in a hung GPU.
     Runs in a child process: the trap poisons the CUDA context."""
     import subprocess
     import sys
@@ -281,5 +281,6 @@ except RuntimeError as exc:
     sys.exit(0)
 print("NO-ERROR")
 """ % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    env = dict(os.environ, FEDICRA_WATCHDOG_MS="1500", FEDICRA_FILTER="resident")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120, env=env)
     assert "CUDA-ERROR" in r.stdout, (r.stdout[-500:], r.stderr[-500:])

@@ -39,13 +39,41 @@ def test_noalloc_matches_the_workspace_entry_point_twice_in_a_row():
         ref_loss, ref_grad = ops.gcrf_fwd_bwd(y, img, 5, [(1.0, 6.0, 0.1)])
         loss = torch.full((1,), float("nan"), device="cuda")
         grad = torch.full_like(y, float("nan"))
+        rc = _call_noalloc(y, img, 5, loss, grad)          # also the set-up call: loads the module, looks the array up
+        assert rc == 0, lib.fedicra_last_error().decode()
         torch.cuda.synchronize()
-        before = torch.cuda.memory_allocated()
+        assert _rel(loss, ref_loss) < TOL and _rel(grad, ref_grad) < TOL
+        # the driver's own count of free device memory (cudaMemGetInfo) sees every allocation, whoever made it
+        loss.fill_(float("nan"))
+        grad.fill_(float("nan"))
+        torch.cuda.synchronize()
+        free_before, _ = torch.cuda.mem_get_info()
         rc = _call_noalloc(y, img, 5, loss, grad)
         assert rc == 0, lib.fedicra_last_error().decode()
         torch.cuda.synchronize()
-        assert torch.cuda.memory_allocated() == before
+        free_after, _ = torch.cuda.mem_get_info()
+        assert free_after == free_before, "the call changed the amount of free device memory"
         assert _rel(loss, ref_loss) < TOL and _rel(grad, ref_grad) < TOL
+
+
+def test_noalloc_after_a_refused_call_and_on_a_second_device():
+    """A refused call must leave the shared array usable, and every GPU has its own copy of it (the address is looked up
+    per device)."""
+    from fedicra_b200 import ops
+    from fedicra_b200._lib import lib
+    assert lib.fedicra_gcrf_fwd_bwd_noalloc(None, None, 20000, 2, 1, 1, 33, 5, None, 1, None, None, None) < 0
+    g = torch.Generator().manual_seed(7)
+    for dev in range(min(torch.cuda.device_count(), 2)):
+        with torch.cuda.device(dev):
+            y = torch.softmax(torch.randn(2, 2, 40, 64, generator=g), 1).cuda()
+            img = torch.rand(2, 1, 40, 64, generator=g).cuda()
+            ref_loss, ref_grad = ops.gcrf_fwd_bwd(y, img, 5, [(1.0, 6.0, 0.1)])
+            loss = torch.full((1,), float("nan"), device="cuda")
+            grad = torch.full_like(y, float("nan"))
+            rc = _call_noalloc(y, img, 5, loss, grad)
+            assert rc == 0, lib.fedicra_last_error().decode()
+            torch.cuda.synchronize()
+            assert _rel(loss, ref_loss) < TOL and _rel(grad, ref_grad) < TOL
 
 
 def test_noalloc_refuses_problems_beyond_its_built_in_scratch():
@@ -55,3 +83,6 @@ def test_noalloc_refuses_problems_beyond_its_built_in_scratch():
     assert rc < 0
     msg = lib.fedicra_last_error().decode()
     assert "built-in array" in msg and "32768" in msg
+    # thin images are limited by the tile count, not by the pixel count: 660 000 pixels, 40 000 tiles
+    rc = lib.fedicra_gcrf_fwd_bwd_noalloc(None, None, 20000, 2, 1, 1, 33, 5, None, 1, None, None, None)
+    assert rc < 0 and "40000 thread blocks" in lib.fedicra_last_error().decode()
