@@ -11,24 +11,35 @@ Differences a caller can observe:
   * ``bfs_forward`` returns the canonical level order (the reference: an atomic-dependent topological order) and only
     supports ``max_adj_per_vertex == 4`` (the only value the reference ever passes, tree_filter.py:135);
   * the refine operators need the sorted_* arrays of this module's ``bfs_forward`` (they rely on its level structure,
-    remembered on the ``sorted_index`` tensor object) and raise on foreign arrays.
+    remembered per ``sorted_index`` address, the tensor kept alive) and raise on foreign arrays.
 """
+import collections
+
 import torch
 
 from . import ops
 
+_LEVELS = collections.OrderedDict()   # sorted_index.data_ptr() -> (sorted_index itself, level_start, n_levels)
+_LEVELS_MAX = 32
+
+
 def _remember_levels(si, ls, nl):
-    """The level structure rides on the sorted_index tensor OBJECT the caller gets back (not on its address: a freed and
-    re-used block must not inherit another tree's levels)."""
-    si._fedicra_levels = (ls, nl)
+    """The reference's autograd glue hands the refine operators re-wrapped tensors (ctx.saved_tensors), so the level
+    structure cannot ride on the tensor object; it is looked up by address.  The entry holds a reference to the
+    sorted_index tensor itself: while it is listed its memory cannot be freed and handed to another tree, so an address
+    hit always is the same tree.  The last 32 orderings are kept; an older one raises instead of guessing."""
+    _LEVELS[si.data_ptr()] = (si, ls, nl)
+    _LEVELS.move_to_end(si.data_ptr())
+    while len(_LEVELS) > _LEVELS_MAX:
+        _LEVELS.popitem(last=False)
 
 
 def _levels_of(si):
-    hit = getattr(si, "_fedicra_levels", None)
-    if hit is None:
-        raise RuntimeError("tree_filter_cuda.refine_*: sorted_index was not produced by this module's bfs_forward "
-                           "(the kernels need its level structure); pass the tensor bfs_forward returned, not a copy")
-    return hit
+    hit = _LEVELS.get(si.data_ptr())
+    if hit is None or hit[0].shape != si.shape or hit[0].device != si.device:
+        raise RuntimeError("tree_filter_cuda.refine_*: sorted_index was not produced by one of this module's last "
+                           f"{_LEVELS_MAX} bfs_forward calls (the kernels need its level structure)")
+    return hit[1], hit[2]
 
 
 def mst_forward(edge_index, edge_weight, vertex_count):

@@ -261,3 +261,38 @@ def test_unmodified_reference_gated_crf_equals_ours():
         loss.backward()
         res.append((loss.detach().cpu(), lg.grad.cpu()))
     assert rel_err(res[1][0], res[0][0]) < TOL and rel_err(res[1][1], res[0][1]) < TOL
+
+
+@pytest.mark.parametrize("variant", ["TreeEnergyLoss", "MScaleAddTreeEnergyLoss"])
+@pytest.mark.parametrize("B,C,Cin,H,W,kind", [(2, 2, 1, 64, 64, "quant8"), (2, 3, 3, 256, 256, "uniform")])
+def test_loss_variants_equal_the_unmodified_reference_classes(variant, B, C, Cin, H, W, kind):
+    """TreeEnergyLoss and MScaleAddTreeEnergyLoss (flower_common.py:646-753) as this package mirrors them, against the
+    reference's own classes on the reference's own kernels: loss values and filter outputs directly, gradients through
+    a smooth functional of the outputs (the |.| kink, see test_gpu_loss_stack)."""
+    import fedicra_b200 as fb
+    image, logits, a1, a2, a3, label = loss_inputs(B, C, Cin, H, W, kind, seed=5)
+    three = (image.repeat(1, 3, 1, 1) if Cin == 1 else image).cuda()
+    roi = (label == C).cuda()
+    ref_gpu.install("reference")
+    fc = ref_gpu.flower_common()
+    results = []
+    for mod in (getattr(fc, variant)(), getattr(fb, variant)()):
+        xs = [t.clone().cuda().requires_grad_() for t in (logits, a1, a2, a3)]
+        if variant == "TreeEnergyLoss":
+            out = mod(xs[0], three, xs[3], roi, 0.1)          # one high-level tree, on the full-size head
+        else:
+            out = mod(xs[0], three, xs[1], xs[2], xs[3], roi, 0.1)
+        g = torch.Generator().manual_seed(3)
+        smooth = sum((o * torch.randn(o.shape, generator=g).cuda()).sum() for o in out[1:])
+        smooth.backward()
+        torch.cuda.synchronize()
+        results.append((out[0].detach().cpu(), [o.detach().cpu() for o in out[1:]],
+                        [None if x.grad is None else x.grad.cpu() for x in xs]))
+    ref, got = results
+    assert rel_err(got[0], ref[0]) < TOL
+    for a, b in zip(got[1], ref[1]):
+        assert rel_err(a, b) < TOL
+    for name, a, b in zip(("logits", "aux1", "aux2", "aux3"), got[2], ref[2]):
+        assert (a is None) == (b is None), name
+        if a is not None:
+            assert rel_err(a, b) < 3 * TOL, name      # two fp32 evaluations of a cancelling sum (see the N1 test)
