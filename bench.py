@@ -148,7 +148,7 @@ def profile_ops(step, data, steps, flush_buf):
     from fedicra_b200 import ops
     names = ["gcrf_fwd_bwd", "mst_grid", "mst_grid_multi", "bfs_forward", "bfs_grid", "bfs_euler", "edge_weight_fwd",
              "edge_weight_bwd", "refine_forward", "refine_backward_feature", "refine_backward_weight", "tree_filter_forward",
-             "tree_filter_backward", "band_plan", "chain_order", "chain_filter_forward", "chain_filter_backward", "channel_softmax_fwd", "channel_softmax_bwd", "masked_l1_fwd",
+             "tree_filter_backward", "band_plan", "chain_order", "chain_order_weights", "chain_filter_forward", "chain_filter_backward", "channel_softmax_fwd", "channel_softmax_bwd", "masked_l1_fwd",
              "masked_l1_bwd"]
     records, originals = {n: [] for n in names}, {}
 
@@ -300,6 +300,7 @@ def group_bytes_table(B, C, ab):
         "mst_grid_multi": B * (all_stages("mst_bfs") - 4 * u),          # one launch for the 4 embeddings
         "bfs_forward": B * u, "bfs_grid": B * u,
         "bfs_euler": 4 * B * u, "chain_order": 4 * B * u,                 # one call for the 4 trees
+        "chain_order_weights": 4 * B * u + B * (3 + 3 * C + 4) * u,       # ... plus the 4 edge-weight builds
         "refine_forward": B * ab["stages"][1]["filter_fwd"],
         "refine_backward_feature": B * (2 * C + 3) * u,
         "refine_backward_weight": B * (2 * C + 2 * C) * u,

@@ -51,6 +51,8 @@ SIGNATURES = {
                                          c_void_p, c_void_p, c_size_t, c_void_p]),
     "fedicra_chain_order": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                     c_void_p]),
+    "fedicra_chain_order_weights": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                                            c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "fedicra_chain_filter_max_channels": (c_int, []),
     "fedicra_chain_filter_saved_bytes": (c_size_t, [c_int, c_int, c_int]),
     "fedicra_chain_filter_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),

@@ -698,16 +698,29 @@ __global__ void __launch_bounds__(1024) chain_place_kernel(Ws ws, Dims dm, const
     sorted_index[(size_t)b * V + pos] = u;
 }
 
-// parent position; children positions: slot 0 = heavy child (always position + 1), then the light ones by increasing id
+// Embeddings the edge weights of a batch of trees come from: tree t belongs to embedding t / per, image t % per.
+constexpr int CHAIN_MAX_EMBEDS = 8;
+struct ChainEmbeds {
+    const float *ptr[CHAIN_MAX_EMBEDS];
+    int D[CHAIN_MAX_EMBEDS];
+    float inv_sigma[CHAIN_MAX_EMBEDS];
+    int per;              // images per embedding; 0 = no edge weights wanted
+};
+
+// parent position; children positions: slot 0 = heavy child (always position + 1), then the light ones by increasing id;
+// and, when asked, the filter's edge weight of the position: exp(-|e_u - e_parent|^2 * inv_sigma), the arithmetic of
+// edge_weight_fwd_kernel (csrc/refine.cu; tree_filter.py:91-108)
 __global__ void __launch_bounds__(NT) chain_finalize_kernel(const unsigned char *__restrict__ mask, Ws ws, Dims dm,
-                                                            int *__restrict__ sorted_parent, int *__restrict__ sorted_child) {
+                                                            int *__restrict__ sorted_parent, int *__restrict__ sorted_child,
+                                                            ChainEmbeds ce, float *__restrict__ edge_weight) {
     const long long idx = (long long)blockIdx.x * NT + threadIdx.x;
     if (idx >= (long long)dm.B * dm.V) return;
     const int b = (int)(idx / dm.V), u = (int)(idx - (long long)b * dm.V), V = dm.V, W = dm.W;
     const size_t o = (size_t)b * V;
     const int *pos = ws.pos + o;
     const int i = pos[u], pd = ws.pdir[o + u];
-    sorted_parent[o + i] = (u == dm.root) ? 0 : pos[u + dir_delta(pd, W)];
+    const int pu = (u == dm.root) ? u : u + dir_delta(pd, W);
+    sorted_parent[o + i] = (u == dm.root) ? 0 : pos[pu];
     int sz[4];
     const int hd = heavy_dir(mask[o + u], pd, ws.size + o, u, W, sz);
     int c[4] = {0, 0, 0, 0}, k = 1;
@@ -716,6 +729,16 @@ __global__ void __launch_bounds__(NT) chain_finalize_kernel(const unsigned char 
     for (int d = 0; d < 4; ++d)
         if (sz[d] > 0 && d != hd) c[k++] = pos[u + dir_delta(d, W)];
     reinterpret_cast<int4 *>(sorted_child)[o + i] = make_int4(c[0], c[1], c[2], c[3]);
+    if (ce.per > 0) {
+        const int e = b / ce.per, D = ce.D[e];
+        const float *x = ce.ptr[e] + (size_t)(b % ce.per) * D * V;
+        float d2 = 0.f;
+        for (int ch = 0; ch < D; ++ch) {
+            const float t = x[(size_t)ch * V + u] - x[(size_t)ch * V + pu];
+            d2 = fmaf(t, t, d2);
+        }
+        edge_weight[o + i] = expf(-d2 * ce.inv_sigma[e]);
+    }
 }
 
 // Euler tour of every tree ranked, entering / leaving ranks, parent direction and subtree size of every vertex
@@ -805,9 +828,10 @@ extern "C" int fedicra_bfs_euler_rooted(const unsigned char *tree_mask, int B, i
 }
 
 
-extern "C" int fedicra_chain_order(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index,
-                                   int *sorted_parent, int *sorted_child, int *group_start, void *workspace,
-                                   size_t workspace_bytes, void *stream) {
+namespace {
+int chain_order_impl(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index, int *sorted_parent,
+                     int *sorted_child, int *group_start, const ChainEmbeds &ce, float *edge_weight, void *workspace,
+                     size_t workspace_bytes, void *stream) {
     FEDICRA_REQUIRE(tree_mask && sorted_index && sorted_parent && sorted_child && group_start && workspace,
                     "chain_order: null pointer");
     FEDICRA_REQUIRE(B > 0 && B <= 65535 && H >= 1 && W >= 1 && (long long)H * W <= (1ll << 18),
@@ -839,7 +863,34 @@ extern "C" int fedicra_chain_order(const unsigned char *tree_mask, int B, int H,
     FEDICRA_CHECK_LAUNCH("chain_offsets_kernel");
     chain_place_kernel<<<dim3(dm.NTILE, B), 1024, 0, st>>>(ws, dm, group_start, sorted_index);
     FEDICRA_CHECK_LAUNCH("chain_place_kernel");
-    chain_finalize_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm, sorted_parent, sorted_child);
+    chain_finalize_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm, sorted_parent, sorted_child, ce, edge_weight);
     FEDICRA_CHECK_LAUNCH("chain_finalize_kernel");
     return 0;
+}
+}  // namespace
+
+extern "C" int fedicra_chain_order(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index,
+                                   int *sorted_parent, int *sorted_child, int *group_start, void *workspace,
+                                   size_t workspace_bytes, void *stream) {
+    ChainEmbeds ce = {};
+    return chain_order_impl(tree_mask, B, H, W, sorted_index, sorted_parent, sorted_child, group_start, ce, nullptr,
+                            workspace, workspace_bytes, stream);
+}
+
+extern "C" int fedicra_chain_order_weights(const unsigned char *tree_mask, const float *const *h_embeds, const int *h_D,
+                                           const float *h_inv_sigma, int K, int B, int H, int W, int *sorted_index,
+                                           int *sorted_parent, int *sorted_child, int *group_start, float *edge_weight,
+                                           void *workspace, size_t workspace_bytes, void *stream) {
+    FEDICRA_REQUIRE(h_embeds && h_D && h_inv_sigma && edge_weight, "chain_order_weights: null pointer");
+    FEDICRA_REQUIRE(K >= 1 && K <= CHAIN_MAX_EMBEDS && B >= 1, "chain_order_weights: %d embeddings (1..%d)", K, CHAIN_MAX_EMBEDS);
+    ChainEmbeds ce = {};
+    for (int k = 0; k < K; ++k) {
+        FEDICRA_REQUIRE(h_embeds[k] && h_D[k] >= 1, "chain_order_weights: embedding %d is null or has no channels", k);
+        ce.ptr[k] = h_embeds[k];
+        ce.D[k] = h_D[k];
+        ce.inv_sigma[k] = h_inv_sigma[k];
+    }
+    ce.per = B;
+    return chain_order_impl(tree_mask, K * B, H, W, sorted_index, sorted_parent, sorted_child, group_start, ce,
+                            edge_weight, workspace, workspace_bytes, stream);
 }

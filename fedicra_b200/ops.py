@@ -203,6 +203,31 @@ def chain_order(mask, H, W):
     return si, sp, sc, gs
 
 
+def chain_order_weights(mask, embeds, inv_sigmas, H, W):
+    """chain_order of the K*B trees of K embeddings ([B,D_k,H,W] each) plus, from the same pass, their filter edge
+    weights [K*B,V] in chain order (inv_sigmas[k] = 1/sigma of embedding k's filter).  Returns (si, sp, sc, gs, ew)."""
+    import ctypes
+    m = _cuda(mask, torch.uint8, "tree_mask")
+    es = [_cuda(e, torch.float32, "embed_in") for e in embeds]
+    K, B = len(es), es[0].shape[0]
+    KB, V = m.shape
+    assert KB == K * B and V == H * W and all(e.shape[0] == B and tuple(e.shape[2:]) == (H, W) for e in es)
+    dev = m.device
+    with torch.cuda.device(dev):
+        si = torch.empty(KB, V, dtype=torch.int32, device=dev)
+        sp = torch.empty(KB, V, dtype=torch.int32, device=dev)
+        sc = torch.empty(KB, V, 4, dtype=torch.int32, device=dev)
+        gs = torch.empty(KB, 33, dtype=torch.int32, device=dev)
+        ew = torch.empty(KB, V, dtype=torch.float32, device=dev)
+        ws = workspace("bfs_euler", lib.fedicra_bfs_euler_workspace_bytes(KB, H, W), dev)
+        ptrs = (ctypes.c_void_p * K)(*[e.data_ptr() for e in es])
+        dims = (ctypes.c_int * K)(*[e.shape[1] for e in es])
+        sig = (ctypes.c_float * K)(*[float(x) for x in inv_sigmas])
+        check(lib.fedicra_chain_order_weights(_p(m), ptrs, dims, sig, K, B, H, W, _p(si), _p(sp), _p(sc), _p(gs), _p(ew),
+                                              _p(ws), ws.numel(), _stream()), "chain_order_weights")
+    return si, sp, sc, gs, ew
+
+
 CHAIN_MAX_V = 1 << 18
 CHAIN_MAX_C = lib.fedicra_chain_filter_max_channels()
 

@@ -119,9 +119,11 @@ class _TreeLossBase(nn.Module):
         self.tree_filter_layers = TreeFilter2D(groups=1, sigma=0.02)
 
     def _trees(self, embeds):
-        """Topology of all the embeddings of this step at once (they do not depend on the filter chain)."""
+        """Topology of all the embeddings of this step at once (they do not depend on the filter chain), and with it the
+        filters' edge weights: embedding 0 is the image (low-level tree, 1/sigma), the others are decoder heads (1)."""
         if all(e.is_cuda and e.shape[1] <= 4 for e in embeds) and len({(e.shape[0],) + tuple(e.shape[2:]) for e in embeds}) == 1:
-            return batched_tree_orders(embeds)
+            inv = [1.0 / self.tree_filter_layers.sigma] + [1.0] * (len(embeds) - 1)
+            return batched_tree_orders(embeds, inv)
         return [self.mst_layers(e) for e in embeds]
 
     def _low(self, prob, low_feats, tree=None):

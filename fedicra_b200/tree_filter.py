@@ -26,10 +26,13 @@ class _Arrays:
     sorted_child; bfs.cu:46-98) plus what this library's filter kernels need on top of it:
       kind "chain": group_start (heavy-chain order, csrc/chains.cu);  kind "bfs": level_start, n_levels, band plan."""
 
-    __slots__ = ("kind", "si", "sp", "sc", "gs", "ls", "nl", "bands")
+    __slots__ = ("kind", "si", "sp", "sc", "gs", "ls", "nl", "bands", "ew", "ew_key")
 
-    def __init__(self, kind, si, sp, sc, gs=None, ls=None, nl=None, bands=None):
+    def __init__(self, kind, si, sp, sc, gs=None, ls=None, nl=None, bands=None, ew=None, ew_key=None):
         self.kind, self.si, self.sp, self.sc, self.gs, self.ls, self.nl, self.bands = kind, si, sp, sc, gs, ls, nl, bands
+        # edge weights that came out of the ordering pass, and what they were computed from: (embedding address,
+        # shape, 1/sigma) -- build_edge_weight takes them only for exactly that request
+        self.ew, self.ew_key = ew, ew_key
 
 
 def _want_chain(V):
@@ -65,10 +68,15 @@ class _TreeOrder:
         return self.bfs()
 
 
-def batched_tree_orders(embeds):
+def _ew_key(embed, inv_sigma):
+    return (embed.data_ptr(), embed.shape[0], embed.shape[1], int(embed.numel()), float(inv_sigma))
+
+
+def batched_tree_orders(embeds, inv_sigmas=None):
     """MST + ordering of several embeddings of one batch in ONE pass: the embeddings ([B,D_k,H,W], same B/H/W) are
     stacked along the batch axis -- by a pointer table, not by a copy -- so that each kernel of the topology stage is
-    launched once for all of them.  Returns one _TreeOrder per embedding."""
+    launched once for all of them.  With `inv_sigmas` (one per embedding) the filters' edge weights come out of the same
+    pass.  Returns one _TreeOrder per embedding."""
     B, _, H, W = embeds[0].shape
     K = len(embeds)
     with torch.no_grad():
@@ -81,6 +89,12 @@ def batched_tree_orders(embeds):
             tree, mask = ops.mst_grid(stacked, want_mask=True, want_edges=not fits)  # the mask alone feeds the ordering
         cut = lambda a, k: a[k * B:(k + 1) * B]
         if _want_chain(H * W):
+            if inv_sigmas is not None and K <= 8:
+                srcs = [e.detach().float().contiguous() for e in embeds]
+                *arrays, ew = ops.chain_order_weights(mask, srcs, inv_sigmas, H, W)
+                return [_TreeOrder(mask=cut(mask, k), hw=(H, W),
+                                   chain=_Arrays("chain", *(cut(a, k) for a in arrays), ew=cut(ew, k),
+                                                 ew_key=_ew_key(srcs[k], inv_sigmas[k]))) for k in range(K)]
             arrays = ops.chain_order(mask, H, W)
             return [_TreeOrder(mask=cut(mask, k), hw=(H, W), chain=_Arrays("chain", *(cut(a, k) for a in arrays)))
                     for k in range(K)]
@@ -146,7 +160,10 @@ class _EdgeWeight(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, embed, order, inv_sigma):
-        ew = ops.edge_weight_fwd(embed, order.si, order.sp, inv_sigma)
+        if order.ew is not None and order.ew_key == _ew_key(embed, inv_sigma):
+            ew, order.ew = order.ew, None      # computed by the ordering pass from this very tensor; used once (the
+        else:                                  # filter writes w_0 = 0 into it)
+            ew = ops.edge_weight_fwd(embed, order.si, order.sp, inv_sigma)
         ctx.order, ctx.inv_sigma = order, inv_sigma
         ctx.save_for_backward(embed, ew)
         return ew

@@ -141,6 +141,14 @@ int fedicra_bfs_euler_rooted(const unsigned char *tree_mask, int B, int H, int W
  * (refine.cu:19-199 only follow parent / child links).  Same size limit and workspace as fedicra_bfs_euler. */
 int fedicra_chain_order(const unsigned char *tree_mask, int B, int H, int W, int *sorted_index, int *sorted_parent,
                         int *sorted_child, int *group_start, void *workspace, size_t workspace_bytes, void *stream);
+/* The same for the K*B trees of K embeddings of one batch (h_embeds[k] = [B,D_k,H,W] on the device; tree t belongs to
+ * embedding t / B) and, in the same pass, the filter's edge weights of every tree in chain order,
+ * edge_weight [K*B,V] = exp(-|e[v(i)] - e[v(par i)]|^2 * h_inv_sigma[k])  (TreeFilter2D.build_edge_weight,
+ * LTF/modules/tree_filter.py:91-108; same arithmetic as fedicra_edge_weight_fwd).  h_* are HOST arrays of K entries. */
+int fedicra_chain_order_weights(const unsigned char *tree_mask, const float *const *h_embeds, const int *h_D,
+                                const float *h_inv_sigma, int K, int B, int H, int W, int *sorted_index,
+                                int *sorted_parent, int *sorted_child, int *group_start, float *edge_weight,
+                                void *workspace, size_t workspace_bytes, void *stream);
 
 /* ------------------------------------------------------------------------------------------------ tree filter -- */
 /* TreeFilter2D.build_edge_weight (LTF/modules/tree_filter.py:91-108): ew[b,i] = exp(-|e[v(i)] - e[v(par i)]|^2 *
