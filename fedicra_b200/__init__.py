@@ -18,6 +18,7 @@ from .tree_filter import MinimumSpanningTree, TreeFilter2D
 from .tree_energy import MScaleAddTreeEnergyLoss, MScaleRecurveTreeEnergyLoss, TreeEnergyLoss
 from .aggregation import AdaptiveAggregation, FlatModelState, fedavg_allreduce, fused_ala_update
 from .runner import GraphedLossStack, LossStackStep, PipelinedLossStack
+from .adaptive import adaptive_set_weights, install_set_weights
 from . import tree_filter_cuda
 from .dropin import install as install_dropin
 
@@ -25,4 +26,5 @@ __all__ = [
     "ModelLossSemsegGatedCRF", "MinimumSpanningTree", "TreeFilter2D", "TreeEnergyLoss", "MScaleAddTreeEnergyLoss",
     "MScaleRecurveTreeEnergyLoss", "AdaptiveAggregation", "FlatModelState", "fedavg_allreduce", "fused_ala_update",
     "tree_filter_cuda", "install_dropin", "LossStackStep", "GraphedLossStack", "PipelinedLossStack",
+    "adaptive_set_weights", "install_set_weights",
 ]

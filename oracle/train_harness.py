@@ -120,9 +120,50 @@ def run(backend, img_class, iters, rep_iters, n_batches=2, batch_size=12, img_si
     }
 
 
+def check_set_weights(img_class="faz", n_batches=2, batch_size=6, img_size=128, use_graph=False):
+    """MyModel.set_weights of the reference (flower_common.py:491-633) and fedicra_b200.adaptive.adaptive_set_weights on
+    two copies of one client, same global weights, same batches: returns the largest relative difference of the
+    initialised decoder parameters and of the learned aggregation weights, plus timings."""
+    import copy
+    import torch
+    from fedicra_b200.adaptive import adaptive_set_weights
+    ours, fc, args, client = build_client("modules", img_class, 4, 3, n_batches, batch_size, img_size)
+    wrapper = client.model
+    g = torch.Generator().manual_seed(7)
+    weights = []
+    trainable = {n for n, _ in wrapper.model.named_parameters()}
+    for k, v in wrapper.model.state_dict().items():        # a "global model": the local one, parameters perturbed
+        a = v.detach().cpu()
+        weights.append((a + 0.02 * torch.randn(a.shape, generator=g)).numpy() if k in trainable else a.numpy())
+    config = {"iter_global": 51}
+    a_w, b_w = copy.deepcopy(wrapper), copy.deepcopy(wrapper)
+    out = {}
+    for tag, w, fn in (("reference", a_w, lambda: fc.MyModel.set_weights(a_w, weights, config)),
+                       ("ours", b_w, lambda: adaptive_set_weights(b_w, weights, config, use_graph=use_graph,
+                                                                  log=lambda *x: None))):
+        torch.manual_seed(3)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        fn()
+        torch.cuda.synchronize()
+        out[tag + "_seconds"] = time.perf_counter() - t0
+    keys = [n for n, _ in a_w.model.named_parameters() if any(k in n for k in ("out_conv", "up4", "up3", "up2", "up1"))]
+    pa, pb, p0 = (dict(m.model.named_parameters()) for m in (a_w, b_w, wrapper))
+    scale = max(float(pa[k].data.abs().max()) for k in keys)          # tensors that are all (near) zero share the global scale
+    rel = lambda x, y: float((x.double() - y.double()).abs().max() / max(float(y.abs().max()), 1e-2 * scale))
+    out["param_rel"] = max(rel(pb[k].data, pa[k].data) for k in keys)
+    out["weight_rel"] = max(rel(y, x) for x, y in zip(a_w.fedaa_weights, b_w.fedaa_weights))
+    out["other_params_equal"] = all(torch.equal(pa[k].data, pb[k].data) for k in pa if k not in keys)
+    out["moved"] = max(rel(pa[k].data, p0[k].data) for k in keys)
+    out["n_tensors"], out["use_graph"] = len(keys), use_graph
+    out["start_phase_after"] = [bool(a_w.start_phase), bool(b_w.start_phase)]
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--backend", required=True, choices=["reference", "ops", "modules"])
+    ap.add_argument("--backend", default="modules", choices=["reference", "ops", "modules"])
+    ap.add_argument("--mode", default="train", choices=["train", "set_weights", "set_weights_graph"])
     ap.add_argument("--img-class", default="faz", choices=["faz", "odoc"])
     ap.add_argument("--iters", type=int, default=4)
     ap.add_argument("--rep-iters", type=int, default=3)
@@ -132,7 +173,10 @@ def main():
     ap.add_argument("--warmup-iters", type=int, default=0)
     ap.add_argument("--json", default=None)
     a = ap.parse_args()
-    res = run(a.backend, a.img_class, a.iters, a.rep_iters, a.batches, a.batch_size, a.img_size, a.warmup_iters)
+    if a.mode != "train":
+        res = check_set_weights(a.img_class, a.batches, min(a.batch_size, 6), min(a.img_size, 128), a.mode.endswith("graph"))
+    else:
+        res = run(a.backend, a.img_class, a.iters, a.rep_iters, a.batches, a.batch_size, a.img_size, a.warmup_iters)
     text = json.dumps(res)
     if a.json:
         with open(a.json, "w") as f:

@@ -57,3 +57,41 @@ def test_scale_inplace():
     y = x.cuda()
     ops.scale_inplace(y, 21.0 / 113.0)
     assert np.array_equal(y.cpu().numpy(), (x * np.float32(21.0 / 113.0)).numpy())
+
+
+def test_adaptive_set_weights_graph_mode_on_a_capture_safe_network():
+    """adaptive_set_weights with use_graph=True against its own eager mode on a small network whose forward can be
+    captured (the reference's UNet_LC_MultiHead cannot: unet.py:182 copies a host tensor per call)."""
+    import copy
+    import types
+    from fedicra_b200.adaptive import adaptive_set_weights
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.down = torch.nn.Conv2d(1, 8, 3, padding=1)
+            self.up1 = torch.nn.Conv2d(8, 8, 3, padding=1)
+            self.out_conv = torch.nn.Conv2d(8, 2, 1)
+
+        def forward(self, x):
+            return (self.out_conv(torch.relu(self.up1(torch.relu(self.down(x))))),)
+
+    torch.manual_seed(0)
+    g = torch.Generator().manual_seed(1)
+    loader = [{"image": torch.rand(4, 32, 32, generator=g), "label": torch.randint(0, 3, (4, 32, 32), generator=g, dtype=torch.uint8)}
+              for _ in range(3)]
+    args = types.SimpleNamespace(img_class="faz", num_classes=2, cid=0, strategy="FedICRA")
+    base = types.SimpleNamespace(model=Net().cuda(), args=args, trainloader=loader, start_phase=False)
+    weights = [(v.detach().cpu() + 0.1 * torch.randn(v.shape, generator=g)).numpy() for v in base.model.state_dict().values()]
+    outs = []
+    for use_graph in (False, True):
+        w = types.SimpleNamespace(model=copy.deepcopy(base.model), args=args, trainloader=loader, start_phase=False)
+        adaptive_set_weights(w, weights, {"iter_global": 51}, use_graph=use_graph, log=lambda *a: None)
+        torch.cuda.synchronize()
+        outs.append(([p.detach().clone() for p in w.model.parameters()], [x.clone() for x in w.fedaa_weights]))
+    assert len(outs[0][1]) == 4                                    # up1 and out_conv, weight + bias
+    # graph mode sees the first batch three extra times during its warm-up: same direction, not the same bits
+    for a, b in zip(outs[0][1], outs[1][1]):
+        assert float((a - b).abs().max()) < 0.05 and float(b.min()) >= 0.0 and float(b.max()) <= 1.0
+    for a, b in zip(outs[0][0], outs[1][0]):
+        assert float((a - b).abs().max()) < 0.05 * float(a.abs().max())

@@ -51,3 +51,15 @@ def test_reference_train_loop_runs_unchanged_on_the_dropin(img_class, batch_size
         noise = max(rel(ref2["per_iter"][k]["loss"], ref["per_iter"][k]["loss"]), 1e-3)
         for got in (mods, ops_level):
             assert rel(got["per_iter"][k]["loss"], ref["per_iter"][k]["loss"]) < 20 * noise, (got["backend"], k, got["per_iter"], ref["per_iter"], ref2["per_iter"])
+
+
+def test_adaptive_set_weights_equals_the_reference_set_weights():
+    """fedicra_b200.adaptive.adaptive_set_weights (fused element-wise update, no dummy optimizer step) against the
+    unmodified MyModel.set_weights (flower_common.py:491-633) on two copies of one UNet_LC_MultiHead client."""
+    cmd = [sys.executable, "-m", "oracle.train_harness", "--mode", "set_weights", "--img-class", "faz"]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-4000:])
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    assert res["n_tensors"] == 42 and res["moved"] > 1e-3            # the call did initialise the 42 decoder tensors
+    assert res["param_rel"] < 1e-4 and res["weight_rel"] < 1e-4, res
+    assert res["other_params_equal"] and res["start_phase_after"] == [False, False]
