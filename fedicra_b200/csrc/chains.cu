@@ -36,6 +36,9 @@ constexpr int CT = 128;          // threads per CTA
 constexpr int PPT = 4;           // positions per thread
 constexpr int TILE = CT * PPT;   // positions per item
 constexpr int NW = CT / 32;
+#ifndef CHAIN_MINB
+#define CHAIN_MINB 5
+#endif
 constexpr int SYNC_HEAD = 64;    // ints ahead of the hand-over values: [0] ticket - 1, [1] watchdog trips - 1
 constexpr unsigned PENDING = 0xffffffffu;
 
@@ -561,7 +564,7 @@ __device__ __forceinline__ void down_item(const ChainArgs &a, const Item &it, fl
 }
 
 template <int MODE, int NC>
-__global__ void __launch_bounds__(CT) chain_filter_kernel(ChainArgs a) {
+__global__ void __launch_bounds__(CT, CHAIN_MINB) chain_filter_kernel(ChainArgs a) {
     __shared__ int s_gs[33], s_cum[33], s_ticket;
     __shared__ float s_agg[NW][NC + 1];
     const int tid = threadIdx.x, lane = tid & 31;
