@@ -393,193 +393,6 @@ __global__ void __launch_bounds__(1024) sweep_kernel(TreeView t, SweepArgs a, in
         sweep_body<MODE, INJECT, false>(t, a, b, beta, nb, L0, L1, p0, p1, pcap, reinterpret_cast<char *>(smem4));
 }
 
-// ------------------------------------------------------------------------------------------------ async staging
-__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gsrc) {
-    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
-    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-constexpr int SCAPW = 512;    // level width staged in shared memory by the two stitch kernels
-constexpr int NSTAGE = 4;     // staging buffers: operands are fetched NSTAGE-1 bands ahead (one L2 round trip ~ 2 bands)
-
-// ------------------------------------------------------------------------------------------------ U2 / D2: stitching
-// The band-to-band recurrences are sequential over the ~40 bands of an image but independent across channels, and a
-// band's last level is only ~50 vertices wide.  So ONE WARP owns one (image, channel): no block barrier, no other warp
-// to wait for, the per-band step is a few dozen instructions on shared memory.  Operands are contiguous slices of
-// position-indexed arrays, fetched by cp.async NSTAGE-1 bands ahead.
-//
-// U2 (deepest band first): X'[j'] = base[j'] + sum_{j in E(beta), entry(j) = j'} A[j] * X[j] for j' in E(beta-1): a warp
-// segmented inclusive scan of A*X over E(beta) keyed by entry(j), carried across 32-entry chunks, leaves every run's
-// total at the run's last entry, where j' picks it up (run bounds rs/re come from consts_kernel).  Fixed summation order.
-__global__ void __launch_bounds__(32) stitch_up_kernel(TreeView t, Consts k, SweepArgs a) {
-    extern __shared__ float4 smem4[];
-    __shared__ int s_e0[MAXBANDS], s_e1[MAXBANDS];  // last level of every band
-    const int c = blockIdx.x, b = blockIdx.y, lane = threadIdx.x, V = t.V, NC = a.NC;
-    const int *ls = t.ls + (size_t)b * (V + 1);
-    const float *A = k.A + (size_t)b * V;
-    const int *ent = k.ent + (size_t)b * V;
-    const int *rs = k.run_s + (size_t)b * V, *re = k.run_e + (size_t)b * V;
-    float *Xg = a.X + ((size_t)b * NC + c) * V;
-    const int *plan = t.bands + (size_t)b * PLAN_STRIDE;
-    const int nb = plan[0];
-    for (int beta = lane; beta < nb; beta += 32) {
-        const int L1 = plan[2 + beta];
-        s_e0[beta] = ls[L1 - 1];
-        s_e1[beta] = ls[L1];
-    }
-    // shared memory: NSTAGE staging buffers {A[E], ent[E], base X[E'], rs[E'], re[E']} + X[2] + S, SCAPW entries each
-    float *base = reinterpret_cast<float *>(smem4);
-    const int stage_words = 5 * SCAPW;
-    float *sX[2] = {base + NSTAGE * stage_words, base + NSTAGE * stage_words + SCAPW};
-    float *sS = base + NSTAGE * stage_words + 2 * SCAPW;
-    __syncwarp();
-
-    // step `beta` consumes X of E(beta) and produces X of E(beta-1)
-    auto fits = [&](int beta) { return (s_e1[beta] - s_e0[beta]) <= SCAPW && (s_e1[beta - 1] - s_e0[beta - 1]) <= SCAPW; };
-    auto prefetch = [&](int beta) {
-        if (beta >= 1 && fits(beta)) {
-            const int e0 = s_e0[beta], ne = s_e1[beta] - e0, q0 = s_e0[beta - 1], nq = s_e1[beta - 1] - q0;
-            float *st = base + (beta % NSTAGE) * stage_words;
-            for (int i = lane; i < ne; i += 32) {
-                cp_async4(st + i, A + e0 + i);
-                cp_async4(st + SCAPW + i, ent + e0 + i);
-            }
-            for (int i = lane; i < nq; i += 32) {
-                cp_async4(st + 2 * SCAPW + i, Xg + q0 + i);
-                cp_async4(st + 3 * SCAPW + i, rs + q0 + i);
-                cp_async4(st + 4 * SCAPW + i, re + q0 + i);
-            }
-        }
-        cp_async_commit();
-    };
-
-    int cur = 0;
-    for (int d = 0; d < NSTAGE - 1; ++d) prefetch(nb - 1 - d);
-    for (int beta = nb - 1; beta >= 1; --beta) {
-        cp_async_wait<NSTAGE - 2>();
-        __syncwarp();
-        prefetch(beta - (NSTAGE - 1));
-        const int e0 = s_e0[beta], ne = s_e1[beta] - e0, q0 = s_e0[beta - 1], nq = s_e1[beta - 1] - q0;
-        const bool sm = fits(beta), has_x = beta < nb - 1;
-        const float *st = base + (beta % NSTAGE) * stage_words;
-        const int *st_ent = reinterpret_cast<const int *>(st + SCAPW);
-        const int *st_rs = reinterpret_cast<const int *>(st + 3 * SCAPW);
-        const int *st_re = reinterpret_cast<const int *>(st + 4 * SCAPW);
-        if (has_x && sm) {
-            int carry_seg = -1;
-            float carry_val = 0.f;
-            for (int s0 = 0; s0 < ne; s0 += 32) {
-                const int jl = s0 + lane;
-                const bool ok = jl < ne;
-                const int seg = ok ? st_ent[jl] : -2 - lane;
-                float v = ok ? st[jl] * sX[cur][jl] : 0.f;
-                if (lane == 0 && seg == carry_seg) v += carry_val;  // the run continues from the previous chunk
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const float pv = __shfl_up_sync(0xffffffffu, v, o);
-                    const int ps = __shfl_up_sync(0xffffffffu, seg, o);
-                    if (lane >= o && ps == seg) v += pv;
-                }
-                if (ok) sS[jl] = v;
-                carry_seg = __shfl_sync(0xffffffffu, seg, 31);
-                carry_val = __shfl_sync(0xffffffffu, v, 31);
-            }
-            __syncwarp();
-        }
-        for (int jl = lane; jl < nq; jl += 32) {
-            const int j = q0 + jl;
-            float acc = sm ? st[2 * SCAPW + jl] : Xg[j];
-            if (has_x) {
-                const int j0 = sm ? st_rs[jl] : rs[j], j1 = sm ? st_re[jl] : re[j];
-                if (sm) {
-                    if (j1 > j0) acc += sS[j1 - 1 - e0];
-                } else {  // oversized level: plain sequential run sum from global memory
-                    for (int jj = j0; jj < j1; ++jj) acc += A[jj] * Xg[jj];
-                }
-            }
-            Xg[j] = acc;
-            if (nq <= SCAPW) sX[cur ^ 1][jl] = acc;
-        }
-        __syncwarp();
-        if (!sm) __threadfence_block();
-        cur ^= 1;
-    }
-}
-
-// D2 (shallowest band first): out[j] = B[j] + A[j] * out[entry(j)] for j in E(beta), entry(j) in E(beta-1).
-__global__ void __launch_bounds__(32) stitch_down_kernel(TreeView t, Consts k, SweepArgs a, float *outE) {
-    extern __shared__ float4 smem4[];
-    __shared__ int s_e0[MAXBANDS], s_e1[MAXBANDS];
-    const int c = blockIdx.x, b = blockIdx.y, lane = threadIdx.x, V = t.V, NC = a.NC;
-    const int *ls = t.ls + (size_t)b * (V + 1);
-    const float *A = k.A + (size_t)b * V;
-    const int *ent = k.ent + (size_t)b * V;
-    const float *Bv = a.Bv + ((size_t)b * NC + c) * V;
-    float *og = outE + ((size_t)b * NC + c) * V;
-    const int *plan = t.bands + (size_t)b * PLAN_STRIDE;
-    const int nb = plan[0];
-    for (int beta = lane; beta < nb; beta += 32) {
-        const int L1 = plan[2 + beta];
-        s_e0[beta] = ls[L1 - 1];
-        s_e1[beta] = ls[L1];
-    }
-    // shared memory: NSTAGE staging buffers {Bv, A, ent} + out[2], SCAPW entries each
-    float *base = reinterpret_cast<float *>(smem4);
-    const int stage_words = 3 * SCAPW;
-    float *sO[2] = {base + NSTAGE * stage_words, base + NSTAGE * stage_words + SCAPW};
-    __syncwarp();
-
-    auto prefetch = [&](int beta) {
-        if (beta < nb) {
-            const int e0 = s_e0[beta], n = s_e1[beta] - e0;
-            if (n <= SCAPW) {
-                float *st = base + (beta % NSTAGE) * stage_words;
-                for (int i = lane; i < n; i += 32) {
-                    cp_async4(st + i, Bv + e0 + i);
-                    cp_async4(st + SCAPW + i, A + e0 + i);
-                    cp_async4(st + 2 * SCAPW + i, ent + e0 + i);
-                }
-            }
-        }
-        cp_async_commit();
-    };
-
-    int cur = 0, pe0 = 0, pn = 0;
-    for (int d = 0; d < NSTAGE - 1; ++d) prefetch(d);
-    for (int beta = 0; beta < nb; ++beta) {
-        cp_async_wait<NSTAGE - 2>();
-        __syncwarp();
-        prefetch(beta + NSTAGE - 1);
-        const int e0 = s_e0[beta], n = s_e1[beta] - e0;
-        const bool sm = n <= SCAPW;
-        const float *st = base + (beta % NSTAGE) * stage_words;
-        const int *st_ent = reinterpret_cast<const int *>(st + 2 * SCAPW);
-        for (int jl = lane; jl < n; jl += 32) {
-            const int j = e0 + jl;
-            float o = sm ? st[jl] : Bv[j];
-            if (beta > 0) {
-                const int en = sm ? st_ent[jl] : ent[j];
-                const float aj = sm ? st[SCAPW + jl] : A[j];
-                o = fmaf(aj, (pn <= SCAPW ? sO[cur][en - pe0] : og[en]), o);
-            }
-            og[j] = o;
-            if (sm) sO[cur ^ 1][jl] = o;
-        }
-        __syncwarp();
-        if (!sm) __threadfence_block();
-        cur ^= 1;
-        pe0 = e0;
-        pn = n;
-    }
-}
-
 // ------------------------------------------------------------------------------------------------ D3 epilogues
 __device__ __forceinline__ float down_value(const float *A, const int *ent, const float *Bv, const float *og, int i) {
     const float a = A[i];
@@ -713,26 +526,18 @@ int run_sweeps(const TreeView &t, const Consts &k, SweepArgs a, float *outE, int
     const int pcap = multi_pcap(V, NC);
     const size_t smem = (size_t)pcap * per_pos + (LSCAP + 1) * sizeof(int) + 16;
     if (set_smem(sweep_kernel<MODE, false>, smem, "sweep_kernel") || set_smem(sweep_kernel<MODE, true>, smem, "sweep_kernel")) return -2;
-    const size_t smem_u2 = (size_t)(NSTAGE * 5 + 3) * SCAPW * sizeof(float) + 16;
-    const size_t smem_d2 = (size_t)(NSTAGE * 3 + 2) * SCAPW * sizeof(float) + 16;
-    if (set_smem(stitch_up_kernel, smem_u2, "stitch_up_kernel") || set_smem(stitch_down_kernel, smem_d2, "stitch_down_kernel")) return -2;
-    // band-to-band recurrences: all last levels of a channel in shared memory (stitch2.cuh); FEDICRA_STITCH=ring selects
-    // the older cp.async-ring kernels
-    const char *sv = getenv("FEDICRA_STITCH");
-    const bool ring = sv && strcmp(sv, "ring") == 0;
+    // band-to-band recurrences: all last levels of a channel in shared memory (stitch2.cuh)
     const size_t smem_s2 = SMEM_MAX;
     const int tcap2 = (int)((smem_s2 - 3 * (MAXBANDS + 2) * sizeof(int) - 64) / 12);
-    if (!ring && (set_smem(stitch2_kernel<true>, smem_s2, "stitch2_kernel") || set_smem(stitch2_kernel<false>, smem_s2, "stitch2_kernel")))
+    if (set_smem(stitch2_kernel<true>, smem_s2, "stitch2_kernel") || set_smem(stitch2_kernel<false>, smem_s2, "stitch2_kernel"))
         return -2;
     sweep_kernel<MODE, false><<<dim3(nb, B), nthr_sweep, smem, st>>>(t, a, pcap);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U1>");
-    if (ring) stitch_up_kernel<<<dim3(NC, B), 32, smem_u2, st>>>(t, k, a);
-    else stitch2_kernel<true><<<dim3(NC, B), ST2_NT, smem_s2, st>>>(t, k, a.X, nullptr, nullptr, NC, tcap2);
+    stitch2_kernel<true><<<dim3(NC, B), ST2_NT, smem_s2, st>>>(t, k, a.X, nullptr, nullptr, NC, tcap2);
     FEDICRA_CHECK_LAUNCH("stitch_up");
     sweep_kernel<MODE, true><<<dim3(nb, B), nthr_sweep, smem, st>>>(t, a, pcap);
     FEDICRA_CHECK_LAUNCH("sweep_kernel<U3D1>");
-    if (ring) stitch_down_kernel<<<dim3(NC, B), 32, smem_d2, st>>>(t, k, a, outE);
-    else stitch2_kernel<false><<<dim3(NC, B), ST2_NT, smem_s2, st>>>(t, k, nullptr, a.Bv, outE, NC, tcap2);
+    stitch2_kernel<false><<<dim3(NC, B), ST2_NT, smem_s2, st>>>(t, k, nullptr, a.Bv, outE, NC, tcap2);
     FEDICRA_CHECK_LAUNCH("stitch_down");
     return 0;
 }
