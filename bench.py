@@ -182,6 +182,50 @@ def profile_ops(step, data, steps, flush_buf):
 
 
 # ----------------------------------------------------------------------------------------------- reference arms
+def isolated_call_times(data, C, H, W, flush_buf, reps=10, n=5):
+    """Device time per CALL of the four heavy C-ABI calls of a step, each replayed alone from a CUDA graph (`reps` calls
+    back to back, L2 flushed before every replay, CUDA events on the launching stream): no host launch gaps, no other
+    kernels in between.  Inputs are the step's own image and decoder heads."""
+    from fedicra_b200 import ops
+    image = data["image"]
+    three = image.repeat(1, 3, 1, 1) if image.shape[1] == 1 else image
+    embs = [three.contiguous()] + [F.interpolate(data[k], size=(H, W), mode="bilinear", align_corners=False).contiguous()
+                                   for k in ("aux1", "aux2", "aux3")]
+    B, V = image.shape[0], H * W
+    inv = [50.0, 1.0, 1.0, 1.0]
+    _, mask = ops.mst_grid_multi(embs, want_mask=True, want_edges=False)
+    si, sp, sc, gs, ew = ops.chain_order_weights(mask, embs, inv, H, W)
+    cut = lambda a: a[B:2 * B]                                  # the first decoder-head tree
+    feat = torch.softmax(data["logits"], 1).reshape(B, C, V).contiguous()
+    gout = torch.randn_like(feat)
+    o = [cut(a) for a in (si, sp, sc, gs)]
+    w1 = cut(ew).clone()
+    _, saved = ops.chain_filter_forward(feat, w1, *o)
+    calls = {
+        "mst_grid_multi": lambda: ops.mst_grid_multi(embs, want_mask=True, want_edges=False),
+        "chain_order_weights": lambda: ops.chain_order_weights(mask, embs, inv, H, W),
+        "chain_filter_forward": lambda: ops.chain_filter_forward(feat, w1, *o),
+        "chain_filter_backward": lambda: ops.chain_filter_backward(gout, w1, *o, saved, True),
+    }
+    out = {}
+    for name, fn in calls.items():
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                fn()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(reps):
+                fn()
+        ts = time_steps(g.replay, n, flush_buf)
+        out[name] = sorted(ts)[len(ts) // 2] / reps
+        g.reset()
+    return out
+
+
 def cpu_reference_setup():
     """The reference's CPU path.  Where oracle/_ref was built (it travels to the GPU box) this is the reference's OWN
     Python, unmodified -- utils/gate_crf_loss.py, flower_common.MScaleRecurveTreeEnergyLoss, modules/tree_filter.py,
@@ -429,14 +473,28 @@ def measure_workload(name, steps, warmup, dev, rank, world, use_graph, flush_buf
         gb = group_bytes_table(B, C, ab)
         traffic_path = os.path.join(ROOT, "profiles", "traffic.json")
         traffic_tab = json.load(open(traffic_path)).get(name, {}) if os.path.exists(traffic_path) else {}
-        dominant = max(ops_prof, key=lambda n: ops_prof[n]["ms_per_step"]) if ops_prof else None
+        # the four heavy calls once more, each alone in a graph: their device time without the instrumented pass's host gaps
+        iso = {}
+        try:
+            if os.environ.get("FEDICRA_FILTER", "chain") == "chain" and H * W <= (1 << 18) and C <= 4:
+                iso = isolated_call_times(data, C, H, W, flush_buf)
+        except Exception as exc:
+            print(f"[bench] isolated timing of the heavy calls failed: {exc}", file=sys.stderr)
+        for n_, ms in iso.items():
+            if n_ in ops_prof:
+                ops_prof[n_]["ms_per_call_isolated"] = ms
+        per_step = lambda n_: ops_prof[n_]["calls_per_step"] * ops_prof[n_].get("ms_per_call_isolated", ops_prof[n_]["ms_per_call"])
+        dominant = max(ops_prof, key=per_step) if ops_prof else None
         if dominant:
             p = ops_prof[dominant]
-            achieved = gb[dominant] / (p["ms_per_call"] * 1e-3) / 1e9
+            ms = p.get("ms_per_call_isolated", p["ms_per_call"])
+            achieved = gb[dominant] / (ms * 1e-3) / 1e9
             res["roofline"] = {"kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                                "frac": achieved / peak, "traffic": traffic_tab.get(dominant), "peak_source": peak_src,
-                               "algorithmic_bytes_per_launch": gb[dominant], "ms_per_launch": p["ms_per_call"],
-                               "share_of_step": p["ms_per_step"] / (total_ms / steps)}
+                               "algorithmic_bytes_per_launch": gb[dominant], "ms_per_launch": ms,
+                               "timed": "alone, CUDA-graph replay of 10 calls, L2 flushed before each replay" if "ms_per_call_isolated" in p
+                                        else "inside the instrumented eager pass (includes host launch gaps)",
+                               "share_of_step": per_step(dominant) / (total_ms / steps)}
         step_bytes = B * (ab["tree"] + ab["gcrf"])
         res["step_roofline"] = {"bound": "hbm", "algorithmic_bytes_per_step": step_bytes,
                                 "frac": step_bytes / (total_ms / steps * 1e-3) / 1e9 / peak, "peak": peak,

@@ -58,12 +58,15 @@ struct Ws {
     int2 *tmp;                      // [B,V]  per level, unordered: (preorder, vertex)
     int *pos;                       // [B,V]  BFS position of a vertex
     int *hist;                      // [B,NTILE,32] chain order: vertices per (1024-wide preorder tile, light depth)   (zeroed per call)
+    unsigned long long *scan_state; // [B,NSCAN]    chain order: look-back words of the single-pass tour scan             (zeroed per call)
+    int *scan_ticket;               // [B]          chain order: tile tickets of that scan                                (zeroed per call)
 };
 
 struct Dims {
     int root;  // the vertex the order starts from (0 = the reference's, bfs.cu:69-74)
     int B, V, H, W, SP, SPLOG, NS, T, NBLK, SPC;  // T = 2(V-1) arcs on the tour; NBLK = ceil(T / 1024); SPC splitters per walk CTA
     int NTILE;                                    // ceil(V / 1024)
+    int NSCAN;                                    // ceil(T / 2048), at least 1: tiles of the single-pass tour scan
 };
 
 size_t ws_layout(const Dims &d, char *base, Ws *w) {
@@ -77,7 +80,9 @@ size_t ws_layout(const Dims &d, char *base, Ws *w) {
     Ws t;
     t.cnt = (int *)take(B * (V + 1) * 4);      // cnt and cursor first and adjacent: one memset clears both
     t.cursor = (int *)take(B * (V + 1) * 4);
-    t.hist = (int *)take(B * (size_t)d.NTILE * 32 * 4);   // directly ahead of arc: the chain order clears hist + arc at once
+    t.hist = (int *)take(B * (size_t)d.NTILE * 32 * 4);   // hist .. arc are one range: the chain order clears it at once
+    t.scan_state = (unsigned long long *)take(B * (size_t)d.NSCAN * 8);
+    t.scan_ticket = (int *)take(B * 4);
     t.arc = (unsigned *)take(B * 4 * V * 4);
     t.snext = (int *)take(B * d.NS * 4);
     t.slen = (int *)take(B * d.NS * 4);
@@ -112,6 +117,7 @@ Dims make_dims(int B, int H, int W, int root = 0) {
     d.T = 2 * (d.V - 1);
     d.NBLK = (d.T + 1023) / 1024;
     d.NTILE = (d.V + 1023) / 1024;
+    d.NSCAN = d.T > 0 ? (d.T + 2047) / 2048 : 1;
     d.SPC = split_per_cta();
     return d;
 }
@@ -538,98 +544,179 @@ __device__ __forceinline__ int heavy_dir(unsigned m, int pd, const int *__restri
     return best;
 }
 
-// tour-ordered increments: x = +-o with o(u) = 1 + sizes of the siblings visited before u when the heavy child goes
-// first and the light ones follow by increasing id;  y = (u << 1 | light(u)) where the tour enters u, -(1 + light(u))
-// where it leaves
-__global__ void __launch_bounds__(NT) chain_increments_kernel(const unsigned char *__restrict__ mask, Ws ws, Dims dm) {
+// Tour entries of the chain order: x = +-o with o(u) = 1 + sizes of the siblings visited before u when the heavy child
+// goes first and the light ones follow by increasing id;  y = (u << 1 | light(u)) where the tour enters u,
+// -(1 + light(u)) where it leaves.
+__device__ __forceinline__ int2 chain_delta(int2 s) {   // (d light depth, d preorder) of one tour entry
+    return make_int2(s.y >= 0 ? (s.y & 1) : (s.y + 1), s.x);
+}
+
+// ---- chain order, steps 2 + 3a in one pass over the vertices: where the tour enters and leaves u (as enter_leave_kernel),
+// then -- straight from the arc ranks around u's parent, without waiting for a size array -- the subtree sizes of u's
+// siblings, the parent's heavy child, and u's two tour entries.
+__global__ void __launch_bounds__(NT) chain_enter_kernel(const unsigned char *__restrict__ mask, Ws ws, Dims dm) {
     const long long idx = (long long)blockIdx.x * NT + threadIdx.x;
     if (idx >= (long long)dm.B * dm.V) return;
     const int b = (int)(idx / dm.V), u = (int)(idx - (long long)b * dm.V), V = dm.V, W = dm.W;
-    if (u == dm.root) return;
+    const unsigned *arc = ws.arc + (size_t)b * 4 * V;
+    const int *sbase = ws.sbase + (size_t)b * dm.NS;
     const size_t o = (size_t)b * V;
-    const int pd = ws.pdir[o + u], p = u + dir_delta(pd, W), du = 3 - pd;  // u is p's child in direction du
-    int sz[4];
-    const int hd = heavy_dir(mask[o + p], ws.pdir[o + p], ws.size + o, p, W, sz);
+    if (u == dm.root) {
+        ws.pdir[o + u] = 4;
+        ws.size[o + u] = V;
+        return;
+    }
+    const unsigned m = mask[o + u];
+    int rin = 0x7fffffff, pd = 0;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        if (m & (1u << d)) {
+            const int r = arc_rank_raw(arc, sbase, 4 * (u + dir_delta(d, W)) + (3 - d));   // the arc neighbour -> u
+            if (r < rin) { rin = r; pd = d; }
+        }
+    }
+    const int rout = arc_rank_raw(arc, sbase, 4 * u + pd);
+    ws.pdir[o + u] = pd;
+    ws.size[o + u] = (rout - rin + 1) >> 1;
+    // around the parent: ranks of the arcs into p (the smallest one comes from p's parent) and out of p
+    const int p = u + dir_delta(pd, W), du = 3 - pd;
+    const unsigned mp = mask[o + p];
+    int pin[4], pout[4], ppd = 4, pmin = 0x7fffffff;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        pin[d] = pout[d] = 0;
+        if (mp & (1u << d)) {
+            pin[d] = (d == du) ? rout : arc_rank_raw(arc, sbase, 4 * (p + dir_delta(d, W)) + (3 - d));
+            pout[d] = (d == du) ? rin : arc_rank_raw(arc, sbase, 4 * p + d);
+            if (p != dm.root && pin[d] < pmin) { pmin = pin[d]; ppd = d; }
+        }
+    }
+    int sz[4], hd = -1, hsz = 0;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        sz[d] = ((mp >> d) & 1u) && d != ppd ? (pin[d] - pout[d] + 1) >> 1 : 0;
+        if (sz[d] > hsz) { hsz = sz[d]; hd = d; }
+    }
     int offs = 1, light = 0;
     if (hd != du) {
         light = 1;
-        offs += sz[hd];
+        offs += hsz;
 #pragma unroll
         for (int d = 0; d < 3; ++d)
             if (d < du && d != hd) offs += sz[d];
     }
     int2 *S = ws.S + (size_t)b * 2 * V;
-    S[ws.rin[o + u]] = make_int2(offs, (u << 1) | light);
-    S[ws.rout[o + u]] = make_int2(-offs, -(1 + light));
+    S[rin] = make_int2(offs, (u << 1) | light);
+    S[rout] = make_int2(-offs, -(1 + light));
 }
 
-__device__ __forceinline__ int2 chain_delta(int2 s) {   // (d light depth, d preorder) of one tour entry
-    return make_int2(s.y >= 0 ? (s.y & 1) : (s.y + 1), s.x);
+// ---- chain order, step 3b: prefix sums along the tour in ONE pass (tiles of 2048 entries handed out by ticket, each
+// publishing its aggregate and then its inclusive prefix in one self-validating 64-bit word; a tile looks back over its
+// predecessors' words instead of waiting for a separate scan-of-sums launch), keys and histogram written on the way.
+constexpr int SCAN_NT = 256, SCAN_PER = 8, SCAN_TILE = SCAN_NT * SCAN_PER;
+__device__ __forceinline__ unsigned long long scan_pack(unsigned flag, int ld, int pre) {
+    return ((unsigned long long)flag << 62) | ((unsigned long long)(unsigned)(ld & 0xffff) << 32) | (unsigned)pre;
 }
-
-__global__ void __launch_bounds__(1024) chain_block_sum_kernel(Ws ws, Dims dm) {
-    const int b = blockIdx.y, blk = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int r = blk * 1024 + tid;
-    int2 v = make_int2(0, 0);
-    if (r < dm.T) v = chain_delta(ws.S[(size_t)b * 2 * dm.V + r]);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
-        v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
-    }
-    __shared__ int2 s_w[32];
-    if (lane == 0) s_w[wid] = v;
+__device__ __forceinline__ int2 scan_unpack(unsigned long long w) {
+    return make_int2((int)(short)((w >> 32) & 0xffffu), (int)(unsigned)(w & 0xffffffffull));
+}
+__global__ void __launch_bounds__(SCAN_NT) chain_scan_kernel(Ws ws, Dims dm) {
+    const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = dm.V;
+    __shared__ int s_blk;
+    __shared__ int2 s_w[SCAN_NT / 32], s_excl;
+    if (tid == 0) s_blk = atomicAdd(ws.scan_ticket + b, 1);
     __syncthreads();
-    if (wid == 0) {
-        int2 t = s_w[lane];
+    const int blk = s_blk;
+    const int2 *S = ws.S + (size_t)b * 2 * V;
+    const int r0 = blk * SCAN_TILE + tid * SCAN_PER;
+    int2 e[SCAN_PER], x[SCAN_PER];
+    int2 run = make_int2(0, 0);
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            t.x += __shfl_xor_sync(0xffffffffu, t.x, o);
-            t.y += __shfl_xor_sync(0xffffffffu, t.y, o);
+    for (int k = 0; k < SCAN_PER; k += 2) {
+        if (r0 + k + 1 < dm.T) {
+            const int4 q = *reinterpret_cast<const int4 *>(S + r0 + k);
+            e[k] = make_int2(q.x, q.y);
+            e[k + 1] = make_int2(q.z, q.w);
+        } else {
+            e[k] = (r0 + k < dm.T) ? S[r0 + k] : make_int2(0, -1);
+            e[k + 1] = make_int2(0, -1);
         }
-        if (lane == 0) ws.bsum[(size_t)b * dm.NBLK + blk] = t;
     }
-}
-
-// prefix sums along the tour: where it enters u the inclusive sums are (ld(u), heavy-first preorder index of u);
-// key[preorder] = u << 5 | ld, and the (preorder tile, ld) histogram that the placement needs
-__global__ void __launch_bounds__(1024) chain_apply_kernel(Ws ws, Dims dm) {
-    const int b = blockIdx.y, blk = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = dm.V;
-    const int r = blk * 1024 + tid;
-    int2 sp = make_int2(0, -1);
-    bool enter = false;
-    if (r < dm.T) { sp = ws.S[(size_t)b * 2 * V + r]; enter = sp.y >= 0; }
-    int2 x = (r < dm.T) ? chain_delta(sp) : make_int2(0, 0);
+#pragma unroll
+    for (int k = 0; k < SCAN_PER; ++k) {
+        const int2 d = (r0 + k < dm.T) ? chain_delta(e[k]) : make_int2(0, 0);
+        run.x += d.x;
+        run.y += d.y;
+        x[k] = run;                       // inclusive inside the thread
+    }
+    int2 t = run;                         // inclusive over the warp's threads
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        const int tx = __shfl_up_sync(0xffffffffu, x.x, o), ty = __shfl_up_sync(0xffffffffu, x.y, o);
-        if (lane >= o) { x.x += tx; x.y += ty; }
+        const int tx = __shfl_up_sync(0xffffffffu, t.x, o), ty = __shfl_up_sync(0xffffffffu, t.y, o);
+        if (lane >= o) { t.x += tx; t.y += ty; }
     }
-    __shared__ int2 s_w[32];
-    if (lane == 31) s_w[wid] = x;
+    if (lane == 31) s_w[wid] = t;
     __syncthreads();
-    if (wid == 0) {
-        int2 t = s_w[lane], y = t;
+    int2 woff = make_int2(0, 0), agg = make_int2(0, 0);
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int tx = __shfl_up_sync(0xffffffffu, y.x, o), ty = __shfl_up_sync(0xffffffffu, y.y, o);
-            if (lane >= o) { y.x += tx; y.y += ty; }
+    for (int w2 = 0; w2 < SCAN_NT / 32; ++w2) {
+        const int2 v = s_w[w2];
+        if (w2 < wid) { woff.x += v.x; woff.y += v.y; }
+        agg.x += v.x;
+        agg.y += v.y;
+    }
+    unsigned long long *state = ws.scan_state + (size_t)b * dm.NSCAN;
+    if (wid == 0) {   // publish the aggregate, look back for the exclusive prefix, publish the inclusive prefix
+        int2 excl = make_int2(0, 0);
+        if (blk > 0) {
+            if (lane == 0) asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(state + blk), "l"(scan_pack(1u, agg.x, agg.y)));
+            int j = blk - 1;
+            while (true) {
+                const int mine = j - lane;
+                unsigned long long wv = 3ull << 62;   // lanes before the first tile: "inclusive, zero"
+                if (mine >= 0) {
+                    do {
+                        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(wv) : "l"(state + mine));
+                    } while ((wv >> 62) == 0);
+                }
+                const unsigned fl = (unsigned)(wv >> 62);
+                const unsigned done = __ballot_sync(0xffffffffu, fl >= 2u);
+                const int stop = done ? __ffs(done) - 1 : 31;          // nearest tile with an inclusive prefix
+                int2 v = scan_unpack(wv);
+                if (lane > stop || fl == 3u) v = make_int2(0, 0);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+                    v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+                }
+                excl.x += v.x;
+                excl.y += v.y;
+                if (done) break;
+                j -= 32;
+            }
         }
-        s_w[lane] = make_int2(y.x - t.x, y.y - t.y);
+        if (lane == 0) {
+            asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(state + blk), "l"(scan_pack(2u, excl.x + agg.x, excl.y + agg.y)));
+            s_excl = excl;
+        }
     }
     __syncthreads();
+    const int2 excl = s_excl;
+    int2 before = make_int2(excl.x + woff.x + t.x - run.x, excl.y + woff.y + t.y - run.y);   // everything ahead of this thread
     int *key = ws.depth + (size_t)b * V;                     // reused: [B,V] keys in preorder
     int *hist = ws.hist + (size_t)b * dm.NTILE * 32;
     if (blk == 0 && tid == 0) {  // the root is never entered
         key[0] = dm.root << 5;
         atomicAdd(hist, 1);
     }
-    if (enter) {
-        const int2 base = (dm.NBLK > 0) ? ws.bsum[(size_t)b * dm.NBLK + blk] : make_int2(0, 0), wo = s_w[wid];
-        const int ld = min(base.x + wo.x + x.x, 31), pre = base.y + wo.y + x.y;
-        if (pre >= 0 && pre < V) {               // always, for a consistent tree mask
-            key[pre] = ((sp.y >> 1) << 5) | ld;
-            atomicAdd(hist + (pre >> 10) * 32 + ld, 1);
+#pragma unroll
+    for (int k = 0; k < SCAN_PER; ++k) {
+        if (r0 + k < dm.T && e[k].y >= 0) {   // the tour enters vertex e.y >> 1 here
+            const int ld = min(before.x + x[k].x, 31), pre = before.y + x[k].y;
+            if (pre >= 0 && pre < V) {         // always, for a consistent tree mask
+                key[pre] = ((e[k].y >> 1) << 5) | ld;
+                atomicAdd(hist + (pre >> 10) * 32 + ld, 1);
+            }
         }
     }
 }
@@ -742,7 +829,8 @@ __global__ void __launch_bounds__(NT) chain_finalize_kernel(const unsigned char 
 }
 
 // Euler tour of every tree ranked, entering / leaving ranks, parent direction and subtree size of every vertex
-int run_tour(const unsigned char *tree_mask, const Ws &ws, const Dims &dm, cudaStream_t st, const char *who) {
+int run_tour(const unsigned char *tree_mask, const Ws &ws, const Dims &dm, cudaStream_t st, const char *who,
+             bool with_enter_leave = true) {
     const int B = dm.B, V = dm.V;
     const unsigned vb = (unsigned)(((long long)B * V + NT - 1) / NT);
     const size_t smem_mask = (size_t)(V + 1) / 2;
@@ -760,8 +848,10 @@ int run_tour(const unsigned char *tree_mask, const Ws &ws, const Dims &dm, cudaS
     if (e != cudaSuccess) return fedicra_fail(-2, "%s: shared memory: %s", who, cudaGetErrorString(e));
     rank_splitters_kernel<<<B, 1024, smem_rank, st>>>(ws, dm);
     FEDICRA_CHECK_LAUNCH("rank_splitters_kernel");
-    enter_leave_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm);
-    FEDICRA_CHECK_LAUNCH("enter_leave_kernel");
+    if (with_enter_leave) {
+        enter_leave_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm);
+        FEDICRA_CHECK_LAUNCH("enter_leave_kernel");
+    }
     return 0;
 }
 
@@ -848,17 +938,11 @@ int chain_order_impl(const unsigned char *tree_mask, int B, int H, int W, int *s
     cudaError_t e = cudaMemsetAsync(ws.hist, 0, (size_t)((char *)ws.snext - (char *)ws.hist), st);
     if (e != cudaSuccess) return fedicra_fail(-2, "chain_order: memset: %s", cudaGetErrorString(e));
     const unsigned vb = (unsigned)(((long long)B * V + NT - 1) / NT);
-    if (int rc = run_tour(tree_mask, ws, dm, st, "chain_order")) return rc;
-    if (dm.T > 0) {
-        chain_increments_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm);
-        FEDICRA_CHECK_LAUNCH("chain_increments_kernel");
-        chain_block_sum_kernel<<<dim3(dm.NBLK, B), 1024, 0, st>>>(ws, dm);
-        FEDICRA_CHECK_LAUNCH("chain_block_sum_kernel");
-        tour_scan_sums_kernel<<<B, 1024, 0, st>>>(ws, dm);
-        FEDICRA_CHECK_LAUNCH("tour_scan_sums_kernel");
-    }
-    chain_apply_kernel<<<dim3(dm.NBLK > 0 ? dm.NBLK : 1, B), 1024, 0, st>>>(ws, dm);
-    FEDICRA_CHECK_LAUNCH("chain_apply_kernel");
+    if (int rc = run_tour(tree_mask, ws, dm, st, "chain_order", false)) return rc;
+    chain_enter_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm);
+    FEDICRA_CHECK_LAUNCH("chain_enter_kernel");
+    chain_scan_kernel<<<dim3(dm.NSCAN, B), SCAN_NT, 0, st>>>(ws, dm);
+    FEDICRA_CHECK_LAUNCH("chain_scan_kernel");
     chain_offsets_kernel<<<B, 1024, 0, st>>>(ws, dm, group_start);
     FEDICRA_CHECK_LAUNCH("chain_offsets_kernel");
     chain_place_kernel<<<dim3(dm.NTILE, B), 1024, 0, st>>>(ws, dm, group_start, sorted_index);
