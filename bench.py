@@ -495,6 +495,10 @@ def measure_workload(name, steps, warmup, dev, rank, world, use_graph, flush_buf
                                "timed": "alone, CUDA-graph replay of 10 calls, L2 flushed before each replay" if "ms_per_call_isolated" in p
                                         else "inside the instrumented eager pass (includes host launch gaps)",
                                "share_of_step": per_step(dominant) / (total_ms / steps)}
+        res["heavy_calls"] = {n_: {"ms_per_call": ms, "calls_per_step": ops_prof[n_]["calls_per_step"],
+                                   "algorithmic_bytes_per_call": gb[n_], "GBps": gb[n_] / (ms * 1e-3) / 1e9,
+                                   "frac_of_hbm_peak": gb[n_] / (ms * 1e-3) / 1e9 / peak, "traffic": traffic_tab.get(n_)}
+                              for n_, ms in iso.items() if n_ in ops_prof}
         step_bytes = B * (ab["tree"] + ab["gcrf"])
         res["step_roofline"] = {"bound": "hbm", "algorithmic_bytes_per_step": step_bytes,
                                 "frac": step_bytes / (total_ms / steps * 1e-3) / 1e9 / peak, "peak": peak,
@@ -542,7 +546,7 @@ def run_ours(args):
             keep = {"describes": r["desc"], "value": r["value"], "unit": "images/s", "ms_per_step": r["ms_per_step"],
                     "eager_ms_per_step": r["eager_ms_per_step"], "e2e": r["e2e"], "steps": max(3, args.steps // 4)}
             if "roofline" in r:
-                keep.update({"roofline": r["roofline"], "step_roofline": r["step_roofline"],
+                keep.update({"roofline": r["roofline"], "step_roofline": r["step_roofline"], "heavy_calls": r.get("heavy_calls"),
                              "kernel_groups": {k: round(v["ms_per_step"], 4) for k, v in r["kernel_groups"].items()}})
             extras[name] = keep
     if world > 1:
@@ -583,6 +587,7 @@ def run_ours(args):
         "roofline": main.get("roofline"),
         "step_roofline": main.get("step_roofline"),
         "kernel_groups": main.get("kernel_groups"),
+        "heavy_calls": main.get("heavy_calls"),
         "cpu_baseline": cpu,
         "reference_gpu": ref_gpu_blk,
         "extra_workloads": extras,
