@@ -432,29 +432,36 @@ def measure_workload(name, steps, warmup, dev, rank, world, use_graph, flush_buf
     barrier()
     serial_ms = rank_max(sum(time_steps(serial_e2e, min(steps, 10), flush_buf))) / min(steps, 10)
     d2h = 4 + sum(g.numel() * g.element_size() for g in grads_host)
-    e2e_ms, pipelined = serial_ms, False
+    e2e_ms, pipelined, loss_only_ms = serial_ms, False, None
     if graphed:
-        try:
-            pipe = PipelinedLossStack(eager_step, data, depth=2)
-            for _ in pipe.run([pinned] * 4):
-                pass
-            barrier()
-            flush_l2(flush_buf)
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()          # host clock: the pipeline spans three streams
-            n = 0
-            for loss, grads in pipe.run([pinned] * steps):
-                n += 1
-            torch.cuda.synchronize()
-            e2e_ms = rank_max((time.perf_counter() - t0) * 1e3) / steps
-            pipelined = True
-            barrier()
-            pipe.reset()
-        except Exception as exc:
-            print(f"[bench] pipelined end-to-end run failed, reporting the serial one: {exc}", file=sys.stderr)
+        for copy_grads in (True, False):
+            try:
+                pipe = PipelinedLossStack(eager_step, data, depth=2, copy_gradients=copy_grads)
+                for _ in pipe.run([pinned] * 4):
+                    pass
+                barrier()
+                flush_l2(flush_buf)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()          # host clock: the pipeline spans three streams
+                for loss, grads in pipe.run([pinned] * steps):
+                    pass
+                torch.cuda.synchronize()
+                ms = rank_max((time.perf_counter() - t0) * 1e3) / steps
+                if copy_grads:
+                    e2e_ms, pipelined = ms, True
+                else:
+                    loss_only_ms = ms
+                barrier()
+                pipe.reset()
+            except Exception as exc:
+                print(f"[bench] pipelined end-to-end run failed, reporting the serial one: {exc}", file=sys.stderr)
     res["e2e"] = {"value": B * world / (e2e_ms * 1e-3), "unit": "images/s", "h2d_bytes_per_step": h2d,
                   "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "serial_ms_per_step": serial_ms,
                   "pipelined": pipelined,
+                  "loss_only": None if loss_only_ms is None else {
+                      "value": B * world / (loss_only_ms * 1e-3), "ms_per_step": loss_only_ms, "d2h_bytes_per_step": 4,
+                      "note": "same pipeline, every input from the host every step, only the loss read back (in a "
+                              "training loop the gradients stay on the device)"},
                   "how": "fedicra_b200.PipelinedLossStack: two graphed copies of the step, H2D of step k+1 and D2H of step "
                          "k-1 on side streams under the replay of step k; host wall clock over all steps" if pipelined
                          else "serial: H2D, replay, D2H on one stream"}

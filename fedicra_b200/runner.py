@@ -29,10 +29,12 @@ class LossStackStep:
     included); by default this package's."""
 
     def __init__(self, num_classes, height, width, tree_weight=0.1, crf_weight=0.1, distributed=False, world=1,
-                 tel=None, crf=None):
+                 tel=None, crf=None, local_share=True):
         self.C, self.H, self.W = num_classes, height, width
         self.tree_weight = tree_weight
-        self.tel = tel if tel is not None else MScaleRecurveTreeEnergyLoss(distributed=distributed)
+        # sharded: the returned loss is this rank's share of the global loss (gradients are the global ones); the count
+        # of unlabelled pixels is all-reduced on a side stream under the step
+        self.tel = tel if tel is not None else MScaleRecurveTreeEnergyLoss(distributed=distributed, local_share=local_share)
         self.crf = crf if crf is not None else ModelLossSemsegGatedCRF()
         # Gated CRF normalises by the LOCAL N*H*W (gate_crf_loss.py:63); the global batch is `world` times larger
         self.crf_scale = crf_weight / world
@@ -92,7 +94,10 @@ class PipelinedLossStack:
     used again).  With depth 2 the copies of the neighbouring steps overlap the replay of the current one; every step
     still moves all its inputs in and all its outputs out."""
 
-    def __init__(self, step, example, depth=2):
+    def __init__(self, step, example, depth=2, copy_gradients=True):
+        """copy_gradients=False: only the loss travels back to the host every step (in a training loop the gradients
+        are consumed on the device by the network's backward); the inputs still come from the host every step."""
+        self.copy_gradients = copy_gradients
         self.slots = []
         self.h2d, self.d2h = torch.cuda.Stream(), torch.cuda.Stream()
         self.compute = torch.cuda.current_stream()
@@ -105,7 +110,7 @@ class PipelinedLossStack:
                                "out_ready": torch.cuda.Event(), "busy": False})
         self.next, self.pending = 0, []
         self.h2d_bytes = sum(v.numel() * v.element_size() for v in example.values())
-        self.d2h_bytes = 4 + sum(x.numel() * x.element_size() for x in self.slots[0]["g"].grads)
+        self.d2h_bytes = 4 + (sum(x.numel() * x.element_size() for x in self.slots[0]["g"].grads) if copy_gradients else 0)
 
     def submit(self, pinned):
         s = self.slots[self.next % len(self.slots)]
@@ -124,8 +129,9 @@ class PipelinedLossStack:
         self.d2h.wait_event(s["computed"])
         with torch.cuda.stream(self.d2h):
             s["host_loss"].copy_(g.loss.reshape(1), non_blocking=True)
-            for h, x in zip(s["host_grads"], g.grads):
-                h.copy_(x, non_blocking=True)
+            if self.copy_gradients:
+                for h, x in zip(s["host_grads"], g.grads):
+                    h.copy_(x, non_blocking=True)
             s["out_ready"].record(self.d2h)
         s["busy"] = True
         self.pending.append(s)

@@ -24,3 +24,27 @@ def sharded_masked_l1(local_sum, local_n, group=None):
     dist.all_reduce(pair, op=dist.ReduceOp.SUM, group=group)
     # value = global sum / max(global N, 1); the gradient flows through this rank's share only (no host sync)
     return (local_sum + (pair[0] - local_sum.detach())) / torch.clamp(pair[1], min=1.0)
+
+
+class GlobalCount:
+    """The global normaliser N = ROI.sum() over all ranks, fetched AHEAD of the step: N depends on the labels alone, so
+    its all-reduce can run on a side stream while the trees and filters of the step are computed, and nothing is left
+    between the forward and the backward pass.  `start(roi)` launches it, `get()` joins and returns the [1] tensor."""
+
+    def __init__(self, group=None):
+        self.group, self.side, self.value = group, None, None
+
+    def start(self, roi):
+        main = torch.cuda.current_stream()
+        if self.side is None:
+            self.side = torch.cuda.Stream()
+        self.side.wait_stream(main)
+        with torch.cuda.stream(self.side):
+            self.value = roi.sum(dtype=torch.float32).reshape(1)
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+                dist.all_reduce(self.value, op=dist.ReduceOp.SUM, group=self.group)
+        return self
+
+    def get(self):
+        torch.cuda.current_stream().wait_stream(self.side)
+        return self.value

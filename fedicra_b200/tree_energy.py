@@ -98,12 +98,17 @@ class _MaskedL1(torch.autograd.Function):
         return gp, gf, None, None
 
 
-def _masked_l1(roi, prob, filtered, n, distributed=False, weight=1.0, roi_u8=None):
-    """weight * (roi * |prob - filtered|).sum() / N   (N over the global batch when `distributed`)."""
+def _masked_l1(roi, prob, filtered, n, distributed=False, weight=1.0, roi_u8=None, n_global=None):
+    """weight * (roi * |prob - filtered|).sum() / N   (N over the global batch when `distributed`).  With `n_global` (a
+    sharding.GlobalCount started before the step) the value is this rank's SHARE of the global loss -- local sum over
+    global N; the shares of all ranks add up to the reference's value, the gradients are the reference's -- and no
+    collective sits between forward and backward."""
     if isinstance(weight, torch.Tensor):   # keep a tensor weight on the device: scale outside the kernel
-        return weight * _masked_l1(roi, prob, filtered, n, distributed, 1.0, roi_u8)
+        return weight * _masked_l1(roi, prob, filtered, n, distributed, 1.0, roi_u8, n_global)
     if roi_u8 is not None and prob.is_cuda and prob.dtype == torch.float32 and filtered.dtype == torch.float32:
         loss, sums = _MaskedL1.apply(prob.contiguous(), filtered.contiguous(), roi_u8, weight)
+        if n_global is not None:
+            return weight * sums[0] / torch.clamp(n_global.get()[0], min=1.0)
         if not distributed:
             return loss
         return weight * _normalise(sums[0], sums[1].detach(), True)
@@ -111,10 +116,20 @@ def _masked_l1(roi, prob, filtered, n, distributed=False, weight=1.0, roi_u8=Non
 
 
 class _TreeLossBase(nn.Module):
-    def __init__(self, distributed=False):
-        """distributed=True: the batch is one shard of a global batch split by image over torch.distributed ranks."""
+    def __init__(self, distributed=False, local_share=False):
+        """distributed=True: the batch is one shard of a global batch split by image over torch.distributed ranks; the
+        returned loss is the GLOBAL value (one 2-scalar all-reduce between forward and backward).  With
+        local_share=True it is this rank's share of it (the shares add up to the global value, gradients identical) and
+        the only collective, the count of unlabelled pixels, runs on a side stream under the step."""
         super().__init__()
         self.distributed = distributed
+        self.local_share = bool(distributed and local_share)
+
+    def _count(self, roi_u8):
+        if not (self.local_share and roi_u8 is not None):
+            return None
+        from .sharding import GlobalCount
+        return GlobalCount().start(roi_u8)
         self.mst_layers = MinimumSpanningTree(TreeFilter2D.norm2_distance)
         self.tree_filter_layers = TreeFilter2D(groups=1, sigma=0.02)
 
@@ -166,6 +181,7 @@ class MScaleAddTreeEnergyLoss(_TreeLossBase):
 class MScaleRecurveTreeEnergyLoss(_TreeLossBase):
     def forward(self, preds, low_feats, high_feats_1, high_feats_2, high_feats_3, unlabeled_ROIs, weight):
         low_feats, roi, n, roi_u8 = _prepare(preds, low_feats, unlabeled_ROIs)
+        n_global = self._count(roi_u8)
         h, w = preds.shape[2:]
         prob = _softmax(preds)
         highs = [_resize(hf, h, w) for hf in (high_feats_1, high_feats_2, high_feats_3)]
@@ -175,4 +191,4 @@ class MScaleRecurveTreeEnergyLoss(_TreeLossBase):
         for hf, t in zip(highs, trees[1:]):
             cur = self._high(cur, hf, h, w, t)
             outs.append(cur)
-        return (_masked_l1(roi, prob, cur, n, self.distributed, weight, roi_u8), *outs)
+        return (_masked_l1(roi, prob, cur, n, self.distributed, weight, roi_u8, n_global), *outs)

@@ -49,3 +49,23 @@ def test_two_shards_with_a_shared_normaliser_equal_the_whole_batch(monkeypatch):
         whole = xs_all[i].grad
         got = torch.cat([grads[0][i], grads[1][i]], 0)
         assert rel_err(got.cpu(), whole.cpu()) < 1e-4, name
+
+
+def test_local_share_mode_with_the_count_fetched_on_a_side_stream_equals_the_plain_loss():
+    """distributed + local_share: N comes from sharding.GlobalCount (side stream, started before the trees are built);
+    with one rank the share is the whole loss, gradients included."""
+    import fedicra_b200 as fb
+    B, C, H, W = 3, 2, 64, 96
+    image, logits, a1, a2, a3, label = loss_inputs(B, C, 1, H, W, "quant8", seed=4)
+    three = image.repeat(1, 3, 1, 1).cuda()
+    roi = (label == C).cuda()
+    res = []
+    for kw in ({}, {"distributed": True, "local_share": True}):
+        xs = [t.clone().cuda().requires_grad_() for t in (logits, a1, a2, a3)]
+        out = fb.MScaleRecurveTreeEnergyLoss(**kw)(xs[0], three, xs[1], xs[2], xs[3], roi, 0.1)
+        out[0].backward()
+        torch.cuda.synchronize()
+        res.append((out[0].detach().cpu(), [x.grad.cpu() for x in xs]))
+    assert rel_err(res[1][0], res[0][0]) < 1e-6
+    for a, b in zip(res[1][1], res[0][1]):
+        assert rel_err(a, b) < 1e-5
