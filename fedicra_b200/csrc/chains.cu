@@ -83,14 +83,17 @@ __device__ __forceinline__ bool pending(float v) { return __float_as_uint(v) == 
 __device__ __forceinline__ void keep(float x) { asm volatile("" ::"f"(x)); }
 __device__ __forceinline__ void keep(int x) { asm volatile("" ::"r"(x)); }
 
-// Spin control: every item waits only for items with smaller tickets, which are running, so a wait ends; the bound
-// (about a second) turns a corrupted buffer into a counted error instead of a hang.
+// Spin control: every item waits only for items with smaller tickets, which are running, so a wait ends within
+// microseconds; the bound (2e10 cycles, about ten seconds -- generous, because wall time also passes while the context is
+// time-sliced with other processes or stopped under a debugger) turns a corrupted buffer into a counted error instead of
+// a hang.  A feature value with the bit pattern 0xFFFFFFFF (a NaN that arithmetic never produces but passes on) would
+// look "pending" for ever and end the same way.
 struct Spin {
     long long t0 = 0;
     __device__ __forceinline__ bool again(int *sync) {
         __nanosleep(20);
         if (t0 == 0) { t0 = clock64(); return true; }
-        if (clock64() - t0 > 2000000000ll) { atomicAdd(sync + 1, 1); return false; }
+        if (clock64() - t0 > 20000000000ll) { atomicAdd(sync + 1, 1); return false; }
         return true;
     }
 };

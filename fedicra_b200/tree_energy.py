@@ -124,14 +124,14 @@ class _TreeLossBase(nn.Module):
         super().__init__()
         self.distributed = distributed
         self.local_share = bool(distributed and local_share)
+        self.mst_layers = MinimumSpanningTree(TreeFilter2D.norm2_distance)
+        self.tree_filter_layers = TreeFilter2D(groups=1, sigma=0.02)
 
     def _count(self, roi_u8):
         if not (self.local_share and roi_u8 is not None):
             return None
         from .sharding import GlobalCount
         return GlobalCount().start(roi_u8)
-        self.mst_layers = MinimumSpanningTree(TreeFilter2D.norm2_distance)
-        self.tree_filter_layers = TreeFilter2D(groups=1, sigma=0.02)
 
     def _trees(self, embeds):
         """Topology of all the embeddings of this step at once (they do not depend on the filter chain), and with it the
