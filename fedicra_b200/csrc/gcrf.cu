@@ -13,6 +13,11 @@
 // xy_q = 0, I_q = 0, y_q = 0; it adds exp(-0.5*|f_p|^2) to sum K and nothing to agg.
 //
 // Roofline: 120 ex2 + ~120*(2Cin+C+3) FP32 ops per pixel against (2C+Cin)*4 bytes -> MUFU/FP32-pipe bound, not HBM.
+#include <cuda.h>   // CUtensorMap (types only: the encoder is looked up through the runtime, no -lcuda)
+#include <mutex>
+#include <stdlib.h>
+#include <string.h>
+
 #include "common.cuh"
 
 namespace {
@@ -22,6 +27,8 @@ constexpr int TH = 16;          // tile height (pixels)
 constexpr int PX = 4;           // pixels per thread along x
 constexpr int BX = TW / PX;     // 8 threads along x
 constexpr int NT = BX * TH;     // 128 threads
+constexpr int XOFF = 8;         // halo columns kept left of the tile in shared memory: a multiple of 4 floats, because a
+                               // tensor-map copy must start on a 16-byte boundary of the image row (the window needs 5)
 constexpr float LOG2E = 1.4426950408889634f;
 
 struct FastParams {
@@ -72,8 +79,11 @@ template <int C, int CIN, int R, bool BORDER>
 __device__ __forceinline__ float gcrf_tile_body(const float *s_img, const float *s_y, float *grad, int n, int x0,
                                                 int y0, int H, int W, FastParams prm, float gscale) {
     constexpr int HH = TH + 2 * R;
-    constexpr int PITCH = (TW + 2 * R + 3) / 4 * 4;
-    constexpr int NV = (PX + 2 * R + 3) / 4 * 4;  // window row segment, padded to whole float4s
+    constexpr int PITCH = TW + 2 * XOFF;
+    constexpr int SHIFT = XOFF - R;               // the window row segment starts SHIFT columns into an aligned read
+    constexpr int NV4 = (PX + 2 * R + SHIFT) / 4; // whole float4s of that read; one scalar column follows
+    constexpr int NV = 4 * NV4 + 1;
+    static_assert(XOFF >= R && NV >= PX + 2 * R + SHIFT, "window segment does not fit the aligned read");
     const int tid = threadIdx.x, tx = tid % BX, ty = tid / BX;
     const int px0 = x0 + tx * PX, py = y0 + ty;
 
@@ -81,7 +91,7 @@ __device__ __forceinline__ float gcrf_tile_body(const float *s_img, const float 
 #pragma unroll
     for (int c = 0; c < CIN; ++c)
 #pragma unroll
-        for (int p = 0; p < PX; ++p) ip[c][p] = s_img[(c * HH + ty + R) * PITCH + tx * PX + R + p];
+        for (int p = 0; p < PX; ++p) ip[c][p] = s_img[(c * HH + ty + R) * PITCH + tx * PX + XOFF + p];
 
     float agg[C][PX], ks[PX], oob[PX];
 #pragma unroll
@@ -106,19 +116,21 @@ __device__ __forceinline__ float gcrf_tile_body(const float *s_img, const float 
         for (int c = 0; c < CIN; ++c) {
             const float4 *src = reinterpret_cast<const float4 *>(s_img + (c * HH + row) * PITCH + tx * PX);
 #pragma unroll
-            for (int v = 0; v < NV / 4; ++v) {
+            for (int v = 0; v < NV4; ++v) {
                 float4 t = src[v];
                 si[c][4 * v] = t.x; si[c][4 * v + 1] = t.y; si[c][4 * v + 2] = t.z; si[c][4 * v + 3] = t.w;
             }
+            si[c][4 * NV4] = s_img[(c * HH + row) * PITCH + tx * PX + 4 * NV4];
         }
 #pragma unroll
         for (int c = 0; c < C; ++c) {
             const float4 *src = reinterpret_cast<const float4 *>(s_y + (c * HH + row) * PITCH + tx * PX);
 #pragma unroll
-            for (int v = 0; v < NV / 4; ++v) {
+            for (int v = 0; v < NV4; ++v) {
                 float4 t = src[v];
                 sy[c][4 * v] = t.x; sy[c][4 * v + 1] = t.y; sy[c][4 * v + 2] = t.z; sy[c][4 * v + 3] = t.w;
             }
+            sy[c][4 * NV4] = s_y[(c * HH + row) * PITCH + tx * PX + 4 * NV4];
         }
         const float rterm = prm.axy * (float)(dy * dy);
         const bool row_in = BORDER ? (py + dy >= 0 && py + dy < H) : true;
@@ -127,7 +139,7 @@ __device__ __forceinline__ float gcrf_tile_body(const float *s_img, const float 
             const float base_in = rterm + cdx[dx < 0 ? -dx : dx];
 #pragma unroll
             for (int p = 0; p < PX; ++p) {
-                const int q = p + dx + R;
+                const int q = p + dx + R + SHIFT;
                 float d = 0.f;
 #pragma unroll
                 for (int c = 0; c < CIN; ++c) {
@@ -156,7 +168,7 @@ __device__ __forceinline__ float gcrf_tile_body(const float *s_img, const float 
         const bool ok = row_ok && (px0 + p < W);
         float dot = 0.f;
 #pragma unroll
-        for (int c = 0; c < C; ++c) dot = fmaf(s_y[(c * HH + ty + R) * PITCH + tx * PX + R + p], agg[c][p], dot);
+        for (int c = 0; c < C; ++c) dot = fmaf(s_y[(c * HH + ty + R) * PITCH + tx * PX + XOFF + p], agg[c][p], dot);
         part += ok ? (ks[p] - dot) : 0.f;
     }
     if (grad != nullptr && row_ok) {
@@ -176,31 +188,66 @@ __device__ __forceinline__ float gcrf_tile_body(const float *s_img, const float 
     return part;
 }
 
-template <int C, int CIN, int R>
+// ---- TMA staging.  The image tile and the prediction tile (each with its halo) are ONE 3-D box each of the tensors
+// viewed as [planes, H, W]: box = (PITCH, HH, channels), start = (x0 - XOFF, y0 - R, n * channels).  The tensor-map unit
+// zero-fills whatever lies outside the image -- exactly the zero padding of F.unfold (gate_crf_loss.py:183-188) -- and
+// lands the box in shared memory in the [channel][row][PITCH] layout the tile body reads.  One thread arms an mbarrier
+// with the byte count and issues the two copies; everybody waits on the barrier.  Needs W % 4 == 0 (16-byte row pitch).
+__device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, int c0, int c1, int c2, unsigned long long *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(smem_addr(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_addr(bar))
+        : "memory");
+}
+
+template <int C, int CIN, int R, bool TMA>
 __global__ void __launch_bounds__(NT, 3)
 gcrf_fast_kernel(const float *__restrict__ y, const float *__restrict__ img, float *__restrict__ grad,
                  float *partials, unsigned *ticket, float *loss, int H, int W, FastParams prm, float gscale,
-                 double inv_denom) {
+                 double inv_denom, const __grid_constant__ CUtensorMap map_img, const __grid_constant__ CUtensorMap map_y) {
     constexpr int HH = TH + 2 * R;
-    constexpr int HWID = TW + 2 * R;
-    constexpr int PITCH = (HWID + 3) / 4 * 4;
-    extern __shared__ float4 smem4[];
+    constexpr int PITCH = TW + 2 * XOFF;
+    constexpr int IMG_FLOATS = (CIN * HH * PITCH + 31) / 32 * 32;   // the second box starts 128-byte aligned
+    extern __shared__ __align__(128) float4 smem4[];
     float *s_img = reinterpret_cast<float *>(smem4);  // [CIN][HH][PITCH]
-    float *s_y = s_img + CIN * HH * PITCH;             // [C][HH][PITCH]
+    float *s_y = s_img + IMG_FLOATS;                   // [C][HH][PITCH]
     const int n = blockIdx.z, x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
 
-    // stage tile + halo, zero outside the image (coalesced along x)
-    for (int idx = threadIdx.x; idx < (CIN + C) * HH * PITCH; idx += NT) {
-        const int ch = idx / (HH * PITCH), rem = idx - ch * (HH * PITCH), r = rem / PITCH, c = rem - r * PITCH;
-        const int gy = y0 - R + r, gx = x0 - R + c;
-        float v = 0.f;
-        if (c < HWID && gy >= 0 && gy < H && gx >= 0 && gx < W) {
-            v = (ch < CIN) ? __ldg(img + (((size_t)n * CIN + ch) * H + gy) * W + gx)
-                           : __ldg(y + (((size_t)n * C + (ch - CIN)) * H + gy) * W + gx);
+    if (TMA) {
+        __shared__ __align__(8) unsigned long long s_bar;
+        if (threadIdx.x == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&s_bar)) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
-        s_img[idx] = v;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            constexpr unsigned BYTES = (unsigned)((C + CIN) * HH * PITCH * sizeof(float));
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&s_bar)), "r"(BYTES) : "memory");
+            tma_load_3d(s_img, &map_img, x0 - XOFF, y0 - R, n * CIN, &s_bar);
+            tma_load_3d(s_y, &map_y, x0 - XOFF, y0 - R, n * C, &s_bar);
+        }
+        unsigned done = 0;
+        for (unsigned spins = 0; !done; ++spins) {
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(done) : "r"(smem_addr(&s_bar)) : "memory");
+            if (spins > (1u << 26)) __trap();   // a copy that never lands (bad tensor map): fail the launch, do not hang
+        }
+    } else {
+        // stage tile + halo, zero outside the image (coalesced along x)
+        for (int idx = threadIdx.x; idx < (CIN + C) * HH * PITCH; idx += NT) {
+            const int ch = idx / (HH * PITCH), rem = idx - ch * (HH * PITCH), r = rem / PITCH, c = rem - r * PITCH;
+            const int gy = y0 - R + r, gx = x0 - XOFF + c;
+            float v = 0.f;
+            if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+                v = (ch < CIN) ? __ldg(img + (((size_t)n * CIN + ch) * H + gy) * W + gx)
+                               : __ldg(y + (((size_t)n * C + (ch - CIN)) * H + gy) * W + gx);
+            }
+            (ch < CIN ? s_img : s_y - CIN * HH * PITCH)[idx] = v;
+        }
+        __syncthreads();
     }
-    __syncthreads();
 
     const bool border = (x0 < R) || (y0 < R) || (x0 + TW + R > W) || (y0 + TH + R > H);
     float part;
@@ -270,15 +317,56 @@ gcrf_generic_kernel(const float *__restrict__ y, const float *__restrict__ img, 
     finish_loss(part, partials, ticket, loss, inv_denom);
 }
 
+// cuTensorMapEncodeTiled, looked up once through the runtime (the library does not link libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn tensor_map_encoder() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const char *off = getenv("FEDICRA_GCRF_TMA");
+        if (off && *off == '0') return;
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+// [planes, H, W] fp32 tensor, box (pitch, rows, channels), no swizzle, zeros outside
+bool make_tile_map(CUtensorMap *m, const float *base, int planes, int H, int W, int pitch, int rows, int channels) {
+    EncodeTiledFn enc = tensor_map_encoder();
+    if (enc == nullptr || (W & 3) != 0 || ((uintptr_t)base & 15) != 0) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)planes};
+    const cuuint64_t strides[2] = {(cuuint64_t)W * 4, (cuuint64_t)W * H * 4};
+    const cuuint32_t box[3] = {(cuuint32_t)pitch, (cuuint32_t)rows, (cuuint32_t)channels};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float *>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <int C, int CIN>
 int launch_fast(const float *y, const float *img, float *grad, float *partials, unsigned *ticket, float *loss, int N,
                 int H, int W, FastParams prm, float gscale, double inv_denom, cudaStream_t st) {
     constexpr int R = 5;
-    constexpr int PITCH = (TW + 2 * R + 3) / 4 * 4;
-    const size_t smem = (size_t)(C + CIN) * (TH + 2 * R) * PITCH * sizeof(float);
+    constexpr int HH = TH + 2 * R;
+    constexpr int PITCH = TW + 2 * XOFF;
+    constexpr int IMG_FLOATS = (CIN * HH * PITCH + 31) / 32 * 32;
+    const size_t smem = (size_t)(IMG_FLOATS + C * HH * PITCH) * sizeof(float);
     dim3 grid((W + TW - 1) / TW, (H + TH - 1) / TH, N);
-    gcrf_fast_kernel<C, CIN, R><<<grid, NT, smem, st>>>(y, img, grad, partials, ticket, loss, H, W, prm, gscale,
-                                                       inv_denom);
+    CUtensorMap map_img, map_y;
+    memset(&map_img, 0, sizeof(map_img));
+    memset(&map_y, 0, sizeof(map_y));
+    if (make_tile_map(&map_img, img, N * CIN, H, W, PITCH, HH, CIN) && make_tile_map(&map_y, y, N * C, H, W, PITCH, HH, C))
+        gcrf_fast_kernel<C, CIN, R, true><<<grid, NT, smem, st>>>(y, img, grad, partials, ticket, loss, H, W, prm, gscale,
+                                                                 inv_denom, map_img, map_y);
+    else   // rows that are not a multiple of 16 bytes, or no tensor-map encoder: stage with ordinary loads
+        gcrf_fast_kernel<C, CIN, R, false><<<grid, NT, smem, st>>>(y, img, grad, partials, ticket, loss, H, W, prm, gscale,
+                                                                  inv_denom, map_img, map_y);
     return 0;
 }
 
@@ -368,8 +456,6 @@ extern "C" int fedicra_gcrf_fwd_bwd(const float *y, const float *image, int N, i
 // host-side handle, not something a kernel can be given).  That lookup is a one-off set-up step: make the first call
 // on a device before starting any stream capture on it.  The address is remembered per device ordinal for the life of
 // the process: it assumes the primary context and no cudaDeviceReset in between.
-#include <mutex>
-
 namespace {
 
 constexpr int FEDICRA_GCRF_NOALLOC_MAX_CTAS = 32768;
