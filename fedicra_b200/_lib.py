@@ -83,6 +83,8 @@ SIGNATURES = {
                                       c_void_p, c_void_p, c_size_t, c_void_p]),
     "fedicra_masked_l1_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int, c_int,
                                       ctypes.c_longlong, c_void_p, c_void_p, c_void_p]),
+    "fedicra_bilinear_resize_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "fedicra_bilinear_resize_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "fedicra_debug_filter_profile": (c_int, [c_void_p, c_int]),
     "fedicra_debug_chain_profile": (c_int, [c_void_p, c_int]),
     "fedicra_ala_update_flat": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_void_p]),

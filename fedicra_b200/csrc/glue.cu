@@ -7,6 +7,8 @@
 // In PyTorch these are ~20 small kernels per step (sub, abs, mul, sum, clamp, div, sign, neg, ...), each a full HBM round
 // trip of a [B,C,H,W] tensor; here each direction is one pass at HBM rate.  The reductions are deterministic: per-CTA
 // partial sums in a fixed order, combined by the last CTA to arrive in CTA-index order.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -187,5 +189,125 @@ extern "C" int fedicra_masked_l1_bwd(const float *prob, const float *filtered, c
     masked_l1_bwd_kernel<<<(unsigned)((BP + NT - 1) / NT), NT, 0, (cudaStream_t)stream>>>(prob, filtered, roi, grad_out, n, weight, C,
                                                                                        P, BP, grad_prob, grad_filtered);
     FEDICRA_CHECK_LAUNCH("masked_l1_bwd_kernel");
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Bilinear resize of the decoder heads to the prediction size, F.interpolate(mode='bilinear', align_corners=False)
+// (flower_common.py:789,796,803), and its gradient.  The forward follows torch's CUDA kernel expression for expression
+// (source index = max(0, scale * (dst + 0.5) - 0.5), scale = in / out; val = h0 * (w0 * v00 + w1 * v01) + h1 * (w0 * v10
+// + w1 * v11)) because the resized head is the embedding the MST is built on and the tree is decided on its exact bits
+// (tests compare the outputs bit for bit with torch's).  Several heads share one launch (pointer table in the
+// arguments).  The gradient is a gather over the output pixels that read an input pixel -- fixed summation order,
+// where torch scatters with atomics.
+namespace {
+
+constexpr int RESIZE_MAX = 4;
+struct ResizeSet {
+    const float *src[RESIZE_MAX];
+    float *dst[RESIZE_MAX];
+    int h[RESIZE_MAX], w[RESIZE_MAX];
+    long long begin[RESIZE_MAX + 1];   // element range of every head in the flat index space of the launch
+    int n;
+};
+
+// a * x + b * y the way torch's kernel comes out of nvcc: the second product rounded, then one fused multiply-add
+// (of the nine ways to round the interpolation expression this is the one whose results equal torch's bit for bit;
+// scripts/probe/resize_variants.py tried them all)
+__device__ __forceinline__ float combine2(float a, float x, float b, float y) { return __fmaf_rn(a, x, __fmul_rn(b, y)); }
+
+struct Tap {
+    int i0, ip;      // first source index, 0/1 step to the second
+    float l0, l1;    // weights of the two
+};
+__device__ __forceinline__ Tap resize_tap(int dst, float scale, int in_size) {
+    float r = scale * ((float)dst + 0.5f) - 0.5f;
+    r = r < 0.f ? 0.f : r;
+    Tap t;
+    t.i0 = (int)r;
+    t.ip = (t.i0 < in_size - 1) ? 1 : 0;
+    t.l1 = r - (float)t.i0;
+    t.l0 = 1.f - t.l1;
+    return t;
+}
+
+__global__ void __launch_bounds__(NT) bilinear_fwd_kernel(ResizeSet rs, int planes, int H, int W) {
+    const long long idx = (long long)blockIdx.x * NT + threadIdx.x;
+    if (idx >= rs.begin[rs.n]) return;
+    int k = 0;
+    while (k + 1 < rs.n && idx >= rs.begin[k + 1]) ++k;
+    const long long e = idx - rs.begin[k];
+    const int x = (int)(e % W), y = (int)((e / W) % H);
+    const long long plane = e / ((long long)W * H);
+    const int h = rs.h[k], w = rs.w[k];
+    const Tap ty = resize_tap(y, (float)h / (float)H, h), tx = resize_tap(x, (float)w / (float)W, w);
+    const float *s = rs.src[k] + plane * h * w;
+    const float v00 = s[ty.i0 * w + tx.i0], v01 = s[ty.i0 * w + tx.i0 + tx.ip];
+    const float v10 = s[(ty.i0 + ty.ip) * w + tx.i0], v11 = s[(ty.i0 + ty.ip) * w + tx.i0 + tx.ip];
+    rs.dst[k][e] = combine2(ty.l0, combine2(tx.l0, v00, tx.l1, v01), ty.l1, combine2(tx.l0, v10, tx.l1, v11));
+}
+
+// src = gradient w.r.t. the resized head [planes,H,W]; dst = gradient w.r.t. the head [planes,h,w]
+__global__ void __launch_bounds__(NT) bilinear_bwd_kernel(ResizeSet rs, int planes, int H, int W) {
+    const long long idx = (long long)blockIdx.x * NT + threadIdx.x;
+    if (idx >= rs.begin[rs.n]) return;
+    int k = 0;
+    while (k + 1 < rs.n && idx >= rs.begin[k + 1]) ++k;
+    const long long e = idx - rs.begin[k];
+    const int h = rs.h[k], w = rs.w[k];
+    const int x = (int)(e % w), y = (int)((e / w) % h);
+    const long long plane = e / ((long long)w * h);
+    const float sy = (float)h / (float)H, sx = (float)w / (float)W;
+    // output rows / columns whose taps can touch (y, x): source index in (y - 1, y + 1)
+    const int y_lo = max(0, (int)floorf(((float)y - 1.f + 0.5f) / sy - 0.5f) - 1), y_hi = min(H - 1, (int)ceilf(((float)y + 1.f + 0.5f) / sy - 0.5f) + 1);
+    const int x_lo = max(0, (int)floorf(((float)x - 1.f + 0.5f) / sx - 0.5f) - 1), x_hi = min(W - 1, (int)ceilf(((float)x + 1.f + 0.5f) / sx - 0.5f) + 1);
+    const float *g = rs.src[k] + plane * H * W;
+    float acc = 0.f;
+    for (int yy = y_lo; yy <= y_hi; ++yy) {
+        const Tap ty = resize_tap(yy, sy, h);
+        const float wy = (ty.i0 == y ? ty.l0 : 0.f) + (ty.i0 + ty.ip == y ? ty.l1 : 0.f);
+        if (wy == 0.f) continue;
+        float row = 0.f;
+        for (int xx = x_lo; xx <= x_hi; ++xx) {
+            const Tap tx = resize_tap(xx, sx, w);
+            const float wx = (tx.i0 == x ? tx.l0 : 0.f) + (tx.i0 + tx.ip == x ? tx.l1 : 0.f);
+            if (wx != 0.f) row = fmaf(wx, g[(long long)yy * W + xx], row);
+        }
+        acc = fmaf(wy, row, acc);
+    }
+    rs.dst[k][e] = acc;
+}
+
+}  // namespace
+
+extern "C" int fedicra_bilinear_resize_fwd(const float *const *h_src, float *const *h_dst, const int *h_h, const int *h_w,
+                                           int n, int planes, int H, int W, void *stream) {
+    FEDICRA_REQUIRE(h_src && h_dst && h_h && h_w, "bilinear_resize_fwd: null pointer");
+    FEDICRA_REQUIRE(n >= 1 && n <= RESIZE_MAX && planes > 0 && H > 0 && W > 0, "bilinear_resize_fwd: bad sizes n=%d (1..%d) planes=%d H=%d W=%d", n, RESIZE_MAX, planes, H, W);
+    ResizeSet rs = {};
+    rs.n = n;
+    for (int k = 0; k < n; ++k) {
+        FEDICRA_REQUIRE(h_src[k] && h_dst[k] && h_h[k] > 0 && h_w[k] > 0, "bilinear_resize_fwd: head %d is null or empty", k);
+        rs.src[k] = h_src[k]; rs.dst[k] = h_dst[k]; rs.h[k] = h_h[k]; rs.w[k] = h_w[k];
+        rs.begin[k + 1] = rs.begin[k] + (long long)planes * H * W;
+    }
+    bilinear_fwd_kernel<<<(unsigned)((rs.begin[n] + NT - 1) / NT), NT, 0, (cudaStream_t)stream>>>(rs, planes, H, W);
+    FEDICRA_CHECK_LAUNCH("bilinear_fwd_kernel");
+    return 0;
+}
+
+extern "C" int fedicra_bilinear_resize_bwd(const float *const *h_grad_out, float *const *h_grad_in, const int *h_h,
+                                           const int *h_w, int n, int planes, int H, int W, void *stream) {
+    FEDICRA_REQUIRE(h_grad_out && h_grad_in && h_h && h_w, "bilinear_resize_bwd: null pointer");
+    FEDICRA_REQUIRE(n >= 1 && n <= RESIZE_MAX && planes > 0 && H > 0 && W > 0, "bilinear_resize_bwd: bad sizes n=%d (1..%d) planes=%d H=%d W=%d", n, RESIZE_MAX, planes, H, W);
+    ResizeSet rs = {};
+    rs.n = n;
+    for (int k = 0; k < n; ++k) {
+        FEDICRA_REQUIRE(h_grad_out[k] && h_grad_in[k] && h_h[k] > 0 && h_w[k] > 0, "bilinear_resize_bwd: head %d is null or empty", k);
+        rs.src[k] = h_grad_out[k]; rs.dst[k] = h_grad_in[k]; rs.h[k] = h_h[k]; rs.w[k] = h_w[k];
+        rs.begin[k + 1] = rs.begin[k] + (long long)planes * h_h[k] * h_w[k];
+    }
+    bilinear_bwd_kernel<<<(unsigned)((rs.begin[n] + NT - 1) / NT), NT, 0, (cudaStream_t)stream>>>(rs, planes, H, W);
+    FEDICRA_CHECK_LAUNCH("bilinear_bwd_kernel");
     return 0;
 }

@@ -437,6 +437,30 @@ def masked_l1_bwd(prob, filtered, roi_u8, grad_out, n, weight, want_prob=True, w
     return gp, gf
 
 
+def bilinear_resize(heads, H, W, backward=False):
+    """forward: heads = list of [B,C,h_k,w_k] -> list of [B,C,H,W] (torch's bilinear, align_corners=False, bit for bit);
+    backward: heads = list of (grad [B,C,H,W], (h_k, w_k)) -> list of [B,C,h_k,w_k].  One launch for all heads."""
+    import ctypes
+    n = len(heads)
+    if backward:
+        srcs = [_cuda(g, torch.float32, "grad_resized") for g, _ in heads]
+        sizes = [hw for _, hw in heads]
+    else:
+        srcs = [_cuda(x, torch.float32, "head") for x in heads]
+        sizes = [tuple(x.shape[2:]) for x in srcs]
+    B, C = srcs[0].shape[:2]
+    dev = srcs[0].device
+    with torch.cuda.device(dev):
+        outs = [torch.empty(B, C, *(hw if backward else (H, W)), dtype=torch.float32, device=dev) for hw in sizes]
+        sp = (ctypes.c_void_p * n)(*[x.data_ptr() for x in srcs])
+        dp = (ctypes.c_void_p * n)(*[x.data_ptr() for x in outs])
+        hh = (ctypes.c_int * n)(*[hw[0] for hw in sizes])
+        ww = (ctypes.c_int * n)(*[hw[1] for hw in sizes])
+        fn = lib.fedicra_bilinear_resize_bwd if backward else lib.fedicra_bilinear_resize_fwd
+        check(fn(sp, dp, hh, ww, n, B * C, H, W, _stream()), "bilinear_resize")
+    return outs
+
+
 # ------------------------------------------------------------------ aggregation
 
 

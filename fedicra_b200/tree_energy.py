@@ -31,6 +31,39 @@ def _prepare(preds, low_feats, unlabeled_ROIs):
         return low_feats, roi, roi.sum(), None
 
 
+class _BilinearHeads(torch.autograd.Function):
+    """F.interpolate(head, size=(h, w), mode='bilinear', align_corners=False) of several heads in ONE launch per
+    direction (csrc/glue.cu); the forward has torch's bits (the trees are built on them)."""
+
+    @staticmethod
+    def forward(ctx, h, w, *heads):
+        ctx.hw, ctx.sizes = (h, w), [tuple(x.shape[2:]) for x in heads]
+        return tuple(ops.bilinear_resize([x.contiguous() for x in heads], h, w))
+
+    @staticmethod
+    def backward(ctx, *grads):
+        h, w = ctx.hw
+        todo = [(k, g) for k, g in enumerate(grads) if g is not None and ctx.needs_input_grad[2 + k]]
+        out = [None] * len(grads)
+        if todo:
+            res = ops.bilinear_resize([(g.contiguous(), ctx.sizes[k]) for k, g in todo], h, w, backward=True)
+            for (k, _), r in zip(todo, res):
+                out[k] = r
+        return (None, None, *out)
+
+
+def _resize_heads(heads, h, w):
+    """All decoder heads brought to the prediction size (identity for those already there)."""
+    out = list(heads)
+    todo = [k for k, x in enumerate(heads) if x.shape[2:] != (h, w)]
+    fused = [k for k in todo if heads[k].is_cuda and heads[k].dtype == torch.float32]
+    if len(fused) == len(todo) and 1 <= len(fused) <= 4 and len({heads[k].shape[:2] for k in fused}) == 1:
+        for k, r in zip(fused, _BilinearHeads.apply(h, w, *[heads[k] for k in fused])):
+            out[k] = r
+        return out
+    return [_resize(x, h, w) for x in heads]
+
+
 def _resize(feats, h, w):
     """Bilinear resize of a decoder head to the prediction size (identity when already there)."""
     if feats.shape[2:] == (h, w):
@@ -156,7 +189,7 @@ class TreeEnergyLoss(_TreeLossBase):
         low_feats, roi, n, roi_u8 = _prepare(preds, low_feats, unlabeled_ROIs)
         h, w = preds.shape[2:]
         prob = _softmax(preds)
-        highs = [] if high_feats is None else [_resize(high_feats, h, w)]
+        highs = [] if high_feats is None else _resize_heads([high_feats], h, w)
         trees = self._trees([low_feats] + highs)
         AS = self._low(prob, low_feats, trees[0])
         if highs:
@@ -169,7 +202,7 @@ class MScaleAddTreeEnergyLoss(_TreeLossBase):
         low_feats, roi, n, roi_u8 = _prepare(preds, low_feats, unlabeled_ROIs)
         h, w = preds.shape[2:]
         prob = _softmax(preds)
-        highs = [_resize(hf, h, w) for hf in (high_feats_1, high_feats_2, high_feats_3)]
+        highs = _resize_heads([high_feats_1, high_feats_2, high_feats_3], h, w)
         trees = self._trees([low_feats] + highs)
         AS = self._low(prob, low_feats, trees[0])
         outs = [self._high(AS, hf, h, w, t) for hf, t in zip(highs, trees[1:])]
@@ -184,7 +217,7 @@ class MScaleRecurveTreeEnergyLoss(_TreeLossBase):
         n_global = self._count(roi_u8)
         h, w = preds.shape[2:]
         prob = _softmax(preds)
-        highs = [_resize(hf, h, w) for hf in (high_feats_1, high_feats_2, high_feats_3)]
+        highs = _resize_heads([high_feats_1, high_feats_2, high_feats_3], h, w)
         trees = self._trees([low_feats] + highs)
         cur = self._low(prob, low_feats, trees[0])
         outs = []

@@ -232,6 +232,16 @@ int fedicra_chain_filter_backward(const float *grad_out, float *edge_weight, con
                                   int V, const void *saved, float *grad_feature, float *grad_weight, void *workspace,
                                   size_t workspace_bytes, void *stream);
 
+/* F.interpolate(x, size=(H, W), mode='bilinear', align_corners=False) of up to 4 decoder heads in one launch
+ * (flower_common.py:789,796,803) and its gradient.  h_src[k] = [planes, h_k, w_k], h_dst[k] = [planes, H, W] (forward);
+ * h_grad_out[k] = [planes, H, W], h_grad_in[k] = [planes, h_k, w_k] (backward); the h_* arrays are HOST arrays.  The
+ * forward reproduces torch's CUDA result bit for bit (the MST is built on these values); the backward gathers in a fixed
+ * order where torch scatters with atomics. */
+int fedicra_bilinear_resize_fwd(const float *const *h_src, float *const *h_dst, const int *h_h, const int *h_w, int n,
+                                int planes, int H, int W, void *stream);
+int fedicra_bilinear_resize_bwd(const float *const *h_grad_out, float *const *h_grad_in, const int *h_h, const int *h_w,
+                                int n, int planes, int H, int W, void *stream);
+
 /* ------------------------------------------------------------------------------------------------ loss glue ---- */
 /* prob = softmax over the channel axis of x [B,C,P]  (flower_common.py:781, torch.softmax(preds, dim=1)); C <= 16. */
 int fedicra_channel_softmax_fwd(const float *x, int B, int C, long long P, float *y, void *stream);

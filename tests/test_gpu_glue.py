@@ -77,3 +77,24 @@ def test_mst_grid_multi_equals_separate_launches():
     for k, e in enumerate(embs):
         e1, m1 = ops.mst_grid(e, want_mask=True)
         assert torch.equal(edges[k * B:(k + 1) * B], e1) and torch.equal(mask[k * B:(k + 1) * B], m1)
+
+
+@pytest.mark.parametrize("B,C,sizes,H,W", [(2, 2, [(64, 64), (128, 128)], 256, 256), (12, 3, [(64, 64), (128, 128)], 256, 256),
+                                           (1, 2, [(16, 20)], 48, 64), (2, 3, [(13, 17), (30, 7)], 40, 52),
+                                           (1, 1, [(128, 128), (256, 256)], 512, 512)])
+def test_bilinear_resize_has_torchs_bits_and_its_gradient(B, C, sizes, H, W):
+    """fedicra_bilinear_resize_fwd == F.interpolate(mode='bilinear', align_corners=False) BIT FOR BIT (the resized heads
+    are the embeddings the trees are built on); the gather backward == autograd of F.interpolate within rounding."""
+    import torch.nn.functional as F
+    from fedicra_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    heads = [torch.randn(B, C, h, w, generator=g).cuda() for h, w in sizes]
+    outs = ops.bilinear_resize(heads, H, W)
+    gouts = [torch.randn(B, C, H, W, generator=g).cuda() for _ in sizes]
+    back = ops.bilinear_resize([(go, hw) for go, hw in zip(gouts, sizes)], H, W, backward=True)
+    for x, o, go, gi in zip(heads, outs, gouts, back):
+        xr = x.clone().requires_grad_()
+        want = F.interpolate(xr, size=(H, W), mode="bilinear", align_corners=False)
+        assert torch.equal(o, want.detach()), "resized head differs from torch's bits"
+        want.backward(go)
+        assert rel(gi, xr.grad) < 1e-5
