@@ -263,15 +263,36 @@ __global__ void __launch_bounds__(NT) bilinear_bwd_kernel(ResizeSet rs, int plan
     const int x_lo = max(0, (int)floorf(((float)x - 1.f + 0.5f) / sx - 0.5f) - 1), x_hi = min(W - 1, (int)ceilf(((float)x + 1.f + 0.5f) / sx - 0.5f) + 1);
     const float *g = rs.src[k] + plane * H * W;
     float acc = 0.f;
+    constexpr int XW = 16;                      // x weights of up to 16 output columns kept in registers (x4 needs 12)
+    float wxs[XW];
+    const bool cached = x_hi - x_lo < XW;
+    if (cached) {
+#pragma unroll
+        for (int t = 0; t < XW; ++t) {
+            const int xx = x_lo + t;
+            float wx = 0.f;
+            if (xx <= x_hi) {
+                const Tap tx = resize_tap(xx, sx, w);
+                wx = (tx.i0 == x ? tx.l0 : 0.f) + (tx.i0 + tx.ip == x ? tx.l1 : 0.f);
+            }
+            wxs[t] = wx;
+        }
+    }
     for (int yy = y_lo; yy <= y_hi; ++yy) {
         const Tap ty = resize_tap(yy, sy, h);
         const float wy = (ty.i0 == y ? ty.l0 : 0.f) + (ty.i0 + ty.ip == y ? ty.l1 : 0.f);
         if (wy == 0.f) continue;
         float row = 0.f;
-        for (int xx = x_lo; xx <= x_hi; ++xx) {
-            const Tap tx = resize_tap(xx, sx, w);
-            const float wx = (tx.i0 == x ? tx.l0 : 0.f) + (tx.i0 + tx.ip == x ? tx.l1 : 0.f);
-            if (wx != 0.f) row = fmaf(wx, g[(long long)yy * W + xx], row);
+        if (cached) {
+#pragma unroll
+            for (int t = 0; t < XW; ++t)
+                if (wxs[t] != 0.f) row = fmaf(wxs[t], g[(long long)yy * W + x_lo + t], row);
+        } else {
+            for (int xx = x_lo; xx <= x_hi; ++xx) {
+                const Tap tx = resize_tap(xx, sx, w);
+                const float wx = (tx.i0 == x ? tx.l0 : 0.f) + (tx.i0 + tx.ip == x ? tx.l1 : 0.f);
+                if (wx != 0.f) row = fmaf(wx, g[(long long)yy * W + xx], row);
+            }
         }
         acc = fmaf(wy, row, acc);
     }
