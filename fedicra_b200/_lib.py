@@ -87,6 +87,7 @@ SIGNATURES = {
     "fedicra_bilinear_resize_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "fedicra_debug_filter_profile": (c_int, [c_void_p, c_int]),
     "fedicra_debug_chain_profile": (c_int, [c_void_p, c_int]),
+    "fedicra_debug_mst_profile": (c_int, [c_void_p, c_int]),
     "fedicra_ala_update_flat": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_void_p]),
     "fedicra_ala_update_multi": (c_int, [c_void_p] * 8 + [c_int, c_int, c_float, c_void_p]),
     "fedicra_scale_inplace": (c_int, [c_void_p, c_int64, c_float, c_void_p]),

@@ -22,6 +22,7 @@ namespace {
 typedef unsigned long long u64;
 constexpr u64 KEY_INF = ~0ull;
 
+struct Rec;
 struct Ws {
     int *comp;       // [B,V] component root of every vertex (fully compressed between rounds)
     int *parent;     // [B,V] hook target of a root (self when not hooked)
@@ -33,7 +34,19 @@ struct Ws {
     int *act;        // [B,2,V] active-vertex lists (vertices that still see another component), ping-pong
     int *roots;      // [B,2,V] component-root lists, ping-pong
     int *cnt;        // [B,4]   list lengths: act[0], act[1], roots[0], roots[1]
+                     //         (contraction: [0] cross-edge records, [2] components left by the tile rounds)
+    struct Rec *rec; // [B,E]   contraction: cross edges left by the tile rounds (edge id, the two components)
+    unsigned char *tmask;   // [B,V] adjacency mask when the caller wants only the edge list
 };
+
+// A cross edge of the contracted graph: `a`, `b` are dense component numbers (per tree, handed out tile by tile);
+// b = UNRESOLVED when the far end lies in another tile, whose numbering the emitting tile cannot know.
+struct __align__(16) Rec {
+    unsigned eid;
+    int a, b;
+    unsigned ow;   // orderable bits of the edge weight
+};
+constexpr int UNRESOLVED = -1;
 
 size_t ws_layout(int B, int V, int E, char *base, Ws *w) {
     size_t off = 0;
@@ -53,6 +66,8 @@ size_t ws_layout(int B, int V, int E, char *base, Ws *w) {
     t.act = (int *)take((size_t)B * 2 * V * sizeof(int));
     t.roots = (int *)take((size_t)B * 2 * V * sizeof(int));
     t.cnt = (int *)take((size_t)B * 4 * sizeof(int));
+    t.rec = (Rec *)take((size_t)B * (E > 0 ? E : 1) * sizeof(Rec));
+    t.tmask = (unsigned char *)take((size_t)B * V);
     if (w) *w = t;
     return off;
 }
@@ -164,7 +179,8 @@ __global__ void mst_compress_kernel(Ws ws, int V) {
 // input) are filled with -1.
 template <bool GRID>
 __global__ void __launch_bounds__(1024)
-mst_compact_kernel(Ws ws, const int *__restrict__ edge_index, int *__restrict__ edge_out, int V, int E, int H, int W) {
+mst_compact_kernel(Ws ws, const int *__restrict__ edge_index, int *__restrict__ edge_out, int V, int E, int H, int W,
+                   const unsigned char *__restrict__ mask_all) {   // mask_all: take the flags from the adjacency masks (grid)
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const unsigned char *flag = ws.intree + (size_t)b * E;
     int2 *out = reinterpret_cast<int2 *>(edge_out) + (size_t)b * (V - 1);
@@ -174,7 +190,21 @@ mst_compact_kernel(Ws ws, const int *__restrict__ edge_index, int *__restrict__ 
     __syncthreads();
     for (int e0 = 0; e0 < E; e0 += 1024) {
         const int e = e0 + tid;
-        const int f = (e < E) ? flag[e] : 0;
+        int f = 0;
+        if (e < E) {
+            if (GRID && mask_all != nullptr) {
+                const unsigned char *mk = mask_all + (size_t)b * V;
+                const int nvert = (H - 1) * W;
+                if (e < nvert) {
+                    f = mk[e] & 8;
+                } else {
+                    const int r = e - nvert, h = r / (W - 1);
+                    f = mk[h * W + (r - h * (W - 1))] & 4;
+                }
+            } else {
+                f = flag[e];
+            }
+        }
         const unsigned m = __ballot_sync(0xffffffffu, f);
         if (lane == 0) s_warp[wid] = __popc(m);
         __syncthreads();
@@ -453,9 +483,10 @@ mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, in
 // Output: edge weights and tree flags of the tile's own edges (down / right of each of its vertices), fresh labels
 // (DEAD for vertices whose neighbours all share their component), identity hooks, and the root / active lists.
 constexpr int TS = 64, TV = TS * TS, TNT = 512;
-constexpr size_t TILE_SMEM = (size_t)TV * 8 + 2 * (size_t)(TS + 1) * TS * 4 + 2 * (size_t)TV * 2;
+constexpr size_t TILE_SMEM = (size_t)TV * 8 + 2 * (size_t)(TS + 1) * TS * 4 + 2 * (size_t)TV * 2 + (size_t)TV + (size_t)TV * 4;
 
-__global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, int H, int W, int tiles_x, int max_rounds) {
+__global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, int H, int W, int tiles_x, int max_rounds,
+                                                          unsigned char *__restrict__ mask_out, int contract) {
     // cheapest outgoing edge per component as two 32-bit words (orderable weight, edge code): shared memory has native
     // 32-bit atomicMin.  min weight first, then min code among the edges of that weight.  The code of an edge that
     // touches the tile is type << 14 | row << 7 | column (see s_wv / s_wh); among such edges it orders like the global
@@ -466,6 +497,8 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
     float *s_wh = s_wv + (TS + 1) * TS;                               // [TS][TS+1] edge (col c-1, col c) of row r;    0 = none
     unsigned short *s_lab = reinterpret_cast<unsigned short *>(s_wh + TS * (TS + 1));   // [TV]
     unsigned short *s_par = s_lab + TV;                               // [TV]
+    unsigned *s_sel = reinterpret_cast<unsigned *>(s_par + TV);       // [TV] bytes: adjacency mask of the edges chosen here
+    unsigned *s_te = s_sel + TV / 4;                                  // [TV] contraction hand-over: third table column
     float *s_x = reinterpret_cast<float *>(s_bw);                     // [(TS+2)][(TS+2)] one channel of the tile + halo (init only)
     constexpr int XS = TS + 2;
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
@@ -521,8 +554,10 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
             wt = __fadd_rn(s_wv[i], 1.f);
             if (r >= 1) {
                 const int e = (h0 + r - 1) * W + w0 + c;
-                wgt[e] = wt;
-                intree[e] = 0;
+                if (!contract) {
+                    wgt[e] = wt;
+                    intree[e] = 0;
+                }
             }
         }
         s_wv[i] = wt;
@@ -534,8 +569,10 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
             wt = __fadd_rn(s_wh[i], 1.f);
             if (c >= 1) {
                 const int e = nvert + (h0 + r) * (W - 1) + w0 + c - 1;
-                wgt[e] = wt;
-                intree[e] = 0;
+                if (!contract) {
+                    wgt[e] = wt;
+                    intree[e] = 0;
+                }
             }
         }
         s_wh[i] = wt;
@@ -546,6 +583,7 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
         s_bw[l] = 0xffffffffu;
         s_be[l] = 0xffffffffu;
     }
+    for (int l = tid; l < TV / 4; l += TNT) s_sel[l] = 0u;
     __syncthreads();
     // ---- rounds.  Thread t owns vertices (row (t >> 6) + 8q, column t & 63), q = 0..7.
     constexpr int PER = TV / TNT;
@@ -637,7 +675,12 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
             const int other = (ca == l) ? cb : ca;
             if (s_be[other] == code && l < other) continue;   // same edge from both sides (codes are unique)
             s_par[l] = (unsigned short)other;
-            intree[horiz ? nvert + (h0 + er) * (W - 1) + w0 + ec - 1 : (h0 + er - 1) * W + w0 + ec] = 1;
+            if (contract) {   // mask bits of both endpoints: 1 up, 2 left, 4 right, 8 down
+                atomicOr(s_sel + (la >> 2), (horiz ? 4u : 8u) << ((la & 3) * 8));
+                atomicOr(s_sel + (lb >> 2), (horiz ? 2u : 1u) << ((lb & 3) * 8));
+            } else {
+                intree[horiz ? nvert + (h0 + er) * (W - 1) + w0 + ec - 1 : (h0 + er - 1) * W + w0 + ec] = 1;
+            }
             merged = 1;
         }
         merged = __syncthreads_or(merged);
@@ -654,10 +697,136 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
         __syncthreads();
         if (!merged) break;
     }
+    __shared__ int s_nact, s_nroot, s_abase, s_rbase;
+    if (contract) {
+        // ---- hand over the CONTRACTED graph: the tile's components get dense numbers (one reservation per tile on the
+        //      tree's counter), and every edge the tile owns (below / right of its vertices) whose ends lie in different
+        //      components -- or in different tiles -- becomes one record.  The adjacency mask of the edges chosen so far
+        //      is final for this tile; the contraction kernel only adds bits.
+        if (tid == 0) { s_nact = 0; s_nroot = 0; s_abase = 0; }
+        __syncthreads();
+        // Of all the edges between the same two components of the tile only the cheapest can ever be chosen, so only that
+        // one is handed on (256^2: ~1 400 cross edges per tile, ~300 component pairs): a hash table over the pairs in the
+        // cheapest-edge slots, which are free now -- key = the two tile ranks, min weight, then min edge id among the
+        // edges of that weight.  An edge that finds no slot (table full around its hash) is handed on as it is.
+        unsigned *tk = s_bw, *tw_ = s_be, *te = s_te;
+        constexpr unsigned EMPTY = 0xffffffffu;
+        for (int l = tid; l < TV; l += TNT) { tk[l] = EMPTY; tw_[l] = EMPTY; te[l] = EMPTY; }
+#pragma unroll
+        for (int q = 0; q < PER; ++q) {
+            const int r = rbase + q * (TNT / TS), l = r * TS + c;
+            const bool valid = r < th && c < tw;
+            const bool is_root = valid && s_lab[l] == l;
+            const unsigned m = __ballot_sync(0xffffffffu, is_root);
+            if (m) {
+                const int leader = __ffs(m) - 1;
+                int base = 0;
+                if (lane == leader) base = atomicAdd(&s_nroot, __popc(m));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (is_root) s_par[l] = (unsigned short)(base + __popc(m & ((1u << lane) - 1u)));   // dense rank in the tile
+            }
+        }
+        __syncthreads();
+        // edge k = 2q + kind of this thread: kind 0 = to the vertex below, 1 = to the right.  First which of the 16 join two
+        // components inside the tile (in_mask) or leave the tile (out_mask); the passes below only visit those.
+        unsigned in_mask = 0, out_mask = 0;
+#pragma unroll
+        for (int k = 0; k < 2 * PER; ++k) {
+            const int r = rbase + (k >> 1) * (TNT / TS), l = r * TS + c;
+            const bool valid = r < th && c < tw;
+            const bool exists = valid && ((k & 1) ? (w0 + c + 1 < W) : (h0 + r + 1 < H));
+            const bool inside = exists && ((k & 1) ? (c + 1 < tw) : (r + 1 < th));
+            if (inside && s_lab[l] != s_lab[(k & 1) ? l + 1 : l + TS]) in_mask |= 1u << k;
+            if (exists && !inside) out_mask |= 1u << k;
+        }
+        struct EdgeInfo { unsigned pk, ow, eid; int ra, rb; };
+        auto edge = [&](int k, bool inside) {
+            EdgeInfo x;
+            const int kind = k & 1, r = rbase + (k >> 1) * (TNT / TS), l = r * TS + c;
+            x.ra = s_par[s_lab[l]];
+            x.rb = inside ? s_par[s_lab[kind ? l + 1 : l + TS]] : 0;
+            x.pk = (unsigned)min(x.ra, x.rb) << 12 | (unsigned)max(x.ra, x.rb);
+            x.ow = orderable(kind ? s_wh[l + r + 1] : s_wv[l + TS]);
+            x.eid = (unsigned)(kind ? nvert + (h0 + r) * (W - 1) + w0 + c : (h0 + r) * W + w0 + c);
+            return x;
+        };
+        auto slot_of = [&](unsigned pk, bool insert) {
+            const unsigned h = (pk * 2654435761u) >> 20;
+            for (int t = 0; t < 32; ++t) {
+                const unsigned sl = (h + t) & (TV - 1);
+                unsigned k = tk[sl];
+                if (k == EMPTY && insert) k = atomicCAS(tk + sl, EMPTY, pk), k = (k == EMPTY) ? pk : k;
+                if (k == pk) return (int)sl;
+                if (k == EMPTY) return -1;
+            }
+            return -1;
+        };
+        for (unsigned m = in_mask; m; m &= m - 1) {
+            const EdgeInfo x = edge(__ffs(m) - 1, true);
+            const int sl = slot_of(x.pk, true);
+            if (sl >= 0) atomicMin(tw_ + sl, x.ow);
+        }
+        __syncthreads();
+        for (unsigned m = in_mask; m; m &= m - 1) {
+            const EdgeInfo x = edge(__ffs(m) - 1, true);
+            const int sl = slot_of(x.pk, false);
+            if (sl >= 0 && tw_[sl] == x.ow) atomicMin(te + sl, x.eid);
+        }
+        __syncthreads();
+        unsigned emit_mask = out_mask;
+        for (unsigned m = in_mask; m; m &= m - 1) {
+            const int k = __ffs(m) - 1;
+            const EdgeInfo x = edge(k, true);
+            const int sl = slot_of(x.pk, false);
+            if (sl < 0 || (tw_[sl] == x.ow && te[sl] == x.eid)) emit_mask |= 1u << k;
+        }
+        int nrec = __popc(emit_mask);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) nrec += __shfl_xor_sync(0xffffffffu, nrec, o);
+        if (lane == 0 && nrec) atomicAdd(&s_nact, nrec);
+        __syncthreads();
+        if (tid == 0) s_rbase = atomicAdd(cnt + 2, s_nroot);
+        if (tid == 32) s_nact = atomicAdd(cnt + 0, s_nact);   // from here on: first record slot of this tile
+        __syncthreads();
+        Rec *rec = ws.rec + (size_t)b * E + s_nact;
+        unsigned char *mask = mask_out + (size_t)b * V;
+        const unsigned char *s_sel8 = reinterpret_cast<const unsigned char *>(s_sel);
+#pragma unroll
+        for (int q = 0; q < PER; ++q) {
+            const int r = rbase + q * (TNT / TS), l = r * TS + c;
+            if (r < th && c < tw) {
+                const int gv = (h0 + r) * W + w0 + c;
+                mask[gv] = s_sel8[l];
+                if (r == 0 || c == 0) comp[gv] = s_rbase + s_par[s_lab[l]];   // the far end of an edge owned by the tile above / to the left
+            }
+        }
+        if (__any_sync(0xffffffffu, emit_mask != 0u)) {
+            int mine = __popc(emit_mask), x = mine;   // one reservation per warp, lanes in order
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, x, o);
+                if (lane >= o) x += t;
+            }
+            int base = 0;
+            if (lane == 31) base = atomicAdd(&s_abase, x);
+            base = __shfl_sync(0xffffffffu, base, 31) + x - mine;
+            for (unsigned m = emit_mask; m; m &= m - 1) {
+                const int k = __ffs(m) - 1;
+                const bool inside = (in_mask >> k) & 1u;
+                const EdgeInfo e = edge(k, inside);
+                Rec y;
+                y.eid = e.eid;
+                y.a = s_rbase + e.ra;
+                y.b = inside ? s_rbase + e.rb : UNRESOLVED;
+                y.ow = e.ow;
+                rec[base++] = y;
+            }
+        }
+        return;
+    }
     // ---- hand over to the cluster kernel: global labels, identity hooks, root and active lists.  The two lists are
     //      collected in shared memory (the cheapest-edge slots are free now) and appended with ONE reservation each.
     int *s_act = reinterpret_cast<int *>(s_bw), *s_root = reinterpret_cast<int *>(s_be);
-    __shared__ int s_nact, s_nroot, s_abase, s_rbase;
     if (tid == 0) { s_nact = 0; s_nroot = 0; }
     __syncthreads();
 #pragma unroll
@@ -700,6 +869,222 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
     for (int i = tid; i < s_nroot; i += TNT) roots[s_rbase + i] = s_root[i];
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Boruvka rounds on the CONTRACTED graph the tile kernel leaves behind (256^2: ~1 500 components and ~4 500 cross
+// edges per tree instead of 65 536 vertices), one CTA per tree, out of shared memory: per round three light passes over
+// the edge records (native 32-bit atomicMin of the orderable weight on both components, then of the edge id among the
+// edges of that weight -- the same total order as everywhere else, hence the same edge set -- then which record it
+// was), the hooks with the mutual-pair rule, a pointer chase over the components, and an in-place ordered compaction of
+// the records that still join two components.  A round costs a few microseconds of shared-memory traffic instead of
+// ~20 us of dependent L2 round trips in the cluster kernel.
+// Storage: records and component arrays in shared memory when they fit (MODE 0); else the records stay where the tile
+// kernel put them and are streamed from L2 (MODE 1: component arrays in shared memory, 16-bit numbers; MODE 2: in the
+// workspace, any count).
+template <int MODE> struct CStore;
+template <> struct CStore<0> {
+    typedef unsigned short id_t;
+    unsigned *e, *w;
+    id_t *a, *b;
+    unsigned *bw, *be; int *bi; id_t *par, *lab;
+    __device__ __forceinline__ void get(int i, unsigned &x, unsigned &ow, int &ca, int &cb) const { x = e[i]; ow = w[i]; ca = a[i]; cb = b[i]; }
+    __device__ __forceinline__ void ends(int i, int &ca, int &cb) const { ca = a[i]; cb = b[i]; }
+    __device__ __forceinline__ void set(int i, unsigned x, unsigned ow, int ca, int cb) { e[i] = x; w[i] = ow; a[i] = (id_t)ca; b[i] = (id_t)cb; }
+};
+template <typename ID> struct CStoreGlobal {
+    typedef ID id_t;
+    Rec *rec;
+    unsigned *bw, *be; int *bi; id_t *par, *lab;
+    __device__ __forceinline__ void get(int i, unsigned &x, unsigned &ow, int &ca, int &cb) const {
+        const int4 t = *reinterpret_cast<const int4 *>(rec + i);
+        x = (unsigned)t.x; ca = t.y; cb = t.z; ow = (unsigned)t.w;
+    }
+    __device__ __forceinline__ void ends(int i, int &ca, int &cb) const { ca = rec[i].a; cb = rec[i].b; }
+    __device__ __forceinline__ void set(int i, unsigned x, unsigned ow, int ca, int cb) {
+        *reinterpret_cast<int4 *>(rec + i) = make_int4((int)x, ca, cb, (int)ow);
+    }
+};
+template <> struct CStore<1> : CStoreGlobal<unsigned short> {};
+template <> struct CStore<2> : CStoreGlobal<int> {};
+
+constexpr int CNT = 1024;   // threads of the contraction CTA
+
+// FEDICRA_PROF=1: clock64 stamps of tree 0's contraction (start, records, components, loaded, then per round: found,
+// located, hooked, chased, compacted, records left) -- read back with fedicra_debug_mst_profile
+constexpr int MPROF = 128;
+__device__ long long g_mst_prof[MPROF];
+#define MST_STAMP(val)                                                                    \
+    do {                                                                                  \
+        if (prof && blockIdx.x == 0 && threadIdx.x == 0 && pslot < MPROF) g_mst_prof[pslot++] = (val); \
+    } while (0)
+
+__device__ __forceinline__ void or_mask_bit(unsigned char *mask, int v, unsigned bit) {
+    const uintptr_t p = (uintptr_t)(mask + v);
+    atomicOr(reinterpret_cast<unsigned *>(p & ~(uintptr_t)3), bit << ((p & 3) * 8));
+}
+
+template <int MODE>
+__device__ void contract_rounds(CStore<MODE> g, int R, int n, unsigned char *mask, int H, int W, int prof, int pslot) {
+    typedef typename CStore<MODE>::id_t id_t;
+    __shared__ int s_wcnt[2][32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nvert = (H - 1) * W;
+    for (int c = tid; c < R; c += CNT) g.par[c] = (id_t)c;
+    while (n > 0) {
+        for (int c = tid; c < R; c += CNT) { g.bw[c] = 0xffffffffu; g.be[c] = 0xffffffffu; }
+        __syncthreads();
+        for (int i = tid; i < n; i += CNT) {   // cheapest weight of every component
+            unsigned e, ow; int a, b;
+            g.get(i, e, ow, a, b);
+            if (ow < g.bw[a]) atomicMin(g.bw + a, ow);
+            if (ow < g.bw[b]) atomicMin(g.bw + b, ow);
+        }
+        __syncthreads();
+        for (int i = tid; i < n; i += CNT) {   // smallest edge id among the edges of that weight
+            unsigned e, ow; int a, b;
+            g.get(i, e, ow, a, b);
+            if (ow == g.bw[a] && e < g.be[a]) atomicMin(g.be + a, e);
+            if (ow == g.bw[b] && e < g.be[b]) atomicMin(g.be + b, e);
+        }
+        __syncthreads();
+        MST_STAMP(clock64());
+        for (int i = tid; i < n; i += CNT) {   // which record it was (edge ids are unique)
+            unsigned e, ow; int a, b;
+            g.get(i, e, ow, a, b);
+            if (g.be[a] == e) g.bi[a] = i;
+            if (g.be[b] == e) g.bi[b] = i;
+        }
+        __syncthreads();
+        MST_STAMP(clock64());
+        int any = 0;
+        for (int c = tid; c < R; c += CNT) {   // hooks: of two roots that picked the same edge the larger one hooks
+            if (g.par[c] != c) continue;
+            const unsigned e = g.be[c];
+            if (e == 0xffffffffu) continue;
+            int a, b;
+            g.ends(g.bi[c], a, b);
+            const int other = (a == c) ? b : a;
+            if (g.be[other] == e && c < other) continue;
+            g.par[c] = (id_t)other;
+            if ((int)e < nvert) {
+                or_mask_bit(mask, (int)e, 8u);
+                or_mask_bit(mask, (int)e + W, 1u);
+            } else {
+                const int r = (int)e - nvert, h = r / (W - 1), u = h * W + (r - h * (W - 1));
+                or_mask_bit(mask, u, 4u);
+                or_mask_bit(mask, u + 1, 2u);
+            }
+            any = 1;
+        }
+        if (!__syncthreads_or(any)) break;
+        MST_STAMP(clock64());
+        for (int c = tid; c < R; c += CNT) {
+            int r = c, p = g.par[r];
+            while (p != r) { r = p; p = g.par[r]; }
+            g.lab[c] = (id_t)r;
+        }
+        __syncthreads();
+        for (int c = tid; c < R; c += CNT) g.par[c] = g.lab[c];
+        MST_STAMP(clock64());
+        // relabel the records and keep those that still join two components: ordered compaction in place, a chunk of
+        // CNT records at a time (a chunk's survivors land at or before the chunk, its reads precede its writes)
+        int out = 0, buf = 0;
+        for (int i0 = 0; i0 < n; i0 += CNT, buf ^= 1) {
+            const int i = i0 + tid;
+            unsigned e = 0, ow = 0;
+            int a = 0, b = 0;
+            if (i < n) {
+                g.get(i, e, ow, a, b);
+                a = g.lab[a];
+                b = g.lab[b];
+            }
+            const bool keep = a != b;
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            if (lane == 0) s_wcnt[buf][wid] = __popc(m);
+            __syncthreads();
+            const int mine = s_wcnt[buf][lane];
+            int x = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, x, o);
+                if (lane >= o) x += t;
+            }
+            const int total = __shfl_sync(0xffffffffu, x, 31);
+            const int before = __shfl_sync(0xffffffffu, x - mine, wid);
+            if (keep) g.set(out + before + __popc(m & ((1u << lane) - 1u)), e, ow, a, b);
+            out += total;
+        }
+        __syncthreads();
+        n = out;
+        MST_STAMP(clock64());
+        MST_STAMP((long long)n);
+    }
+    MST_STAMP(-1ll);
+}
+
+__global__ void __launch_bounds__(CNT) mst_contract_kernel(Ws ws, unsigned char *__restrict__ mask_out, int H, int W, int pool_bytes,
+                                                           int prof) {
+    extern __shared__ __align__(16) unsigned char s_pool[];
+    const int b = blockIdx.x, tid = threadIdx.x, V = H * W, E = 2 * H * W - H - W, nvert = (H - 1) * W;
+    const int n = ws.cnt[(size_t)b * 4 + 0], R = ws.cnt[(size_t)b * 4 + 2];
+    Rec *rec = ws.rec + (size_t)b * E;
+    const int *comp = ws.comp + (size_t)b * V;
+    unsigned char *mask = mask_out + (size_t)b * V;
+    auto far_end = [&](unsigned e) {   // second endpoint (below / right) of a grid edge
+        if ((int)e < nvert) return (int)e + W;
+        const int r = (int)e - nvert, h = r / (W - 1);
+        return h * W + (r - h * (W - 1)) + 1;
+    };
+    int pslot = 0;
+    MST_STAMP(clock64());
+    MST_STAMP((long long)n);
+    MST_STAMP((long long)R);
+    const size_t comps_bytes = (size_t)R * 16 + 32;
+    if (R <= 65534 && comps_bytes + (size_t)n * 12 <= (size_t)pool_bytes) {
+        CStore<0> g;
+        g.bw = reinterpret_cast<unsigned *>(s_pool);
+        g.be = g.bw + R;
+        g.bi = reinterpret_cast<int *>(g.be + R);
+        g.e = reinterpret_cast<unsigned *>(g.bi + R);
+        g.w = g.e + n;
+        g.par = reinterpret_cast<unsigned short *>(g.w + n);
+        g.lab = g.par + R;
+        g.a = g.lab + R;
+        g.b = g.a + n;
+        for (int i = tid; i < n; i += CNT) {
+            const int4 t = *reinterpret_cast<const int4 *>(rec + i);
+            g.set(i, (unsigned)t.x, (unsigned)t.w, t.y, t.z == UNRESOLVED ? comp[far_end((unsigned)t.x)] : t.z);
+        }
+        __syncthreads();
+        MST_STAMP(clock64());
+        contract_rounds<0>(g, R, n, mask, H, W, prof, pslot);
+        return;
+    }
+    for (int i = tid; i < n; i += CNT)
+        if (rec[i].b == UNRESOLVED) rec[i].b = comp[far_end(rec[i].eid)];
+    if (R <= 65534 && comps_bytes <= (size_t)pool_bytes) {
+        CStore<1> g;
+        g.rec = rec;
+        g.bw = reinterpret_cast<unsigned *>(s_pool);
+        g.be = g.bw + R;
+        g.bi = reinterpret_cast<int *>(g.be + R);
+        g.par = reinterpret_cast<unsigned short *>(g.bi + R);
+        g.lab = g.par + R;
+        __syncthreads();
+        MST_STAMP(clock64());
+        contract_rounds<1>(g, R, n, mask, H, W, prof, pslot);
+    } else {
+        CStore<2> g;
+        g.rec = rec;
+        g.bw = reinterpret_cast<unsigned *>(ws.best + (size_t)b * V);
+        g.be = g.bw + V;
+        g.bi = ws.act + (size_t)b * 2 * V;
+        g.lab = g.bi + V;
+        g.par = ws.parent + (size_t)b * V;
+        __syncthreads();
+        MST_STAMP(clock64());
+        contract_rounds<2>(g, R, n, mask, H, W, prof, pslot);
+    }
+}
+
 // Tile-local rounds before the cluster kernel takes over.  The tile kernel is issue-bound (~9 us per round and CTA, 2.6
 // waves of CTAs for 48 trees of 256^2) and its late rounds hook little; measured on B200, 48 trees, total MST time:
 // 3 rounds 381 us, 4 rounds 367 us, 5 rounds 377 us, 6 rounds 393 us, until nothing hooks (7-8 rounds) 420 us, no tile
@@ -713,6 +1098,13 @@ int env_tile_rounds() {
 int env_tiles() {
     const char *v = getenv("FEDICRA_MST_TILES");
     return !(v && *v == '0');
+}
+
+// FEDICRA_MST_FINISH=cluster: the rounds after the tile kernel on the vertex lists, by thread-block clusters (round 1's
+// path); default: on the contracted graph
+int env_contract() {
+    const char *v = getenv("FEDICRA_MST_FINISH");
+    return !(v && *v == 'c' && v[1] == 'l');
 }
 
 int env_cl(int dflt) {
@@ -744,7 +1136,7 @@ int run_mst(const int *edge_index, const float *edge_weight, int B, int E, int V
     fedicra_count_launches(3 * rounds - 1);
     FEDICRA_CHECK_LAUNCH("mst round kernels");
     if (edge_out != nullptr) {
-        mst_compact_kernel<GRID><<<B, 1024, 0, st>>>(ws, edge_index, edge_out, V, E, H, W);
+        mst_compact_kernel<GRID><<<B, 1024, 0, st>>>(ws, edge_index, edge_out, V, E, H, W, nullptr);
         FEDICRA_CHECK_LAUNCH("mst_compact_kernel");
     }
     return 0;
@@ -797,13 +1189,32 @@ int mst_grid_launch(const EmbedSet &es, int B, int H, int W, int *edge_out, unsi
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
+        if (env_tiles() && env_contract()) {   // tile rounds, then the contracted graph: one CTA per tree
+            constexpr int POOL = 220 * 1024;
+            cudaError_t e0 = cudaFuncSetAttribute(mst_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_SMEM);
+            if (e0 == cudaSuccess) e0 = cudaFuncSetAttribute(mst_contract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POOL);
+            if (e0 != cudaSuccess) return fedicra_fail(-2, "mst kernels: %s", cudaGetErrorString(e0));
+            unsigned char *mask = tree_mask != nullptr ? tree_mask : ws.tmask;
+            cudaMemsetAsync(ws.cnt, 0, (size_t)B * 4 * sizeof(int), st);
+            const int tiles_x = (W + TS - 1) / TS, tiles_y = (H + TS - 1) / TS;
+            mst_tile_kernel<<<dim3(tiles_x * tiles_y, B), TNT, TILE_SMEM, st>>>(ws, es, H, W, tiles_x, env_tile_rounds(), mask, 1);
+            FEDICRA_CHECK_LAUNCH("mst_tile_kernel");
+            static const int prof = [] { const char *v = getenv("FEDICRA_PROF"); return (v && *v && *v != '0') ? 1 : 0; }();
+            mst_contract_kernel<<<B, CNT, POOL, st>>>(ws, mask, H, W, POOL, prof);
+            FEDICRA_CHECK_LAUNCH("mst_contract_kernel");
+            if (edge_out != nullptr) {
+                mst_compact_kernel<true><<<B, 1024, 0, st>>>(ws, nullptr, edge_out, V, E, H, W, mask);
+                FEDICRA_CHECK_LAUNCH("mst_compact_kernel");
+            }
+            return 0;
+        }
         int prepared = 0;
         if (env_tiles()) {   // rounds that stay inside 64x64 tiles first, out of shared memory
             cudaError_t e0 = cudaFuncSetAttribute(mst_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_SMEM);
             if (e0 != cudaSuccess) return fedicra_fail(-2, "mst_tile_kernel: %s", cudaGetErrorString(e0));
             cudaMemsetAsync(ws.cnt, 0, (size_t)B * 4 * sizeof(int), st);
             const int tiles_x = (W + TS - 1) / TS, tiles_y = (H + TS - 1) / TS;
-            mst_tile_kernel<<<dim3(tiles_x * tiles_y, B), TNT, TILE_SMEM, st>>>(ws, es, H, W, tiles_x, env_tile_rounds());
+            mst_tile_kernel<<<dim3(tiles_x * tiles_y, B), TNT, TILE_SMEM, st>>>(ws, es, H, W, tiles_x, env_tile_rounds(), nullptr, 0);
             FEDICRA_CHECK_LAUNCH("mst_tile_kernel");
             prepared = 1;
         }
@@ -811,7 +1222,7 @@ int mst_grid_launch(const EmbedSet &es, int B, int H, int W, int *edge_out, unsi
         fedicra_count_launches(1);
         if (e != cudaSuccess) return fedicra_fail(-2, "mst_grid_cluster_kernel: %s", cudaGetErrorString(e));
         if (edge_out != nullptr) {
-            mst_compact_kernel<true><<<B, 1024, 0, st>>>(ws, nullptr, edge_out, V, E, H, W);
+            mst_compact_kernel<true><<<B, 1024, 0, st>>>(ws, nullptr, edge_out, V, E, H, W, nullptr);
             FEDICRA_CHECK_LAUNCH("mst_compact_kernel");
         }
         return 0;
@@ -851,4 +1262,13 @@ extern "C" int fedicra_mst_grid_multi(const float *const *h_embeds, const int *h
     }
     es.per = B;
     return mst_grid_launch(es, B * K, H, W, edge_out, tree_mask, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+/* Debug: clock64 stamps of tree 0's last contraction (FEDICRA_PROF=1); see g_mst_prof.  Synchronises the device. */
+extern "C" int fedicra_debug_mst_profile(long long *h_out, int n) {
+    if (!h_out || n < MPROF) return fedicra_fail(-1, "debug_mst_profile: need room for %d values", MPROF);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(h_out, g_mst_prof, sizeof(long long) * MPROF);
+    if (e != cudaSuccess) return fedicra_fail(-2, "debug_mst_profile: %s", cudaGetErrorString(e));
+    return MPROF;
 }

@@ -17,6 +17,7 @@ import torch
 
 from .gate_crf_loss import ModelLossSemsegGatedCRF
 from .tree_energy import MScaleRecurveTreeEnergyLoss
+from .tree_filter import side_stream
 
 KERNELS_DESC = [{"weight": 1, "xy": 6, "rgb": 0.1}]  # OURS.py:68
 RADIUS = 5                                           # OURS.py:69
@@ -44,10 +45,24 @@ class LossStackStep:
         image = d["image"]
         three = image.repeat(1, 3, 1, 1) if image.shape[1] == 1 else image          # OURS.py:137-141
         roi = d["label"] == self.C                                                    # OURS.py:135
-        tel = self.tel(leaves[0], three, leaves[1], leaves[2], leaves[3], roi, self.tree_weight)[0]
-        soft = torch.softmax(leaves[0], dim=1)                                        # OURS.py:132
-        crf = self.crf(soft, KERNELS_DESC, RADIUS, image, self.H, self.W)["loss"]     # OURS.py:143-150
-        loss = tel + self.crf_scale * crf                                             # OURS.py:151 (without pCE)
+        side = side_stream("crf")
+        if side is None:
+            tel = self.tel(leaves[0], three, leaves[1], leaves[2], leaves[3], roi, self.tree_weight)[0]
+            soft = torch.softmax(leaves[0], dim=1)                                        # OURS.py:132
+            crf = self.crf(soft, KERNELS_DESC, RADIUS, image, self.H, self.W)["loss"]     # OURS.py:143-150
+        else:
+            # the Gated CRF term shares only `logits` and `image` with the tree term: it runs (forward, and through
+            # autograd its backward) on a helper stream under the latency-bound tree kernels
+            main = torch.cuda.current_stream()
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                soft = torch.softmax(leaves[0], dim=1)
+                crf = self.crf(soft, KERNELS_DESC, RADIUS, image, self.H, self.W)["loss"]
+                crf = self.crf_scale * crf
+            tel = self.tel(leaves[0], three, leaves[1], leaves[2], leaves[3], roi, self.tree_weight)[0]
+            main.wait_stream(side)
+            crf.record_stream(main)
+        loss = tel + (crf if side is not None else self.crf_scale * crf)              # OURS.py:151 (without pCE)
         loss.backward()                                                               # OURS.py:172
         return loss.detach(), [x.grad for x in leaves]
 

@@ -14,6 +14,23 @@ from torch import nn
 from . import ops
 
 
+_SIDE = {}
+
+
+def side_stream(tag="crf"):
+    """Per-device helper stream for work that is off the critical path of the step (the Gated CRF term beside the tree
+    term, runner.py).  FEDICRA_OVERLAP=0 keeps everything on the caller's stream.  Measured and dropped: the edge-weight
+    gradients of the high-level trees on a helper stream (+7 us per step: the chain filter's persistent CTAs hold the
+    registers of every SM, so nothing runs beside them)."""
+    want = os.environ.get("FEDICRA_OVERLAP", "1")
+    if want == "0" or (want != "1" and tag not in want.split(",")):
+        return None
+    key = (torch.cuda.current_device(), tag)
+    if key not in _SIDE:
+        _SIDE[key] = torch.cuda.Stream()
+    return _SIDE[key]
+
+
 def _is_norm2(fn):
     """True when `fn` is this module's squared-L2 distance (or absent): only then may the fused weight + MST and
     edge-weight kernels stand in for it.  Identity, not name: a user function that happens to be called

@@ -270,6 +270,7 @@ int fedicra_masked_l1_bwd(const float *prob, const float *filtered, const unsign
  * returned; synchronises the device). */
 int fedicra_debug_filter_profile(long long *h_out, int n);
 int fedicra_debug_chain_profile(long long *h_out, int n);   /* same for csrc/chains.cu: returns the value count */
+int fedicra_debug_mst_profile(long long *h_out, int n);     /* clock64 stamps of tree 0's MST contraction (csrc/mst.cu) */
 
 /* ------------------------------------------------------------------------------------------------ aggregation -- */
 /* Adaptive local aggregation, element-wise part of MyModel.set_weights (flower_common.py:590-602) over one flat
