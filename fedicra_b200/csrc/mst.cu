@@ -482,6 +482,15 @@ mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, in
 // kernel is the tile boundaries: a few hundred components per tile instead of 4 096 vertices.
 // Output: edge weights and tree flags of the tile's own edges (down / right of each of its vertices), fresh labels
 // (DEAD for vertices whose neighbours all share their component), identity hooks, and the root / active lists.
+// FEDICRA_PROF=1: clock64 stamps of tree 0's contraction (start, records, components, loaded, then per round: found,
+// located, hooked, chased, compacted, records left) -- read back with fedicra_debug_mst_profile
+constexpr int MPROF = 128;   // [0,64) contraction kernel, [64,128) tile kernel (tile 0 of tree 0: start, weights, each round, ranks, tables, emitted)
+__device__ long long g_mst_prof[MPROF];
+#define MST_STAMP(val)                                                                    \
+    do {                                                                                  \
+        if (prof && blockIdx.x == 0 && threadIdx.x == 0 && pslot < MPROF) g_mst_prof[pslot++] = (val); \
+    } while (0)
+
 constexpr int TS = 64, TV = TS * TS, TNT = 512;
 constexpr size_t TILE_SMEM = (size_t)TV * 8 + 2 * (size_t)(TS + 1) * TS * 4 + 2 * (size_t)TV * 2 + (size_t)TV + (size_t)TV * 4;
 
@@ -502,6 +511,10 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
     float *s_x = reinterpret_cast<float *>(s_bw);                     // [(TS+2)][(TS+2)] one channel of the tile + halo (init only)
     constexpr int XS = TS + 2;
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
+    const int prof = (contract >> 1) & (blockIdx.y == 0);
+    contract &= 1;
+    int pslot = 64;
+    MST_STAMP(clock64());
     const int ty = blockIdx.x / tiles_x, tx = blockIdx.x - ty * tiles_x, h0 = ty * TS, w0 = tx * TS;
     const int th = min(TS, H - h0), tw = min(TS, W - w0);
     const int V = H * W, E = 2 * H * W - H - W, nvert = (H - 1) * W;
@@ -585,6 +598,7 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
     }
     for (int l = tid; l < TV / 4; l += TNT) s_sel[l] = 0u;
     __syncthreads();
+    MST_STAMP(clock64());
     // ---- rounds.  Thread t owns vertices (row (t >> 6) + 8q, column t & 63), q = 0..7.
     constexpr int PER = TV / TNT;
     const int c = tid & (TS - 1), rbase = tid >> 6;
@@ -695,6 +709,7 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
             s_be[l] = 0xffffffffu;
         }
         __syncthreads();
+        MST_STAMP(clock64());
         if (!merged) break;
     }
     __shared__ int s_nact, s_nroot, s_abase, s_rbase;
@@ -727,6 +742,8 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
             }
         }
         __syncthreads();
+        MST_STAMP(-2ll);
+        MST_STAMP(clock64());
         // edge k = 2q + kind of this thread: kind 0 = to the vertex below, 1 = to the right.  First which of the 16 join two
         // components inside the tile (in_mask) or leave the tile (out_mask); the passes below only visit those.
         unsigned in_mask = 0, out_mask = 0;
@@ -764,13 +781,13 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
         for (unsigned m = in_mask; m; m &= m - 1) {
             const EdgeInfo x = edge(__ffs(m) - 1, true);
             const int sl = slot_of(x.pk, true);
-            if (sl >= 0) atomicMin(tw_ + sl, x.ow);
+            if (sl >= 0 && x.ow < tw_[sl]) atomicMin(tw_ + sl, x.ow);   // (a long common boundary: hundreds of edges on one slot)
         }
         __syncthreads();
         for (unsigned m = in_mask; m; m &= m - 1) {
             const EdgeInfo x = edge(__ffs(m) - 1, true);
             const int sl = slot_of(x.pk, false);
-            if (sl >= 0 && tw_[sl] == x.ow) atomicMin(te + sl, x.eid);
+            if (sl >= 0 && tw_[sl] == x.ow && x.eid < te[sl]) atomicMin(te + sl, x.eid);
         }
         __syncthreads();
         unsigned emit_mask = out_mask;
@@ -785,6 +802,7 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
         for (int o = 16; o > 0; o >>= 1) nrec += __shfl_xor_sync(0xffffffffu, nrec, o);
         if (lane == 0 && nrec) atomicAdd(&s_nact, nrec);
         __syncthreads();
+        MST_STAMP(clock64());
         if (tid == 0) s_rbase = atomicAdd(cnt + 2, s_nroot);
         if (tid == 32) s_nact = atomicAdd(cnt + 0, s_nact);   // from here on: first record slot of this tile
         __syncthreads();
@@ -822,6 +840,8 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
                 rec[base++] = y;
             }
         }
+        MST_STAMP(clock64());
+        MST_STAMP(-1ll);
         return;
     }
     // ---- hand over to the cluster kernel: global labels, identity hooks, root and active lists.  The two lists are
@@ -907,15 +927,6 @@ template <> struct CStore<1> : CStoreGlobal<unsigned short> {};
 template <> struct CStore<2> : CStoreGlobal<int> {};
 
 constexpr int CNT = 1024;   // threads of the contraction CTA
-
-// FEDICRA_PROF=1: clock64 stamps of tree 0's contraction (start, records, components, loaded, then per round: found,
-// located, hooked, chased, compacted, records left) -- read back with fedicra_debug_mst_profile
-constexpr int MPROF = 128;
-__device__ long long g_mst_prof[MPROF];
-#define MST_STAMP(val)                                                                    \
-    do {                                                                                  \
-        if (prof && blockIdx.x == 0 && threadIdx.x == 0 && pslot < MPROF) g_mst_prof[pslot++] = (val); \
-    } while (0)
 
 __device__ __forceinline__ void or_mask_bit(unsigned char *mask, int v, unsigned bit) {
     const uintptr_t p = (uintptr_t)(mask + v);
@@ -1195,11 +1206,11 @@ int mst_grid_launch(const EmbedSet &es, int B, int H, int W, int *edge_out, unsi
             if (e0 == cudaSuccess) e0 = cudaFuncSetAttribute(mst_contract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POOL);
             if (e0 != cudaSuccess) return fedicra_fail(-2, "mst kernels: %s", cudaGetErrorString(e0));
             unsigned char *mask = tree_mask != nullptr ? tree_mask : ws.tmask;
+            static const int prof = [] { const char *v = getenv("FEDICRA_PROF"); return (v && *v && *v != '0') ? 1 : 0; }();
             cudaMemsetAsync(ws.cnt, 0, (size_t)B * 4 * sizeof(int), st);
             const int tiles_x = (W + TS - 1) / TS, tiles_y = (H + TS - 1) / TS;
-            mst_tile_kernel<<<dim3(tiles_x * tiles_y, B), TNT, TILE_SMEM, st>>>(ws, es, H, W, tiles_x, env_tile_rounds(), mask, 1);
+            mst_tile_kernel<<<dim3(tiles_x * tiles_y, B), TNT, TILE_SMEM, st>>>(ws, es, H, W, tiles_x, env_tile_rounds(), mask, 1 | (prof << 1));
             FEDICRA_CHECK_LAUNCH("mst_tile_kernel");
-            static const int prof = [] { const char *v = getenv("FEDICRA_PROF"); return (v && *v && *v != '0') ? 1 : 0; }();
             mst_contract_kernel<<<B, CNT, POOL, st>>>(ws, mask, H, W, POOL, prof);
             FEDICRA_CHECK_LAUNCH("mst_contract_kernel");
             if (edge_out != nullptr) {

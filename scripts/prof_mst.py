@@ -31,3 +31,18 @@ while i + 5 < 128 and v[i] != -1:
     print(f"round {rnd}: find {(f-prev)/mhz:5.1f} locate {(l-f)/mhz:5.1f} hook {(hk-l)/mhz:5.1f} chase {(ch-hk)/mhz:5.1f} compact {(cp-ch)/mhz:5.1f} us -> {left} records")
     prev, i, rnd = cp, i + 6, rnd + 1
 print(f"total {(prev - t0) / mhz:.1f} us")
+t = v[64:]
+if t[0] > 0:
+    names, out, prev, k = ["weights"], [], t[0], 1
+    while k < 64 and t[k] not in (-1, -2, 0):
+        out.append(f"{'weights' if k == 1 else 'round %d' % (k - 2)} {(t[k] - prev) / mhz:.1f}")
+        prev = t[k]; k += 1
+    if t[k] == -2:
+        labels = ["ranks+classify", "tables", "emit"]
+        prev2 = prev
+        for j, lab in enumerate(labels):
+            cur = t[k + 1 + j]
+            out.append(f"{lab} {(cur - prev2) / mhz:.1f}")
+            prev2 = cur
+        out.append(f"total {(prev2 - t[0]) / mhz:.1f}")
+    print("tile 0 of tree 0 (us):", ", ".join(out))
