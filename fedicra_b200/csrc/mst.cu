@@ -610,62 +610,85 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
         // find: cheapest outgoing edge per component (outgoing = other label, or the other side of the tile boundary)
         unsigned kw[PER], ke[PER];
         unsigned short kc[PER];
+        if (round == 0) {
+            // every vertex is a component of its own: its cheapest edge is the cheapest of its (at most four) edges -- no
+            // labels to compare, no atomics; the slot of a vertex simply takes the code
 #pragma unroll
-        for (int q = 0; q < PER; ++q) {
-            kw[q] = ke[q] = 0xffffffffu;
-            kc[q] = 0;
-            if (interior & (1u << q)) continue;
-            const int r = rbase + q * (TNT / TS), l = r * TS + c;
-            const unsigned short cl = s_lab[l];
-            kc[q] = cl;
-            const float wu = s_wv[l], wd = s_wv[l + TS], wl = s_wh[l + r], wr = s_wh[l + r + 1];
-            // candidates in increasing code order (up, down are vertical: codes r<<7|c and (r+1)<<7|c; then left, right)
-            unsigned bw = 0xffffffffu, be = 0xffffffffu;
-            auto take = [&](float wt, unsigned code) {
-                const unsigned o = orderable(wt);
-                if (o < bw) { bw = o; be = code; }   // strict: on equal weight the earlier (smaller) code stays
-            };
-            if (wu > 0.f && (r == 0 || s_lab[l - TS] != cl)) take(wu, (unsigned)(r << 7 | c));
-            if (wd > 0.f && (r + 1 >= th || s_lab[l + TS] != cl)) take(wd, (unsigned)((r + 1) << 7 | c));
-            if (wl > 0.f && (c == 0 || s_lab[l - 1] != cl)) take(wl, (unsigned)(1 << 14 | r << 7 | c));
-            if (wr > 0.f && (c + 1 >= tw || s_lab[l + 1] != cl)) take(wr, (unsigned)(1 << 14 | r << 7 | (c + 1)));
-            kw[q] = bw;
-            ke[q] = be;
-            if (be == 0xffffffffu) interior |= 1u << q;
-        }
-        // one atomic per warp when all its candidates belong to one component (the usual case once components are
-        // large: a warp is 32 consecutive pixels of a row), else one per lane -- and only when it can lower the slot
-#pragma unroll
-        for (int q = 0; q < PER; ++q) {
-            const bool has = ke[q] != 0xffffffffu;
-            const unsigned m = __ballot_sync(0xffffffffu, has);
-            if (m == 0) continue;
-            const int first = __ffs(m) - 1;
-            const unsigned c0l = __shfl_sync(0xffffffffu, (unsigned)kc[q], first);
-            if (__all_sync(0xffffffffu, !has || kc[q] == c0l)) {
-                const unsigned wmin = __reduce_min_sync(0xffffffffu, kw[q]);
-                if (lane == first && wmin < s_bw[c0l]) atomicMin(s_bw + c0l, wmin);
-            } else if (has && kw[q] < s_bw[kc[q]]) {
-                atomicMin(s_bw + kc[q], kw[q]);
+            for (int q = 0; q < PER; ++q) {
+                if (interior & (1u << q)) continue;
+                const int r = rbase + q * (TNT / TS), l = r * TS + c;
+                const float wu = s_wv[l], wd = s_wv[l + TS], wl = s_wh[l + r], wr = s_wh[l + r + 1];
+                unsigned bw = 0xffffffffu, be = 0xffffffffu;
+                auto take = [&](float wt, unsigned code) {
+                    const unsigned o = orderable(wt);
+                    if (o < bw) { bw = o; be = code; }
+                };
+                if (wu > 0.f) take(wu, (unsigned)(r << 7 | c));
+                if (wd > 0.f) take(wd, (unsigned)((r + 1) << 7 | c));
+                if (wl > 0.f) take(wl, (unsigned)(1 << 14 | r << 7 | c));
+                if (wr > 0.f) take(wr, (unsigned)(1 << 14 | r << 7 | (c + 1)));
+                s_be[l] = be;
+                if (be == 0xffffffffu) interior |= 1u << q;
             }
-        }
-        __syncthreads();
-#pragma unroll
-        for (int q = 0; q < PER; ++q) {
-            const bool has = ke[q] != 0xffffffffu && s_bw[kc[q]] == kw[q];
-            const unsigned m = __ballot_sync(0xffffffffu, has);
-            if (m == 0) continue;
-            const int first = __ffs(m) - 1;
-            const unsigned c0l = __shfl_sync(0xffffffffu, (unsigned)kc[q], first);
-            if (__all_sync(0xffffffffu, !has || kc[q] == c0l)) {
-                const unsigned emin = __reduce_min_sync(0xffffffffu, has ? ke[q] : 0xffffffffu);
-                if (lane == first && emin < s_be[c0l]) atomicMin(s_be + c0l, emin);
-            } else if (has && ke[q] < s_be[kc[q]]) {
-                atomicMin(s_be + kc[q], ke[q]);
+            __syncthreads();
+        } else {
+    #pragma unroll
+            for (int q = 0; q < PER; ++q) {
+                kw[q] = ke[q] = 0xffffffffu;
+                kc[q] = 0;
+                if (interior & (1u << q)) continue;
+                const int r = rbase + q * (TNT / TS), l = r * TS + c;
+                const unsigned short cl = s_lab[l];
+                kc[q] = cl;
+                const float wu = s_wv[l], wd = s_wv[l + TS], wl = s_wh[l + r], wr = s_wh[l + r + 1];
+                // candidates in increasing code order (up, down are vertical: codes r<<7|c and (r+1)<<7|c; then left, right)
+                unsigned bw = 0xffffffffu, be = 0xffffffffu;
+                auto take = [&](float wt, unsigned code) {
+                    const unsigned o = orderable(wt);
+                    if (o < bw) { bw = o; be = code; }   // strict: on equal weight the earlier (smaller) code stays
+                };
+                if (wu > 0.f && (r == 0 || s_lab[l - TS] != cl)) take(wu, (unsigned)(r << 7 | c));
+                if (wd > 0.f && (r + 1 >= th || s_lab[l + TS] != cl)) take(wd, (unsigned)((r + 1) << 7 | c));
+                if (wl > 0.f && (c == 0 || s_lab[l - 1] != cl)) take(wl, (unsigned)(1 << 14 | r << 7 | c));
+                if (wr > 0.f && (c + 1 >= tw || s_lab[l + 1] != cl)) take(wr, (unsigned)(1 << 14 | r << 7 | (c + 1)));
+                kw[q] = bw;
+                ke[q] = be;
+                if (be == 0xffffffffu) interior |= 1u << q;
             }
-        }
-        __syncthreads();
+            // one atomic per warp when all its candidates belong to one component (the usual case once components are
+            // large: a warp is 32 consecutive pixels of a row), else one per lane -- and only when it can lower the slot
+    #pragma unroll
+            for (int q = 0; q < PER; ++q) {
+                const bool has = ke[q] != 0xffffffffu;
+                const unsigned m = __ballot_sync(0xffffffffu, has);
+                if (m == 0) continue;
+                const int first = __ffs(m) - 1;
+                const unsigned c0l = __shfl_sync(0xffffffffu, (unsigned)kc[q], first);
+                if (__all_sync(0xffffffffu, !has || kc[q] == c0l)) {
+                    const unsigned wmin = __reduce_min_sync(0xffffffffu, kw[q]);
+                    if (lane == first && wmin < s_bw[c0l]) atomicMin(s_bw + c0l, wmin);
+                } else if (has && kw[q] < s_bw[kc[q]]) {
+                    atomicMin(s_bw + kc[q], kw[q]);
+                }
+            }
+            __syncthreads();
+    #pragma unroll
+            for (int q = 0; q < PER; ++q) {
+                const bool has = ke[q] != 0xffffffffu && s_bw[kc[q]] == kw[q];
+                const unsigned m = __ballot_sync(0xffffffffu, has);
+                if (m == 0) continue;
+                const int first = __ffs(m) - 1;
+                const unsigned c0l = __shfl_sync(0xffffffffu, (unsigned)kc[q], first);
+                if (__all_sync(0xffffffffu, !has || kc[q] == c0l)) {
+                    const unsigned emin = __reduce_min_sync(0xffffffffu, has ? ke[q] : 0xffffffffu);
+                    if (lane == first && emin < s_be[c0l]) atomicMin(s_be + c0l, emin);
+                } else if (has && ke[q] < s_be[kc[q]]) {
+                    atomicMin(s_be + kc[q], ke[q]);
+                }
+            }
+            __syncthreads();
 
+        }
         // hook: a root whose cheapest edge lies inside the tile follows it (of a mutual pair the larger root hooks)
         int merged = 0;
 #pragma unroll
@@ -1202,6 +1225,11 @@ int mst_grid_launch(const EmbedSet &es, int B, int H, int W, int *edge_out, unsi
         cfg.numAttrs = 1;
         if (env_tiles() && env_contract()) {   // tile rounds, then the contracted graph: one CTA per tree
             constexpr int POOL = 220 * 1024;
+            int pool = POOL;   // FEDICRA_MST_POOL_KB: shared memory the contraction may use (tests: forces the streaming modes)
+            if (const char *v = getenv("FEDICRA_MST_POOL_KB")) {
+                const int x = atoi(v);
+                if (x >= 1 && x * 1024 < POOL) pool = x * 1024;
+            }
             cudaError_t e0 = cudaFuncSetAttribute(mst_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_SMEM);
             if (e0 == cudaSuccess) e0 = cudaFuncSetAttribute(mst_contract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POOL);
             if (e0 != cudaSuccess) return fedicra_fail(-2, "mst kernels: %s", cudaGetErrorString(e0));
@@ -1211,7 +1239,7 @@ int mst_grid_launch(const EmbedSet &es, int B, int H, int W, int *edge_out, unsi
             const int tiles_x = (W + TS - 1) / TS, tiles_y = (H + TS - 1) / TS;
             mst_tile_kernel<<<dim3(tiles_x * tiles_y, B), TNT, TILE_SMEM, st>>>(ws, es, H, W, tiles_x, env_tile_rounds(), mask, 1 | (prof << 1));
             FEDICRA_CHECK_LAUNCH("mst_tile_kernel");
-            mst_contract_kernel<<<B, CNT, POOL, st>>>(ws, mask, H, W, POOL, prof);
+            mst_contract_kernel<<<B, CNT, POOL, st>>>(ws, mask, H, W, pool, prof);
             FEDICRA_CHECK_LAUNCH("mst_contract_kernel");
             if (edge_out != nullptr) {
                 mst_compact_kernel<true><<<B, 1024, 0, st>>>(ws, nullptr, edge_out, V, E, H, W, mask);

@@ -183,6 +183,29 @@ def test_depth_banded_filter_vs_oracle(kind, B, C, D, H, W, inv_sigma, impl, mon
     cgf2, none = ops.tree_filter_backward(gout.cuda(), cew, *order, bands, sv, False)
     assert none is None and rel_err(cgf2.cpu(), gf) < TOL
 
+@pytest.mark.parametrize("finish,pool_kb", [("contract", None), ("contract", 24), ("contract", 1), ("cluster", None)])
+@pytest.mark.parametrize("kind,B,D,H,W", [("quant8", 4, 3, 256, 256), ("uniform", 2, 2, 130, 200), ("constant", 1, 1, 70, 65),
+                                          ("quant8", 1, 3, 512, 512)])
+def test_mst_finish_paths_bit_exact(kind, B, D, H, W, finish, pool_kb, monkeypatch):
+    """Rounds after the tile kernel: on the contracted graph in shared memory (default), with the records streamed from L2
+    (component arrays in shared memory: 24 KB hold ~1 500 components, not the records), wholly on the workspace (1 KB),
+    and round 1's cluster kernel -- same edge set as the reference's Boruvka (oracle) and the same adjacency mask."""
+    from fedicra_b200 import ops
+    monkeypatch.setenv("FEDICRA_MST_FINISH", finish)
+    if pool_kb is not None:
+        monkeypatch.setenv("FEDICRA_MST_POOL_KB", str(pool_kb))
+    emb = make_image(kind, B, D, H, W, torch.Generator().manual_seed(H + W))
+    ref = losses_cpu.minimum_spanning_tree(emb).numpy()
+    tree, mask = ops.mst_grid(emb.cuda(), want_mask=True)
+    tree, mask = tree.cpu().numpy(), mask.cpu().long()
+    only_mask = ops.mst_grid_multi([emb.cuda()], want_mask=True, want_edges=False)[1].cpu().long()
+    assert torch.equal(mask, only_mask)
+    V = H * W
+    for b in range(B):
+        assert np.array_equal(edge_set(tree[b]), edge_set(ref[b]))
+        deg = torch.bincount(torch.from_numpy(ref[b]).reshape(-1).long(), minlength=V)
+        assert torch.equal(sum(((mask[b] >> k) & 1) for k in range(4)), deg)
+
 
 @pytest.mark.parametrize("kind,B,D,H,W", [("quant8", 3, 3, 33, 47), ("constant", 1, 1, 40, 24), ("uniform", 2, 2, 1, 17),
                                           ("uniform", 2, 2, 19, 1), ("uniform", 1, 1, 1, 1), ("quant8", 12, 3, 256, 256),
