@@ -60,6 +60,10 @@ SIGNATURES = {
     "fedicra_chain_filter_forward": (c_int, [c_void_p] * 6 + [c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
     "fedicra_chain_filter_backward": (c_int, [c_void_p] * 6 + [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                                                 c_size_t, c_void_p]),
+    "fedicra_chain_filter_forward_armed": (c_int, [c_void_p] * 6 + [c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "fedicra_chain_filter_backward_armed": (c_int, [c_void_p] * 6 + [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                                                c_size_t, c_void_p]),
+    "fedicra_chain_filter_arm": (c_int, [c_void_p, c_size_t, c_void_p]),
     "fedicra_edge_weight_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p]),
     "fedicra_edge_weight_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                         c_float, c_void_p, c_void_p]),

@@ -671,10 +671,10 @@ extern "C" size_t fedicra_chain_filter_workspace_bytes(int B, int C, int V) {
     return sync_bytes(B, V) + (size_t)2 * B * (C + 1) * V * sizeof(float);
 }
 
-extern "C" int fedicra_chain_filter_forward(const float *feature_in, float *edge_weight, const int *sorted_index,
-                                            const int *sorted_parent, const int *sorted_child, const int *group_start,
-                                            int B, int C, int V, float *feature_out, void *saved, size_t saved_bytes,
-                                            void *stream) {
+namespace {
+int chain_forward_impl(const float *feature_in, float *edge_weight, const int *sorted_index, const int *sorted_parent,
+                       const int *sorted_child, const int *group_start, int B, int C, int V, float *feature_out, void *saved,
+                       size_t saved_bytes, void *stream, bool armed) {
     FEDICRA_REQUIRE(feature_in && edge_weight && sorted_index && sorted_parent && sorted_child && group_start &&
                         feature_out && saved, "chain_filter_forward: null pointer");
     FEDICRA_REQUIRE(B > 0 && C >= 1 && C <= 4 && V >= 1, "chain_filter_forward: bad sizes B=%d C=%d V=%d (1..4 channels)", B, C, V);
@@ -691,15 +691,42 @@ extern "C" int fedicra_chain_filter_forward(const float *feature_in, float *edge
     a.vec = (V % 4 == 0) && aligned16(sorted_index) && aligned16(sorted_parent) && aligned16(edge_weight);
     // every intermediate word starts as "pending" (all bits set): the counters and hand-over values at the head of
     // `saved`, and the two result arrays behind them -- one range, one memset
-    cudaError_t e = cudaMemsetAsync(saved, 0xff, fedicra_chain_filter_saved_bytes(B, C, V), st);
-    if (e != cudaSuccess) return fedicra_fail(-2, "chain_filter_forward: memset: %s", cudaGetErrorString(e));
+    if (!armed) {
+        cudaError_t e = cudaMemsetAsync(saved, 0xff, fedicra_chain_filter_saved_bytes(B, C, V), st);
+        if (e != cudaSuccess) return fedicra_fail(-2, "chain_filter_forward: memset: %s", cudaGetErrorString(e));
+    }
     return dispatch<0>(a, C, st);
 }
+}  // namespace
 
-extern "C" int fedicra_chain_filter_backward(const float *grad_out, float *edge_weight, const int *sorted_index,
-                                             const int *sorted_parent, const int *sorted_child, const int *group_start,
-                                             int B, int C, int V, const void *saved, float *grad_feature,
-                                             float *grad_weight, void *workspace, size_t workspace_bytes, void *stream) {
+extern "C" int fedicra_chain_filter_forward(const float *feature_in, float *edge_weight, const int *sorted_index,
+                                            const int *sorted_parent, const int *sorted_child, const int *group_start,
+                                            int B, int C, int V, float *feature_out, void *saved, size_t saved_bytes,
+                                            void *stream) {
+    return chain_forward_impl(feature_in, edge_weight, sorted_index, sorted_parent, sorted_child, group_start, B, C, V,
+                              feature_out, saved, saved_bytes, stream, false);
+}
+
+extern "C" int fedicra_chain_filter_forward_armed(const float *feature_in, float *edge_weight, const int *sorted_index,
+                                                  const int *sorted_parent, const int *sorted_child, const int *group_start,
+                                                  int B, int C, int V, float *feature_out, void *saved, size_t saved_bytes,
+                                                  void *stream) {
+    return chain_forward_impl(feature_in, edge_weight, sorted_index, sorted_parent, sorted_child, group_start, B, C, V,
+                              feature_out, saved, saved_bytes, stream, true);
+}
+
+extern "C" int fedicra_chain_filter_arm(void *buffers, size_t bytes, void *stream) {
+    FEDICRA_REQUIRE(buffers != nullptr && bytes > 0, "chain_filter_arm: null pointer or no bytes");
+    cudaError_t e = cudaMemsetAsync(buffers, 0xff, bytes, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fedicra_fail(-2, "chain_filter_arm: memset: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+namespace {
+int chain_backward_impl(const float *grad_out, float *edge_weight, const int *sorted_index, const int *sorted_parent,
+                        const int *sorted_child, const int *group_start, int B, int C, int V, const void *saved,
+                        float *grad_feature, float *grad_weight, void *workspace, size_t workspace_bytes, void *stream,
+                        bool armed) {
     FEDICRA_REQUIRE(grad_out && edge_weight && sorted_index && sorted_parent && sorted_child && group_start && saved &&
                         grad_feature && workspace, "chain_filter_backward: null pointer");
     FEDICRA_REQUIRE(B > 0 && C >= 1 && C <= 4 && V >= 1, "chain_filter_backward: bad sizes B=%d C=%d V=%d (1..4 channels)", B, C, V);
@@ -717,9 +744,28 @@ extern "C" int fedicra_chain_filter_backward(const float *grad_out, float *edge_
     a.vec = (V % 4 == 0) && aligned16(sorted_index) && aligned16(sorted_parent) && aligned16(edge_weight) &&
             aligned16(saved) && aligned16(a.up) && (grad_weight == nullptr || aligned16(grad_weight));
     // counters, hand-over values and both scratch arrays are one range: one memset marks them all "pending"
-    cudaError_t e = cudaMemsetAsync(workspace, 0xff, fedicra_chain_filter_workspace_bytes(B, C, V), st);
-    if (e != cudaSuccess) return fedicra_fail(-2, "chain_filter_backward: memset: %s", cudaGetErrorString(e));
+    if (!armed) {
+        cudaError_t e = cudaMemsetAsync(workspace, 0xff, fedicra_chain_filter_workspace_bytes(B, C, V), st);
+        if (e != cudaSuccess) return fedicra_fail(-2, "chain_filter_backward: memset: %s", cudaGetErrorString(e));
+    }
     return dispatch<1>(a, C, st);
+}
+}  // namespace
+
+extern "C" int fedicra_chain_filter_backward(const float *grad_out, float *edge_weight, const int *sorted_index,
+                                             const int *sorted_parent, const int *sorted_child, const int *group_start,
+                                             int B, int C, int V, const void *saved, float *grad_feature,
+                                             float *grad_weight, void *workspace, size_t workspace_bytes, void *stream) {
+    return chain_backward_impl(grad_out, edge_weight, sorted_index, sorted_parent, sorted_child, group_start, B, C, V, saved,
+                               grad_feature, grad_weight, workspace, workspace_bytes, stream, false);
+}
+
+extern "C" int fedicra_chain_filter_backward_armed(const float *grad_out, float *edge_weight, const int *sorted_index,
+                                                   const int *sorted_parent, const int *sorted_child, const int *group_start,
+                                                   int B, int C, int V, const void *saved, float *grad_feature,
+                                                   float *grad_weight, void *workspace, size_t workspace_bytes, void *stream) {
+    return chain_backward_impl(grad_out, edge_weight, sorted_index, sorted_parent, sorted_child, group_start, B, C, V, saved,
+                               grad_feature, grad_weight, workspace, workspace_bytes, stream, true);
 }
 
 /* Debug: %globaltimer stamps of the last profiled chain-filter launch (FEDICRA_PROF=1), [2 phases][2 images][768 items][4]:

@@ -232,9 +232,21 @@ CHAIN_MAX_V = 1 << 18
 CHAIN_MAX_C = lib.fedicra_chain_filter_max_channels()
 
 
-def chain_filter_forward(feature_in, edge_weight, si, sp, sc, gs):
+def chain_arm(B, C, V, n, device):
+    """n buffers for chain-filter launches (forward `saved` or backward workspace: same size), armed by ONE memset so
+    that none sits between the filters of a step.  Each serves one launch (chain_filter_forward(..., saved=buf) /
+    chain_filter_backward(..., armed_workspace=buf))."""
+    size = (int(lib.fedicra_chain_filter_saved_bytes(B, C, V)) + 255) // 256 * 256
+    with torch.cuda.device(device):
+        block = torch.empty(n * size, dtype=torch.uint8, device=device)
+        check(lib.fedicra_chain_filter_arm(_p(block), block.numel(), _stream()), "chain_filter_arm")
+    return [block[i * size:(i + 1) * size] for i in range(n)]
+
+
+def chain_filter_forward(feature_in, edge_weight, si, sp, sc, gs, saved=None):
     """Tree filter on chain-ordered trees.  Returns (feature_out [B,C,V] vertex order, saved); `saved` is an opaque
-    byte buffer for chain_filter_backward, chain_saved_arrays(saved, B, C, V) views its two [B,C+1,V] arrays."""
+    byte buffer for chain_filter_backward, chain_saved_arrays(saved, B, C, V) views its two [B,C+1,V] arrays.
+    `saved`: a buffer from chain_arm (not used by any launch yet)."""
     f = _cuda(feature_in, torch.float32, "feature_in")
     if not (edge_weight.is_cuda and edge_weight.dtype == torch.float32 and edge_weight.is_contiguous()):
         raise RuntimeError("edge_weight must be a contiguous float32 CUDA tensor (it is written in place)")
@@ -242,9 +254,13 @@ def chain_filter_forward(feature_in, edge_weight, si, sp, sc, gs):
     dev = f.device
     with torch.cuda.device(dev):
         out = torch.empty_like(f)
-        saved = torch.empty(lib.fedicra_chain_filter_saved_bytes(B, C, V), dtype=torch.uint8, device=dev)
-        check(lib.fedicra_chain_filter_forward(_p(f), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(gs), B, C, V, _p(out),
-                                               _p(saved), saved.numel(), _stream()), "chain_filter_forward")
+        need = lib.fedicra_chain_filter_saved_bytes(B, C, V)
+        if saved is not None and saved.numel() >= need and saved.device == dev:
+            fn = lib.fedicra_chain_filter_forward_armed
+        else:
+            fn, saved = lib.fedicra_chain_filter_forward, torch.empty(need, dtype=torch.uint8, device=dev)
+        check(fn(_p(f), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(gs), B, C, V, _p(out), _p(saved), saved.numel(),
+                 _stream()), "chain_filter_forward")
     return out, saved
 
 
@@ -259,7 +275,7 @@ def chain_watchdog_trips(saved):
     return int(saved[:8].view(torch.int32)[1]) + 1
 
 
-def chain_filter_backward(grad_out, edge_weight, si, sp, sc, gs, saved, want_weight_grad):
+def chain_filter_backward(grad_out, edge_weight, si, sp, sc, gs, saved, want_weight_grad, armed_workspace=None):
     """Returns (grad_feature [B,C,V] vertex order, grad_weight [B,V] chain order or None)."""
     g = _cuda(grad_out, torch.float32, "grad_output")
     B, C, V = g.shape
@@ -267,9 +283,13 @@ def chain_filter_backward(grad_out, edge_weight, si, sp, sc, gs, saved, want_wei
     with torch.cuda.device(dev):
         gf = torch.empty_like(g)
         gw = torch.empty(B, V, dtype=torch.float32, device=dev) if want_weight_grad else None
-        ws = workspace("chain_filter", lib.fedicra_chain_filter_workspace_bytes(B, C, V), dev)
-        check(lib.fedicra_chain_filter_backward(_p(g), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(gs), B, C, V, _p(saved),
-                                                _p(gf), _p(gw), _p(ws), ws.numel(), _stream()), "chain_filter_backward")
+        need = lib.fedicra_chain_filter_workspace_bytes(B, C, V)
+        if armed_workspace is not None and armed_workspace.numel() >= need and armed_workspace.device == dev:
+            fn, ws = lib.fedicra_chain_filter_backward_armed, armed_workspace
+        else:
+            fn, ws = lib.fedicra_chain_filter_backward, workspace("chain_filter", need, dev)
+        check(fn(_p(g), _p(edge_weight), _p(si), _p(sp), _p(sc), _p(gs), B, C, V, _p(saved), _p(gf), _p(gw), _p(ws),
+                 ws.numel(), _stream()), "chain_filter_backward")
     return gf, gw
 
 

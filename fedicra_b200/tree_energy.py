@@ -166,12 +166,23 @@ class _TreeLossBase(nn.Module):
         from .sharding import GlobalCount
         return GlobalCount().start(roi_u8)
 
-    def _trees(self, embeds):
+    def _trees(self, embeds, channels=None):
         """Topology of all the embeddings of this step at once (they do not depend on the filter chain), and with it the
         filters' edge weights: embedding 0 is the image (low-level tree, 1/sigma), the others are decoder heads (1)."""
         if all(e.is_cuda and e.shape[1] <= 4 for e in embeds) and len({(e.shape[0],) + tuple(e.shape[2:]) for e in embeds}) == 1:
             inv = [1.0 / self.tree_filter_layers.sigma] + [1.0] * (len(embeds) - 1)
-            return batched_tree_orders(embeds, inv)
+            orders = batched_tree_orders(embeds, inv)
+            B, V = embeds[0].shape[0], embeds[0].shape[2] * embeds[0].shape[3]
+            if channels is not None and channels <= ops.CHAIN_MAX_C and V <= ops.CHAIN_MAX_V and torch.is_grad_enabled():
+                # ONE memset arms the buffers of every filter launch of this step (forward and backward of each tree)
+                # instead of one in front of each launch.  (Measured: on a helper stream beside the topology kernels it
+                # gains nothing more in graph replay and costs 80 us of host time per eager step.)
+                chains = [a for a in (o.for_channels(channels) for o in orders) if a.kind == "chain"]
+                if chains:
+                    bufs = ops.chain_arm(B, channels, V, 2 * len(chains), embeds[0].device)
+                    for a in chains:
+                        a.armed = [bufs.pop(), bufs.pop()]
+            return orders
         return [self.mst_layers(e) for e in embeds]
 
     def _low(self, prob, low_feats, tree=None):
@@ -190,7 +201,7 @@ class TreeEnergyLoss(_TreeLossBase):
         h, w = preds.shape[2:]
         prob = _softmax(preds)
         highs = [] if high_feats is None else _resize_heads([high_feats], h, w)
-        trees = self._trees([low_feats] + highs)
+        trees = self._trees([low_feats] + highs, prob.shape[1])
         AS = self._low(prob, low_feats, trees[0])
         if highs:
             AS = self._high(AS, highs[0], h, w, trees[1])
@@ -203,7 +214,7 @@ class MScaleAddTreeEnergyLoss(_TreeLossBase):
         h, w = preds.shape[2:]
         prob = _softmax(preds)
         highs = _resize_heads([high_feats_1, high_feats_2, high_feats_3], h, w)
-        trees = self._trees([low_feats] + highs)
+        trees = self._trees([low_feats] + highs, prob.shape[1])
         AS = self._low(prob, low_feats, trees[0])
         outs = [self._high(AS, hf, h, w, t) for hf, t in zip(highs, trees[1:])]
         # flower_common.py:748-751: the three masked-L1 sums share one normaliser
@@ -218,7 +229,7 @@ class MScaleRecurveTreeEnergyLoss(_TreeLossBase):
         h, w = preds.shape[2:]
         prob = _softmax(preds)
         highs = _resize_heads([high_feats_1, high_feats_2, high_feats_3], h, w)
-        trees = self._trees([low_feats] + highs)
+        trees = self._trees([low_feats] + highs, prob.shape[1])
         cur = self._low(prob, low_feats, trees[0])
         outs = []
         for hf, t in zip(highs, trees[1:]):

@@ -43,13 +43,15 @@ class _Arrays:
     sorted_child; bfs.cu:46-98) plus what this library's filter kernels need on top of it:
       kind "chain": group_start (heavy-chain order, csrc/chains.cu);  kind "bfs": level_start, n_levels, band plan."""
 
-    __slots__ = ("kind", "si", "sp", "sc", "gs", "ls", "nl", "bands", "ew", "ew_key")
+    __slots__ = ("kind", "si", "sp", "sc", "gs", "ls", "nl", "bands", "ew", "ew_key", "armed")
 
     def __init__(self, kind, si, sp, sc, gs=None, ls=None, nl=None, bands=None, ew=None, ew_key=None):
         self.kind, self.si, self.sp, self.sc, self.gs, self.ls, self.nl, self.bands = kind, si, sp, sc, gs, ls, nl, bands
         # edge weights that came out of the ordering pass, and what they were computed from: (embedding address,
         # shape, 1/sigma) -- build_edge_weight takes them only for exactly that request
         self.ew, self.ew_key = ew, ew_key
+        # chain kind: buffers armed ahead for the filter launches on these trees (ops.chain_arm), each used once
+        self.armed = []
 
 
 def _want_chain(V):
@@ -200,7 +202,8 @@ class _Refine(torch.autograd.Function):
     @staticmethod
     def forward(ctx, feature_in, edge_weight, order, low_tree):
         if order.kind == "chain":
-            out, saved = ops.chain_filter_forward(feature_in, edge_weight, order.si, order.sp, order.sc, order.gs)
+            out, saved = ops.chain_filter_forward(feature_in, edge_weight, order.si, order.sp, order.sc, order.gs,
+                                                  saved=order.armed.pop() if order.armed else None)
         else:
             out, saved = ops.tree_filter_forward(feature_in, edge_weight, order.si, order.sp, order.sc, order.ls,
                                                  order.nl, order.bands)
@@ -215,7 +218,8 @@ class _Refine(torch.autograd.Function):
         want_w = (not ctx.low_tree) and ctx.needs_input_grad[1]
         if o.kind == "chain":
             grad_feature, grad_weight = ops.chain_filter_backward(grad_out.contiguous(), edge_weight, o.si, o.sp, o.sc,
-                                                                  o.gs, saved, want_w)
+                                                                  o.gs, saved, want_w,
+                                                                  armed_workspace=o.armed.pop() if o.armed else None)
         else:
             grad_feature, grad_weight = ops.tree_filter_backward(grad_out.contiguous(), edge_weight, o.si, o.sp, o.sc,
                                                                  o.ls, o.nl, o.bands, saved, want_w)

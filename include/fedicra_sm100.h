@@ -231,6 +231,20 @@ int fedicra_chain_filter_backward(const float *grad_out, float *edge_weight, con
                                   const int *sorted_parent, const int *sorted_child, const int *group_start, int B, int C,
                                   int V, const void *saved, float *grad_feature, float *grad_weight, void *workspace,
                                   size_t workspace_bytes, void *stream);
+/* The same two calls for buffers the caller has ARMED ahead of time: every intermediate word of a chain-filter launch
+ * must read "all bits set" when the kernel starts, which the plain calls do with a memset in front of the kernel -- on
+ * the critical path of a chain of filters (flower_common.py:786-806 runs four in a row, each consuming the previous
+ * one's output).  fedicra_chain_filter_arm(buffers, bytes) sets any number of `saved` / `workspace` buffers at once
+ * (one contiguous range), e.g. all eight of a training step before the first filter; each armed buffer serves ONE
+ * launch.  (No counterpart in the reference: its kernels keep no cross-CTA state.) */
+int fedicra_chain_filter_arm(void *buffers, size_t bytes, void *stream);
+int fedicra_chain_filter_forward_armed(const float *feature_in, float *edge_weight, const int *sorted_index,
+                                       const int *sorted_parent, const int *sorted_child, const int *group_start, int B,
+                                       int C, int V, float *feature_out, void *saved, size_t saved_bytes, void *stream);
+int fedicra_chain_filter_backward_armed(const float *grad_out, float *edge_weight, const int *sorted_index,
+                                        const int *sorted_parent, const int *sorted_child, const int *group_start, int B,
+                                        int C, int V, const void *saved, float *grad_feature, float *grad_weight,
+                                        void *workspace, size_t workspace_bytes, void *stream);
 
 /* F.interpolate(x, size=(H, W), mode='bilinear', align_corners=False) of up to 4 decoder heads in one launch
  * (flower_common.py:789,796,803) and its gradient.  h_src[k] = [planes, h_k, w_k], h_dst[k] = [planes, H, W] (forward);
