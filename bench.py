@@ -217,7 +217,7 @@ def isolated_call_times(data, C, H, W, flush_buf, reps=10, n=5):
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
+        with torch.cuda.graph(g, stream=side):   # same stream as the warm-up: scratch buffers are cached per stream
             for _ in range(reps):
                 fn()
         ts = time_steps(g.replay, n, flush_buf)
@@ -394,10 +394,12 @@ def measure_workload(name, steps, warmup, dev, rank, world, use_graph, flush_buf
     for _ in range(max(warmup, 3)):
         step(data)
     barrier()
-    sampler = ClockSampler(dev.index) if sampler_rank == rank else None
+    sampler = ClockSampler(dev.index) if (sampler_rank == rank and os.environ.get("BENCH_NO_SAMPLER") != "1") else None
     times = time_steps(lambda: step(data), steps, flush_buf)
     barrier()
     total_ms = rank_max(sum(times))
+    if rank == 0:
+        print(f"[bench] {name}: per-step ms min {min(times):.4f} median {statistics.median(times):.4f} max {max(times):.4f}", file=sys.stderr)
     launches0 = _lib.lib.fedicra_launch_count()
     # ---- the same step launched eagerly (what the reference's loop, which is not captured, gets)
     n_eager = min(steps, 10)

@@ -53,7 +53,7 @@ class _GraphedBatch:
             update()
             return loss.detach()
 
-        side = torch.cuda.Stream()
+        side = torch.cuda.Stream()         # warm-up and capture on the same stream (scratch buffers are cached per stream)
         side.wait_stream(torch.cuda.current_stream())
         self.warm = 3
         with torch.cuda.stream(side):
@@ -62,7 +62,7 @@ class _GraphedBatch:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        with torch.cuda.graph(self.graph, stream=side):
             self.loss = one()
 
     def __call__(self, volume, label):

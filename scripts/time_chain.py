@@ -15,7 +15,7 @@ def timeit_graph(fn, reps=20, n=10):
     torch.cuda.current_stream().wait_stream(side)
     torch.cuda.synchronize()
     g = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(g):
+    with torch.cuda.graph(g, stream=side):   # same stream as the warm-up: scratch buffers are cached per stream
         for _ in range(reps):
             fn()
     ts = []

@@ -10,7 +10,7 @@ def timeit_graph(fn, reps=10, n=10):
         for _ in range(3): fn()
     torch.cuda.current_stream().wait_stream(side); torch.cuda.synchronize()
     g = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(g):
+    with torch.cuda.graph(g, stream=side):   # same stream as the warm-up: scratch buffers are cached per stream
         for _ in range(reps): fn()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     ts = []
