@@ -13,6 +13,8 @@ cross-entropy term: from (logits, aux1..3, image, label) to (loss, d/dlogits, d/
 graphed copies and overlaps the host->device copy of step k+1 and the device->host copy of step k-1 with the replay of
 step k on separate streams.
 """
+import os
+
 import torch
 
 from .gate_crf_loss import ModelLossSemsegGatedCRF
@@ -54,12 +56,30 @@ class LossStackStep:
             # the Gated CRF term shares only `logits` and `image` with the tree term: it runs (forward, and through
             # autograd its backward) on a helper stream under the latency-bound tree kernels
             main = torch.cuda.current_stream()
-            side.wait_stream(main)
-            with torch.cuda.stream(side):
-                soft = torch.softmax(leaves[0], dim=1)
-                crf = self.crf(soft, KERNELS_DESC, RADIUS, image, self.H, self.W)["loss"]
-                crf = self.crf_scale * crf
-            tel = self.tel(leaves[0], three, leaves[1], leaves[2], leaves[3], roi, self.tree_weight)[0]
+            box = {}
+
+            def crf_branch():
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    soft = torch.softmax(leaves[0], dim=1)
+                    box["crf"] = self.crf_scale * self.crf(soft, KERNELS_DESC, RADIUS, image, self.H, self.W)["loss"]
+
+            # where the branch forks: measured at faz256, per step: at the start 1.373 ms (it then competes with the MST tile
+            # kernel, which fills every SM), once the topology is enqueued 1.347 ms, after the tree term 1.386 ms
+            at = os.environ.get("FEDICRA_CRF_AT", "topology")
+            hook = at == "topology" and hasattr(self.tel, "on_topology_enqueued")
+            if at == "start" or (at == "topology" and not hook):
+                crf_branch()
+            if hook:
+                self.tel.on_topology_enqueued = crf_branch
+            try:
+                tel = self.tel(leaves[0], three, leaves[1], leaves[2], leaves[3], roi, self.tree_weight)[0]
+            finally:
+                if hook:
+                    self.tel.on_topology_enqueued = None
+            if "crf" not in box:
+                crf_branch()
+            crf = box["crf"]
             main.wait_stream(side)
             crf.record_stream(main)
         loss = tel + (crf if side is not None else self.crf_scale * crf)              # OURS.py:151 (without pCE)

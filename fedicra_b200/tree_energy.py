@@ -159,6 +159,9 @@ class _TreeLossBase(nn.Module):
         self.local_share = bool(distributed and local_share)
         self.mst_layers = MinimumSpanningTree(TreeFilter2D.norm2_distance)
         self.tree_filter_layers = TreeFilter2D(groups=1, sigma=0.02)
+        # called (no arguments) when the topology kernels of a forward have been enqueued and the filters have not: the
+        # point where a caller with independent work for a helper stream (runner.py: the Gated CRF term) forks it
+        self.on_topology_enqueued = None
 
     def _count(self, roi_u8):
         if not (self.local_share and roi_u8 is not None):
@@ -182,6 +185,8 @@ class _TreeLossBase(nn.Module):
                     bufs = ops.chain_arm(B, channels, V, 2 * len(chains), embeds[0].device)
                     for a in chains:
                         a.armed = [bufs.pop(), bufs.pop()]
+            if self.on_topology_enqueued is not None:
+                self.on_topology_enqueued()
             return orders
         return [self.mst_layers(e) for e in embeds]
 
