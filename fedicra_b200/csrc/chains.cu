@@ -628,7 +628,12 @@ int launch(const ChainArgs &a, cudaStream_t st) {
         if (ctas_per_sm < 1) ctas_per_sm = 1;
     }
     const long long items = 2ll * a.B * a.Kmax;
-    const int grid = (int)(items < (long long)sms * ctas_per_sm ? items : (long long)sms * ctas_per_sm);
+    int per_sm = ctas_per_sm;
+    if (const char *v = getenv("FEDICRA_CHAIN_CTAS")) {   // resident CTAs per SM (default: all that fit)
+        const int x = atoi(v);
+        if (x >= 1 && x < per_sm) per_sm = x;
+    }
+    const int grid = (int)(items < (long long)sms * per_sm ? items : (long long)sms * per_sm);
     chain_filter_kernel<MODE, NC><<<grid, CT, 0, st>>>(a);
     FEDICRA_CHECK_LAUNCH(MODE == 0 ? "chain_filter_kernel<forward>" : "chain_filter_kernel<backward>");
     return 0;
