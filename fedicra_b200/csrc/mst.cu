@@ -8,6 +8,13 @@
 // atomicMin of the packed key (orderable fp32 bits << 32 | edge index) over its outgoing edges -- the same total order,
 // hence the same edge set, bit for bit, whatever the tie structure.
 //
+// Three paths, same edge sets:
+//   explicit edge list (fedicra_mst_forward): find / hook / compress kernels per round;
+//   implicit grid, default: mst_tile_kernel (rounds inside 64x64 tiles out of shared memory, hands over the CONTRACTED
+//     graph) + mst_contract_kernel (one CTA per tree finishes on that graph out of shared memory);
+//   implicit grid, FEDICRA_MST_FINISH=cluster (round 1): mst_tile_kernel + mst_grid_cluster_kernel (thread-block cluster
+//     per tree on vertex lists in L2), or the cluster kernel alone (FEDICRA_MST_TILES=0).
+//
 // Also fuses MinimumSpanningTree._build_matrix_index / _build_feature_weight (LTF/modules/tree_filter.py:15-34): on the
 // implicit 4-connected grid the edge list is never materialised and the weights come straight from the embedding.
 #include <cooperative_groups.h>
@@ -478,10 +485,12 @@ mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, in
 // tile; when it leaves the tile the component waits for the global rounds (it may still be hooked INTO by others, after
 // which its cheapest edge is looked at again).  A component's cheapest outgoing edge belongs to the MST whatever the
 // others do (cut property, keys are distinct), so the edges chosen here are exactly those the untiled rounds would
-// choose: same edge set, bit for bit.  The rounds stop after `max_rounds` or when a whole round hooks nothing.  What is left for the cluster
-// kernel is the tile boundaries: a few hundred components per tile instead of 4 096 vertices.
-// Output: edge weights and tree flags of the tile's own edges (down / right of each of its vertices), fresh labels
-// (DEAD for vertices whose neighbours all share their component), identity hooks, and the root / active lists.
+// choose: same edge set, bit for bit.  The rounds stop after `max_rounds` or when a whole round hooks nothing.  What is
+// left is the tile boundaries: a few hundred components per tile instead of 4 096 vertices.
+// Output, contract = 1 (default): the adjacency-mask bits of the edges chosen here, dense component numbers on the tile's
+// first row and column, and one record per cross edge (see the hand-over below).  contract = 0 (cluster finish): edge
+// weights and tree flags of the tile's own edges (down / right of each of its vertices), fresh labels (DEAD for vertices
+// whose neighbours all share their component), identity hooks, and the root / active lists.
 // FEDICRA_PROF=1: clock64 stamps of tree 0's contraction (start, records, components, loaded, then per round: found,
 // located, hooked, chased, compacted, records left) -- read back with fedicra_debug_mst_profile
 constexpr int MPROF = 128;   // [0,64) contraction kernel, [64,128) tile kernel (tile 0 of tree 0: start, weights, each round, ranks, tables, emitted)
@@ -1119,10 +1128,10 @@ __global__ void __launch_bounds__(CNT) mst_contract_kernel(Ws ws, unsigned char 
     }
 }
 
-// Tile-local rounds before the cluster kernel takes over.  The tile kernel is issue-bound (~9 us per round and CTA, 2.6
-// waves of CTAs for 48 trees of 256^2) and its late rounds hook little; measured on B200, 48 trees, total MST time:
-// 3 rounds 381 us, 4 rounds 367 us, 5 rounds 377 us, 6 rounds 393 us, until nothing hooks (7-8 rounds) 420 us, no tile
-// kernel at all 490 us.
+// Tile-local rounds before the finish.  The tile kernel is issue-bound (~10 us per round and CTA, 2.6 waves of CTAs for 48
+// trees of 256^2) and its late rounds hook little; measured on B200, 48 trees, total MST time with the contracted
+// finish: 3 rounds 245 us, 4 rounds 244 us, 5 rounds 273 us (512^2: 955 / 928 / 1 021); with the cluster finish: 3 rounds
+// 381 us, 4 rounds 367 us, 5 rounds 377 us, 6 rounds 393 us, until nothing hooks (7-8 rounds) 420 us, no tile kernel 490 us.
 int env_tile_rounds() {
     const char *v = getenv("FEDICRA_MST_TILE_ROUNDS");
     const int x = (v && *v) ? atoi(v) : 4;

@@ -267,7 +267,7 @@ def chain_filter_forward(feature_in, edge_weight, si, sp, sc, gs, saved=None):
 def chain_saved_arrays(saved, B, C, V):
     """(leaf->root values, root->leaf aggregates), each [B,C+1,V] float32 in chain order (channel C = weight sums)."""
     off = lib.fedicra_chain_filter_saved_offset(B, C, V)
-    return saved[off:].view(torch.float32).view(2, B, C + 1, V)
+    return saved[off:off + 2 * B * (C + 1) * V * 4].view(torch.float32).view(2, B, C + 1, V)   # (an armed buffer is padded)
 
 
 def chain_watchdog_trips(saved):

@@ -129,6 +129,33 @@ def test_chain_filter_vs_oracle(kind, B, C, D, H, W, inv_sigma):
     assert none is None and rel_err(cgf2.cpu(), gf) < TOL
 
 
+@pytest.mark.parametrize("kind,B,C,D,H,W", [("quant8", 3, 2, 3, 96, 80), ("uniform", 2, 3, 2, 33, 47), ("uniform", 1, 1, 1, 1, 1)])
+def test_armed_buffers_give_the_same_bits(kind, B, C, D, H, W):
+    """fedicra_chain_filter_arm + _forward_armed / _backward_armed (one memset for several launches) against the calls
+    that arm their own buffer: the same bits; an armed buffer serves one launch, a used one must not be passed again
+    (here: re-armed by hand and used again)."""
+    from fedicra_b200 import ops
+    emb, feat, gout = _case(kind, B, C, D, H, W)
+    V = H * W
+    _, mask = ops.mst_grid(emb.cuda(), want_mask=True)
+    si, sp, sc, gs = ops.chain_order(mask, H, W)
+    cew = ops.edge_weight_fwd(emb.reshape(B, D, V).cuda(), si, sp, 1.0)
+    out, sv = ops.chain_filter_forward(feat.cuda(), cew, si, sp, sc, gs)
+    gf, gw = ops.chain_filter_backward(gout.cuda(), cew, si, sp, sc, gs, sv, True)
+    bufs = ops.chain_arm(B, C, V, 3, feat.cuda().device)
+    assert all(b.data_ptr() % 256 == 0 for b in bufs)
+    out2, sv2 = ops.chain_filter_forward(feat.cuda(), cew, si, sp, sc, gs, saved=bufs[0])
+    assert sv2.data_ptr() == bufs[0].data_ptr()
+    gf2, gw2 = ops.chain_filter_backward(gout.cuda(), cew, si, sp, sc, gs, sv2, True, armed_workspace=bufs[1])
+    torch.cuda.synchronize()
+    assert ops.chain_watchdog_trips(sv2) == 0 and ops.chain_watchdog_trips(bufs[1]) == 0
+    assert torch.equal(out, out2) and torch.equal(gf, gf2) and torch.equal(gw, gw2)
+    assert torch.equal(ops.chain_saved_arrays(sv, B, C, V), ops.chain_saved_arrays(sv2, B, C, V))
+    bufs[1].fill_(255)                     # what fedicra_chain_filter_arm does
+    gf3, gw3 = ops.chain_filter_backward(gout.cuda(), cew, si, sp, sc, gs, sv2, True, armed_workspace=bufs[1])
+    assert torch.equal(gf, gf3) and torch.equal(gw, gw3)
+
+
 def test_chain_and_band_filters_agree_at_full_size():
     """Two independent implementations (depth bands on the BFS order, affine scans on the chain order) of the same filter."""
     from fedicra_b200 import ops
