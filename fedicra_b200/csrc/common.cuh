@@ -6,7 +6,7 @@
 
 #include "../../include/fedicra_sm100.h"
 
-#define FEDICRA_ABI_VERSION 3
+#define FEDICRA_ABI_VERSION 4
 
 // Record an error message for fedicra_last_error() and return `code` (always negative).
 int fedicra_fail(int code, const char *fmt, ...);

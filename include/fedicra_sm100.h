@@ -30,7 +30,8 @@ extern "C" {
 
 /* Text of the last error raised on the calling thread ("" if none). */
 const char *fedicra_last_error(void);
-/* ABI version of this header (bumped on any signature change). */
+/* ABI version of this header (bumped on any signature change or added entry point; 4 = round 2: chain order / chain
+ * filter, armed filter buffers, bilinear resize, MST profile). */
 int fedicra_abi_version(void);
 /* Telemetry: kernels launched by this library in this process so far (no counterpart in the reference). */
 long long fedicra_launch_count(void);

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     for name in declared_symbols():
         assert hasattr(_lib.lib, name), f"{name} declared in the header but not exported"
         assert name in _lib.SIGNATURES, f"{name} has no ctypes signature"
-    assert _lib.lib.fedicra_abi_version() == 3
+    assert _lib.lib.fedicra_abi_version() == 4
     assert _lib.lib.fedicra_last_error() == b""
 
 
