@@ -67,6 +67,7 @@ SIGNATURES = {
     "fedicra_edge_weight_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p]),
     "fedicra_edge_weight_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                         c_float, c_void_p, c_void_p]),
+    "fedicra_edge_weight_bwd_multi": (c_int, [c_void_p] * 8 + [c_int, c_int, c_int, c_void_p, c_void_p]),
     "fedicra_refine_forward": (c_int, [c_void_p] * 7 + [c_int, c_int, c_int] + [c_void_p] * 5 + [c_void_p]),
     "fedicra_refine_backward_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "fedicra_refine_backward_feature": (c_int, [c_void_p] * 8 + [c_int, c_int, c_int, c_void_p, c_void_p, c_size_t,

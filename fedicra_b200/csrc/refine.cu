@@ -255,6 +255,48 @@ __global__ void edge_weight_bwd_kernel(const float *__restrict__ embed, const in
     }
 }
 
+// The same gradient for the trees of several embeddings of one batch in ONE launch (the heads of the multiscale loss:
+// their filters run one after the other, their weight gradients are all there when the last filter's backward is done).
+constexpr int EWB_MAX = 8;
+struct EwbSet {
+    const float *embed[EWB_MAX], *ew[EWB_MAX], *gew[EWB_MAX];
+    const int *si[EWB_MAX], *sp[EWB_MAX], *sc[EWB_MAX];
+    float *grad[EWB_MAX];
+    int D[EWB_MAX];
+    float inv_sigma[EWB_MAX];
+};
+__global__ void edge_weight_bwd_multi_kernel(EwbSet es, int V, size_t per) {   // per = B * V positions per embedding
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int k = blockIdx.y;
+    if (idx >= per) return;
+    const size_t b = idx / V;
+    const int i = (int)(idx % V);
+    const int *sib = es.si[k] + b * V;
+    const float *ewb = es.ew[k] + b * V, *gb = es.gew[k] + b * V;
+    const float inv_sigma = es.inv_sigma[k];
+    const int D = es.D[k];
+    const int v = sib[i], pv = sib[es.sp[k][b * V + i]];
+    const int4 ch = reinterpret_cast<const int4 *>(es.sc[k])[b * V + i];
+    const float kk = (i > 0) ? -2.f * inv_sigma * ewb[i] * gb[i] : 0.f;
+    const int cj[4] = {ch.x, ch.y, ch.z, ch.w};
+    float kj[4];
+    int vj[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        kj[j] = (cj[j] > 0) ? -2.f * inv_sigma * ewb[cj[j]] * gb[cj[j]] : 0.f;
+        vj[j] = (cj[j] > 0) ? sib[cj[j]] : v;
+    }
+    const float *e = es.embed[k] + b * D * V;
+    float *g = es.grad[k] + b * D * V;
+    for (int c = 0; c < D; ++c) {
+        const float ev = e[(size_t)c * V + v];
+        float acc = kk * (ev - e[(size_t)c * V + pv]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc -= kj[j] * (e[(size_t)c * V + vj[j]] - ev);
+        g[(size_t)c * V + v] = acc;
+    }
+}
+
 unsigned blocks_for(size_t n, int t) { return (unsigned)((n + t - 1) / t); }
 
 }  // namespace
@@ -282,6 +324,31 @@ extern "C" int fedicra_edge_weight_bwd(const float *embed, const int *sorted_ind
         embed, sorted_index, sorted_parent, sorted_child, edge_weight, grad_edge_weight, D, V, inv_sigma, grad_embed,
         total);
     FEDICRA_CHECK_LAUNCH("edge_weight_bwd_kernel");
+    return 0;
+}
+
+extern "C" int fedicra_edge_weight_bwd_multi(const float *const *h_embed, const int *const *h_sorted_index,
+                                             const int *const *h_sorted_parent, const int *const *h_sorted_child,
+                                             const float *const *h_edge_weight, const float *const *h_grad_edge_weight,
+                                             const int *h_D, const float *h_inv_sigma, int K, int B, int V,
+                                             float *const *h_grad_embed, void *stream) {
+    FEDICRA_REQUIRE(h_embed && h_sorted_index && h_sorted_parent && h_sorted_child && h_edge_weight &&
+                        h_grad_edge_weight && h_D && h_inv_sigma && h_grad_embed, "edge_weight_bwd_multi: null pointer");
+    FEDICRA_REQUIRE(K >= 1 && K <= EWB_MAX && B > 0 && V > 0, "edge_weight_bwd_multi: bad sizes K=%d (1..%d) B=%d V=%d", K,
+                    EWB_MAX, B, V);
+    EwbSet es = {};
+    for (int k = 0; k < K; ++k) {
+        FEDICRA_REQUIRE(h_embed[k] && h_sorted_index[k] && h_sorted_parent[k] && h_sorted_child[k] && h_edge_weight[k] &&
+                            h_grad_edge_weight[k] && h_grad_embed[k] && h_D[k] > 0,
+                        "edge_weight_bwd_multi: entry %d has a null pointer or no channels", k);
+        FEDICRA_REQUIRE(((uintptr_t)h_sorted_child[k] & 15) == 0, "edge_weight_bwd_multi: sorted_child must be 16-byte aligned");
+        es.embed[k] = h_embed[k]; es.si[k] = h_sorted_index[k]; es.sp[k] = h_sorted_parent[k]; es.sc[k] = h_sorted_child[k];
+        es.ew[k] = h_edge_weight[k]; es.gew[k] = h_grad_edge_weight[k]; es.grad[k] = h_grad_embed[k];
+        es.D[k] = h_D[k]; es.inv_sigma[k] = h_inv_sigma[k];
+    }
+    const size_t per = (size_t)B * V;
+    edge_weight_bwd_multi_kernel<<<dim3(blocks_for(per, 256), K), 256, 0, (cudaStream_t)stream>>>(es, V, per);
+    FEDICRA_CHECK_LAUNCH("edge_weight_bwd_multi_kernel");
     return 0;
 }
 

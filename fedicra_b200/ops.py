@@ -317,6 +317,26 @@ def edge_weight_bwd(embed, si, sp, sc, ew, grad_ew, inv_sigma):
     return out
 
 
+def edge_weight_bwd_multi(embeds, orders, ews, grad_ews, inv_sigmas):
+    """edge_weight_bwd of K embeddings of one batch ([B,D_k,V]; orders[k] = (si, sp, sc)) in one launch.  Returns the
+    K gradients."""
+    import ctypes
+    es = [_cuda(e, torch.float32, "embed_in") for e in embeds]
+    gs = [_cuda(g, torch.float32, "grad_edge_weight") for g in grad_ews]
+    K = len(es)
+    B, _, V = es[0].shape
+    assert all(e.shape[0] == B and e.shape[2] == V for e in es)
+    with torch.cuda.device(es[0].device):
+        outs = [torch.empty_like(e) for e in es]
+        arr = lambda ts: (ctypes.c_void_p * K)(*[t.data_ptr() for t in ts])
+        dims = (ctypes.c_int * K)(*[e.shape[1] for e in es])
+        sig = (ctypes.c_float * K)(*[float(x) for x in inv_sigmas])
+        check(lib.fedicra_edge_weight_bwd_multi(arr(es), arr([o[0] for o in orders]), arr([o[1] for o in orders]),
+                                                arr([o[2] for o in orders]), arr(ews), arr(gs), dims, sig, K, B, V,
+                                                arr(outs), _stream()), "edge_weight_bwd_multi")
+    return outs
+
+
 # ------------------------------------------------------------------ refine
 
 

@@ -10,7 +10,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from . import ops
-from .tree_filter import MinimumSpanningTree, TreeFilter2D, batched_tree_orders
+from .tree_filter import MinimumSpanningTree, TreeFilter2D, batched_tree_orders, edge_weights_multi
 
 
 def _prepare(preds, low_feats, unlabeled_ROIs):
@@ -185,6 +185,12 @@ class _TreeLossBase(nn.Module):
                     bufs = ops.chain_arm(B, channels, V, 2 * len(chains), embeds[0].device)
                     for a in chains:
                         a.armed = [bufs.pop(), bufs.pop()]
+            # the heads' edge weights as ONE autograd node: one backward launch for all of them
+            if channels is not None and torch.is_grad_enabled():
+                joint = [(o.for_channels(channels), e, s) for o, e, s in zip(orders[1:], embeds[1:], inv[1:]) if e.requires_grad]
+                joint = [t for t in joint if t[0].kind == "chain" and t[0].ew is not None]
+                if len(joint) >= 2:
+                    edge_weights_multi([t[0] for t in joint], [t[1] for t in joint], [t[2] for t in joint])
             if self.on_topology_enqueued is not None:
                 self.on_topology_enqueued()
             return orders

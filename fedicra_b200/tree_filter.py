@@ -43,7 +43,7 @@ class _Arrays:
     sorted_child; bfs.cu:46-98) plus what this library's filter kernels need on top of it:
       kind "chain": group_start (heavy-chain order, csrc/chains.cu);  kind "bfs": level_start, n_levels, band plan."""
 
-    __slots__ = ("kind", "si", "sp", "sc", "gs", "ls", "nl", "bands", "ew", "ew_key", "armed")
+    __slots__ = ("kind", "si", "sp", "sc", "gs", "ls", "nl", "bands", "ew", "ew_key", "armed", "ew_out")
 
     def __init__(self, kind, si, sp, sc, gs=None, ls=None, nl=None, bands=None, ew=None, ew_key=None):
         self.kind, self.si, self.sp, self.sc, self.gs, self.ls, self.nl, self.bands = kind, si, sp, sc, gs, ls, nl, bands
@@ -52,6 +52,8 @@ class _Arrays:
         self.ew, self.ew_key = ew, ew_key
         # chain kind: buffers armed ahead for the filter launches on these trees (ops.chain_arm), each used once
         self.armed = []
+        # the same edge weights as an output of the step's joint autograd node (edge_weights_multi), if there is one
+        self.ew_out = None
 
 
 def _want_chain(V):
@@ -194,6 +196,49 @@ class _EdgeWeight(torch.autograd.Function):
         return ops.edge_weight_bwd(embed, o.si, o.sp, o.sc, ew, grad_ew, ctx.inv_sigma), None, None
 
 
+class _EdgeWeightMulti(torch.autograd.Function):
+    """Edge weights of the trees of SEVERAL embeddings of one batch as one autograd node: the weights came out of the
+    ordering pass, and the backward -- the gradients w.r.t. all the embeddings -- is one launch, issued when the last
+    of their filters has delivered its weight gradient, instead of one launch between every two filter backwards."""
+
+    @staticmethod
+    def forward(ctx, orders, inv_sigmas, *embeds):
+        ews = []
+        for o in orders:
+            ews.append(o.ew)
+            o.ew = None
+        ctx.orders, ctx.inv_sigmas = orders, inv_sigmas
+        ctx.save_for_backward(*embeds, *ews)
+        ctx.set_materialize_grads(False)
+        return tuple(e.view_as(e) for e in ews)
+
+    @staticmethod
+    def backward(ctx, *grad_ews):
+        K = len(ctx.orders)
+        embeds, ews = ctx.saved_tensors[:K], ctx.saved_tensors[K:]
+        live = [k for k in range(K) if grad_ews[k] is not None and ctx.needs_input_grad[2 + k]]
+        out = [None] * K
+        if live:
+            grads = ops.edge_weight_bwd_multi([embeds[k] for k in live],
+                                              [(ctx.orders[k].si, ctx.orders[k].sp, ctx.orders[k].sc) for k in live],
+                                              [ews[k] for k in live], [grad_ews[k] for k in live],
+                                              [ctx.inv_sigmas[k] for k in live])
+            for k, g in zip(live, grads):
+                out[k] = g
+        return (None, None, *out)
+
+
+def edge_weights_multi(orders, embeds, inv_sigmas):
+    """Joins the edge weights that batched_tree_orders computed for `embeds` ([B,D,H,W], requiring grad) into one autograd
+    node; `TreeFilter2D.build_edge_weight` then hands out its outputs.  orders: the chain `_Arrays` of those embeddings."""
+    flat = [e.reshape(e.shape[0], e.shape[1], -1).float() for e in embeds]
+    if any(o.ew is None or o.ew_key != _ew_key(f, s) for o, f, s in zip(orders, flat, inv_sigmas)):
+        return
+    outs = _EdgeWeightMulti.apply(tuple(orders), tuple(float(s) for s in inv_sigmas), *flat)
+    for o, w in zip(orders, outs):
+        o.ew_out = w
+
+
 class _Refine(torch.autograd.Function):
     """Two-pass tree filter (affine scans along heavy chains, csrc/chains.cu; or the depth-banded kernels,
     csrc/bands.cu); same gradient policy as functions/refine.py:23-40 (weight gradient for the high-level trees only,
@@ -244,7 +289,11 @@ class TreeFilter2D(nn.Module):
         batch, channel = fm.shape[0], fm.shape[1]
         fm = fm.reshape(batch, channel, -1)
         if _is_norm2(self.distance_func):
-            return _EdgeWeight.apply(fm.float(), order, 1.0 / self.sigma if low_tree else 1.0)
+            inv_sigma = 1.0 / self.sigma if low_tree else 1.0
+            if order.ew_out is not None and order.ew_key == _ew_key(fm.float(), inv_sigma):
+                out, order.ew_out = order.ew_out, None      # used once: the filter writes w_0 = 0 into it
+                return out
+            return _EdgeWeight.apply(fm.float(), order, inv_sigma)
         idx = order.si.long().unsqueeze(1).expand(-1, channel, -1)
         src = torch.gather(fm, 2, idx)
         dst = torch.gather(src, 2, order.sp.long().unsqueeze(1).expand(-1, channel, -1))

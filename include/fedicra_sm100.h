@@ -161,6 +161,14 @@ int fedicra_edge_weight_fwd(const float *embed, const int *sorted_index, const i
 int fedicra_edge_weight_bwd(const float *embed, const int *sorted_index, const int *sorted_parent,
                             const int *sorted_child, const float *edge_weight, const float *grad_edge_weight, int B,
                             int D, int V, float inv_sigma, float *grad_embed, void *stream);
+/* The same for the trees of K <= 8 embeddings of one batch ([B,D_k,V] each, own orderings and edge weights) in one
+ * launch -- the decoder heads of the multiscale loss (flower_common.py:786-806).  The h_* arrays are HOST arrays of K
+ * device pointers / values. */
+int fedicra_edge_weight_bwd_multi(const float *const *h_embed, const int *const *h_sorted_index,
+                                  const int *const *h_sorted_parent, const int *const *h_sorted_child,
+                                  const float *const *h_edge_weight, const float *const *h_grad_edge_weight,
+                                  const int *h_D, const float *h_inv_sigma, int K, int B, int V,
+                                  float *const *h_grad_embed, void *stream);
 
 /* refine_forward (LTF/src/refine/refine.cu:201-249).  Writes 0 into edge_weight[:,0] like the reference (:43-46).
  *   feature_in [B,C,V] vertex order; edge_weight [B,V] BFS order
