@@ -98,3 +98,38 @@ def test_bilinear_resize_has_torchs_bits_and_its_gradient(B, C, sizes, H, W):
         assert torch.equal(o, want.detach()), "resized head differs from torch's bits"
         want.backward(go)
         assert rel(gi, xr.grad) < 1e-5
+
+
+def test_edge_weight_backward_of_several_embeddings_in_one_launch():
+    """fedicra_edge_weight_bwd_multi == fedicra_edge_weight_bwd per embedding, bit for bit (different channel counts,
+    different trees, different 1/sigma), and the joint autograd node of the loss modules hands out exactly the weights
+    the ordering pass computed."""
+    from fedicra_b200 import ops
+    from fedicra_b200.tree_filter import TreeFilter2D, batched_tree_orders, edge_weights_multi
+    g = torch.Generator().manual_seed(5)
+    B, H, W = 3, 40, 56
+    V = H * W
+    embeds = [torch.randn(B, D, H, W, generator=g).cuda().requires_grad_() for D in (2, 3, 1)]
+    inv = [1.0, 0.5, 50.0]
+    orders = batched_tree_orders(embeds, inv)
+    arrays = [o.for_channels(2) for o in orders]
+    assert all(a.kind == "chain" for a in arrays)
+    ews = [a.ew.clone() for a in arrays]
+    gews = [torch.randn(B, V, generator=g).cuda() for _ in embeds]
+    flat = [e.detach().reshape(B, e.shape[1], V) for e in embeds]
+    single = [ops.edge_weight_bwd(f, a.si, a.sp, a.sc, w, gw, s) for f, a, w, gw, s in zip(flat, arrays, ews, gews, inv)]
+    multi = ops.edge_weight_bwd_multi(flat, [(a.si, a.sp, a.sc) for a in arrays], ews, gews, inv)
+    for x, y in zip(single, multi):
+        assert torch.equal(x, y)
+    edge_weights_multi(arrays, embeds, inv)
+    tf = TreeFilter2D()
+    outs = []
+    for a, e, s, w in zip(arrays, embeds, inv, ews):
+        assert a.ew is None and a.ew_out is not None
+        tf.sigma = 1.0 / s
+        out = tf.build_edge_weight(e, a, low_tree=True)       # low_tree: 1/sigma as given
+        assert a.ew_out is None and torch.equal(out.detach(), w)
+        outs.append(out)
+    sum((o * gw).sum() for o, gw in zip(outs, gews)).backward()
+    for e, want in zip(embeds, single):
+        assert torch.equal(e.grad.reshape(B, -1, V), want)
