@@ -493,7 +493,9 @@ mst_grid_cluster_kernel(Ws ws, EmbedSet es, unsigned char *__restrict__ mask, in
 // whose neighbours all share their component), identity hooks, and the root / active lists.
 // FEDICRA_PROF=1: clock64 stamps of tree 0's contraction (start, records, components, loaded, then per round: found,
 // located, hooked, chased, compacted, records left) -- read back with fedicra_debug_mst_profile
-constexpr int MPROF = 128;   // [0,64) contraction kernel, [64,128) tile kernel (tile 0 of tree 0: start, weights, each round, ranks, tables, emitted)
+constexpr int MPROF = 128;   // [0,64) contraction kernel, [64,128) tile kernel (tile 0 of tree 0: start, weights; per round the
+                             // phases as (marker, time) pairs -- -10 found, -11 min weight, -12 min code, -13 hooked -- then the
+                             // round's end; -2, ranks, tables, emitted, -1)
 __device__ long long g_mst_prof[MPROF];
 #define MST_STAMP(val)                                                                    \
     do {                                                                                  \
@@ -650,86 +652,86 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
                 const unsigned short cl = s_lab[l];
                 kc[q] = cl;
                 const float wu = s_wv[l], wd = s_wv[l + TS], wl = s_wh[l + r], wr = s_wh[l + r + 1];
+                // the neighbours' labels are read unconditionally (own label where the neighbour is outside the tile), so
+                // that all nine loads of a vertex are in flight together instead of behind short-circuit branches
+                const bool in_u = r > 0, in_d = r + 1 < th, in_l = c > 0, in_r = c + 1 < tw;
+                const unsigned short lu = s_lab[in_u ? l - TS : l], ld = s_lab[in_d ? l + TS : l],
+                                     ll = s_lab[in_l ? l - 1 : l], lr = s_lab[in_r ? l + 1 : l];
                 // candidates in increasing code order (up, down are vertical: codes r<<7|c and (r+1)<<7|c; then left, right)
                 unsigned bw = 0xffffffffu, be = 0xffffffffu;
-                auto take = [&](float wt, unsigned code) {
-                    const unsigned o = orderable(wt);
+                auto take = [&](bool out, float wt, unsigned code) {
+                    const unsigned o = out ? orderable(wt) : 0xffffffffu;
                     if (o < bw) { bw = o; be = code; }   // strict: on equal weight the earlier (smaller) code stays
                 };
-                if (wu > 0.f && (r == 0 || s_lab[l - TS] != cl)) take(wu, (unsigned)(r << 7 | c));
-                if (wd > 0.f && (r + 1 >= th || s_lab[l + TS] != cl)) take(wd, (unsigned)((r + 1) << 7 | c));
-                if (wl > 0.f && (c == 0 || s_lab[l - 1] != cl)) take(wl, (unsigned)(1 << 14 | r << 7 | c));
-                if (wr > 0.f && (c + 1 >= tw || s_lab[l + 1] != cl)) take(wr, (unsigned)(1 << 14 | r << 7 | (c + 1)));
+                take((wu > 0.f) & (!in_u | (lu != cl)), wu, (unsigned)(r << 7 | c));
+                take((wd > 0.f) & (!in_d | (ld != cl)), wd, (unsigned)((r + 1) << 7 | c));
+                take((wl > 0.f) & (!in_l | (ll != cl)), wl, (unsigned)(1 << 14 | r << 7 | c));
+                take((wr > 0.f) & (!in_r | (lr != cl)), wr, (unsigned)(1 << 14 | r << 7 | (c + 1)));
                 kw[q] = bw;
                 ke[q] = be;
                 if (be == 0xffffffffu) interior |= 1u << q;
             }
-            // one atomic per warp when all its candidates belong to one component (the usual case once components are
-            // large: a warp is 32 consecutive pixels of a row), else one per lane -- and only when it can lower the slot
-    #pragma unroll
-            for (int q = 0; q < PER; ++q) {
-                const bool has = ke[q] != 0xffffffffu;
-                const unsigned m = __ballot_sync(0xffffffffu, has);
-                if (m == 0) continue;
-                const int first = __ffs(m) - 1;
-                const unsigned c0l = __shfl_sync(0xffffffffu, (unsigned)kc[q], first);
-                if (__all_sync(0xffffffffu, !has || kc[q] == c0l)) {
-                    const unsigned wmin = __reduce_min_sync(0xffffffffu, kw[q]);
-                    if (lane == first && wmin < s_bw[c0l]) atomicMin(s_bw + c0l, wmin);
-                } else if (has && kw[q] < s_bw[kc[q]]) {
-                    atomicMin(s_bw + kc[q], kw[q]);
-                }
-            }
+            MST_STAMP(-10ll); MST_STAMP(clock64());
+            // min weight per component, then min code among the edges of that weight; an atomic is issued only when it
+            // can lower the slot.  (Measured: electing one lane per warp when all its candidates share a component -- the
+            // usual case once components are large -- costs more in votes and shuffles than it saves in atomics.)
+#pragma unroll
+            for (int q = 0; q < PER; ++q)
+                if (ke[q] != 0xffffffffu && kw[q] < s_bw[kc[q]]) atomicMin(s_bw + kc[q], kw[q]);
             __syncthreads();
-    #pragma unroll
-            for (int q = 0; q < PER; ++q) {
-                const bool has = ke[q] != 0xffffffffu && s_bw[kc[q]] == kw[q];
-                const unsigned m = __ballot_sync(0xffffffffu, has);
-                if (m == 0) continue;
-                const int first = __ffs(m) - 1;
-                const unsigned c0l = __shfl_sync(0xffffffffu, (unsigned)kc[q], first);
-                if (__all_sync(0xffffffffu, !has || kc[q] == c0l)) {
-                    const unsigned emin = __reduce_min_sync(0xffffffffu, has ? ke[q] : 0xffffffffu);
-                    if (lane == first && emin < s_be[c0l]) atomicMin(s_be + c0l, emin);
-                } else if (has && ke[q] < s_be[kc[q]]) {
-                    atomicMin(s_be + kc[q], ke[q]);
-                }
-            }
+            MST_STAMP(-11ll); MST_STAMP(clock64());
+#pragma unroll
+            for (int q = 0; q < PER; ++q)
+                if (ke[q] != 0xffffffffu && s_bw[kc[q]] == kw[q] && ke[q] < s_be[kc[q]]) atomicMin(s_be + kc[q], ke[q]);
             __syncthreads();
-
+            MST_STAMP(-12ll); MST_STAMP(clock64());
         }
         // hook: a root whose cheapest edge lies inside the tile follows it (of a mutual pair the larger root hooks)
         int merged = 0;
+        // four vertices at a time, every stage's loads issued together (labels, codes, endpoint labels, the other root's
+        // code): the stages are chains of dependent shared-memory reads
 #pragma unroll
-        for (int q = 0; q < PER; ++q) {
-            const int r = rbase + q * (TNT / TS), l = r * TS + c;
-            if (r >= th || c >= tw || s_lab[l] != l) continue;
-            const unsigned code = s_be[l];
-            if (code == 0xffffffffu) continue;
-            const int horiz = code >> 14, er = (code >> 7) & 127, ec = code & 127;
-            int la, lb;   // local endpoints
-            if (!horiz) {
-                if (er < 1 || er >= th) continue;   // leaves the tile
-                la = (er - 1) * TS + ec;
-                lb = er * TS + ec;
-            } else {
-                if (ec < 1 || ec >= tw) continue;
-                la = er * TS + ec - 1;
-                lb = er * TS + ec;
+        for (int h = 0; h < PER; h += 4) {
+            int l4[4], la[4], lb[4], other[4];
+            unsigned code[4];
+            bool act[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int r = rbase + (h + k) * (TNT / TS);
+                l4[k] = r * TS + c;
+                act[k] = r < th && c < tw && s_lab[l4[k]] == l4[k];
             }
-            const int ca = s_lab[la], cb = s_lab[lb];
-            const int other = (ca == l) ? cb : ca;
-            if (s_be[other] == code && l < other) continue;   // same edge from both sides (codes are unique)
-            s_par[l] = (unsigned short)other;
-            if (contract) {   // mask bits of both endpoints: 1 up, 2 left, 4 right, 8 down
-                atomicOr(s_sel + (la >> 2), (horiz ? 4u : 8u) << ((la & 3) * 8));
-                atomicOr(s_sel + (lb >> 2), (horiz ? 2u : 1u) << ((lb & 3) * 8));
-            } else {
-                intree[horiz ? nvert + (h0 + er) * (W - 1) + w0 + ec - 1 : (h0 + er - 1) * W + w0 + ec] = 1;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) code[k] = act[k] ? s_be[l4[k]] : 0xffffffffu;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int horiz = code[k] >> 14, er = (code[k] >> 7) & 127, ec = code[k] & 127;
+                act[k] = code[k] != 0xffffffffu && (horiz ? (ec >= 1 && ec < tw) : (er >= 1 && er < th));   // else: leaves the tile
+                lb[k] = act[k] ? er * TS + ec : 0;
+                la[k] = act[k] ? (horiz ? lb[k] - 1 : lb[k] - TS) : 0;
             }
-            merged = 1;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int ca = s_lab[la[k]], cb = s_lab[lb[k]];
+                other[k] = (ca == l4[k]) ? cb : ca;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (!act[k] || (s_be[other[k]] == code[k] && l4[k] < other[k])) continue;   // same edge from both sides: the smaller root stays
+                const int horiz = code[k] >> 14;
+                s_par[l4[k]] = (unsigned short)other[k];
+                if (contract) {   // mask bits of both endpoints: 1 up, 2 left, 4 right, 8 down
+                    atomicOr(s_sel + (la[k] >> 2), (horiz ? 4u : 8u) << ((la[k] & 3) * 8));
+                    atomicOr(s_sel + (lb[k] >> 2), (horiz ? 2u : 1u) << ((lb[k] & 3) * 8));
+                } else {
+                    const int er = (code[k] >> 7) & 127, ec = code[k] & 127;
+                    intree[horiz ? nvert + (h0 + er) * (W - 1) + w0 + ec - 1 : (h0 + er - 1) * W + w0 + ec] = 1;
+                }
+                merged = 1;
+            }
         }
         merged = __syncthreads_or(merged);
+        MST_STAMP(-13ll); MST_STAMP(clock64());
         // chase: labels follow the hooks; cheapest-edge slots are cleared for the next round
 #pragma unroll
         for (int q = 0; q < PER; ++q) {

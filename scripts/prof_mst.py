@@ -33,16 +33,19 @@ while i + 5 < 128 and v[i] != -1:
 print(f"total {(prev - t0) / mhz:.1f} us")
 t = v[64:]
 if t[0] > 0:
-    names, out, prev, k = ["weights"], [], t[0], 1
-    while k < 64 and t[k] not in (-1, -2, 0):
-        out.append(f"{'weights' if k == 1 else 'round %d' % (k - 2)} {(t[k] - prev) / mhz:.1f}")
-        prev = t[k]; k += 1
-    if t[k] == -2:
-        labels = ["ranks+classify", "tables", "emit"]
-        prev2 = prev
-        for j, lab in enumerate(labels):
+    names = {-10: "find", -11: "min weight", -12: "min code", -13: "hook"}
+    out, prev, k, rnd = [f"weights {(t[1] - t[0]) / mhz:.1f}"], t[1], 2, 0
+    while k < 64 and t[k] not in (0, -1, -2):
+        if t[k] in names:
+            out.append(f"{names[t[k]]} {(t[k + 1] - prev) / mhz:.1f}")
+            prev, k = t[k + 1], k + 2
+        else:
+            out.append(f"rest {(t[k] - prev) / mhz:.1f} (round {rnd} done) |")
+            prev, k, rnd = t[k], k + 1, rnd + 1
+    if k < 61 and t[k] == -2:
+        for j, lab in enumerate(["ranks+classify", "pair table", "emit"]):
             cur = t[k + 1 + j]
-            out.append(f"{lab} {(cur - prev2) / mhz:.1f}")
-            prev2 = cur
-        out.append(f"total {(prev2 - t[0]) / mhz:.1f}")
-    print("tile 0 of tree 0 (us):", ", ".join(out))
+            out.append(f"{lab} {(cur - prev) / mhz:.1f}")
+            prev = cur
+        out.append(f"| total {(prev - t[0]) / mhz:.1f}")
+    print("tile 0 of tree 0 (us):", " ".join(out))
