@@ -541,65 +541,72 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
     auto h_valid = [&](int r, int c) { return r < th && c <= tw && w0 + c >= 1 && w0 + c < W; };      // s_wh[r][c]
     // ---- weights of every edge that touches the tile: sum_c (delta)^2 + 1, channels in order, no fused multiply-add
     //      (tree_filter.py:27-34); the embedding is staged one channel at a time (tile + one pixel of halo)
-    for (int i = tid; i < (TS + 1) * TS; i += TNT) s_wv[i] = 0.f;
-    for (int i = tid; i < TS * (TS + 1); i += TNT) s_wh[i] = 0.f;
+    //      The sums live in registers (each thread owns the same nine vertical and nine horizontal edges in every
+    //      channel) and the next channel's pixels are already on their way while the current one is being differenced.
+    constexpr int NX = (XS * XS + TNT - 1) / TNT, NE = ((TS + 1) * TS + TNT - 1) / TNT;
+    float av[NE], ah[NE], xv[NX];
+#pragma unroll
+    for (int k = 0; k < NE; ++k) av[k] = ah[k] = 0.f;
+    auto fetch = [&](int ch) {
+#pragma unroll
+        for (int k = 0; k < NX; ++k) {
+            const int i = tid + k * TNT, r = i / XS, c = i - r * XS, hh = h0 + r - 1, ww = w0 + c - 1;
+            xv[k] = (i < XS * XS && hh >= 0 && hh < H && ww >= 0 && ww < W) ? x[(size_t)ch * V + (size_t)hh * W + ww] : 0.f;
+        }
+    };
+    fetch(0);
     for (int ch = 0; ch < D; ++ch) {
         __syncthreads();
-        {   // all of a thread's loads first (one round trip), then the stores
-            constexpr int NX = (XS * XS + TNT - 1) / TNT;
-            float xv[NX];
 #pragma unroll
-            for (int k = 0; k < NX; ++k) {
-                const int i = tid + k * TNT, r = i / XS, c = i - r * XS, hh = h0 + r - 1, ww = w0 + c - 1;
-                xv[k] = (i < XS * XS && hh >= 0 && hh < H && ww >= 0 && ww < W) ? x[(size_t)ch * V + (size_t)hh * W + ww] : 0.f;
-            }
-#pragma unroll
-            for (int k = 0; k < NX; ++k)
-                if (tid + k * TNT < XS * XS) s_x[tid + k * TNT] = xv[k];
-        }
+        for (int k = 0; k < NX; ++k)
+            if (tid + k * TNT < XS * XS) s_x[tid + k * TNT] = xv[k];
         __syncthreads();
-        for (int i = tid; i < (TS + 1) * TS; i += TNT) {
-            const int r = i / TS, c = i - r * TS;   // pixels (r-1, c) and (r, c) of the tile = s_x rows r, r+1, column c+1
-            const float t = __fsub_rn(s_x[r * XS + c + 1], s_x[(r + 1) * XS + c + 1]);
-            s_wv[i] = __fadd_rn(s_wv[i], __fmul_rn(t, t));
-        }
-        for (int i = tid; i < TS * (TS + 1); i += TNT) {
-            const int r = i / (TS + 1), c = i - r * (TS + 1);   // pixels (r, c-1) and (r, c) = s_x row r+1, columns c, c+1
-            const float t = __fsub_rn(s_x[(r + 1) * XS + c], s_x[(r + 1) * XS + c + 1]);
-            s_wh[i] = __fadd_rn(s_wh[i], __fmul_rn(t, t));
+        if (ch + 1 < D) fetch(ch + 1);
+#pragma unroll
+        for (int k = 0; k < NE; ++k) {
+            const int i = tid + k * TNT;
+            if (i < (TS + 1) * TS) {
+                const int r = i / TS, c = i - r * TS;   // pixels (r-1, c) and (r, c) of the tile = s_x rows r, r+1, column c+1
+                const float t = __fsub_rn(s_x[r * XS + c + 1], s_x[(r + 1) * XS + c + 1]);
+                av[k] = __fadd_rn(av[k], __fmul_rn(t, t));
+                const int r2 = i / (TS + 1), c2 = i - r2 * (TS + 1);   // pixels (r, c-1) and (r, c) = s_x row r+1, columns c, c+1
+                const float t2 = __fsub_rn(s_x[(r2 + 1) * XS + c2], s_x[(r2 + 1) * XS + c2 + 1]);
+                ah[k] = __fadd_rn(ah[k], __fmul_rn(t2, t2));
+            }
         }
     }
-    __syncthreads();
+    __syncthreads();   // s_x aliases the cheapest-edge slots that are initialised below
     // finish (+1, or 0 for "no such edge") and publish the edges the tile owns (below / right of its vertices)
-    for (int i = tid; i < (TS + 1) * TS; i += TNT) {
-        const int r = i / TS, c = i - r * TS;
-        float wt = 0.f;
-        if (v_valid(r, c)) {
-            wt = __fadd_rn(s_wv[i], 1.f);
-            if (r >= 1) {
-                const int e = (h0 + r - 1) * W + w0 + c;
-                if (!contract) {
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+        const int i = tid + k * TNT;
+        if (i >= (TS + 1) * TS) continue;
+        {
+            const int r = i / TS, c = i - r * TS;
+            float wt = 0.f;
+            if (v_valid(r, c)) {
+                wt = __fadd_rn(av[k], 1.f);
+                if (r >= 1 && !contract) {
+                    const int e = (h0 + r - 1) * W + w0 + c;
                     wgt[e] = wt;
                     intree[e] = 0;
                 }
             }
+            s_wv[i] = wt;
         }
-        s_wv[i] = wt;
-    }
-    for (int i = tid; i < TS * (TS + 1); i += TNT) {
-        const int r = i / (TS + 1), c = i - r * (TS + 1);
-        float wt = 0.f;
-        if (h_valid(r, c)) {
-            wt = __fadd_rn(s_wh[i], 1.f);
-            if (c >= 1) {
-                const int e = nvert + (h0 + r) * (W - 1) + w0 + c - 1;
-                if (!contract) {
+        {
+            const int r = i / (TS + 1), c = i - r * (TS + 1);
+            float wt = 0.f;
+            if (h_valid(r, c)) {
+                wt = __fadd_rn(ah[k], 1.f);
+                if (c >= 1 && !contract) {
+                    const int e = nvert + (h0 + r) * (W - 1) + w0 + c - 1;
                     wgt[e] = wt;
                     intree[e] = 0;
                 }
             }
+            s_wh[i] = wt;
         }
-        s_wh[i] = wt;
     }
     for (int l = tid; l < TV; l += TNT) {
         s_lab[l] = (unsigned short)l;
@@ -758,9 +765,13 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
         // one is handed on (256^2: ~1 400 cross edges per tile, ~300 component pairs): a hash table over the pairs in the
         // cheapest-edge slots, which are free now -- key = the two tile ranks, min weight, then min edge id among the
         // edges of that weight.  An edge that finds no slot (table full around its hash) is handed on as it is.
-        unsigned *tk = s_bw, *tw_ = s_be, *te = s_te;
+        // Table of T2 slots in the cheapest-edge arrays; the slot an edge found is remembered (two bytes per edge, in the
+        // third array) so that the second and third pass neither look the ranks up nor probe again.
+        constexpr int T2 = TV / 2;
+        unsigned *tk = s_bw, *tw_ = s_bw + T2, *te = s_be;
+        unsigned short *s_slot = reinterpret_cast<unsigned short *>(s_te);   // [2 TV]: edge 2 l + kind -> slot, 0xffff = none
         constexpr unsigned EMPTY = 0xffffffffu;
-        for (int l = tid; l < TV; l += TNT) { tk[l] = EMPTY; tw_[l] = EMPTY; te[l] = EMPTY; }
+        for (int l = tid; l < T2; l += TNT) { tk[l] = EMPTY; tw_[l] = EMPTY; te[l] = EMPTY; }
 #pragma unroll
         for (int q = 0; q < PER; ++q) {
             const int r = rbase + q * (TNT / TS), l = r * TS + c;
@@ -802,9 +813,9 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
             return x;
         };
         auto slot_of = [&](unsigned pk, bool insert) {
-            const unsigned h = (pk * 2654435761u) >> 20;
+            const unsigned h = (pk * 2654435761u) >> 21;
             for (int t = 0; t < 32; ++t) {
-                const unsigned sl = (h + t) & (TV - 1);
+                const unsigned sl = (h + t) & (T2 - 1);
                 unsigned k = tk[sl];
                 if (k == EMPTY && insert) k = atomicCAS(tk + sl, EMPTY, pk), k = (k == EMPTY) ? pk : k;
                 if (k == pk) return (int)sl;
@@ -812,24 +823,36 @@ __global__ void __launch_bounds__(TNT, 2) mst_tile_kernel(Ws ws, EmbedSet es, in
             }
             return -1;
         };
+        auto light = [&](int k, int &l, unsigned &ow, unsigned &eid) {   // what the later passes need of edge k: no ranks
+            const int kind = k & 1, r = rbase + (k >> 1) * (TNT / TS);
+            l = r * TS + c;
+            ow = orderable(kind ? s_wh[l + r + 1] : s_wv[l + TS]);
+            eid = (unsigned)(kind ? nvert + (h0 + r) * (W - 1) + w0 + c : (h0 + r) * W + w0 + c);
+        };
         for (unsigned m = in_mask; m; m &= m - 1) {
-            const EdgeInfo x = edge(__ffs(m) - 1, true);
+            const int k = __ffs(m) - 1;
+            const EdgeInfo x = edge(k, true);
             const int sl = slot_of(x.pk, true);
+            s_slot[2 * (((rbase + (k >> 1) * (TNT / TS)) * TS) + c) + (k & 1)] = (unsigned short)(sl < 0 ? 0xffff : sl);
             if (sl >= 0 && x.ow < tw_[sl]) atomicMin(tw_ + sl, x.ow);   // (a long common boundary: hundreds of edges on one slot)
         }
         __syncthreads();
         for (unsigned m = in_mask; m; m &= m - 1) {
-            const EdgeInfo x = edge(__ffs(m) - 1, true);
-            const int sl = slot_of(x.pk, false);
-            if (sl >= 0 && tw_[sl] == x.ow && x.eid < te[sl]) atomicMin(te + sl, x.eid);
+            int l;
+            unsigned ow, eid;
+            light(__ffs(m) - 1, l, ow, eid);
+            const unsigned sl = s_slot[2 * l + ((__ffs(m) - 1) & 1)];
+            if (sl != 0xffffu && tw_[sl] == ow && eid < te[sl]) atomicMin(te + sl, eid);
         }
         __syncthreads();
         unsigned emit_mask = out_mask;
         for (unsigned m = in_mask; m; m &= m - 1) {
             const int k = __ffs(m) - 1;
-            const EdgeInfo x = edge(k, true);
-            const int sl = slot_of(x.pk, false);
-            if (sl < 0 || (tw_[sl] == x.ow && te[sl] == x.eid)) emit_mask |= 1u << k;
+            int l;
+            unsigned ow, eid;
+            light(k, l, ow, eid);
+            const unsigned sl = s_slot[2 * l + (k & 1)];
+            if (sl == 0xffffu || (tw_[sl] == ow && te[sl] == eid)) emit_mask |= 1u << k;
         }
         int nrec = __popc(emit_mask);
 #pragma unroll
