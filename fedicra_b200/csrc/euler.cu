@@ -22,6 +22,13 @@ namespace {
 
 constexpr int NT = 256;
 constexpr int NIL = -1;
+#ifndef SCAN_NT_
+#define SCAN_NT_ 256
+#endif
+#ifndef SCAN_PER_
+#define SCAN_PER_ 8
+#endif
+constexpr int SCAN_NT = SCAN_NT_, SCAN_PER = SCAN_PER_, SCAN_TILE = SCAN_NT * SCAN_PER;   // tiles of the single-pass tour scan
 // splitters handed out dynamically inside one CTA of the tour walk (FEDICRA_EULER_SPC overrides; see run time notes below)
 // Every walk CTA first packs the whole tree mask into shared memory, so larger images want fewer, longer-lived CTAs:
 // measured on B200, chain order of 48 trees: 256^2: 512 -> 313 us, 1024 -> 309, 2048 -> 334; 512^2: 512 -> 1 694 us,
@@ -70,7 +77,7 @@ struct Dims {
     int root;  // the vertex the order starts from (0 = the reference's, bfs.cu:69-74)
     int B, V, H, W, SP, SPLOG, NS, T, NBLK, SPC;  // T = 2(V-1) arcs on the tour; NBLK = ceil(T / 1024); SPC splitters per walk CTA
     int NTILE;                                    // ceil(V / 1024)
-    int NSCAN;                                    // ceil(T / 2048), at least 1: tiles of the single-pass tour scan
+    int NSCAN;                                    // ceil(T / SCAN_TILE), at least 1: tiles of the single-pass tour scan
 };
 
 size_t ws_layout(const Dims &d, char *base, Ws *w) {
@@ -121,7 +128,7 @@ Dims make_dims(int B, int H, int W, int root = 0) {
     d.T = 2 * (d.V - 1);
     d.NBLK = (d.T + 1023) / 1024;
     d.NTILE = (d.V + 1023) / 1024;
-    d.NSCAN = d.T > 0 ? (d.T + 2047) / 2048 : 1;
+    d.NSCAN = d.T > 0 ? (d.T + SCAN_TILE - 1) / SCAN_TILE : 1;
     d.SPC = split_per_cta(d.V);
     return d;
 }
@@ -617,7 +624,6 @@ __global__ void __launch_bounds__(NT) chain_enter_kernel(const unsigned char *__
 // ---- chain order, step 3b: prefix sums along the tour in ONE pass (tiles of 2048 entries handed out by ticket, each
 // publishing its aggregate and then its inclusive prefix in one self-validating 64-bit word; a tile looks back over its
 // predecessors' words instead of waiting for a separate scan-of-sums launch), keys and histogram written on the way.
-constexpr int SCAN_NT = 256, SCAN_PER = 8, SCAN_TILE = SCAN_NT * SCAN_PER;
 __device__ __forceinline__ unsigned long long scan_pack(unsigned flag, int ld, int pre) {
     return ((unsigned long long)flag << 62) | ((unsigned long long)(unsigned)(ld & 0xffff) << 32) | (unsigned)pre;
 }
@@ -625,7 +631,9 @@ __device__ __forceinline__ int2 scan_unpack(unsigned long long w) {
     return make_int2((int)(short)((w >> 32) & 0xffffu), (int)(unsigned)(w & 0xffffffffull));
 }
 __global__ void __launch_bounds__(SCAN_NT) chain_scan_kernel(Ws ws, Dims dm) {
-    const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = dm.V;
+    // tree = blockIdx.x: CTAs are handed out x-fastest, so the first tiles of ALL trees start together and the look-back
+    // chains of the trees advance side by side (tree = blockIdx.y ran them three waves of ~18 trees after each other)
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, V = dm.V;
     __shared__ int s_blk;
     __shared__ int2 s_w[SCAN_NT / 32], s_excl;
     if (tid == 0) s_blk = atomicAdd(ws.scan_ticket + b, 1);
@@ -945,7 +953,7 @@ int chain_order_impl(const unsigned char *tree_mask, int B, int H, int W, int *s
     if (int rc = run_tour(tree_mask, ws, dm, st, "chain_order", false)) return rc;
     chain_enter_kernel<<<vb, NT, 0, st>>>(tree_mask, ws, dm);
     FEDICRA_CHECK_LAUNCH("chain_enter_kernel");
-    chain_scan_kernel<<<dim3(dm.NSCAN, B), SCAN_NT, 0, st>>>(ws, dm);
+    chain_scan_kernel<<<dim3(B, dm.NSCAN), SCAN_NT, 0, st>>>(ws, dm);
     FEDICRA_CHECK_LAUNCH("chain_scan_kernel");
     chain_offsets_kernel<<<B, 1024, 0, st>>>(ws, dm, group_start);
     FEDICRA_CHECK_LAUNCH("chain_offsets_kernel");
