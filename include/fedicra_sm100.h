@@ -90,7 +90,9 @@ int fedicra_mst_forward(const int *edge_index, const float *edge_weight, int B, 
  * CUDA reduction interleaves four accumulators beyond that -- the Python modules take torch's own weights for D > 4).
  *   embed [B,D,H,W]  ->  edge_out [B,H*W-1,2] int32 (increasing edge index; may be NULL when only the mask is wanted);
  *   tree_mask [B,H*W] uint8 (may be NULL): per vertex, bit 0/1/2/3 set when the tree holds the edge to the pixel
- *   above / left / right / below -- the compact form fedicra_bfs_grid consumes. */
+ *   above / left / right / below -- the compact form fedicra_bfs_grid consumes.  Any alignment; its bits are set with
+ *   32-bit atomics on the aligned words that contain it (up to 3 bytes either side are read and written back unchanged,
+ *   so the buffer must not end at the very end of an allocation that is not a multiple of 4 bytes). */
 int fedicra_mst_grid(const float *embed, int B, int D, int H, int W, int *edge_out, unsigned char *tree_mask,
                      void *workspace, size_t workspace_bytes, void *stream);
 
