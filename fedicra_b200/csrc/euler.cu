@@ -209,31 +209,68 @@ __global__ void __launch_bounds__(NT) walk_kernel(const unsigned char *__restric
     }
 }
 
-// ---- 1b. rank the splitters: suffix sums of the stretch lengths by pointer jumping, one CTA per image
+// ---- 1b. rank the splitters (tour rank of every stretch's first arc), one CTA per image, in shared memory.  Pointer
+// jumping over all NS splitters costs log2(NS) rounds of random shared-memory gathers (27 us for 8 192); instead every
+// ~SPACING-th splitter is a LEADER: each leader walks to the next leader summing the stretch lengths on the way (~SPACING
+// dependent steps), pointer jumping ranks the <= 1 024 leaders, and a second walk hands the ranks down the segments.
 __global__ void __launch_bounds__(1024) rank_splitters_kernel(Ws ws, Dims dm) {
     extern __shared__ int s_mem[];
     const int b = blockIdx.x, tid = threadIdx.x, NS = dm.NS;
-    int *val[2] = {s_mem, s_mem + NS};
-    short *nxt[2] = {reinterpret_cast<short *>(s_mem + 2 * NS), reinterpret_cast<short *>(s_mem + 2 * NS) + NS};   // NS <= 16 384
+    int *len = s_mem;                                               // [NS] stretch length
+    short *nxt = reinterpret_cast<short *>(s_mem + NS);            // [NS] next splitter on the tour (NS <= 16 384), NIL at the cut
+    // One leader per block of `spacing` (a power of two) consecutive splitters, at a pseudo-random place in the block: the
+    // tour mostly steps to a spatial neighbour's splitter, i.e. index +-1 or +- one image row of blocks, so leaders at
+    // fixed residues would be met after ~spacing^2 steps (measured: 150 us), random ones after ~spacing.
+    int lg = 0;
+    while ((1024 << lg) < NS) ++lg;
+    const int spacing = 1 << lg, L = (NS + spacing - 1) >> lg;
+    auto leader_of = [&](int l) {
+        const int s = (l << lg) + ((l == 0 || lg == 0) ? 0 : (int)(((unsigned)l * 2654435761u) >> (32 - lg)));   // splitter 0 (the head) is a leader
+        return s < NS ? s : (l << lg);
+    };
+    auto is_leader = [&](int s) { return leader_of(s >> lg) == s; };
+    int *lval[2] = {s_mem + NS + (NS + 1) / 2, s_mem + NS + (NS + 1) / 2 + 1024};       // [L] arcs from the leader to the end
+    short *lnxt[2] = {reinterpret_cast<short *>(lval[1] + 1024), reinterpret_cast<short *>(lval[1] + 1024) + 1024};   // next leader (index)
     const int *snext = ws.snext + (size_t)b * NS, *slen = ws.slen + (size_t)b * NS;
+    int *sbase = ws.sbase + (size_t)b * NS;
     for (int s = tid; s < NS; s += 1024) {
         const int n = snext[s];
-        val[0][s] = slen[s];
-        nxt[0][s] = (short)((n == 0) ? NIL : n);  // the tour is a cycle through splitter 0 (vertex 0, the root): cut it there
+        len[s] = slen[s];
+        nxt[s] = (short)((n == 0) ? NIL : n);  // the tour is a cycle through splitter 0 (vertex 0, the root): cut it there
+        sbase[s] = 0;                           // (a splitter the walk below never reaches: inconsistent mask)
+    }
+    __syncthreads();
+    int seg = 0, to = NIL;
+    if (tid < L) {   // first walk: own stretch, then on to the next leader
+        int s = leader_of(tid), steps = 0;
+        do {
+            seg += len[s];
+            s = nxt[s];
+        } while (s >= 0 && !is_leader(s) && ++steps < NS);
+        to = (s >= 0 && is_leader(s)) ? (s >> lg) : NIL;
+        lval[0][tid] = seg;
+        lnxt[0][tid] = (short)to;
     }
     __syncthreads();
     int cur = 0;
-    for (int span = 1; span < NS; span <<= 1) {
-        for (int s = tid; s < NS; s += 1024) {
-            const int n = nxt[cur][s];
-            val[cur ^ 1][s] = val[cur][s] + (n >= 0 ? val[cur][n] : 0);
-            nxt[cur ^ 1][s] = (short)((n >= 0) ? nxt[cur][n] : NIL);
+    for (int span = 1; span < L; span <<= 1) {
+        if (tid < L) {
+            const int n = lnxt[cur][tid];
+            lval[cur ^ 1][tid] = lval[cur][tid] + (n >= 0 ? lval[cur][n] : 0);
+            lnxt[cur ^ 1][tid] = (short)((n >= 0) ? lnxt[cur][n] : NIL);
         }
         __syncthreads();
         cur ^= 1;
     }
-    const int total = val[cur][0];
-    for (int s = tid; s < NS; s += 1024) ws.sbase[(size_t)b * NS + s] = total - val[cur][s];
+    const int total = lval[cur][0];   // splitter 0 is a leader and the head of the list
+    if (tid < L) {   // second walk: arcs before a stretch = total - (arcs from it to the end)
+        int s = leader_of(tid), rest = lval[cur][tid], steps = 0;
+        do {
+            sbase[s] = total - rest;
+            rest -= len[s];
+            s = nxt[s];
+        } while (s >= 0 && !is_leader(s) && ++steps < NS);
+    }
 }
 
 __device__ __forceinline__ int arc_rank_raw(const unsigned *arc, const int *sbase, int a) {
@@ -855,7 +892,7 @@ int run_tour(const unsigned char *tree_mask, const Ws &ws, const Dims &dm, cudaS
         walk_kernel<false><<<dim3((dm.NS + dm.SPC - 1) / dm.SPC, B), NT, 0, st>>>(tree_mask, ws, dm);
     }
     FEDICRA_CHECK_LAUNCH("walk_kernel");
-    const size_t smem_rank = (size_t)3 * dm.NS * sizeof(int);
+    const size_t smem_rank = ((size_t)dm.NS + (dm.NS + 1) / 2 + 2 * 1024 + 1024) * sizeof(int);   // len, nxt (16 bit), leader tables
     e = cudaFuncSetAttribute(rank_splitters_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rank);
     if (e != cudaSuccess) return fedicra_fail(-2, "%s: shared memory: %s", who, cudaGetErrorString(e));
     rank_splitters_kernel<<<B, 1024, smem_rank, st>>>(ws, dm);
