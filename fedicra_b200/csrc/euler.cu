@@ -6,7 +6,8 @@
 // logarithmic:
 //   1. Euler tour of the tree (each tree edge = two arcs; successor of the arc into u = next tree edge around u)
 //      ranked with a splitter walk: one thread per 8 vertices walks its stretch of the tour (~16 arcs), the ~8 192
-//      stretches are ranked by pointer jumping in shared memory.
+//      stretches are ranked in shared memory (two short walks between pseudo-random leaders + pointer jumping over the
+//      leaders).
 //   2. From the ranks: the parent of u is where the tour first enters u; subtree size = half the span between entering
 //      and leaving u.
 //   3. One prefix sum along the tour of (+1,-1) gives the depth, of (+o,-o) with o(u) = 1 + sizes of u's smaller siblings
