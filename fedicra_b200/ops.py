@@ -23,6 +23,25 @@ def workspace(tag, nbytes, device):
     return buf
 
 
+class _Here:
+    """No-op context: the tensor's device is already the current one (the usual case; entering torch.cuda.device costs
+    ~10 us of host time per call, and an eager step makes ~30 calls)."""
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+_HERE = _Here()
+
+
+def _on(device):
+    idx = device.index if isinstance(device, torch.device) else device
+    return _HERE if (idx is None or idx == torch.cuda.current_device()) else torch.cuda.device(device)
+
+
 def _cuda(t, dtype, name):
     if not isinstance(t, torch.Tensor) or not t.is_cuda:
         raise RuntimeError(f"{name} must be a CUDA tensor: fedicra_b200 has no CPU path")
@@ -44,7 +63,7 @@ def gcrf_fwd_bwd(y, image, radius, descs, want_grad=True):
     image = _cuda(image, torch.float32, "sample")
     N, C, H, W = y.shape
     assert image.shape[0] == N and image.shape[2:] == (H, W)
-    with torch.cuda.device(y.device):
+    with _on(y.device):
         loss = torch.empty(1, dtype=torch.float32, device=y.device)
         grad = torch.empty_like(y) if want_grad else None
         nbytes = lib.fedicra_gcrf_workspace_bytes(N, H, W)
@@ -63,7 +82,7 @@ def mst_forward(edge_index, edge_weight, vertex_count):
     ew = _cuda(edge_weight, torch.float32, "edge_weight")
     B, E = ei.shape[0], ei.shape[1]
     V = int(vertex_count)
-    with torch.cuda.device(ei.device):
+    with _on(ei.device):
         out = torch.empty(B, V - 1, 2, dtype=torch.int32, device=ei.device)
         ws = workspace("mst", lib.fedicra_mst_workspace_bytes(B, V, E), ei.device)
         check(lib.fedicra_mst_forward(_p(ei), _p(ew), B, E, V, _p(out), _p(ws), ws.numel(), _stream()), "mst_forward")
@@ -75,7 +94,7 @@ def mst_grid(embed, want_mask=False, want_edges=True):
     e = _cuda(embed, torch.float32, "guide_in")
     B, D, H, W = e.shape
     V, E = H * W, 2 * H * W - H - W
-    with torch.cuda.device(e.device):
+    with _on(e.device):
         out = torch.empty(B, V - 1, 2, dtype=torch.int32, device=e.device) if want_edges else None
         mask = torch.empty(B, V, dtype=torch.uint8, device=e.device) if want_mask else None
         ws = workspace("mst", lib.fedicra_mst_workspace_bytes(B, V, E), e.device)
@@ -93,7 +112,7 @@ def mst_grid_multi(embeds, want_mask=True, want_edges=False):
     assert all(e.shape[0] == B and tuple(e.shape[2:]) == (H, W) for e in es)
     V, E = H * W, 2 * H * W - H - W
     dev = es[0].device
-    with torch.cuda.device(dev):
+    with _on(dev):
         out = torch.empty(K * B, V - 1, 2, dtype=torch.int32, device=dev) if want_edges else None
         mask = torch.empty(K * B, V, dtype=torch.uint8, device=dev) if want_mask else None
         ws = workspace("mst", lib.fedicra_mst_workspace_bytes(K * B, V, E), dev)
@@ -124,7 +143,7 @@ def bfs_grid(mask, H, W):
     m = _cuda(mask, torch.uint8, "tree_mask")
     B, V = m.shape
     dev = m.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         si = torch.empty(B, V, dtype=torch.int32, device=dev)
         sp = torch.empty(B, V, dtype=torch.int32, device=dev)
         sc = torch.empty(B, V, 4, dtype=torch.int32, device=dev)
@@ -142,7 +161,7 @@ def bfs_forward(tree):
     t = _cuda(tree, torch.int32, "tree")
     B, V = t.shape[0], t.shape[1] + 1
     dev = t.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         si = torch.zeros(B, V, dtype=torch.int32, device=dev)
         sp = torch.zeros(B, V, dtype=torch.int32, device=dev)
         sc = torch.zeros(B, V, 4, dtype=torch.int32, device=dev)
@@ -174,7 +193,7 @@ def bfs_euler(mask, H, W, root=0):
     m = _cuda(mask, torch.uint8, "tree_mask")
     B, V = m.shape
     dev = m.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         si = torch.empty(B, V, dtype=torch.int32, device=dev)
         sp = torch.empty(B, V, dtype=torch.int32, device=dev)
         sc = torch.empty(B, V, 4, dtype=torch.int32, device=dev)
@@ -192,7 +211,7 @@ def chain_order(mask, H, W):
     m = _cuda(mask, torch.uint8, "tree_mask")
     B, V = m.shape
     dev = m.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         si = torch.empty(B, V, dtype=torch.int32, device=dev)
         sp = torch.empty(B, V, dtype=torch.int32, device=dev)
         sc = torch.empty(B, V, 4, dtype=torch.int32, device=dev)
@@ -213,7 +232,7 @@ def chain_order_weights(mask, embeds, inv_sigmas, H, W):
     KB, V = m.shape
     assert KB == K * B and V == H * W and all(e.shape[0] == B and tuple(e.shape[2:]) == (H, W) for e in es)
     dev = m.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         si = torch.empty(KB, V, dtype=torch.int32, device=dev)
         sp = torch.empty(KB, V, dtype=torch.int32, device=dev)
         sc = torch.empty(KB, V, 4, dtype=torch.int32, device=dev)
@@ -237,7 +256,7 @@ def chain_arm(B, C, V, n, device):
     that none sits between the filters of a step.  Each serves one launch (chain_filter_forward(..., saved=buf) /
     chain_filter_backward(..., armed_workspace=buf))."""
     size = (int(lib.fedicra_chain_filter_saved_bytes(B, C, V)) + 255) // 256 * 256
-    with torch.cuda.device(device):
+    with _on(device):
         block = torch.empty(n * size, dtype=torch.uint8, device=device)
         check(lib.fedicra_chain_filter_arm(_p(block), block.numel(), _stream()), "chain_filter_arm")
     return [block[i * size:(i + 1) * size] for i in range(n)]
@@ -252,7 +271,7 @@ def chain_filter_forward(feature_in, edge_weight, si, sp, sc, gs, saved=None):
         raise RuntimeError("edge_weight must be a contiguous float32 CUDA tensor (it is written in place)")
     B, C, V = f.shape
     dev = f.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         out = torch.empty_like(f)
         need = lib.fedicra_chain_filter_saved_bytes(B, C, V)
         if saved is not None and saved.numel() >= need and saved.device == dev:
@@ -280,7 +299,7 @@ def chain_filter_backward(grad_out, edge_weight, si, sp, sc, gs, saved, want_wei
     g = _cuda(grad_out, torch.float32, "grad_output")
     B, C, V = g.shape
     dev = g.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         gf = torch.empty_like(g)
         gw = torch.empty(B, V, dtype=torch.float32, device=dev) if want_weight_grad else None
         need = lib.fedicra_chain_filter_workspace_bytes(B, C, V)
@@ -299,7 +318,7 @@ def chain_filter_backward(grad_out, edge_weight, si, sp, sc, gs, saved, want_wei
 def edge_weight_fwd(embed, si, sp, inv_sigma):
     e = _cuda(embed, torch.float32, "embed_in")
     B, D, V = e.shape
-    with torch.cuda.device(e.device):
+    with _on(e.device):
         ew = torch.empty(B, V, dtype=torch.float32, device=e.device)
         check(lib.fedicra_edge_weight_fwd(_p(e), _p(si), _p(sp), B, D, V, float(inv_sigma), _p(ew), _stream()),
               "edge_weight_fwd")
@@ -310,7 +329,7 @@ def edge_weight_bwd(embed, si, sp, sc, ew, grad_ew, inv_sigma):
     e = _cuda(embed, torch.float32, "embed_in")
     g = _cuda(grad_ew, torch.float32, "grad_edge_weight")
     B, D, V = e.shape
-    with torch.cuda.device(e.device):
+    with _on(e.device):
         out = torch.empty_like(e)
         check(lib.fedicra_edge_weight_bwd(_p(e), _p(si), _p(sp), _p(sc), _p(ew), _p(g), B, D, V, float(inv_sigma),
                                           _p(out), _stream()), "edge_weight_bwd")
@@ -326,7 +345,7 @@ def edge_weight_bwd_multi(embeds, orders, ews, grad_ews, inv_sigmas):
     K = len(es)
     B, _, V = es[0].shape
     assert all(e.shape[0] == B and e.shape[2] == V for e in es)
-    with torch.cuda.device(es[0].device):
+    with _on(es[0].device):
         outs = [torch.empty_like(e) for e in es]
         arr = lambda ts: (ctypes.c_void_p * K)(*[t.data_ptr() for t in ts])
         dims = (ctypes.c_int * K)(*[e.shape[1] for e in es])
@@ -346,7 +365,7 @@ def refine_forward(feature_in, edge_weight, si, sp, sc, ls, nl):
         raise RuntimeError("edge_weight must be a contiguous float32 CUDA tensor (it is written in place)")
     B, C, V = f.shape
     dev = f.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         out, aggr, aggr_up = torch.empty_like(f), torch.empty_like(f), torch.empty_like(f)
         wsum = torch.empty(B, V, dtype=torch.float32, device=dev)
         wsum_up = torch.empty(B, V, dtype=torch.float32, device=dev)
@@ -359,7 +378,7 @@ def refine_forward(feature_in, edge_weight, si, sp, sc, ls, nl):
 def refine_backward_feature(edge_weight, si, sp, sc, ls, nl, weight_sum, grad_out):
     g = _cuda(grad_out, torch.float32, "grad_output")
     B, C, V = g.shape
-    with torch.cuda.device(g.device):
+    with _on(g.device):
         out = torch.empty_like(g)
         ws = workspace("refine_bwd", lib.fedicra_refine_backward_workspace_bytes(B, C, V), g.device)
         check(lib.fedicra_refine_backward_feature(_p(edge_weight), _p(si), _p(sp), _p(sc), _p(ls), _p(nl),
@@ -372,7 +391,7 @@ def refine_backward_weight(edge_weight, si, sp, sc, ls, nl, feature_out, feature
                            weight_sum_up, grad_out):
     g = _cuda(grad_out, torch.float32, "grad_output")
     B, C, V = g.shape
-    with torch.cuda.device(g.device):
+    with _on(g.device):
         out = torch.empty(B, V, dtype=torch.float32, device=g.device)
         ws = workspace("refine_bwd", lib.fedicra_refine_backward_workspace_bytes(B, C, V), g.device)
         check(lib.fedicra_refine_backward_weight(_p(edge_weight), _p(si), _p(sp), _p(sc), _p(ls), _p(nl),
@@ -385,7 +404,7 @@ def refine_backward_weight(edge_weight, si, sp, sc, ls, nl, feature_out, feature
 def band_plan(ls, nl):
     """Band plan of a batch of trees from their BFS level structure (one per topology, shared by all filter calls)."""
     B, V = ls.shape[0], ls.shape[1] - 1
-    with torch.cuda.device(ls.device):
+    with _on(ls.device):
         bands = torch.empty(lib.fedicra_band_plan_ints(B), dtype=torch.int32, device=ls.device)
         check(lib.fedicra_band_plan(_p(ls), _p(nl), B, V, _p(bands), _stream()), "band_plan")
     return bands
@@ -398,7 +417,7 @@ def tree_filter_forward(feature_in, edge_weight, si, sp, sc, ls, nl, bands, want
         raise RuntimeError("edge_weight must be a contiguous float32 CUDA tensor (it is written in place)")
     B, C, V = f.shape
     dev = f.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         out = torch.empty_like(f)
         saved = torch.empty(lib.fedicra_tree_filter_saved_bytes(B, C, V), dtype=torch.uint8, device=dev)
         aggr = torch.empty_like(f) if want_aggr else None
@@ -415,7 +434,7 @@ def tree_filter_backward(grad_out, edge_weight, si, sp, sc, ls, nl, bands, saved
     g = _cuda(grad_out, torch.float32, "grad_output")
     B, C, V = g.shape
     dev = g.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         gf = torch.empty_like(g)
         gw = torch.empty(B, V, dtype=torch.float32, device=dev) if want_weight_grad else None
         ws = workspace("tree_filter", lib.fedicra_tree_filter_workspace_bytes(B, C, V), dev)
@@ -432,7 +451,7 @@ def channel_softmax_fwd(x):
     x = _cuda(x, torch.float32, "preds")
     B, C = x.shape[0], x.shape[1]
     P = x.numel() // (B * C)
-    with torch.cuda.device(x.device):
+    with _on(x.device):
         y = torch.empty_like(x)
         check(lib.fedicra_channel_softmax_fwd(_p(x), B, C, P, _p(y), _stream()), "channel_softmax_fwd")
     return y
@@ -442,7 +461,7 @@ def channel_softmax_bwd(y, grad_y):
     g = _cuda(grad_y, torch.float32, "grad_prob")
     B, C = y.shape[0], y.shape[1]
     P = y.numel() // (B * C)
-    with torch.cuda.device(y.device):
+    with _on(y.device):
         gx = torch.empty_like(y)
         check(lib.fedicra_channel_softmax_bwd(_p(y), _p(g), B, C, P, _p(gx), _stream()), "channel_softmax_bwd")
     return gx
@@ -456,7 +475,7 @@ def masked_l1_fwd(prob, filtered, roi_u8, weight):
     B, C = prob.shape[0], prob.shape[1]
     P = prob.numel() // (B * C)
     assert roi.numel() == B * P and filtered.shape == prob.shape
-    with torch.cuda.device(prob.device):
+    with _on(prob.device):
         sums = torch.empty(2, dtype=torch.float32, device=prob.device)
         loss = torch.empty(1, dtype=torch.float32, device=prob.device)
         ws = workspace("masked_l1", lib.fedicra_masked_l1_workspace_bytes(), prob.device)
@@ -469,7 +488,7 @@ def masked_l1_bwd(prob, filtered, roi_u8, grad_out, n, weight, want_prob=True, w
     B, C = prob.shape[0], prob.shape[1]
     P = prob.numel() // (B * C)
     g = _cuda(grad_out.reshape(-1), torch.float32, "grad_loss")
-    with torch.cuda.device(prob.device):
+    with _on(prob.device):
         gp = torch.empty_like(prob) if want_prob else None
         gf = torch.empty_like(prob) if want_filtered else None
         check(lib.fedicra_masked_l1_bwd(_p(prob), _p(filtered), _p(roi_u8), _p(g), _p(n), float(weight), B, C, P, _p(gp),
@@ -490,7 +509,7 @@ def bilinear_resize(heads, H, W, backward=False):
         sizes = [tuple(x.shape[2:]) for x in srcs]
     B, C = srcs[0].shape[:2]
     dev = srcs[0].device
-    with torch.cuda.device(dev):
+    with _on(dev):
         outs = [torch.empty(B, C, *(hw if backward else (H, W)), dtype=torch.float32, device=dev) for hw in sizes]
         sp = (ctypes.c_void_p * n)(*[x.data_ptr() for x in srcs])
         dp = (ctypes.c_void_p * n)(*[x.data_ptr() for x in outs])
@@ -509,7 +528,7 @@ def ala_update_flat(p, s, g, w, t, eta):
     for name, x in (("p", p), ("s", s), ("w", w), ("t", t)):
         if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and x.numel() == n):
             raise RuntimeError(f"ala_update_flat: {name} must be a contiguous float32 CUDA tensor of {n} elements")
-    with torch.cuda.device(p.device):
+    with _on(p.device):
         check(lib.fedicra_ala_update_flat(_p(p), _p(s), _p(g), _p(w), _p(t), n, float(eta), _stream()),
               "ala_update_flat")
 
@@ -517,5 +536,5 @@ def ala_update_flat(p, s, g, w, t, eta):
 def scale_inplace(x, alpha):
     if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()):
         raise RuntimeError("scale_inplace: x must be a contiguous float32 CUDA tensor")
-    with torch.cuda.device(x.device):
+    with _on(x.device):
         check(lib.fedicra_scale_inplace(_p(x), x.numel(), float(alpha), _stream()), "scale_inplace")
